@@ -1,0 +1,159 @@
+/* include/poseb200.h -- C ABI of libposeb200.so (sm_100a kernels for pose recovery + evaluation).
+ *
+ * Drop-in boundary for the pose-recovery / evaluation hot path of yaomy533/pose_estimation.
+ * The reference has no FFI of its own: the path is a handful of Python callables backed by
+ * third-party native code (OpenCV, KeOps, torch ops).  Each entry point below names the
+ * reference call site (file:line under /root/reference) whose native work it replaces.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; every pointer is a DEVICE pointer unless marked host.
+ *   - every function returns int: 0 = OK, negative = argument / launch error
+ *     (pb_last_error() gives a thread-local message).  No exception crosses the ABI.
+ *   - per-frame numerical failure (too few points, no valid hypothesis, too few inliers -- what
+ *     OpenCV reports as ok=False and the reference ignores, tools/trainer.py:423) is reported in
+ *     status[F], never through the return code.
+ *   - the caller owns every buffer including the workspace (pb_*_workspace_bytes()); the library
+ *     allocates nothing and keeps no state except the error string.
+ *   - all work is asynchronous on the given stream (a cudaStream_t passed as void*).
+ *   - results are a pure function of (inputs, seed): no dependence on launch geometry.
+ */
+#ifndef POSEB200_H
+#define POSEB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PB_ABI_VERSION 1
+
+/* status codes written to status[F] */
+#define PB_STATUS_OK 0
+#define PB_STATUS_TOO_FEW_POINTS 1
+#define PB_STATUS_NO_MODEL 2
+
+/* rows of the accuracy table (tools/trainer.py:479-509 `result`), each [n_cls] doubles */
+#define PB_ROW_ALL_NUM 0
+#define PB_ROW_OBJ_NUM 1
+#define PB_ROW_VARIANT0 2      /* + 6*variant (0 base, 1 reg, 2 final): succ_rt, dis_rt, succ_r, dis_r, succ_t, dis_t */
+#define PB_ROW_DIS_MASK 20
+#define PB_ROW_DIS_NORMAL 21
+#define PB_ROW_DIS_XYZ 22
+#define PB_ROW_FAILED 23       /* frames whose RANSAC status != 0 (new: the reference drops cv2's ok flag) */
+#define PB_TABLE_ROWS 24
+
+typedef struct pb_ransac_params {
+    int32_t  n_hyp;        /* hypotheses per frame (reference: iterationsCount=100 default of cv2; ours 256) */
+    float    thresh_px;    /* reprojectionError (tools/trainer.py:426: 1)                                     */
+    int32_t  gn_iters;     /* Gauss-Newton iterations of the inlier refit (cv2: EPnP re-solve on inliers)     */
+    int32_t  lo_rounds;    /* extra re-score -> refit rounds ("iterative inlier refine"), 0 = cv2-like        */
+    int32_t  min_inliers;  /* fewer inliers than this -> PB_STATUS_NO_MODEL                                   */
+    uint32_t seed_lo, seed_hi; /* Philox key; replaces cv::RNG inside solvePnPRansac                          */
+} pb_ransac_params;
+
+const char* pb_last_error(void);
+int pb_abi_version(void);
+
+/* ---- K0: coordinate-map stream -> compacted correspondences --------------------------------
+ * Replaces tools/trainer.py:386-421 (D2H of the map, de-normalisation xyz*extent+lfborder,
+ * gather at `choose`) and the dataset-side mask.flatten().nonzero() (batchdataset.py:673).
+ * xyz [F,3,Hh,Ww] f32 planar (pred['xyz']); mask [F,Hh,Ww] u8 or NULL (-> pixel is foreground iff
+ * any channel != 0, the map's "0 = background" convention, batchdataset.py:688-693);
+ * roi [F,2] (rmin,cmin) added to row/col to give image v,u, or NULL; extent/lfborder [F,3].
+ * pts [F,5,cap] SoA (X,Y,Z,U,V) in row-major pixel order; count[F] = min(total, cap);
+ * total[F] optional = number of foreground pixels.                                              */
+size_t pb_compact_workspace_bytes(int F, int Hh, int Ww, int cap);
+int pb_compact_map(const float* xyz, const uint8_t* mask, const int32_t* roi, const float* extent,
+                   const float* lfborder, int F, int Hh, int Ww, int cap, float* pts,
+                   int32_t* count, int32_t* total, void* ws, size_t ws_bytes, void* stream);
+
+/* gather variant for the reference's `choose` index list (tools/trainer.py:408-421):
+ * choose [F,NP] int64 flat indices into Hh*Ww, xmap/ymap [F,NP] f32 pixel coordinates.        */
+int pb_gather_correspondences(const float* xyz, const int64_t* choose, const float* xmap,
+                              const float* ymap, const float* extent, const float* lfborder, int F,
+                              int Hh, int Ww, int NP, int cap, float* pts, int32_t* count, void* stream);
+
+/* ---- K1-K4: PnP-RANSAC --------------------------------------------------------------------
+ * Replaces cv2.solvePnPRansac(obj, img, K, EPNP, conf .9999, 1 px) at tools/trainer.py:423-427,
+ * lib/utils/utlis.py:59-63, tools/script/eval.py:131-135, plus Rodrigues (trainer.py:433).
+ * pts [F,5,cap], count [F], K4 [F,4] (fx,fy,cx,cy; lib/utils/utlis.py:12-34 layout).
+ * sample_idx optional [F,H,4] int32 (forces the minimal sets; else Philox(seed,frame0+f,hyp)).
+ * Outputs: R [F,9] row-major, t [F,3], n_inl [F] (inliers of the best minimal hypothesis),
+ * best_hyp [F], n_inl_refined [F] (inliers of the returned pose), status [F];
+ * optional hyp_counts [F,H] (-1 = no model), inl_bitmap [F,ceil(cap/32)] (inliers of the best
+ * minimal hypothesis -- the set cv2 returns as `inliers`), R0 [F,9] / t0 [F,3] (its pose).      */
+size_t pb_ransac_workspace_bytes(int F, int cap, const pb_ransac_params* prm);
+int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const float* K4, int F, int cap,
+                      uint32_t frame0, const pb_ransac_params* prm /*host*/, const int32_t* sample_idx,
+                      float* R, float* t, int32_t* n_inl, int32_t* best_hyp, int32_t* n_inl_refined,
+                      int32_t* status, int32_t* hyp_counts, uint32_t* inl_bitmap, float* R0, float* t0,
+                      void* ws, size_t ws_bytes, void* stream);
+
+/* map -> pose in one call (K0 + K1-K4); workspace holds the compacted points.                 */
+size_t pb_pnp_ransac_map_workspace_bytes(int F, int Hh, int Ww, int cap, const pb_ransac_params* prm);
+int pb_pnp_ransac_map(const float* xyz, const uint8_t* mask, const int32_t* roi, const float* extent,
+                      const float* lfborder, const float* K4, int F, int Hh, int Ww, int cap,
+                      uint32_t frame0, const pb_ransac_params* prm /*host*/, float* R, float* t,
+                      int32_t* n_inl, int32_t* best_hyp, int32_t* n_inl_refined, int32_t* status,
+                      void* ws, size_t ws_bytes, void* stream);
+
+/* inlier bitmap -> exactly n indices (order-preserving random subset / wrap pad);
+ * replaces lib/utils/utlis.py:64-71.  out [F,n] int32 (-1 if the frame has no inliers).       */
+int pb_resample_inliers(const uint32_t* inl_bitmap, const int32_t* count, int F, int cap, int n,
+                        uint32_t frame0, uint32_t seed_lo, uint32_t seed_hi, int32_t* out, void* stream);
+
+/* ---- K5: nearest neighbour / ADD-S -----------------------------------------------------------
+ * pb_knn1 replaces the KeOps handle generic_argkmin('SqDist(x, y)','a = Vi(1)','x = Vi(3)',
+ * 'y = Vj(3)') (train.py:126; used lib/network/loss.py:34, version/transparent/lib/utils.py:24):
+ * idx[b,i] = argmin_j sum_c (x[b,i,c]-y[b,j,c])^2 in FP32, lowest j on ties.
+ * x [B,N,3], y [B,M,3] (y_batch_stride 0 shares one y), idx [B,N] int64, d2 [B,N] optional.    */
+int pb_knn1(const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx, float* d2,
+            void* stream);
+
+/* replaces Metric.cal_adds_cuda (lib/utils/metric.py:17-36): add[b] = mean_i |pred_i - tgt_i|;
+ * adds[b] = mean_i min_j |pred_j - tgt_i| computed where want_adds[b] != 0 (NULL -> all),
+ * else adds[b] = add[b].  pred/target [B,N,3].                                                  */
+int pb_add_adds(const float* pred, const float* target, int B, int N, const uint8_t* want_adds,
+                float* add, float* adds, void* stream);
+
+/* out[b,i,:] = R[b] * model[b or 0,i,:] + t[b]   (tools/trainer.py:376, lib/network/loss.py:26) */
+int pb_transform_points(const float* model, int model_shared, const float* R, const float* t, int B,
+                        int N, float* out, void* stream);
+
+/* ---- K6: per-frame metrics + accuracy table ---------------------------------------------------
+ * Replaces Trainer.cal_dis (tools/trainer.py:370-381) + Metric.angular_distance /
+ * translation_distance (lib/utils/metric.py:67-84).  model [C,N,3] per-class clouds, cls [F];
+ * target [F,N,3] or NULL (-> model*R_gt^T + t_gt, batchdataset.py:707).  For classes with
+ * is_sym[c] != 0 add[f] is ADD-S (metric.py:24-32).  Outputs all [F].                          */
+int pb_pose_metrics(const float* R, const float* t, const float* R_gt, const float* t_gt,
+                    const float* model, const float* target, const int32_t* cls,
+                    const uint8_t* is_sym, int F, int N, int C, float* add, float* r_deg, float* t_m,
+                    void* stream);
+
+/* success tests + per-object accumulation (tools/trainer.py:156-157,174-221): table [24,C] doubles
+ * += this batch (deterministic, one CTA per class).  add < add_frac*diameter[c], r < r_thr, t < t_thr. */
+int pb_accumulate_results(const float* add, const float* r_deg, const float* t_m, const int32_t* cls,
+                          const int32_t* status, const float* diameter, int F, int C, int variant,
+                          float add_frac, float r_thr_deg, float t_thr_m, int count_frames,
+                          double* table, void* stream);
+
+/* ---- symmetric-KNN pose loss (lib/network/loss.py:25-41) --------------------------------------
+ * forward: pred = model*R^T + t; tgt_i <- tgt[knn(pred_i)] for symmetric samples;
+ * loss_b = mean_i |pred_i - tgt_i|; loss = mean_b loss_b.  nn_idx [B,N] int64 scratch/out
+ * (identity rows for non-symmetric samples).  backward: closed form wrt R [B,9] and t [B,3].   */
+int pb_pose_loss_fwd(const float* R, const float* t, const float* model, const float* target,
+                     const uint8_t* sym /*[B]*/, int B, int N, float* pred /*[B,N,3]*/, int64_t* nn_idx,
+                     float* loss_b /*[B]*/, void* stream);
+int pb_pose_loss_bwd(const float* pred, const float* model, const float* target, const int64_t* nn_idx,
+                     int B, int N, float gscale, float* grad_R /*[B,9]*/, float* grad_t /*[B,3]*/,
+                     void* stream);
+
+/* ---- K7: T-offset voting (lib/network/krrn.py:153) --------------------------------------------
+ * t[b,:] = mean_i (cloud[b,i,:] + t_res[b,:,i]);  cloud [B,NP,3], t_res [B,3,NP].               */
+int pb_vote_translation(const float* cloud, const float* t_res, int B, int NP, float* t, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

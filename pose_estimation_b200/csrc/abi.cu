@@ -1,0 +1,63 @@
+// abi.cu -- error reporting and the composed map -> pose entry point of libposeb200.so.
+#include <cstdarg>
+#include <cstdio>
+#include "common.cuh"
+
+namespace {
+thread_local char g_err[512] = "";
+}
+
+void pb_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int pb_check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        pb_set_error("%s: %s", what, cudaGetErrorString(e));
+        return 1;
+    }
+    return 0;
+}
+
+extern "C" const char* pb_last_error(void) { return g_err; }
+extern "C" int pb_abi_version(void) { return PB_ABI_VERSION; }
+
+namespace {
+inline size_t align256(size_t x) { return (x + 255) / 256 * 256; }
+}
+
+extern "C" size_t pb_pnp_ransac_map_workspace_bytes(int F, int Hh, int Ww, int cap, const pb_ransac_params* prm) {
+    if (F <= 0 || Hh <= 0 || Ww <= 0 || cap <= 0 || !prm) return 0;
+    size_t pts = align256((size_t)F * 5 * cap * sizeof(float));
+    size_t cnt = align256((size_t)F * sizeof(int32_t));
+    return pts + cnt + align256(pb_compact_workspace_bytes(F, Hh, Ww, cap)) + align256(pb_ransac_workspace_bytes(F, cap, prm));
+}
+
+extern "C" int pb_pnp_ransac_map(const float* xyz, const uint8_t* mask, const int32_t* roi, const float* extent,
+                                 const float* lfborder, const float* K4, int F, int Hh, int Ww, int cap, uint32_t frame0,
+                                 const pb_ransac_params* prm, float* R, float* t, int32_t* n_inl, int32_t* best_hyp,
+                                 int32_t* n_inl_refined, int32_t* status, void* ws, size_t ws_bytes, void* stream) {
+    PB_REQUIRE(prm != nullptr, "pb_pnp_ransac_map: prm is null");
+    PB_REQUIRE(F >= 0 && Hh > 0 && Ww > 0 && cap > 0, "pb_pnp_ransac_map: bad sizes");
+    if (F == 0) return 0;
+    const size_t need = pb_pnp_ransac_map_workspace_bytes(F, Hh, Ww, cap, prm);
+    PB_REQUIRE(ws != nullptr && ws_bytes >= need, "pb_pnp_ransac_map: workspace too small (%zu < %zu)", ws_bytes, need);
+    char* base = static_cast<char*>(ws);
+    float* pts = reinterpret_cast<float*>(base);
+    size_t off = align256((size_t)F * 5 * cap * sizeof(float));
+    int32_t* count = reinterpret_cast<int32_t*>(base + off);
+    off += align256((size_t)F * sizeof(int32_t));
+    void* cws = base + off;
+    const size_t cbytes = align256(pb_compact_workspace_bytes(F, Hh, Ww, cap));
+    off += cbytes;
+    void* rws = base + off;
+    const size_t rbytes = align256(pb_ransac_workspace_bytes(F, cap, prm));
+    int rc = pb_compact_map(xyz, mask, roi, extent, lfborder, F, Hh, Ww, cap, pts, count, nullptr, cws, cbytes, stream);
+    if (rc) return rc;
+    return pb_pnp_ransac_pts(pts, count, K4, F, cap, frame0, prm, nullptr, R, t, n_inl, best_hyp, n_inl_refined, status,
+                             nullptr, nullptr, nullptr, nullptr, rws, rbytes, stream);
+}

@@ -1,0 +1,325 @@
+// compact.cu -- K0: stream the coordinate map, compact foreground pixels, de-normalise (sm_100a).
+//
+// Replaces tools/trainer.py:386-421 (whole-map D2H copy, xyz*extent+lfborder, gather at `choose`)
+// and the dataset-side mask.flatten().nonzero() (dataset/linemod/batchdataset.py:673).
+// HBM-bound: every pixel costs 12 B of xyz + 1 B of mask, read exactly once with 128-bit loads,
+// next iteration's loads issued before the current block scan (register double buffer).
+// Output order is row-major pixel order (deterministic): per-iteration block scan, one
+// __syncthreads per 1024 pixels.  When there are too few frames to fill the GPU a frame is split
+// into S row bands; each band writes its own segment and a tiny merge kernel concatenates them.
+#include "common.cuh"
+
+namespace {
+
+constexpr int CT = 256;  // threads per CTA
+
+struct CompactArgs {
+    const float* xyz;
+    const uint8_t* mask;
+    const int32_t* roi;
+    const float* extent;
+    const float* lfborder;
+    float* pts;        // S==1: [F,5,cap] ; S>1: segments [F*S,5,segcap]
+    int32_t* count;    // S==1: [F]
+    int32_t* total;    // S==1: [F] optional
+    int32_t* seg_total;  // S>1: [F*S]
+    int HW, Ww, cap, S, quads_per_split, segcap;
+};
+
+__device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t* p) {
+    uint32_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+
+template <bool HAS_MASK>
+__global__ void __launch_bounds__(CT) compact_kernel(CompactArgs a) {
+    const int f = blockIdx.x / a.S, s = blockIdx.x % a.S;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nq = a.HW >> 2;
+    const int q0 = s * a.quads_per_split;
+    const int q1 = min(nq, q0 + a.quads_per_split);
+    const float4* px = reinterpret_cast<const float4*>(a.xyz + (size_t)f * 3 * a.HW);
+    const float4* py = px + nq;
+    const float4* pz = py + nq;
+    const uint32_t* pm = HAS_MASK ? reinterpret_cast<const uint32_t*>(a.mask + (size_t)f * a.HW) : nullptr;
+    const float e0 = a.extent[3 * f], e1 = a.extent[3 * f + 1], e2 = a.extent[3 * f + 2];
+    const float l0 = a.lfborder[3 * f], l1 = a.lfborder[3 * f + 1], l2 = a.lfborder[3 * f + 2];
+    const int rmin = a.roi ? a.roi[2 * f] : 0, cmin = a.roi ? a.roi[2 * f + 1] : 0;
+    const int ocap = a.S == 1 ? a.cap : a.segcap;
+    float* oX = a.pts + (size_t)blockIdx.x * 5 * ocap;
+    float* oY = oX + ocap; float* oZ = oY + ocap; float* oU = oZ + ocap; float* oV = oU + ocap;
+
+    __shared__ int wtot[2][CT / 32];
+    int running = 0;
+    int buf = 0;
+
+    float4 vx, vy, vz; uint32_t vm = 0;
+    int q = q0 + tid;
+    bool have = q < q1;
+    if (have) {
+        vx = ldg_stream_f4(px + q); vy = ldg_stream_f4(py + q); vz = ldg_stream_f4(pz + q);
+        if (HAS_MASK) vm = ldg_stream_u32(pm + q);
+    }
+    for (int qb = q0; qb < q1; qb += CT) {
+        // current registers
+        const float4 cxv = vx, cyv = vy, czv = vz; const uint32_t cm = vm; const bool chave = have;
+        const int cq = qb + tid;
+        // prefetch next
+        q = qb + CT + tid;
+        have = q < q1;
+        if (have) {
+            vx = ldg_stream_f4(px + q); vy = ldg_stream_f4(py + q); vz = ldg_stream_f4(pz + q);
+            if (HAS_MASK) vm = ldg_stream_u32(pm + q);
+        }
+        unsigned bits = 0;
+        if (chave) {
+            if (HAS_MASK) {
+                bits = ((cm & 0xFFu) ? 1u : 0u) | ((cm & 0xFF00u) ? 2u : 0u) | ((cm & 0xFF0000u) ? 4u : 0u) |
+                       ((cm & 0xFF000000u) ? 8u : 0u);
+            } else {
+                bits = ((cxv.x != 0.0f || cyv.x != 0.0f || czv.x != 0.0f) ? 1u : 0u) |
+                       ((cxv.y != 0.0f || cyv.y != 0.0f || czv.y != 0.0f) ? 2u : 0u) |
+                       ((cxv.z != 0.0f || cyv.z != 0.0f || czv.z != 0.0f) ? 4u : 0u) |
+                       ((cxv.w != 0.0f || cyv.w != 0.0f || czv.w != 0.0f) ? 8u : 0u);
+            }
+        }
+        const int c = __popc(bits);
+        int incl = c;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            int o = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += o;
+        }
+        if (lane == 31) wtot[buf][warp] = incl;
+        __syncthreads();
+        int woff = 0, btot = 0;
+#pragma unroll
+        for (int w = 0; w < CT / 32; ++w) {
+            int v = wtot[buf][w];
+            if (w < warp) woff += v;
+            btot += v;
+        }
+        if (bits) {
+            int pos = running + woff + incl - c;
+            const float xs[4] = {cxv.x, cxv.y, cxv.z, cxv.w};
+            const float ys[4] = {cyv.x, cyv.y, cyv.z, cyv.w};
+            const float zs[4] = {czv.x, czv.y, czv.z, czv.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (bits & (1u << k)) {
+                    if (pos < ocap) {
+                        const int p = 4 * cq + k;
+                        const int row = p / a.Ww, col = p - row * a.Ww;
+                        oX[pos] = fmaf(xs[k], e0, l0);
+                        oY[pos] = fmaf(ys[k], e1, l1);
+                        oZ[pos] = fmaf(zs[k], e2, l2);
+                        oU[pos] = (float)(col + cmin);
+                        oV[pos] = (float)(row + rmin);
+                    }
+                    ++pos;
+                }
+            }
+        }
+        running += btot;
+        buf ^= 1;
+    }
+    if (tid == 0) {
+        if (a.S == 1) {
+            a.count[f] = min(running, a.cap);
+            if (a.total) a.total[f] = running;
+        } else {
+            a.seg_total[blockIdx.x] = running;
+        }
+    }
+}
+
+// generic (any HW, any alignment) scalar variant: one pixel per thread per iteration
+template <bool HAS_MASK>
+__global__ void __launch_bounds__(CT) compact_kernel_scalar(CompactArgs a) {
+    const int f = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float* px = a.xyz + (size_t)f * 3 * a.HW;
+    const float* py = px + a.HW;
+    const float* pz = py + a.HW;
+    const uint8_t* pm = HAS_MASK ? a.mask + (size_t)f * a.HW : nullptr;
+    const float e0 = a.extent[3 * f], e1 = a.extent[3 * f + 1], e2 = a.extent[3 * f + 2];
+    const float l0 = a.lfborder[3 * f], l1 = a.lfborder[3 * f + 1], l2 = a.lfborder[3 * f + 2];
+    const int rmin = a.roi ? a.roi[2 * f] : 0, cmin = a.roi ? a.roi[2 * f + 1] : 0;
+    float* oX = a.pts + (size_t)f * 5 * a.cap;
+    float* oY = oX + a.cap; float* oZ = oY + a.cap; float* oU = oZ + a.cap; float* oV = oU + a.cap;
+    __shared__ int wtot[2][CT / 32];
+    int running = 0, buf = 0;
+    for (int pb = 0; pb < a.HW; pb += CT) {
+        const int p = pb + tid;
+        float x = 0.0f, y = 0.0f, z = 0.0f;
+        bool m = false;
+        if (p < a.HW) {
+            x = px[p]; y = py[p]; z = pz[p];
+            m = HAS_MASK ? (pm[p] != 0) : (x != 0.0f || y != 0.0f || z != 0.0f);
+        }
+        unsigned b = __ballot_sync(0xffffffffu, m);
+        if (lane == 0) wtot[buf][warp] = __popc(b);
+        __syncthreads();
+        int woff = 0, btot = 0;
+#pragma unroll
+        for (int w = 0; w < CT / 32; ++w) {
+            int v = wtot[buf][w];
+            if (w < warp) woff += v;
+            btot += v;
+        }
+        if (m) {
+            int pos = running + woff + __popc(b & ((1u << lane) - 1u));
+            if (pos < a.cap) {
+                const int row = p / a.Ww, col = p - row * a.Ww;
+                oX[pos] = fmaf(x, e0, l0); oY[pos] = fmaf(y, e1, l1); oZ[pos] = fmaf(z, e2, l2);
+                oU[pos] = (float)(col + cmin); oV[pos] = (float)(row + rmin);
+            }
+        }
+        running += btot;
+        buf ^= 1;
+    }
+    if (tid == 0) {
+        a.count[f] = min(running, a.cap);
+        if (a.total) a.total[f] = running;
+    }
+}
+
+__global__ void __launch_bounds__(CT) merge_segments_kernel(const float* seg, const int32_t* seg_total, int S,
+                                                            int segcap, int cap, float* pts, int32_t* count,
+                                                            int32_t* total) {
+    const int f = blockIdx.x;
+    int base = 0;
+    for (int s = 0; s < S; ++s) {
+        const int n_all = seg_total[f * S + s];
+        const int n = min(n_all, segcap);
+        const float* src = seg + (size_t)(f * S + s) * 5 * segcap;
+        for (int i = threadIdx.x; i < n; i += CT) {
+            const int o = base + i;
+            if (o < cap) {
+#pragma unroll
+                for (int c = 0; c < 5; ++c) pts[((size_t)f * 5 + c) * cap + o] = src[(size_t)c * segcap + i];
+            }
+        }
+        base += n_all;
+    }
+    if (threadIdx.x == 0) {
+        count[f] = min(base, cap);
+        if (total) total[f] = base;
+    }
+}
+
+__global__ void gather_kernel(const float* xyz, const int64_t* choose, const float* xmap, const float* ymap,
+                              const float* extent, const float* lfborder, int HW, int NP, int cap, float* pts,
+                              int32_t* count) {
+    const int f = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = min(NP, cap);
+    if (i == 0) count[f] = n;
+    if (i >= n) return;
+    long long p = choose[(size_t)f * NP + i];
+    if (p < 0) p = 0;
+    if (p >= HW) p = HW - 1;
+    const float* base = xyz + (size_t)f * 3 * HW;
+    float* o = pts + (size_t)f * 5 * cap;
+    o[i] = fmaf(base[p], extent[3 * f], lfborder[3 * f]);
+    o[cap + i] = fmaf(base[HW + p], extent[3 * f + 1], lfborder[3 * f + 1]);
+    o[2 * cap + i] = fmaf(base[2 * (size_t)HW + p], extent[3 * f + 2], lfborder[3 * f + 2]);
+    o[3 * cap + i] = xmap[(size_t)f * NP + i];
+    o[4 * cap + i] = ymap[(size_t)f * NP + i];
+}
+
+struct CPlan { int S, quads_per_split, segcap; bool vec; size_t off_tot, total; };
+
+CPlan make_cplan(int F, int Hh, int Ww, int cap) {
+    CPlan p;
+    const long long HW = (long long)Hh * Ww;
+    p.vec = (HW % 4) == 0;
+    int S = 1;
+    if (p.vec && F < 592) {
+        S = (592 + F - 1) / F;                      // ~4 CTAs per SM
+        int maxS = (int)((HW / 4 + 4095) / 4096);   // keep >= 16k pixels per band
+        if (S > maxS) S = maxS;
+        if (S < 1) S = 1;
+    }
+    const int nq = (int)(HW / 4);
+    p.quads_per_split = ((nq + S - 1) / S + CT - 1) / CT * CT;
+    p.S = (nq + p.quads_per_split - 1) / p.quads_per_split;
+    if (p.S < 1) p.S = 1;
+    long long sc = (long long)p.quads_per_split * 4;
+    p.segcap = (int)(sc < cap ? sc : cap);
+    if (p.S == 1) { p.off_tot = 0; p.total = 0; }
+    else {
+        size_t seg = (size_t)F * p.S * 5 * p.segcap * sizeof(float);
+        p.off_tot = (seg + 255) / 256 * 256;
+        p.total = p.off_tot + (size_t)F * p.S * sizeof(int32_t);
+    }
+    return p;
+}
+
+}  // namespace
+
+extern "C" size_t pb_compact_workspace_bytes(int F, int Hh, int Ww, int cap) {
+    if (F <= 0 || Hh <= 0 || Ww <= 0 || cap <= 0) return 0;
+    return make_cplan(F, Hh, Ww, cap).total;
+}
+
+extern "C" int pb_compact_map(const float* xyz, const uint8_t* mask, const int32_t* roi, const float* extent,
+                              const float* lfborder, int F, int Hh, int Ww, int cap, float* pts, int32_t* count,
+                              int32_t* total, void* ws, size_t ws_bytes, void* stream) {
+    PB_REQUIRE(F >= 0 && Hh > 0 && Ww > 0 && cap > 0, "pb_compact_map: bad sizes F=%d H=%d W=%d cap=%d", F, Hh, Ww, cap);
+    PB_REQUIRE((long long)Hh * Ww < (1ll << 30), "pb_compact_map: map too large");
+    if (F == 0) return 0;
+    PB_REQUIRE(xyz && extent && lfborder && pts && count, "pb_compact_map: null pointer argument");
+    CPlan p = make_cplan(F, Hh, Ww, cap);
+    PB_REQUIRE(p.total == 0 || (ws && ws_bytes >= p.total), "pb_compact_map: workspace too small (%zu < %zu)", ws_bytes, p.total);
+    PB_REQUIRE((long long)F * p.S < (1ll << 31), "pb_compact_map: grid too large");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CompactArgs a;
+    a.xyz = xyz; a.mask = mask; a.roi = roi; a.extent = extent; a.lfborder = lfborder;
+    a.count = count; a.total = total;
+    a.HW = Hh * Ww; a.Ww = Ww; a.cap = cap; a.S = p.S; a.quads_per_split = p.quads_per_split; a.segcap = p.segcap;
+    const bool aligned = (reinterpret_cast<uintptr_t>(xyz) % 16 == 0) &&
+                         (!mask || reinterpret_cast<uintptr_t>(mask) % 4 == 0);
+    if (!p.vec || !aligned) {
+        a.pts = pts; a.S = 1; a.seg_total = nullptr;
+        if (mask) compact_kernel_scalar<true><<<F, CT, 0, st>>>(a);
+        else compact_kernel_scalar<false><<<F, CT, 0, st>>>(a);
+        return pb_check_launch("compact_kernel_scalar") ? -2 : 0;
+    }
+    if (p.S == 1) {
+        a.pts = pts; a.seg_total = nullptr;
+    } else {
+        a.pts = static_cast<float*>(ws);
+        a.seg_total = reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_tot);
+    }
+    if (mask) compact_kernel<true><<<F * p.S, CT, 0, st>>>(a);
+    else compact_kernel<false><<<F * p.S, CT, 0, st>>>(a);
+    if (pb_check_launch("compact_kernel")) return -2;
+    if (p.S > 1) {
+        merge_segments_kernel<<<F, CT, 0, st>>>(a.pts, a.seg_total, p.S, p.segcap, cap, pts, count, total);
+        if (pb_check_launch("merge_segments_kernel")) return -2;
+    }
+    return 0;
+}
+
+extern "C" int pb_gather_correspondences(const float* xyz, const int64_t* choose, const float* xmap,
+                                         const float* ymap, const float* extent, const float* lfborder, int F,
+                                         int Hh, int Ww, int NP, int cap, float* pts, int32_t* count, void* stream) {
+    PB_REQUIRE(F >= 0 && Hh > 0 && Ww > 0 && NP > 0 && cap > 0, "pb_gather_correspondences: bad sizes");
+    PB_REQUIRE(F <= 65535, "pb_gather_correspondences: F too large (<= 65535)");
+    if (F == 0) return 0;
+    PB_REQUIRE(xyz && choose && xmap && ymap && extent && lfborder && pts && count,
+               "pb_gather_correspondences: null pointer argument");
+    const int n = NP < cap ? NP : cap;
+    dim3 grid((n + 127) / 128, F);
+    gather_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(xyz, choose, xmap, ymap, extent, lfborder,
+                                                                         Hh * Ww, NP, cap, pts, count);
+    return pb_check_launch("gather_kernel") ? -2 : 0;
+}

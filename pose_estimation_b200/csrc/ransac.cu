@@ -1,0 +1,342 @@
+// ransac.cu -- K1..K4: PnP-RANSAC on compacted correspondences (sm_100a).
+//
+// Replaces cv2.solvePnPRansac at tools/trainer.py:423-427 / lib/utils/utlis.py:59-63.
+//   ransac_score_kernel    one CTA per (frame, hypothesis slice):
+//       K1 Philox minimal-set sampling + K2 P3P solve, one hypothesis per thread;
+//       K3 reprojection scoring of EVERY correspondence: points staged in shared memory (SoA,
+//          conflict-free), lanes <-> points, NH hypotheses register-tiled per warp, per-lane
+//          counters + redux.sync; FP32-pipe bound (15 FMA-pipe ops per hypothesis*point).
+//   ransac_finalize_kernel one CTA per frame:
+//       K4 argmax over slices (lowest hypothesis index on ties), inlier bitmap by warp ballot,
+//          Gauss-Newton refit on the inliers with a fixed reduction tree (bit-reproducible on the
+//          CPU oracle), optional re-score -> refit rounds.
+#include "common.cuh"
+#include "ransac_plan.h"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------
+struct FinalArgs {
+    const float* pts;
+    const int32_t* count;
+    const float* K4;
+    const float* hypRt;
+    const unsigned long long* slice_best;
+    float* R; float* t; int32_t* n_inl; int32_t* best_hyp; int32_t* n_inl_refined; int32_t* status;
+    uint32_t* inl_bitmap; float* R0; float* t0;
+    int cap, H, HS, gn_iters, lo_rounds, min_inliers;
+    float thr2;
+};
+
+// fixed-shape block sum of K floats per thread: butterfly inside each warp, then warps in order.
+template <int K>
+__device__ __forceinline__ void block_tree_sum(float* v, float (*red)[28], float* tot, int tid) {
+    const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+    for (int k = 0; k < K; ++k) v[k] = warp_sum_bfly(v[k]);
+    __syncthreads();  // previous readers of red/tot are done
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) red[warp][k] = v[k];
+    }
+    __syncthreads();
+    if (tid < K) {
+        float s = red[0][tid];
+        for (int w = 1; w < PB_THREADS / 32; ++w) s = s + red[w][tid];
+        tot[tid] = s;
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ bool chol6_solve(const double A21[21], const double g[6], double d[6]) {
+    double A[6][6], L[6][6];
+    int k = 0;
+    for (int i = 0; i < 6; ++i)
+        for (int j = i; j < 6; ++j) { A[i][j] = A21[k]; A[j][i] = A21[k]; ++k; }
+    for (int i = 0; i < 6; ++i)
+        for (int j = 0; j < 6; ++j) L[i][j] = 0.0;
+    for (int j = 0; j < 6; ++j) {
+        double s = A[j][j];
+        for (int m = 0; m < j; ++m) s = s - L[j][m] * L[j][m];
+        if (!(s > 0.0)) return false;
+        double ljj = sqrt(s);
+        L[j][j] = ljj;
+        for (int i = j + 1; i < 6; ++i) {
+            double v = A[i][j];
+            for (int m = 0; m < j; ++m) v = v - L[i][m] * L[j][m];
+            L[i][j] = v / ljj;
+        }
+    }
+    double z[6];
+    for (int i = 0; i < 6; ++i) {
+        double v = g[i];
+        for (int m = 0; m < i; ++m) v = v - L[i][m] * z[m];
+        z[i] = v / L[i][i];
+    }
+    for (int i = 5; i >= 0; --i) {
+        double v = z[i];
+        for (int m = i + 1; m < 6; ++m) v = v - L[m][i] * d[m];
+        d[i] = v / L[i][i];
+    }
+    return true;
+}
+
+__global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* bm = reinterpret_cast<uint32_t*>(smem_raw);  // [ceil(cap/32)]
+    __shared__ float red[PB_THREADS / 32][28];
+    __shared__ float tot[28];
+    __shared__ int ired[PB_THREADS / 32];
+    __shared__ float sdelta[8];
+    __shared__ int sflag;
+
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int P = min(a.count[f], a.cap);
+    const int words = (a.cap + 31) / 32;
+    const float* X = a.pts + (size_t)f * 5 * a.cap;
+    const float* Y = X + a.cap;
+    const float* Z = Y + a.cap;
+    const float* U = Z + a.cap;
+    const float* V = U + a.cap;
+    const float fx = a.K4[4 * f], fy = a.K4[4 * f + 1], cx = a.K4[4 * f + 2], cy = a.K4[4 * f + 3];
+
+    // argmax over slices
+    unsigned long long key = a.slice_best[(size_t)f * a.HS];
+    for (int s = 1; s < a.HS; ++s) {
+        unsigned long long k = a.slice_best[(size_t)f * a.HS + s];
+        key = k > key ? k : key;
+    }
+    const int bc = (int)(uint32_t)(key >> 32) - 1;
+    const int bh = (int)(0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull));
+    const bool fail_pts = P < 4;
+    const bool fail_model = !fail_pts && (bc < 0 || bc < a.min_inliers);
+    if (fail_pts || fail_model) {
+        if (tid < 9) {
+            float v = (tid % 4 == 0) ? 1.0f : 0.0f;
+            a.R[9 * f + tid] = v;
+            if (a.R0) a.R0[9 * f + tid] = v;
+        }
+        if (tid < 3) { a.t[3 * f + tid] = 0.0f; if (a.t0) a.t0[3 * f + tid] = 0.0f; }
+        if (tid == 0) {
+            a.n_inl[f] = 0; a.best_hyp[f] = -1; a.n_inl_refined[f] = 0;
+            a.status[f] = fail_pts ? PB_STATUS_TOO_FEW_POINTS : PB_STATUS_NO_MODEL;
+        }
+        if (a.inl_bitmap)
+            for (int w = tid; w < words; w += PB_THREADS) a.inl_bitmap[(size_t)f * words + w] = 0u;
+        return;
+    }
+
+    float Rb[9], tb[3];
+    {
+        const float* o = a.hypRt + ((size_t)f * a.H + bh) * 12;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) Rb[k] = o[k];
+        tb[0] = o[9]; tb[1] = o[10]; tb[2] = o[11];
+    }
+    if (tid < 9 && a.R0) a.R0[9 * f + tid] = Rb[tid];
+    if (tid < 3 && a.t0) a.t0[3 * f + tid] = tb[tid];
+
+    float q[4], tt[3] = {tb[0], tb[1], tb[2]};
+    rot_to_quat(Rb, q);
+    float M[12];
+    make_proj(fx, fy, cx, cy, Rb, tb, M);
+
+    int nref = bc;
+    for (int w = tid; w < (a.cap + PB_THREADS - 1) / PB_THREADS * (PB_THREADS / 32); w += PB_THREADS) bm[w] = 0u;
+    __syncthreads();
+    // round -1: bitmap of the best minimal hypothesis; rounds 0..lo_rounds: refit then re-score
+    for (int round = -1; round <= a.lo_rounds; ++round) {
+        if (round >= 0) {
+            // ---- centroid of the inlier object points
+            float cs[3] = {0.0f, 0.0f, 0.0f};
+            int cn = 0;
+            for (int i = tid; i < P; i += PB_THREADS)
+                if ((bm[i >> 5] >> (i & 31)) & 1u) { cs[0] += X[i]; cs[1] += Y[i]; cs[2] += Z[i]; ++cn; }
+            cn = __reduce_add_sync(0xffffffffu, cn);
+            block_tree_sum<3>(cs, red, tot, tid);
+            if (lane == 0) ired[warp] = cn;
+            __syncthreads();
+            int cnt_all = 0;
+            for (int w = 0; w < PB_THREADS / 32; ++w) cnt_all += ired[w];
+            if (cnt_all < 4) break;  // uniform
+            const float fn = (float)cnt_all;
+            const float cb[3] = {tot[0] / fn, tot[1] / fn, tot[2] / fn};
+            float R[9];
+            quat_to_rot(q, R);
+            float tc[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+                tc[i] = fmaf(R[3 * i], cb[0], fmaf(R[3 * i + 1], cb[1], fmaf(R[3 * i + 2], cb[2], tt[i])));
+            // ---- Gauss-Newton on the reprojection error of the inliers
+            for (int it = 0; it < a.gn_iters; ++it) {
+                quat_to_rot(q, R);
+                float acc[27];
+#pragma unroll
+                for (int k = 0; k < 27; ++k) acc[k] = 0.0f;
+                for (int i = tid; i < P; i += PB_THREADS) {
+                    if (!((bm[i >> 5] >> (i & 31)) & 1u)) continue;
+                    float xo = X[i] - cb[0], yo = Y[i] - cb[1], zo = Z[i] - cb[2];
+                    float xr = fmaf(R[0], xo, fmaf(R[1], yo, R[2] * zo));
+                    float yr = fmaf(R[3], xo, fmaf(R[4], yo, R[5] * zo));
+                    float zr = fmaf(R[6], xo, fmaf(R[7], yo, R[8] * zo));
+                    float xc = xr + tc[0], yc = yr + tc[1], zc = zr + tc[2];
+                    float iz = 1.0f / zc;
+                    float un = xc * iz, vn = yc * iz;
+                    float ru = fmaf(fx, un, cx) - U[i];
+                    float rv = fmaf(fy, vn, cy) - V[i];
+                    float ja = fx * iz, jb = fy * iz;
+                    float jc = -(ja * un), jd = -(jb * vn);
+                    float ju[6] = {yr * jc, fmaf(zr, ja, -(xr * jc)), -(yr * ja), ja, 0.0f, jc};
+                    float jv[6] = {fmaf(yr, jd, -(zr * jb)), -(xr * jd), xr * jb, 0.0f, jb, jd};
+                    int k = 0;
+#pragma unroll
+                    for (int r = 0; r < 6; ++r)
+#pragma unroll
+                        for (int s2 = r; s2 < 6; ++s2) { acc[k] = fmaf(ju[r], ju[s2], fmaf(jv[r], jv[s2], acc[k])); ++k; }
+#pragma unroll
+                    for (int r = 0; r < 6; ++r) acc[21 + r] = fmaf(ju[r], ru, fmaf(jv[r], rv, acc[21 + r]));
+                }
+                block_tree_sum<27>(acc, red, tot, tid);
+                if (tid == 0) {
+                    double A21[21], g[6], d[6];
+                    for (int k = 0; k < 21; ++k) A21[k] = (double)tot[k];
+                    for (int k = 0; k < 6; ++k) g[k] = -(double)tot[21 + k];
+                    bool ok = chol6_solve(A21, g, d);
+                    float dl[6];
+                    if (ok)
+                        for (int k = 0; k < 6; ++k) { dl[k] = (float)d[k]; ok = ok && isfinite(dl[k]); }
+                    if (ok)
+                        for (int k = 0; k < 6; ++k) sdelta[k] = dl[k];
+                    sflag = ok ? 1 : 0;
+                }
+                __syncthreads();
+                if (!sflag) break;  // uniform
+                const float hx = 0.5f * sdelta[0], hy = 0.5f * sdelta[1], hz = 0.5f * sdelta[2];
+                const float w0 = q[0], x0 = q[1], y0 = q[2], z0 = q[3];
+                float nw = w0 - fmaf(hx, x0, fmaf(hy, y0, hz * z0));
+                float nx = x0 + fmaf(hx, w0, fmaf(hy, z0, -(hz * y0)));
+                float ny = y0 + fmaf(hy, w0, fmaf(hz, x0, -(hx * z0)));
+                float nz = z0 + fmaf(hz, w0, fmaf(hx, y0, -(hy * x0)));
+                float in = 1.0f / sqrtf(fmaf(nw, nw, fmaf(nx, nx, fmaf(ny, ny, nz * nz))));
+                q[0] = nw * in; q[1] = nx * in; q[2] = ny * in; q[3] = nz * in;
+                tc[0] += sdelta[3]; tc[1] += sdelta[4]; tc[2] += sdelta[5];
+            }
+            quat_to_rot(q, R);
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+                tt[i] = tc[i] - fmaf(R[3 * i], cb[0], fmaf(R[3 * i + 1], cb[1], R[3 * i + 2] * cb[2]));
+            make_proj(fx, fy, cx, cy, R, tt, M);
+        }
+        // ---- (re-)score: inlier bitmap by warp ballot
+        __syncthreads();
+        int cn = 0;
+        for (int base = 0; base < P; base += PB_THREADS) {
+            const int i = base + tid;
+            bool in = i < P && inlier_test(M, X[i], Y[i], Z[i], U[i], V[i], a.thr2);
+            unsigned b = __ballot_sync(0xffffffffu, in);
+            if (lane == 0) { bm[(base >> 5) + warp] = b; cn += __popc(b); }
+        }
+        if (lane == 0) ired[warp] = cn;
+        __syncthreads();
+        int tot_in = 0;
+        for (int w = 0; w < PB_THREADS / 32; ++w) tot_in += ired[w];
+        if (round < 0) {
+            if (a.inl_bitmap)
+                for (int w = tid; w < words; w += PB_THREADS) a.inl_bitmap[(size_t)f * words + w] = bm[w];
+        } else {
+            nref = tot_in;
+        }
+        __syncthreads();
+    }
+    float R[9];
+    quat_to_rot(q, R);
+    if (tid < 9) a.R[9 * f + tid] = R[tid];
+    if (tid < 3) a.t[3 * f + tid] = tt[tid];
+    if (tid == 0) { a.n_inl[f] = bc; a.best_hyp[f] = bh; a.n_inl_refined[f] = nref; a.status[f] = PB_STATUS_OK; }
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void resample_inliers_kernel(const uint32_t* bitmap, const int32_t* count, int F, int cap, int n,
+                                        uint32_t frame0, uint32_t seed_lo, uint32_t seed_hi, int32_t* out) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= F) return;
+    const int words = (cap + 31) / 32;
+    const uint32_t* bm = bitmap + (size_t)f * words;
+    const int P = min(count[f], cap);
+    int32_t* o = out + (size_t)f * n;
+    int m = 0;
+    for (int w = 0; w < (P + 31) / 32; ++w) m += __popc(bm[w]);
+    if (m == 0) { for (int k = 0; k < n; ++k) o[k] = -1; return; }
+    if (m > n) {
+        int sel = 0, j = 0;
+        uint32_t r[4] = {0, 0, 0, 0};
+        for (int i = 0; i < P && sel < n; ++i) {
+            if (!((bm[i >> 5] >> (i & 31)) & 1u)) continue;
+            if ((j & 3) == 0) philox4x32_10((uint32_t)(j >> 2), frame0 + (uint32_t)f, 0u, PB_RESAMPLE_TAG, seed_lo, seed_hi, r);
+            uint32_t pick = __umulhi(r[j & 3], (uint32_t)(m - j));
+            if (pick < (uint32_t)(n - sel)) o[sel++] = i;
+            ++j;
+        }
+    } else {
+        int k = 0;
+        for (int i = 0; i < P; ++i)
+            if ((bm[i >> 5] >> (i & 31)) & 1u) o[k++] = i;
+        for (; k < n; ++k) o[k] = o[k - m];
+    }
+}
+
+
+}  // namespace
+
+extern "C" size_t pb_ransac_workspace_bytes(int F, int cap, const pb_ransac_params* prm) {
+    if (F <= 0 || cap <= 0 || !prm || prm->n_hyp <= 0) return 0;
+    return make_plan(F, cap, prm).total;
+}
+
+extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const float* K4, int F, int cap,
+                                 uint32_t frame0, const pb_ransac_params* prm, const int32_t* sample_idx,
+                                 float* R, float* t, int32_t* n_inl, int32_t* best_hyp, int32_t* n_inl_refined,
+                                 int32_t* status, int32_t* hyp_counts, uint32_t* inl_bitmap, float* R0, float* t0,
+                                 void* ws, size_t ws_bytes, void* stream) {
+    PB_REQUIRE(prm != nullptr, "pb_pnp_ransac_pts: prm is null");
+    PB_REQUIRE(F >= 0 && cap > 0, "pb_pnp_ransac_pts: bad sizes F=%d cap=%d", F, cap);
+    PB_REQUIRE(prm->n_hyp > 0 && prm->n_hyp <= (1 << 20), "pb_pnp_ransac_pts: n_hyp=%d out of range", prm->n_hyp);
+    PB_REQUIRE(prm->thresh_px > 0.0f && prm->gn_iters >= 0 && prm->lo_rounds >= 0, "pb_pnp_ransac_pts: bad params");
+    if (F == 0) return 0;
+    PB_REQUIRE(pts && count && K4 && R && t && n_inl && best_hyp && n_inl_refined && status,
+               "pb_pnp_ransac_pts: null pointer argument");
+    Plan p = make_plan(F, cap, prm);
+    PB_REQUIRE(ws != nullptr && ws_bytes >= p.total, "pb_pnp_ransac_pts: workspace too small (%zu < %zu)", ws_bytes, p.total);
+    PB_REQUIRE(p.smem_score <= 227 * 1024 && p.smem_final <= 200 * 1024, "pb_pnp_ransac_pts: shared memory plan too large");
+    PB_REQUIRE((size_t)F * p.HS < (1ull << 31), "pb_pnp_ransac_pts: grid too large");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    ScoreArgs sa;
+    sa.pts = pts; sa.count = count; sa.K4 = K4; sa.sample_idx = sample_idx;
+    sa.hypRt = static_cast<float*>(ws);
+    sa.hyp_counts = hyp_counts;
+    sa.slice_best = reinterpret_cast<unsigned long long*>(static_cast<char*>(ws) + p.off_best);
+    sa.cap = cap; sa.H = prm->n_hyp; sa.HS = p.HS; sa.Hs = p.Hs; sa.CH = p.CH; sa.PP = p.PP;
+    sa.frame0 = frame0; sa.seed_lo = prm->seed_lo; sa.seed_hi = prm->seed_hi;
+    sa.thr2 = prm->thresh_px * prm->thresh_px;
+    if (pb_launch_score(sa, p, F, st)) return -2;
+    FinalArgs fa;
+    fa.pts = pts; fa.count = count; fa.K4 = K4; fa.hypRt = sa.hypRt; fa.slice_best = sa.slice_best;
+    fa.R = R; fa.t = t; fa.n_inl = n_inl; fa.best_hyp = best_hyp; fa.n_inl_refined = n_inl_refined;
+    fa.status = status; fa.inl_bitmap = inl_bitmap; fa.R0 = R0; fa.t0 = t0;
+    fa.cap = cap; fa.H = prm->n_hyp; fa.HS = p.HS; fa.gn_iters = prm->gn_iters; fa.lo_rounds = prm->lo_rounds;
+    fa.min_inliers = prm->min_inliers; fa.thr2 = sa.thr2;
+    cudaFuncSetAttribute(ransac_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_final);
+    ransac_finalize_kernel<<<F, PB_THREADS, p.smem_final, st>>>(fa);
+    if (pb_check_launch("ransac_finalize_kernel")) return -2;
+    return 0;
+}
+
+extern "C" int pb_resample_inliers(const uint32_t* inl_bitmap, const int32_t* count, int F, int cap, int n,
+                                   uint32_t frame0, uint32_t seed_lo, uint32_t seed_hi, int32_t* out, void* stream) {
+    PB_REQUIRE(F >= 0 && cap > 0 && n > 0, "pb_resample_inliers: bad sizes");
+    if (F == 0) return 0;
+    PB_REQUIRE(inl_bitmap && count && out, "pb_resample_inliers: null pointer argument");
+    resample_inliers_kernel<<<(F + 63) / 64, 64, 0, static_cast<cudaStream_t>(stream)>>>(
+        inl_bitmap, count, F, cap, n, frame0, seed_lo, seed_hi, out);
+    return pb_check_launch("resample_inliers_kernel") ? -2 : 0;
+}

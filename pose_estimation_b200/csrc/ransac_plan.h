@@ -1,0 +1,50 @@
+// ransac_plan.h -- launch plan + argument block shared by ransac_score.cu and ransac.cu.
+#pragma once
+#include "common.cuh"
+
+struct ScoreArgs {
+    const float* pts;
+    const int32_t* count;
+    const float* K4;
+    const int32_t* sample_idx;
+    float* hypRt;                    // [F,H,12] R|t of every valid hypothesis
+    int32_t* hyp_counts;             // optional [F,H]
+    unsigned long long* slice_best;  // [F,HS] packed (count+1, ~hyp)
+    int cap, H, HS, Hs, CH, PP;      // Hs hypotheses per slice (power of two >= 32); PP point parts
+    uint32_t frame0, seed_lo, seed_hi;
+    float thr2;
+};
+
+struct Plan {
+    int HS, Hs, CH, PP, NHL;
+    size_t smem_score, smem_final, off_best, total;
+};
+
+// Hypotheses of a frame are cut into HS slices of Hs (power of two) so that few-frame launches
+// still fill 148 SMs; a slice narrower than the CTA splits the points PP ways instead.
+static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm) {
+    Plan p;
+    const int H = prm->n_hyp;
+    int Hs = 32;
+    while (Hs < H && Hs < 1024) Hs <<= 1;              // whole frame in one slice if it fits
+    if (F < 296) {                                     // few frames: more, narrower slices
+        int want = (296 + F - 1) / F;
+        while (Hs > 64 && (H + Hs - 1) / Hs < want) Hs >>= 1;
+    }
+    p.Hs = Hs;
+    p.HS = (H + Hs - 1) / Hs;
+    p.NHL = Hs > PB_THREADS ? Hs / PB_THREADS : 1;
+    p.PP = Hs < PB_THREADS ? PB_THREADS / Hs : 1;
+    int CH = (cap + 127) / 128 * 128;
+    if (CH > 2048) CH = 2048;
+    p.CH = CH;
+    p.smem_score = (size_t)Hs * 13 * 4 + (size_t)CH * 5 * 4;
+    p.smem_final = (size_t)((cap + PB_THREADS - 1) / PB_THREADS) * (PB_THREADS / 32) * 4;
+    size_t hyp = (size_t)F * H * 12 * sizeof(float);
+    p.off_best = (hyp + 255) / 256 * 256;
+    p.total = p.off_best + (size_t)F * p.HS * sizeof(unsigned long long);
+    return p;
+}
+
+// defined in ransac_score.cu
+int pb_launch_score(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st);

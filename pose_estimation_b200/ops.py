@@ -1,0 +1,163 @@
+"""Tensor-level wrappers over the C ABI: torch owns device memory and the stream, nothing else.
+
+Every function takes CUDA tensors, allocates its outputs / workspace with torch, and launches the
+sm_100a kernels asynchronously on ``torch.cuda.current_stream()``.  No host synchronisation
+happens here.  CPU tensors are rejected: there is no fallback implementation.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import torch
+
+from . import _lib
+from ._lib import RansacParams, call
+
+
+@dataclass
+class RansacConfig:
+    """Defaults are the reference's hard-coded constants where it has them
+    (tools/trainer.py:426: reprojectionError=1) plus this path's own (256 hypotheses)."""
+    n_hyp: int = 256
+    thresh_px: float = 1.0
+    gn_iters: int = 6
+    lo_rounds: int = 0
+    min_inliers: int = 5
+    seed: int = 0x5EED
+
+    def c_struct(self) -> RansacParams:
+        return RansacParams(self.n_hyp, self.thresh_px, self.gn_iters, self.lo_rounds, self.min_inliers,
+                            self.seed & 0xFFFFFFFF, (self.seed >> 32) & 0xFFFFFFFF)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _chk(t, dtype, name, allow_none=False):
+    if t is None:
+        if allow_none:
+            return None
+        raise TypeError(f"{name} is required")
+    if not t.is_cuda:
+        raise _lib.PoseB200Error(f"{name} must be a CUDA tensor (pose_estimation_b200 has no CPU path)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t.contiguous()
+
+
+def _ws(nbytes, device):
+    return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=device)
+
+
+# ----------------------------------------------------------------------------- K0
+def compact_map(xyz, mask, extent, lfborder, cap, roi=None, want_total=False):
+    """xyz [F,3,H,W] f32, mask [F,H,W] u8|None, extent/lfborder [F,3] f32 -> pts [F,5,cap], count [F]."""
+    xyz = _chk(xyz, torch.float32, "xyz")
+    mask = _chk(mask, torch.uint8, "mask", True)
+    extent = _chk(extent, torch.float32, "extent")
+    lfborder = _chk(lfborder, torch.float32, "lfborder")
+    roi = _chk(roi, torch.int32, "roi", True)
+    F, _, H, W = xyz.shape
+    dev = xyz.device
+    pts = torch.empty((F, 5, cap), dtype=torch.float32, device=dev)
+    count = torch.empty((F,), dtype=torch.int32, device=dev)
+    total = torch.empty((F,), dtype=torch.int32, device=dev) if want_total else None
+    nb = _lib.load().pb_compact_workspace_bytes(F, H, W, cap)
+    ws = _ws(nb, dev)
+    call("pb_compact_map", _ptr(xyz), _ptr(mask), _ptr(roi), _ptr(extent), _ptr(lfborder), F, H, W, cap,
+         _ptr(pts), _ptr(count), _ptr(total), _ptr(ws), ws.numel(), _stream())
+    return (pts, count, total) if want_total else (pts, count)
+
+
+def gather_correspondences(xyz, choose, xmap, ymap, extent, lfborder, cap=None):
+    xyz = _chk(xyz, torch.float32, "xyz")
+    choose = _chk(choose, torch.int64, "choose")
+    xmap = _chk(xmap, torch.float32, "xmap")
+    ymap = _chk(ymap, torch.float32, "ymap")
+    extent = _chk(extent, torch.float32, "extent")
+    lfborder = _chk(lfborder, torch.float32, "lfborder")
+    F, _, H, W = xyz.shape
+    NP = choose.shape[-1]
+    cap = cap or NP
+    pts = torch.empty((F, 5, cap), dtype=torch.float32, device=xyz.device)
+    count = torch.empty((F,), dtype=torch.int32, device=xyz.device)
+    call("pb_gather_correspondences", _ptr(xyz), _ptr(choose), _ptr(xmap), _ptr(ymap), _ptr(extent),
+         _ptr(lfborder), F, H, W, NP, cap, _ptr(pts), _ptr(count), _stream())
+    return pts, count
+
+
+# ----------------------------------------------------------------------------- K1-K4
+def pnp_ransac_pts(pts, count, K4, cfg: RansacConfig | None = None, frame0=0, sample_idx=None,
+                   want_counts=False, want_bitmap=False, want_minimal=False):
+    """pts [F,5,cap] f32, count [F] i32, K4 [F,4] f32 -> dict of device tensors."""
+    cfg = cfg or RansacConfig()
+    pts = _chk(pts, torch.float32, "pts")
+    count = _chk(count, torch.int32, "count")
+    K4 = _chk(K4, torch.float32, "K4")
+    sample_idx = _chk(sample_idx, torch.int32, "sample_idx", True)
+    F, _, cap = pts.shape
+    dev = pts.device
+    prm = cfg.c_struct()
+    out = dict(R=torch.empty((F, 3, 3), dtype=torch.float32, device=dev),
+               t=torch.empty((F, 3), dtype=torch.float32, device=dev),
+               n_inl=torch.empty((F,), dtype=torch.int32, device=dev),
+               best_hyp=torch.empty((F,), dtype=torch.int32, device=dev),
+               n_inl_refined=torch.empty((F,), dtype=torch.int32, device=dev),
+               status=torch.empty((F,), dtype=torch.int32, device=dev))
+    hc = torch.empty((F, cfg.n_hyp), dtype=torch.int32, device=dev) if want_counts else None
+    bm = torch.empty((F, (cap + 31) // 32), dtype=torch.int32, device=dev) if want_bitmap else None
+    R0 = torch.empty((F, 3, 3), dtype=torch.float32, device=dev) if want_minimal else None
+    t0 = torch.empty((F, 3), dtype=torch.float32, device=dev) if want_minimal else None
+    nb = _lib.load().pb_ransac_workspace_bytes(F, cap, C.byref(prm))
+    ws = _ws(nb, dev)
+    call("pb_pnp_ransac_pts", _ptr(pts), _ptr(count), _ptr(K4), F, cap, frame0, C.byref(prm), _ptr(sample_idx),
+         _ptr(out["R"]), _ptr(out["t"]), _ptr(out["n_inl"]), _ptr(out["best_hyp"]), _ptr(out["n_inl_refined"]),
+         _ptr(out["status"]), _ptr(hc), _ptr(bm), _ptr(R0), _ptr(t0), _ptr(ws), ws.numel(), _stream())
+    if want_counts:
+        out["hyp_counts"] = hc
+    if want_bitmap:
+        out["inl_bitmap"] = bm
+    if want_minimal:
+        out["R0"], out["t0"] = R0, t0
+    return out
+
+
+class MapRansac:
+    """Reusable map -> pose launcher (K0 + K1-K4) with a persistent workspace and outputs."""
+
+    def __init__(self, F, H, W, cap, cfg: RansacConfig | None = None, device="cuda"):
+        self.F, self.H, self.W, self.cap = F, H, W, cap
+        self.cfg = cfg or RansacConfig()
+        self.prm = self.cfg.c_struct()
+        dev = torch.device(device)
+        nb = _lib.load().pb_pnp_ransac_map_workspace_bytes(F, H, W, cap, C.byref(self.prm))
+        self.ws = _ws(nb, dev)
+        self.R = torch.empty((F, 3, 3), dtype=torch.float32, device=dev)
+        self.t = torch.empty((F, 3), dtype=torch.float32, device=dev)
+        self.n_inl = torch.empty((F,), dtype=torch.int32, device=dev)
+        self.best_hyp = torch.empty((F,), dtype=torch.int32, device=dev)
+        self.n_inl_refined = torch.empty((F,), dtype=torch.int32, device=dev)
+        self.status = torch.empty((F,), dtype=torch.int32, device=dev)
+
+    def __call__(self, xyz, mask, extent, lfborder, K4, roi=None, frame0=0):
+        call("pb_pnp_ransac_map", _ptr(xyz), _ptr(mask), _ptr(roi), _ptr(extent), _ptr(lfborder), _ptr(K4),
+             self.F, self.H, self.W, self.cap, frame0, C.byref(self.prm), _ptr(self.R), _ptr(self.t),
+             _ptr(self.n_inl), _ptr(self.best_hyp), _ptr(self.n_inl_refined), _ptr(self.status),
+             _ptr(self.ws), self.ws.numel(), _stream())
+        return self
+
+
+def resample_inliers(inl_bitmap, count, cap, n, seed=0x5EED, frame0=0):
+    inl_bitmap = _chk(inl_bitmap, torch.int32, "inl_bitmap")
+    count = _chk(count, torch.int32, "count")
+    F = count.shape[0]
+    out = torch.empty((F, n), dtype=torch.int32, device=count.device)
+    call("pb_resample_inliers", _ptr(inl_bitmap), _ptr(count), F, cap, n, frame0, seed & 0xFFFFFFFF,
+         (seed >> 32) & 0xFFFFFFFF, _ptr(out), _stream())
+    return out

@@ -1,0 +1,149 @@
+"""Seeded synthetic LineMOD-shaped inputs for tests and bench.
+
+Input generation only -- not part of the timed hot path.  Shapes and conventions follow the
+reference's dataset code (dataset/linemod/batchdataset.py:667-771): a normalised model-coordinate
+map ``xyz [3,h,w]`` (0 = background, :688-693), a mask, integer pixel coordinates, per-class
+``extent`` / ``lfborder`` / ``diameter`` taken from dataset_config/models_info.yml (mm / 1000,
+batchdataset.py:163-165), LineMOD intrinsics (:80-82), ``target = model @ R^T + t`` (:707).
+
+Each frame shows an ellipsoid inscribed in the object's box; a pixel's model coordinate is the
+ray/ellipsoid hit, so correspondences are exact before noise/outliers are injected.  The mask is
+a seeded uniform subset (P of them) of the silhouette pixels: a compact blob of ~1000 px on a
+smooth surface would make PnP itself ill-conditioned (every pose within ~1 cm reprojects the
+whole blob to < 1 px), which says nothing about either implementation.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+IMG_H, IMG_W = 480, 640
+LINEMOD_K4 = np.array([572.4114, 573.57043, 325.2611, 242.04899], dtype=np.float32)
+OBJLIST = [1, 2, 4, 5, 6, 8, 9, 10, 11, 12, 13, 14, 15]     # batchdataset.py:42
+SYM_CLS = [7, 8]                                            # indices into OBJLIST (eggbox, glue), :76
+
+# dataset_config/models_info.yml: id -> (diameter, (min_x,min_y,min_z), (size_x,size_y,size_z)) in mm
+_MODELS_INFO_MM = {
+    1: (102.09865663, (-37.9343, -38.7996, -45.8845), (75.8686, 77.5992, 91.769)),
+    2: (247.50624233, (-107.835, -60.9279, -109.705), (215.67, 121.8557, 219.41)),
+    4: (172.49224865, (-68.3297, -71.5151, -50.2485), (136.6594, 143.0302, 100.497)),
+    5: (201.40358597, (-50.3958, -90.8979, -96.867), (100.7916, 181.7958, 193.734)),
+    6: (154.54551808, (-33.5054, -63.8165, -58.7283), (67.0107, 127.633, 117.4566)),
+    8: (261.47178102, (-114.738, -37.7357, -104.001), (229.476, 75.4714, 208.002)),
+    9: (108.99920102, (-52.2146, -38.7038, -42.8485), (104.4292, 77.4076, 85.697)),
+    10: (164.62758848, (-75.0923, -53.5375, -34.6207), (150.1846, 107.075, 69.2414)),
+    11: (175.88933422, (-18.3605, -38.933, -86.4079), (36.7211, 77.866, 172.8158)),
+    12: (145.54287471, (-50.4439, -54.2485, -45.4), (100.8878, 108.497, 90.8)),
+    13: (278.07811733, (-129.113, -59.241, -70.5662), (258.226, 118.4821, 141.1324)),
+    14: (282.60129399, (-101.573, -58.8763, -106.558), (203.146, 117.7525, 213.116)),
+    15: (212.35825148, (-46.9591, -73.7167, -92.3737), (93.9181, 147.4334, 184.7474)),
+}
+N_CLS = len(OBJLIST)
+DIAMETER = np.array([_MODELS_INFO_MM[o][0] / 1000.0 for o in OBJLIST], dtype=np.float32)
+LFBORDER = np.array([_MODELS_INFO_MM[o][1] for o in OBJLIST], dtype=np.float64) / 1000.0
+EXTENT = np.array([_MODELS_INFO_MM[o][2] for o in OBJLIST], dtype=np.float64) / 1000.0
+IS_SYM = np.array([1 if c in SYM_CLS else 0 for c in range(N_CLS)], dtype=np.uint8)
+
+
+def class_models(n_points: int, seed: int = 0x5EED) -> np.ndarray:
+    """[C, n_points, 3] f32 model clouds, uniform in each class box."""
+    rng = np.random.default_rng([seed, 0xC1A55, n_points])
+    u = rng.random((N_CLS, n_points, 3))
+    return (LFBORDER[:, None, :] + u * EXTENT[:, None, :]).astype(np.float32)
+
+
+def random_rotation(rng) -> np.ndarray:
+    q = rng.normal(size=4)
+    q /= np.linalg.norm(q)
+    w, x, y, z = q
+    return np.array([
+        [1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+        [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+        [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+
+
+def make_frame_sparse(seed: int, config_id: int, frame: int, cls: int | None = None,
+                      p_range=(800, 1200), outlier_frac=0.25, noise_m=1e-3,
+                      K4=LINEMOD_K4, H=IMG_H, W=IMG_W):
+    """One frame in sparse form.  Returns dict with
+       rows,cols [P] int32 (row-major sorted), xyzn [P,3] f32 (normalised map values, never 0),
+       cls, R_gt [3,3] f32, t_gt [3] f32, inlier [P] bool (ground truth of the injected outliers)."""
+    rng = np.random.default_rng([seed, config_id, frame])
+    if cls is None:
+        cls = frame % N_CLS
+    ext, lfb = EXTENT[cls], LFBORDER[cls]
+    fx, fy, cx, cy = [float(v) for v in K4]
+    R = random_rotation(rng)
+    t = np.array([rng.uniform(-0.15, 0.15), rng.uniform(-0.1, 0.1), rng.uniform(0.6, 1.2)])
+    P = int(rng.integers(p_range[0], p_range[1] + 1))
+    uc, vc = fx * t[0] / t[2] + cx, fy * t[1] / t[2] + cy
+    smax = 0.49 * float(ext.max())
+    rad = int(np.ceil(max(fx, fy) * smax / max(t[2] - smax, 0.2))) + 2     # silhouette bound (px)
+    c0, c1 = max(int(uc) - rad, 0), min(int(uc) + rad + 1, W)
+    r0, r1 = max(int(vc) - rad, 0), min(int(vc) + rad + 1, H)
+    rr, cc = np.meshgrid(np.arange(r0, r1), np.arange(c0, c1), indexing='ij')
+    rr, cc = rr.reshape(-1), cc.reshape(-1)
+    d_cam = np.stack([(cc - cx) / fx, (rr - cy) / fy, np.ones_like(cc, dtype=np.float64)], axis=1)
+    o = -R.T @ t                                   # camera centre in the object frame
+    d = d_cam @ R                                  # rows: R^T d_cam
+    centre, semi = lfb + 0.5 * ext, 0.49 * ext
+    oo, dd = (o - centre) / semi, d / semi
+    qa = (dd * dd).sum(1)
+    qb = (dd * oo[None, :]).sum(1)
+    qc = float(oo @ oo) - 1.0
+    disc = qb * qb - qa * qc
+    hit = disc >= 0
+    tau = np.where(hit, (-qb - np.sqrt(np.where(hit, disc, 0.0))) / qa, 0.0)
+    hit &= tau > 0
+    rr, cc, tau, d = rr[hit], cc[hit], tau[hit], d[hit]
+    # the mask is a seeded uniform subset of the silhouette (all of it if it is smaller than P)
+    if rr.shape[0] > P:
+        keep = np.sort(rng.choice(rr.shape[0], size=P, replace=False))   # row-major order kept
+        rr, cc, tau, d = rr[keep], cc[keep], tau[keep], d[keep]
+    P = rr.shape[0]
+    Xo = o[None, :] + tau[:, None] * d             # exact surface points (object frame, metres)
+    inl = rng.random(P) >= outlier_frac
+    Xo = Xo + rng.normal(scale=noise_m, size=(P, 3)) * inl[:, None]
+    Xout = lfb[None, :] + rng.random((P, 3)) * ext[None, :]
+    Xo = np.where(inl[:, None], Xo, Xout)
+    xyzn = np.clip((Xo - lfb[None, :]) / ext[None, :], 1e-3, 1.0).astype(np.float32)
+    return dict(rows=rr.astype(np.int32), cols=cc.astype(np.int32), xyzn=xyzn, cls=int(cls),
+                R_gt=R.astype(np.float32), t_gt=t.astype(np.float32), inlier=inl)
+
+
+def dense_from_sparse(sp, H=IMG_H, W=IMG_W):
+    """-> xyz [3,H,W] f32, mask [H,W] u8."""
+    xyz = np.zeros((3, H, W), np.float32)
+    mask = np.zeros((H, W), np.uint8)
+    xyz[:, sp['rows'], sp['cols']] = sp['xyzn'].T
+    mask[sp['rows'], sp['cols']] = 1
+    return xyz, mask
+
+
+def reference_frame_dict(sp, model_points, H=IMG_H, W=IMG_W, K4=LINEMOD_K4):
+    """The ``datas`` / ``pred`` entries the reference's get_pose / cal_dis read for one frame
+    (tools/trainer.py:383-438, :370-381), built from a sparse synthetic frame."""
+    xyz, mask = dense_from_sparse(sp, H, W)
+    choose = (sp['rows'].astype(np.int64) * W + sp['cols']).astype(np.int64)
+    cls = sp['cls']
+    target = model_points @ sp['R_gt'].T + sp['t_gt'][None, :]
+    return dict(xyz=xyz, mask=mask, choose=choose,
+                x_map_choosed=sp['cols'].astype(np.float32), y_map_choosed=sp['rows'].astype(np.float32),
+                extent=EXTENT[cls].copy(), lfborder=LFBORDER[cls].copy(),
+                intrinsic=np.asarray(K4, np.float32), cls_id=cls,
+                model_points=model_points.astype(np.float32), target=target.astype(np.float32),
+                target_r=sp['R_gt'], target_t=sp['t_gt'])
+
+
+def compact_points(sp):
+    """De-normalised correspondences as the SoA [5,P] f32 the kernels use (FP32 fma like K0)."""
+    cls = sp['cls']
+    ext = EXTENT[cls].astype(np.float32)
+    lfb = LFBORDER[cls].astype(np.float32)
+    # fma(xyzn, ext, lfb) evaluated in float64 then rounded == single-rounded fmaf for f32 inputs
+    obj = (sp['xyzn'].astype(np.float64) * ext.astype(np.float64) + lfb.astype(np.float64)).astype(np.float32)
+    return np.stack([obj[:, 0], obj[:, 1], obj[:, 2],
+                     sp['cols'].astype(np.float32), sp['rows'].astype(np.float32)], axis=0)
+
+
+def make_batch_sparse(seed: int, config_id: int, n_frames: int, first_frame: int = 0, **kw):
+    return [make_frame_sparse(seed, config_id, first_frame + f, **kw) for f in range(n_frames)]

@@ -1,0 +1,220 @@
+"""Host-side mirror of the reference's call sites for the pose-recovery + evaluation path.
+
+Same names, argument meaning and return conventions as the reference (file:line under
+/root/reference), each routed to the C ABI (include/poseb200.h):
+
+  batch_intrinsic_transform   lib/utils/utlis.py:12-34
+  get_pose(pred, data)        tools/trainer.py:383-438   (Trainer.get_pose, @staticmethod)
+  cal_dis(metric, r, t, d)    tools/trainer.py:370-381   (Trainer.cal_dis)
+  Metric                      lib/utils/metric.py:13-84
+  knn(x, y)                   train.py:126               (KeOps generic_argkmin handle)
+  PoseLoss                    lib/network/loss.py:18-41
+  choose_ransac_batch         lib/utils/utlis.py:55-74
+  vote_translation            lib/network/krrn.py:153
+
+Differences that are deliberate: every point in ``choose`` is scored instead of a
+random 256 subset; the map is de-normalised in FP32 (the reference promotes to float64); RANSAC
+failure yields identity/zero plus a status instead of uninitialised memory.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import ops, ops_metric
+from .ops import RansacConfig
+
+DEFAULT_RANSAC = RansacConfig()
+
+
+def _dev(t):
+    if isinstance(t, np.ndarray):
+        t = torch.from_numpy(t)
+    return t.cuda(non_blocking=True) if not t.is_cuda else t
+
+
+def batch_intrinsic_transform(K):
+    """[bs,4] (fx,fy,cx,cy) -> [bs,3,3] and back (lib/utils/utlis.py:12-34)."""
+    if K.dim() == 2 and K.size(-1) == 4:
+        out = torch.zeros((K.size(0), 3, 3), dtype=K.dtype, device=K.device)
+        out[:, 0, 0], out[:, 1, 1], out[:, 0, 2], out[:, 1, 2] = K[:, 0], K[:, 1], K[:, 2], K[:, 3]
+        out[:, 2, 2] = 1
+        return out
+    if K.dim() == 3 and K.size(-1) == 3:
+        return torch.stack([K[:, 0, 0], K[:, 1, 1], K[:, 0, 2], K[:, 1, 2]], dim=1)
+    raise Exception('Wrong Shape!')
+
+
+def get_pose(pred, data, cfg: RansacConfig | None = None, return_info=False):
+    """Trainer.get_pose (tools/trainer.py:383-438).  pred['xyz'] [bs,3,h,w]; data['extent'],
+    data['lfborder'] [bs,3]; data['choose'] [bs,1,NP] int64; data['x_map_choosed'],
+    data['y_map_choosed'] [bs,NP,1]; data['intrinsic'] [bs,4].  Returns (R [bs,3,3], t [bs,3]) as
+    CPU float32 tensors like the reference (which asserts bs == 1; any bs works here)."""
+    xyz = _dev(pred['xyz']).float()
+    bs = xyz.size(0)
+    choose = _dev(data['choose']).long().reshape(bs, -1)
+    xm = _dev(data['x_map_choosed']).float().reshape(bs, -1)
+    ym = _dev(data['y_map_choosed']).float().reshape(bs, -1)
+    ext = _dev(data['extent']).float().reshape(bs, 3)
+    lfb = _dev(data['lfborder']).float().reshape(bs, 3)
+    K4 = _dev(data['intrinsic']).float().reshape(bs, 4)
+    pts, count = ops.gather_correspondences(xyz, choose, xm, ym, ext, lfb)
+    out = ops.pnp_ransac_pts(pts, count, K4, cfg or DEFAULT_RANSAC)
+    R, t = out['R'].cpu(), out['t'].cpu()   # the reference returns CPU tensors (host sync here)
+    if return_info:
+        return R, t, {k: v.cpu() for k, v in out.items() if k not in ('R', 't')}
+    return R, t
+
+
+class Metric:
+    """lib/utils/metric.py:13-84."""
+
+    def __init__(self, sys):
+        self.sys = list(sys)
+
+    def cal_adds_cuda(self, pred, target, idx):
+        """metric.py:17-36: returns (add_dis, adds_dis) Python floats; for a class in ``sys`` both
+        are ADD-S = mean_i min_j |pred_j - target_i|, otherwise both are ADD."""
+        assert pred.dim() == target.dim() == 2
+        p = _dev(pred).float().unsqueeze(0)
+        g = _dev(target).float().unsqueeze(0)
+        sym = int(idx) in self.sys
+        want = torch.full((1,), 1 if sym else 0, dtype=torch.uint8, device=p.device)
+        add, adds = ops_metric.add_adds(p, g, want)
+        add_v, adds_v = float(add.item()), float(adds.item())
+        return (adds_v, adds_v) if sym else (add_v, add_v)
+
+    def cal_auc(self, add_dis, max_dis=0.1):
+        """metric.py:38-50 (host side: one call per object per sweep)."""
+        d = np.sort(np.where(np.asarray(add_dis, dtype=np.float64) > max_dis, np.inf, add_dis))
+        n = len(add_dis)
+        acc = np.cumsum(np.ones((1, n)), dtype=np.float32) / n
+        return self.voc_ap(d, acc) * 100.0
+
+    @staticmethod
+    def voc_ap(rec, prec):
+        """metric.py:52-65: area under the monotone envelope of (rec, prec) on [0, 0.1], times 10."""
+        ok = np.isfinite(rec)
+        if not ok.any():
+            return 0
+        rec, prec = rec[ok], prec[ok]
+        mrec = np.concatenate([[0.0], rec, [0.1]])
+        mpre = np.concatenate([[0.0], prec, [prec[-1]]])
+        # running maximum over the prefix the reference's loop covers (indices 1..len(prec)-1)
+        m = prec.shape[0]
+        if m > 1:
+            mpre[:m] = np.maximum.accumulate(mpre[:m])
+        step = np.nonzero(mrec[1:] != mrec[:-1])[0] + 1
+        return np.sum((mrec[step] - mrec[step - 1]) * mpre[step]) * 10
+
+    @staticmethod
+    def angular_distance(q1, q2, eps: float = 1e-7):
+        """metric.py:67-80 for rotation matrices [B,3,3] -> degrees [B,1] (pairwise diagonal)."""
+        R1, R2 = _dev(q1).float().reshape(-1, 3, 3), _dev(q2).float().reshape(-1, 3, 3)
+        B = R1.size(0)
+        z = torch.zeros((B, 3), device=R1.device)
+        model = torch.zeros((1, 1, 3), device=R1.device)
+        cls = torch.zeros((B,), dtype=torch.int32, device=R1.device)
+        _, r_deg, _ = ops_metric.pose_metrics(R1, z, R2, z, model, cls, None)
+        return r_deg.reshape(B, 1)
+
+    @staticmethod
+    def translation_distance(t1, t2):
+        """metric.py:82-84."""
+        a, b = _dev(t1).float().reshape(-1, 3), _dev(t2).float().reshape(-1, 3)
+        B = a.size(0)
+        eye = torch.eye(3, device=a.device).expand(B, 3, 3).contiguous()
+        model = torch.zeros((1, 1, 3), device=a.device)
+        cls = torch.zeros((B,), dtype=torch.int32, device=a.device)
+        _, _, t_m = ops_metric.pose_metrics(eye, a, eye, b, model, cls, None)
+        return t_m
+
+
+def cal_dis(metric: Metric, pred_r, pred_t, datas):
+    """Trainer.cal_dis (tools/trainer.py:370-381) -> (add_dis, r_dis, t_dis) Python floats."""
+    R = _dev(pred_r).float().reshape(1, 3, 3)
+    t = _dev(pred_t).float().reshape(1, 3)
+    Rg = _dev(datas['target_r']).float().reshape(1, 3, 3)
+    tg = _dev(datas['target_t']).float().reshape(1, 3)
+    model = _dev(datas['model_points']).float().reshape(1, -1, 3)
+    target = _dev(datas['target']).float().reshape(1, -1, 3)
+    cls_id = int(torch.as_tensor(datas['cls_id']).reshape(-1)[0].item())
+    is_sym = torch.full((1,), 1 if cls_id in metric.sys else 0, dtype=torch.uint8, device=R.device)
+    cls = torch.zeros((1,), dtype=torch.int32, device=R.device)
+    add, r_deg, t_m = ops_metric.pose_metrics(R, t, Rg, tg, model, cls, is_sym, target)
+    vals = torch.stack([add[0], r_deg[0], t_m[0]]).cpu()    # one host sync instead of three
+    return float(vals[0]), float(vals[1]), float(vals[2])
+
+
+def knn(x, y):
+    """The KeOps handle of train.py:126: x [N,3], y [M,3] contiguous f32 CUDA -> int64 [N,1]."""
+    if x.dim() != 2 or y.dim() != 2 or x.size(-1) != 3 or y.size(-1) != 3:
+        raise ValueError("knn expects x [N,3] and y [M,3]")
+    if x.device != y.device:
+        raise ValueError("knn: x and y must be on the same device")
+    return ops_metric.knn1(x, y).view(-1, 1)
+
+
+class _PoseLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred_r, pred_t, targets, model_points, sym):
+        loss_b, pred, nn_idx = ops_metric.pose_loss_fwd(pred_r.contiguous(), pred_t.reshape(-1, 3).contiguous(),
+                                                        model_points.contiguous(), targets.contiguous(), sym)
+        ctx.save_for_backward(pred, model_points, targets, nn_idx)
+        ctx.t_shape = pred_t.shape
+        return loss_b.mean()
+
+    @staticmethod
+    def backward(ctx, gout):
+        pred, model_points, targets, nn_idx = ctx.saved_tensors
+        gR, gt = ops_metric.pose_loss_bwd(pred, model_points.contiguous(), targets.contiguous(), nn_idx, 1.0)
+        return gR * gout, (gt * gout).reshape(ctx.t_shape), None, None, None
+
+
+class PoseLoss(torch.nn.Module):
+    """lib/network/loss.py:18-41.  ``knn`` is accepted for signature compatibility; the fused
+    kernel performs the same argmin."""
+
+    def __init__(self, sym_list, knn=None, num_point=1000):
+        super().__init__()
+        self.num_point = num_point
+        self.sym_list = list(sym_list)
+        self.knn = knn
+
+    def forward(self, pred_r, pred_t, targets, model_points, idxs):
+        ids = torch.as_tensor(idxs).reshape(-1).tolist()
+        sym = torch.tensor([1 if int(i) in self.sym_list else 0 for i in ids], dtype=torch.uint8,
+                           device=pred_r.device)
+        return _PoseLossFn.apply(pred_r.float(), pred_t.float(), targets.float(), model_points.float(), sym)
+
+
+class _VoteFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, p_emb, t_res):
+        ctx.np_ = p_emb.size(1)
+        return ops_metric.vote_translation(p_emb.contiguous(), t_res.contiguous())
+
+    @staticmethod
+    def backward(ctx, g):
+        gn = g / ctx.np_
+        return gn.unsqueeze(1).expand(-1, ctx.np_, -1), gn.unsqueeze(2).expand(-1, -1, ctx.np_)
+
+
+def vote_translation(p_emb, t_res):
+    """pred_t = (p_emb + t_res.permute(0, 2, 1)).mean(dim=1)  (lib/network/krrn.py:153)."""
+    return _VoteFn.apply(p_emb.float(), t_res.float())
+
+
+def choose_ransac_batch(coor_emb, uv_emb, K_matrix, n=125, cfg: RansacConfig | None = None):
+    """lib/utils/utlis.py:55-74: numpy in, numpy int32 [bs,1,n] out (indices of RANSAC inliers,
+    order-preserving random subset if more than n, wrap-padded if fewer)."""
+    cfg = cfg or DEFAULT_RANSAC
+    obj = torch.as_tensor(np.asarray(coor_emb, np.float32)).cuda()
+    uv = torch.as_tensor(np.asarray(uv_emb, np.float32)).cuda()
+    K = torch.as_tensor(np.asarray(K_matrix, np.float32)).cuda()
+    bs, m, _ = obj.shape
+    pts = torch.cat([obj.permute(0, 2, 1), uv.permute(0, 2, 1)], dim=1).contiguous()   # [bs,5,m]
+    count = torch.full((bs,), m, dtype=torch.int32, device=pts.device)
+    out = ops.pnp_ransac_pts(pts, count, batch_intrinsic_transform(K).contiguous(), cfg, want_bitmap=True)
+    sel = ops.resample_inliers(out['inl_bitmap'], count, m, n, seed=cfg.seed)
+    return sel.cpu().numpy().astype(np.int32).reshape(bs, 1, n)

@@ -1,0 +1,158 @@
+"""Tensor-level wrappers (continued): KNN / ADD(-S), per-frame metrics, accuracy table, pose loss,
+T-vote.  Same rules as ops.py: CUDA tensors only, asynchronous on the current stream."""
+from __future__ import annotations
+
+import torch
+
+from ._lib import call
+from .ops import _chk, _ptr, _stream
+
+TABLE_ROWS = 24
+ROW_ALL_NUM, ROW_OBJ_NUM, ROW_VARIANT0 = 0, 1, 2
+ROW_DIS_MASK, ROW_DIS_NORMAL, ROW_DIS_XYZ, ROW_FAILED = 20, 21, 22, 23
+VARIANTS = ("base", "reg", "final")
+VARIANT_COLS = ("succ_{}_rt", "dis_{}_rt", "succ_{}_r", "dis_{}_r", "succ_{}_t", "dis_{}_t")
+
+
+def knn1(x, y, want_d2=False):
+    """x [B,N,3] or [N,3]; y [B,M,3], [M,3] (shared) -> idx int64 [B,N] (and d2 f32)."""
+    x = _chk(x, torch.float32, "x")
+    y = _chk(y, torch.float32, "y")
+    squeeze = x.dim() == 2
+    if squeeze:
+        x = x.unsqueeze(0)
+    y_shared = 1 if y.dim() == 2 else 0
+    if not y_shared and y.shape[0] != x.shape[0]:
+        raise ValueError("batch mismatch between x and y")
+    if x.shape[-1] != 3 or y.shape[-1] != 3:
+        raise ValueError("points must be [...,3]")
+    B, N, _ = x.shape
+    M = y.shape[-2]
+    idx = torch.empty((B, N), dtype=torch.int64, device=x.device)
+    d2 = torch.empty((B, N), dtype=torch.float32, device=x.device) if want_d2 else None
+    call("pb_knn1", _ptr(x), _ptr(y), B, N, M, y_shared, _ptr(idx), _ptr(d2), _stream())
+    if squeeze:
+        idx = idx[0]
+        d2 = d2[0] if want_d2 else None
+    return (idx, d2) if want_d2 else idx
+
+
+def add_adds(pred, target, want_adds=None):
+    """pred/target [B,N,3] -> add [B], adds [B]; want_adds u8 [B] or None (all)."""
+    pred = _chk(pred, torch.float32, "pred")
+    target = _chk(target, torch.float32, "target")
+    want_adds = _chk(want_adds, torch.uint8, "want_adds", True)
+    if pred.shape != target.shape:
+        raise ValueError("pred and target must have the same shape")
+    B, N, _ = pred.shape
+    add = torch.empty((B,), dtype=torch.float32, device=pred.device)
+    adds = torch.empty((B,), dtype=torch.float32, device=pred.device)
+    call("pb_add_adds", _ptr(pred), _ptr(target), B, N, _ptr(want_adds), _ptr(add), _ptr(adds), _stream())
+    return add, adds
+
+
+def transform_points(model, R, t):
+    """model [B,N,3] or [N,3] (shared); R [B,3,3]; t [B,3] -> [B,N,3]."""
+    model = _chk(model, torch.float32, "model")
+    R = _chk(R, torch.float32, "R")
+    t = _chk(t, torch.float32, "t")
+    B = R.shape[0]
+    shared = 1 if model.dim() == 2 else 0
+    N = model.shape[-2]
+    out = torch.empty((B, N, 3), dtype=torch.float32, device=R.device)
+    call("pb_transform_points", _ptr(model), shared, _ptr(R), _ptr(t), B, N, _ptr(out), _stream())
+    return out
+
+
+def pose_metrics(R, t, R_gt, t_gt, model, cls, is_sym, target=None):
+    """R,R_gt [F,3,3]; t,t_gt [F,3]; model [C,N,3]; cls i32 [F]; is_sym u8 [C]; target [F,N,3]|None
+    -> add [F] (ADD-S for symmetric classes), r_deg [F], t_m [F]."""
+    R = _chk(R, torch.float32, "R"); t = _chk(t, torch.float32, "t")
+    R_gt = _chk(R_gt, torch.float32, "R_gt"); t_gt = _chk(t_gt, torch.float32, "t_gt")
+    model = _chk(model, torch.float32, "model")
+    cls = _chk(cls, torch.int32, "cls")
+    is_sym = _chk(is_sym, torch.uint8, "is_sym", True)
+    target = _chk(target, torch.float32, "target", True)
+    F = R.shape[0]
+    Cn, N, _ = model.shape
+    dev = R.device
+    add = torch.empty((F,), dtype=torch.float32, device=dev)
+    r_deg = torch.empty((F,), dtype=torch.float32, device=dev)
+    t_m = torch.empty((F,), dtype=torch.float32, device=dev)
+    call("pb_pose_metrics", _ptr(R), _ptr(t), _ptr(R_gt), _ptr(t_gt), _ptr(model), _ptr(target), _ptr(cls),
+         _ptr(is_sym), F, N, Cn, _ptr(add), _ptr(r_deg), _ptr(t_m), _stream())
+    return add, r_deg, t_m
+
+
+def new_table(n_cls, device="cuda"):
+    return torch.zeros((TABLE_ROWS, n_cls), dtype=torch.float64, device=device)
+
+
+def accumulate_results(table, add, r_deg, t_m, cls, diameter, status=None, variant=0, add_frac=0.1,
+                       r_thr_deg=5.0, t_thr_m=0.05, count_frames=True):
+    """table [24,C] f64 += success counts / distance sums of this batch (tools/trainer.py:174-221)."""
+    table = _chk(table, torch.float64, "table")
+    diameter = _chk(diameter, torch.float32, "diameter")
+    status = _chk(status, torch.int32, "status", True)
+    F = add.shape[0]
+    Cn = table.shape[1]
+    call("pb_accumulate_results", _ptr(add), _ptr(r_deg), _ptr(t_m), _ptr(cls), _ptr(status), _ptr(diameter),
+         F, Cn, variant, add_frac, r_thr_deg, t_thr_m, 1 if count_frames else 0, _ptr(table), _stream())
+    return table
+
+
+def table_to_result(table, objlist):
+    """[24,C] table -> the reference's nested ``result`` dict (tools/trainer.py:479-509)."""
+    tb = table.detach().cpu().numpy()
+    res = {"all_num": {}, "obj_num": {}}
+    for v in VARIANTS:
+        for col in VARIANT_COLS:
+            res[col.format(v)] = {}
+    for k in ("dis_mask", "dis_normal", "dis_xyz"):
+        res[k] = {}
+    for c, obj in enumerate(objlist):
+        res["all_num"][obj] = float(tb[ROW_ALL_NUM, c])
+        res["obj_num"][obj] = float(tb[ROW_OBJ_NUM, c])
+        for vi, v in enumerate(VARIANTS):
+            for ci, col in enumerate(VARIANT_COLS):
+                res[col.format(v)][obj] = float(tb[ROW_VARIANT0 + 6 * vi + ci, c])
+        res["dis_mask"][obj] = float(tb[ROW_DIS_MASK, c])
+        res["dis_normal"][obj] = float(tb[ROW_DIS_NORMAL, c])
+        res["dis_xyz"][obj] = float(tb[ROW_DIS_XYZ, c])
+    return res
+
+
+def pose_loss_fwd(R, t, model, target, sym):
+    """-> loss_b [B], pred [B,N,3], nn_idx [B,N] (lib/network/loss.py:25-41)."""
+    R = _chk(R, torch.float32, "R"); t = _chk(t, torch.float32, "t")
+    model = _chk(model, torch.float32, "model"); target = _chk(target, torch.float32, "target")
+    sym = _chk(sym, torch.uint8, "sym")
+    B, N, _ = model.shape
+    dev = model.device
+    pred = torch.empty((B, N, 3), dtype=torch.float32, device=dev)
+    nn_idx = torch.empty((B, N), dtype=torch.int64, device=dev)
+    loss_b = torch.empty((B,), dtype=torch.float32, device=dev)
+    call("pb_pose_loss_fwd", _ptr(R), _ptr(t), _ptr(model), _ptr(target), _ptr(sym), B, N, _ptr(pred),
+         _ptr(nn_idx), _ptr(loss_b), _stream())
+    return loss_b, pred, nn_idx
+
+
+def pose_loss_bwd(pred, model, target, nn_idx, gscale):
+    B, N, _ = pred.shape
+    grad_R = torch.empty((B, 3, 3), dtype=torch.float32, device=pred.device)
+    grad_t = torch.empty((B, 3), dtype=torch.float32, device=pred.device)
+    call("pb_pose_loss_bwd", _ptr(pred), _ptr(model), _ptr(target), _ptr(nn_idx), B, N, float(gscale),
+         _ptr(grad_R), _ptr(grad_t), _stream())
+    return grad_R, grad_t
+
+
+def vote_translation(cloud, t_res):
+    """cloud [B,NP,3], t_res [B,3,NP] -> [B,3] (lib/network/krrn.py:153)."""
+    cloud = _chk(cloud, torch.float32, "cloud")
+    t_res = _chk(t_res, torch.float32, "t_res")
+    B, NP, _ = cloud.shape
+    if t_res.shape != (B, 3, NP):
+        raise ValueError("t_res must be [B,3,NP]")
+    t = torch.empty((B, 3), dtype=torch.float32, device=cloud.device)
+    call("pb_vote_translation", _ptr(cloud), _ptr(t_res), B, NP, _ptr(t), _stream())
+    return t

@@ -63,7 +63,7 @@ def random_rotation(rng) -> np.ndarray:
 
 def make_frame_sparse(seed: int, config_id: int, frame: int, cls: int | None = None,
                       p_range=(800, 1200), outlier_frac=0.25, noise_m=1e-3,
-                      K4=LINEMOD_K4, H=IMG_H, W=IMG_W):
+                      K4=LINEMOD_K4, H=IMG_H, W=IMG_W, outlier_min_px=0.0):
     """One frame in sparse form.  Returns dict with
        rows,cols [P] int32 (row-major sorted), xyzn [P,3] f32 (normalised map values, never 0),
        cls, R_gt [3,3] f32, t_gt [3] f32, inlier [P] bool (ground truth of the injected outliers)."""
@@ -104,6 +104,14 @@ def make_frame_sparse(seed: int, config_id: int, frame: int, cls: int | None = N
     inl = rng.random(P) >= outlier_frac
     Xo = Xo + rng.normal(scale=noise_m, size=(P, 3)) * inl[:, None]
     Xout = lfb[None, :] + rng.random((P, 3)) * ext[None, :]
+    if outlier_min_px > 0:                          # keep injected outliers clearly off their pixel
+        for _ in range(64):
+            Xc = Xout @ R.T + t
+            e = np.hypot(fx * Xc[:, 0] / Xc[:, 2] + cx - cc, fy * Xc[:, 1] / Xc[:, 2] + cy - rr)
+            bad = (~inl) & (e < outlier_min_px)
+            if not bad.any():
+                break
+            Xout[bad] = lfb[None, :] + rng.random((int(bad.sum()), 3)) * ext[None, :]
     Xo = np.where(inl[:, None], Xo, Xout)
     xyzn = np.clip((Xo - lfb[None, :]) / ext[None, :], 1e-3, 1.0).astype(np.float32)
     return dict(rows=rr.astype(np.int32), cols=cc.astype(np.int32), xyzn=xyzn, cls=int(cls),

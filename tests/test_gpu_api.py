@@ -1,0 +1,131 @@
+"""GPU parity through the reference-shaped Python API against the cv2-generated golden vectors
+(tests/golden/pnp_cv2.npz, metric.npz).  Reads like the reference's call sites:
+get_pose(pred, data) -> cal_dis(...) -> success tests (tools/trainer.py:166-191)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import pose_estimation_b200 as pb
+from pose_estimation_b200 import synth
+from tests.test_oracle_golden import GOLD, load_frames
+from tests.util import batch_arrays, rot_angle
+
+pytestmark = pytest.mark.gpu
+
+
+def _datas(sp, models):
+    fr = synth.reference_frame_dict(sp, models[sp["cls"]])
+    pred = {"xyz": torch.from_numpy(fr["xyz"])[None]}
+    data = {"extent": torch.from_numpy(fr["extent"])[None], "lfborder": torch.from_numpy(fr["lfborder"])[None],
+            "choose": torch.from_numpy(fr["choose"])[None, None], "intrinsic": torch.from_numpy(fr["intrinsic"])[None],
+            "x_map_choosed": torch.from_numpy(fr["x_map_choosed"])[None, :, None],
+            "y_map_choosed": torch.from_numpy(fr["y_map_choosed"])[None, :, None],
+            "target_r": torch.from_numpy(fr["target_r"])[None], "target_t": torch.from_numpy(fr["target_t"])[None],
+            "target": torch.from_numpy(fr["target"])[None], "model_points": torch.from_numpy(fr["model_points"])[None],
+            "cls_id": torch.LongTensor([fr["cls_id"]])}
+    return pred, data
+
+
+def test_get_pose_cal_dis_vs_cv2_golden():
+    g = np.load(os.path.join(GOLD, "pnp_cv2.npz"))
+    models = synth.class_models(500)
+    metric = pb.Metric(synth.SYM_CLS)
+    for tag in ("clean", "noisy"):
+        for f, sp in enumerate(load_frames(g, tag)):
+            pred, data = _datas(sp, models)
+            R, t = pb.get_pose(pred, data)
+            assert R.shape == (1, 3, 3) and t.shape == (1, 3) and not R.is_cuda and R.dtype == torch.float32
+            if tag == "clean":      # clear consensus: same pose as cv2 to 1e-4 rad / 1e-4 m
+                assert rot_angle(R[0].numpy(), g["clean_R"][f]) <= 1e-4
+                assert np.abs(t[0].numpy() - g["clean_t"][f]).max() <= 1e-4
+            add, r_dis, t_dis = pb.cal_dis(metric, R, t, data)
+            assert isinstance(add, float)
+            succ = [add < 0.1 * synth.DIAMETER[sp["cls"]], r_dis < 5.0, t_dis < 0.05]
+            assert succ == g[f"{tag}_succ"][f].tolist()          # identical pass/fail
+            if tag == "clean":
+                assert abs(add - g["clean_add"][f]) < 2e-5
+
+
+def test_metric_knn_loss_vs_golden(dev):
+    g = np.load(os.path.join(GOLD, "metric.npz"))
+    for cls in (7, 8, 0):
+        model, R, t, Rg, tg = (torch.from_numpy(g[f"c{cls}_{k}"]).to(dev) for k in ("model", "R", "t", "Rg", "tg"))
+        pred = model @ R.T + t
+        tgt = model @ Rg.T + tg
+        vals = g[f"c{cls}_vals"]
+        add, adds = pb.Metric([cls]).cal_adds_cuda(pred, tgt, cls)
+        assert add == adds and abs(adds - vals[1]) <= 1e-5 * vals[1]
+        add_ns, adds_ns = pb.Metric([]).cal_adds_cuda(pred.cpu(), tgt.cpu(), cls)     # CPU tensors accepted like the ref
+        assert add_ns == adds_ns and abs(add_ns - vals[0]) <= 1e-5 * vals[0]
+        r = pb.Metric.angular_distance(R[None], Rg[None])
+        assert r.shape == (1, 1) and abs(r.item() - vals[2]) < 2e-3
+        assert abs(pb.Metric.translation_distance(t[None], tg[None]).item() - vals[3]) < 1e-6
+        idx = pb.knn(pred.contiguous(), tgt.contiguous())
+        assert idx.shape == (pred.shape[0], 1) and idx.dtype == torch.int64
+        ref_idx = g[f"c{cls}_knn"]
+        diff = np.nonzero(idx.cpu().numpy().reshape(-1) != ref_idx)[0]
+        assert len(diff) <= 2                                    # near-ties of differently-rounded FP32 formulas only
+        loss = pb.PoseLoss([7, 8])(R[None], t[None, None], tgt[None], model[None], torch.tensor([[cls]]))
+        assert abs(loss.item() - float(g[f"c{cls}_loss"])) <= 1e-5 * float(g[f"c{cls}_loss"])
+
+
+def test_auc_matches_reference_restatement():
+    from oracle import ref_callsites as rc
+    rng = np.random.default_rng(0)
+    d = list(rng.random(200) * 0.15)
+    assert abs(pb.Metric([]).cal_auc(d) - rc.Metric([]).cal_auc(d)) < 1e-9
+    assert pb.Metric([]).cal_auc([0.5, 0.7]) == 0
+
+
+def test_choose_ransac_batch_and_vote(dev):
+    sps = synth.make_batch_sparse(0x5EED, 2, 3, p_range=(400, 500))
+    m = min(s["rows"].shape[0] for s in sps)
+    coor = np.stack([synth.compact_points(s)[:3, :m].T for s in sps])
+    uv = np.stack([synth.compact_points(s)[3:, :m].T for s in sps])
+    K = np.tile(np.array([[572.4114, 0, 325.2611], [0, 573.57043, 242.04899], [0, 0, 1]], np.float32), (3, 1, 1))
+    out = pb.choose_ransac_batch(coor, uv, K, n=125)
+    assert out.shape == (3, 1, 125) and out.dtype == np.int32
+    for b in range(3):
+        sel = out[b, 0]
+        u = np.unique(sel)
+        assert sel.min() >= 0 and sel.max() < m
+        if len(u) == 125:
+            assert np.all(np.diff(sel) > 0)                  # order-preserving random subset of the inliers
+        else:
+            assert np.array_equal(sel, np.resize(u, 125))    # fewer inliers than n: np.pad(..., 'wrap')
+        assert sps[b]["inlier"][sel].mean() > 0.95
+    out_pad = pb.choose_ransac_batch(coor, uv, K, n=m)        # fewer inliers than n -> wrap padding
+    assert out_pad.shape == (3, 1, m)
+    p = torch.randn(2, 500, 3, device=dev, requires_grad=True)
+    r = torch.randn(2, 3, 500, device=dev, requires_grad=True)
+    v = pb.vote_translation(p, r)
+    ref = (p + r.permute(0, 2, 1)).mean(dim=1)
+    assert torch.allclose(v, ref, atol=1e-6)
+    v.sum().backward()
+    assert torch.allclose(p.grad, torch.full_like(p, 1 / 500)) and torch.allclose(r.grad, torch.full_like(r, 1 / 500))
+
+
+def test_eval_sweep_table(dev):
+    F = 26
+    sps = synth.make_batch_sparse(0x5EED, 2, F)
+    b = batch_arrays(sps)
+    models = synth.class_models(500)
+    sw = pb.EvalSweep(torch.from_numpy(models), torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM),
+                      F, synth.IMG_H, synth.IMG_W, 1280, device=dev)
+    t = lambda a: torch.from_numpy(a).to(dev)
+    add, r_deg, t_m = sw.step(t(b["xyz"]), t(b["mask"]), t(b["extent"]), t(b["lfborder"]), t(b["K4"]), t(b["cls"]),
+                              t(b["R_gt"]), t(b["t_gt"]))
+    table = sw.finish()
+    s = pb.summarize(table, synth.OBJLIST)
+    assert s["frames"] == F and s["failed"] == 0
+    assert s["succ_base_rt"] >= 0.9 and s["objects"][1]["num"] == 2
+    assert (pb.batch_intrinsic_transform(pb.batch_intrinsic_transform(t(b["K4"]))) == t(b["K4"])).all()
+
+
+def test_cpu_tensors_have_no_fallback():
+    from pose_estimation_b200 import ops_metric
+    from pose_estimation_b200._lib import PoseB200Error
+    with pytest.raises(PoseB200Error):
+        ops_metric.knn1(torch.zeros(4, 3), torch.zeros(4, 3))

@@ -1,0 +1,140 @@
+"""GPU parity: K0 compaction and K1-K4 PnP-RANSAC against the plain-C oracle (bit-exact for every
+integer/index result; R,t within 1e-4 rad / 1e-4 m as BASELINE.json's north_star states)."""
+import numpy as np
+import pytest
+import torch
+
+from pose_estimation_b200 import ops, synth
+from tests.util import batch_arrays, pack_pts, rot_angle
+
+pytestmark = pytest.mark.gpu
+R_TOL_RAD, T_TOL_M = 1e-4, 1e-4
+
+
+def _t(a, dev):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+
+@pytest.mark.parametrize("F,use_mask", [(3, True), (3, False), (40, True)])
+def test_compact_matches_oracle(cref, dev, F, use_mask):
+    sps = synth.make_batch_sparse(0x5EED, 11, F)
+    b = batch_arrays(sps)
+    cap = 1280
+    pts, count, total = ops.compact_map(_t(b["xyz"], dev), _t(b["mask"], dev) if use_mask else None,
+                                        _t(b["extent"], dev), _t(b["lfborder"], dev), cap, want_total=True)
+    pts, count, total = pts.cpu().numpy(), count.cpu().numpy(), total.cpu().numpy()
+    for f in range(F):
+        ref, tot = cref.compact_map(b["xyz"][f], b["mask"][f] if use_mask else None, b["extent"][f],
+                                    b["lfborder"][f], cap=cap)
+        assert count[f] == ref.shape[1] and total[f] == tot
+        assert np.array_equal(pts[f, :, :count[f]], ref)
+
+
+def test_compact_truncation_roi_and_odd_shape(cref, dev):
+    rng = np.random.default_rng(3)
+    # odd H*W (scalar path), dense mask, small cap, ROI offsets
+    F, H, W, cap = 5, 37, 53, 200
+    xyz = rng.random((F, 3, H, W)).astype(np.float32)
+    mask = (rng.random((F, H, W)) < 0.4).astype(np.uint8)
+    mask[1] = 0                      # empty frame
+    mask[2] = 1                      # full frame -> truncated at cap
+    ext = rng.random((F, 3)).astype(np.float32) + 0.1
+    lfb = -rng.random((F, 3)).astype(np.float32)
+    roi = rng.integers(0, 100, (F, 2)).astype(np.int32)
+    for m in (mask, None):
+        pts, count, total = ops.compact_map(_t(xyz, dev), None if m is None else _t(m, dev), _t(ext, dev),
+                                            _t(lfb, dev), cap, roi=_t(roi, dev), want_total=True)
+        pts, count, total = pts.cpu().numpy(), count.cpu().numpy(), total.cpu().numpy()
+        for f in range(F):
+            ref, tot = cref.compact_map(xyz[f], None if m is None else m[f], ext[f], lfb[f],
+                                        rmin=int(roi[f, 0]), cmin=int(roi[f, 1]), cap=cap)
+            assert count[f] == ref.shape[1] and total[f] == tot
+            assert np.array_equal(pts[f, :, :count[f]], ref)
+    # vector path with H*W % 4 == 0 and several row bands per frame (few frames)
+    F, H, W, cap = 2, 480, 640, 5000
+    xyz = np.zeros((F, 3, H, W), np.float32)
+    mask = (rng.random((F, H, W)) < 0.02).astype(np.uint8)
+    xyz[:, :, :, :] = rng.random((F, 3, H, W)).astype(np.float32) * mask[:, None]
+    ext = np.ones((F, 3), np.float32); lfb = np.zeros((F, 3), np.float32)
+    pts, count, total = ops.compact_map(_t(xyz, dev), _t(mask, dev), _t(ext, dev), _t(lfb, dev), cap, want_total=True)
+    for f in range(F):
+        ref, tot = cref.compact_map(xyz[f], mask[f], ext[f], lfb[f], cap=cap)
+        assert int(count[f]) == ref.shape[1] and int(total[f]) == tot
+        assert np.array_equal(pts[f, :, :ref.shape[1]].cpu().numpy(), ref)
+
+
+def _check_ransac(cref, dev, sps, cfg, cap, frame0=0, sample_idx=None):
+    pts_list = [synth.compact_points(s) for s in sps]
+    pts, cnt = pack_pts(pts_list, cap)
+    F = len(sps)
+    K4 = np.tile(synth.LINEMOD_K4, (F, 1))
+    out = ops.pnp_ransac_pts(_t(pts, dev), _t(cnt, dev), _t(K4, dev), cfg, frame0=frame0,
+                             sample_idx=None if sample_idx is None else _t(sample_idx, dev),
+                             want_counts=True, want_bitmap=True, want_minimal=True)
+    out = {k: v.cpu().numpy() for k, v in out.items()}
+    for f in range(F):
+        o = cref.ransac_frame(pts[f, :, :cnt[f]], K4[f], frame=frame0 + f,
+                              sample_idx=None if sample_idx is None else sample_idx[f],
+                              n_hyp=cfg.n_hyp, thresh_px=cfg.thresh_px, gn_iters=cfg.gn_iters,
+                              lo_rounds=cfg.lo_rounds, min_inliers=cfg.min_inliers, seed=cfg.seed)
+        assert out["status"][f] == o["status"], f
+        assert np.array_equal(out["hyp_counts"][f], o["hyp_counts"]), f      # bit-exact inlier counts
+        assert out["best_hyp"][f] == o["best_hyp"] and out["n_inl"][f] == o["n_inl"], f
+        words = (cnt[f] + 31) // 32
+        assert np.array_equal(out["inl_bitmap"][f, :words].view(np.uint32), o["bitmap"][:words]), f
+        assert np.array_equal(out["R0"][f], o["R0"]) and np.array_equal(out["t0"][f], o["t0"]), f
+        assert rot_angle(out["R"][f], o["R"]) <= R_TOL_RAD, f
+        assert np.abs(out["t"][f] - o["t"]).max() <= T_TOL_M, f
+        assert out["n_inl_refined"][f] == o["n_inl_refined"], f
+    return out
+
+
+@pytest.mark.parametrize("n_hyp,F,lo", [(256, 6, 0), (256, 6, 2), (64, 3, 0), (100, 2, 1), (1024, 2, 0),
+                                        (512, 300, 0)])
+def test_ransac_bit_exact_vs_oracle(cref, dev, n_hyp, F, lo):
+    nf = min(F, 12)
+    sps = synth.make_batch_sparse(0x5EED, 2, nf)
+    sps = (sps * ((F + nf - 1) // nf))[:F]
+    cfg = ops.RansacConfig(n_hyp=n_hyp, lo_rounds=lo)
+    _check_ransac(cref, dev, sps[:F] if F <= 12 else sps, cfg, cap=1280, frame0=7)
+
+
+def test_ransac_forced_minimal_sets_and_large_P(cref, dev):
+    sps = synth.make_batch_sparse(0x5EED, 4, 2, p_range=(5000, 6000), outlier_frac=0.3)
+    cap = 6144
+    rng = np.random.default_rng(5)
+    H = 128
+    sidx = np.stack([rng.integers(0, s["rows"].shape[0], (H, 4)) for s in sps]).astype(np.int32)
+    sidx[0, 3] = [-1, 2, 3, 4]                   # invalid index -> hypothesis dropped
+    sidx[1, 5] = [9, 9, 10, 11]                  # duplicate point -> degenerate
+    _check_ransac(cref, dev, sps, ops.RansacConfig(n_hyp=H, lo_rounds=1), cap=cap, sample_idx=sidx)
+
+
+def test_ransac_failure_status(dev):
+    F, cap = 3, 64
+    pts = np.zeros((F, 5, cap), np.float32)
+    cnt = np.array([0, 3, 40], np.int32)
+    rng = np.random.default_rng(0)
+    pts[2, :, :40] = rng.random((5, 40))         # garbage correspondences: no consensus
+    K4 = np.tile(synth.LINEMOD_K4, (F, 1))
+    out = ops.pnp_ransac_pts(_t(pts, dev), _t(cnt, dev), _t(K4, dev), ops.RansacConfig(n_hyp=32, min_inliers=30))
+    st = out["status"].cpu().numpy()
+    assert st[0] == 1 and st[1] == 1 and st[2] == 2
+    assert np.array_equal(out["R"][0].cpu().numpy(), np.eye(3, dtype=np.float32))
+    assert np.all(out["t"].cpu().numpy()[:2] == 0)
+
+
+def test_map_ransac_equals_two_step(dev):
+    sps = synth.make_batch_sparse(0x5EED, 2, 5)
+    b = batch_arrays(sps)
+    cap = 1280
+    cfg = ops.RansacConfig()
+    mr = ops.MapRansac(5, synth.IMG_H, synth.IMG_W, cap, cfg, device=dev)
+    mr(_t(b["xyz"], dev), _t(b["mask"], dev), _t(b["extent"], dev), _t(b["lfborder"], dev), _t(b["K4"], dev))
+    pts, count = ops.compact_map(_t(b["xyz"], dev), _t(b["mask"], dev), _t(b["extent"], dev), _t(b["lfborder"], dev), cap)
+    out = ops.pnp_ransac_pts(pts, count, _t(b["K4"], dev), cfg)
+    assert torch.equal(mr.R, out["R"]) and torch.equal(mr.t, out["t"]) and torch.equal(mr.n_inl, out["n_inl"])
+    # pose quality against ground truth (1 mm noise, 25 % outliers)
+    for f in range(5):
+        assert rot_angle(mr.R[f].cpu().numpy(), b["R_gt"][f]) < np.radians(5.0)
+        assert np.linalg.norm(mr.t[f].cpu().numpy() - b["t_gt"][f]) < 0.05

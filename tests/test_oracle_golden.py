@@ -1,0 +1,145 @@
+"""CPU tests: the oracles against the committed golden vectors (tests/golden/gen_golden.py made them
+with the real cv2 in-container) and against each other."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ref_callsites as rc
+from pose_estimation_b200 import synth
+from tests.util import rot_angle
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def load_frames(g, tag):
+    out = []
+    for f in range(int(g[f"{tag}_n"])):
+        sp = {k: g[f"{tag}_f{f}_{k}"] for k in ("rows", "cols", "xyzn", "R_gt", "t_gt")}
+        sp["cls"] = int(g[f"{tag}_f{f}_cls"])
+        out.append(sp)
+    return out
+
+
+def test_philox_known_answers(cref):
+    # Random123 kat_vectors for philox4x32-10
+    assert list(cref.philox([0, 0, 0, 0], [0, 0])) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert list(cref.philox([0xFFFFFFFF] * 4, [0xFFFFFFFF] * 2)) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert list(cref.philox([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0])) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+    g = np.load(os.path.join(GOLD, "ransac_c.npz"))
+    assert np.array_equal(g["philox"][1], cref.philox([0, 0, 0, 0], [0, 0]))
+
+
+def test_sampler_distinct_and_uniform(cref):
+    seen = np.zeros(50, int)
+    for h in range(2000):
+        ok, idx = cref.sample4(0x5EED, 3, h, 50)
+        assert ok and len(set(idx.tolist())) == 4 and idx.min() >= 0 and idx.max() < 50
+        seen[idx] += 1
+    assert seen.min() > 100 and seen.max() < 230          # 160 expected per bin
+    assert not cref.sample4(1, 0, 0, 3)[0]
+    ok, idx = cref.sample4(1, 0, 0, 4)
+    assert ok and sorted(idx.tolist()) == [0, 1, 2, 3]
+
+
+def test_p3p_recovers_exact_pose(cref):
+    rng = np.random.default_rng(1)
+    errs = []
+    for _ in range(300):
+        R = synth.random_rotation(rng)
+        t = np.array([rng.uniform(-.15, .15), rng.uniform(-.1, .1), rng.uniform(.6, 1.2)])
+        X = (rng.random((3, 3)) - .5) * 0.1
+        Xc = X @ R.T + t
+        Rs, ts = cref.p3p(X, Xc / np.linalg.norm(Xc, axis=1, keepdims=True))
+        assert len(Rs) <= 4
+        if len(Rs):
+            errs.append(min(np.abs(Rs[k] - R).max() + np.abs(ts[k] - t).max() for k in range(len(Rs))))
+    errs = np.array(errs)
+    assert len(errs) >= 295 and np.median(errs) < 5e-4 and np.quantile(errs, 0.9) < 5e-3
+
+
+def test_c_oracle_matches_its_golden(cref):
+    g = np.load(os.path.join(GOLD, "ransac_c.npz"))
+    sps = synth.make_batch_sparse(0x5EED, 2, 6)
+    for lo in (0, 2):
+        for f, sp in enumerate(sps):
+            r = cref.ransac_frame(synth.compact_points(sp), synth.LINEMOD_K4, frame=f, lo_rounds=lo)
+            ints = g[f"lo{lo}_f{f}_ints"]
+            assert [r["status"], r["n_inl"], r["best_hyp"], r["n_inl_refined"]] == ints.tolist()
+            assert np.array_equal(r["hyp_counts"], g[f"lo{lo}_f{f}_hyp_counts"])
+            assert np.array_equal(r["bitmap"], g[f"lo{lo}_f{f}_bitmap"])
+            assert np.array_equal(r["R"], g[f"lo{lo}_f{f}_R"]) and np.array_equal(r["t"], g[f"lo{lo}_f{f}_t"])
+
+
+def test_c_oracle_vs_cv2_golden(cref):
+    """Algorithm oracle vs the reference's cv2 path: clear-consensus frames agree to 1e-4 rad /
+    1e-4 m; noisy frames give identical ADD(-S)/r/t pass-fail (tools/trainer.py:186-191)."""
+    g = np.load(os.path.join(GOLD, "pnp_cv2.npz"))
+    models = synth.class_models(500)
+    metric = rc.Metric(synth.SYM_CLS)
+    for tag in ("clean", "noisy"):
+        assert g[f"{tag}_ok"].all()
+        for f, sp in enumerate(load_frames(g, tag)):
+            o = cref.ransac_frame(synth.compact_points(sp), synth.LINEMOD_K4, frame=f)
+            assert o["status"] == 0
+            if tag == "clean":
+                assert rot_angle(o["R"], g["clean_R"][f]) <= 1e-4
+                assert np.abs(o["t"] - g["clean_t"][f]).max() <= 1e-4
+            fr = synth.reference_frame_dict(sp, models[sp["cls"]])
+            a, rd, td = rc.cal_dis(metric, o["R"], o["t"], fr["target_r"], fr["target_t"], fr["target"],
+                                   fr["model_points"], fr["cls_id"])
+            succ = [a < 0.1 * synth.DIAMETER[sp["cls"]], rd < 5.0, td < 0.05]
+            assert succ == g[f"{tag}_succ"][f].tolist()
+
+
+@pytest.mark.skipif(rc.cv2 is None, reason="cv2 missing")
+def test_ref_callsites_reproduce_golden():
+    """The golden file is what ref_callsites (real cv2) produces today: guards against drift."""
+    g = np.load(os.path.join(GOLD, "pnp_cv2.npz"))
+    models = synth.class_models(500)
+    metric = rc.Metric(synth.SYM_CLS)
+    for f, sp in enumerate(load_frames(g, "clean")[:4]):
+        fr = synth.reference_frame_dict(sp, models[sp["cls"]])
+        e = rc.eval_frame(metric, fr, synth.DIAMETER, np.random.default_rng([7, 101, f]))
+        assert np.allclose(e["R"], g["clean_R"][f], atol=1e-6) and np.allclose(e["t"], g["clean_t"][f], atol=1e-6)
+        assert abs(e["add"] - g["clean_add"][f]) < 1e-6
+
+
+def test_metric_oracles_agree(cref):
+    """C oracle (what the GPU is compared with) vs ref_callsites' restatement of lib/utils/metric.py."""
+    g = np.load(os.path.join(GOLD, "metric.npz"))
+    for cls in (7, 8, 0):
+        model, R, t, Rg, tg = (g[f"c{cls}_{k}"] for k in ("model", "R", "t", "Rg", "tg"))
+        pred, tgt = cref.transform(model, R, t), cref.transform(model, Rg, tg)
+        add, adds = cref.add_adds(pred, tgt)
+        vals = g[f"c{cls}_vals"]
+        assert abs(add - vals[0]) <= 2e-6 * vals[0] + 1e-9 and abs(adds - vals[1]) <= 2e-6 * vals[1] + 1e-9
+        assert abs(cref.angular_deg(R, Rg) - vals[2]) < 2e-3
+        idx, _ = cref.knn1(pred, tgt)
+        ref_idx = g[f"c{cls}_knn"]
+        # FP32 formulas differ in fma contraction: indices may differ only at numerical near-ties
+        diff = np.nonzero(idx != ref_idx)[0]
+        assert len(diff) <= 2
+        for i in diff:
+            da = np.sum((pred[i].astype(np.float64) - tgt[idx[i]]) ** 2)
+            db = np.sum((pred[i].astype(np.float64) - tgt[ref_idx[i]]) ** 2)
+            assert abs(da - db) <= 1e-6 * max(da, db)
+
+
+def test_compaction_oracle_matches_reference_gather(cref):
+    """ref_compact_map == the reference's de-normalise + gather at `choose` (trainer.py:415-421)."""
+    sp = synth.make_frame_sparse(0x5EED, 1, 0)
+    xyz, mask = synth.dense_from_sparse(sp)
+    cls = sp["cls"]
+    pts, total = cref.compact_map(xyz, mask, synth.EXTENT[cls], synth.LFBORDER[cls])
+    assert total == sp["rows"].shape[0] == pts.shape[1]
+    coord = (xyz * synth.EXTENT[cls].reshape(3, 1, 1) + synth.LFBORDER[cls].reshape(3, 1, 1))   # float64
+    choose = sp["rows"].astype(np.int64) * synth.IMG_W + sp["cols"]
+    ref = coord.reshape(3, -1)[:, choose]
+    assert np.abs(pts[:3] - ref).max() < 2e-8            # FP32 fma vs the reference's float64
+    assert np.array_equal(pts[3], sp["cols"]) and np.array_equal(pts[4], sp["rows"])
+    pts2, _ = cref.compact_map(xyz, None, synth.EXTENT[cls], synth.LFBORDER[cls])
+    assert np.array_equal(pts, pts2)                     # xyz != 0 convention gives the same set
+    e, _ = cref.compact_map(np.zeros((3, 8, 8), np.float32), None, np.ones(3), np.zeros(3))
+    assert e.shape == (5, 0)

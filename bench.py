@@ -1,0 +1,376 @@
+#!/usr/bin/env python
+"""bench.py -- frames/s of the PnP-RANSAC + ADD(-S) evaluation pass (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One "step" = one evaluation pass over a batch of 1024 synthetic LineMOD-shaped frames per GPU
+(BASELINE.json configs[1]: 13 objects, 480x640 coordinate map + mask, ~1k masked px, 256 RANSAC
+hypotheses, ADD with 500-pt models, ADD-S for eggbox/glue), ending with the all-reduce of the
+[24,13] accuracy table when N > 1 (weak scaling: every rank evaluates its own 1024-frame shard).
+
+  value     whole-job frames/s with the maps already resident in HBM (CUDA events, max over ranks)
+  e2e       the same pass through HostEvalSweep.run with PINNED HOST inputs: every step copies its
+            maps host->device inside the timed region and reads the accuracy table back
+  roofline  the dominant kernel (K0 map stream + compaction, HBM-bound) timed live with CUDA events
+  cpu_baseline / --impl reference
+            the reference's own per-frame CPU path (tools/trainer.py:166-191: 256-point
+            cv2.solvePnPRansac + ADD(-S)) restated in oracle/ref_callsites.py around the real cv2,
+            one worker process per host core, on a bounded sample of the same frames.
+
+Nothing here reads /root/reference at run time.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import multiprocessing as mp
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+SEED = 0x5EED
+CONFIG_ID = 2                       # C2 of SURVEY.md section 8(d)
+FRAMES_PER_GPU = 1024
+N_HYP = 256
+N_MODEL = 500
+CAP = 1280                          # >= max masked px per frame (P ~ U{800..1200})
+METRIC = "frames/sec PnP-RANSAC+ADD(-S) eval"
+UNIT = "frames/s"
+MAP_BYTES_PER_FRAME = 480 * 640 * (12 + 1)      # xyz 12 B + mask 1 B per pixel
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the reference's per-frame CPU path on the host cores
+def _ref_worker(rank, frames, n_steps, barrier, out_q):
+    """Worker process: builds its frames (untimed), then evaluates them once per step."""
+    try:
+        import numpy as np
+        import cv2
+        cv2.setNumThreads(1)                        # one process per core; no nested OpenCV threads
+        from oracle import ref_callsites as rc
+        from pose_estimation_b200 import synth
+        models = synth.class_models(N_MODEL)
+        metric = rc.Metric(synth.SYM_CLS)
+        fr = []
+        for f in frames:
+            sp = synth.make_frame_sparse(SEED, CONFIG_ID, f)
+            fr.append(synth.reference_frame_dict(sp, models[sp["cls"]]))
+        rng = np.random.default_rng([SEED, rank])
+        for _ in range(n_steps):
+            barrier.wait()
+            t0 = time.time()
+            n_ok = 0
+            for d in fr:
+                r = rc.eval_frame(metric, d, synth.DIAMETER, rng)
+                n_ok += int(r["succ_rt"])
+            out_q.put((rank, t0, time.time(), n_ok))
+    except Exception as e:                          # pragma: no cover
+        out_q.put((rank, "error", repr(e), 0))
+        raise
+
+
+def run_reference_cpu(n_frames, n_steps, n_workers=None):
+    """Times the reference path on ``n_frames`` frames of the workload, ``n_steps`` times.
+    Returns (list of seconds per step, workers, frames)."""
+    n_workers = n_workers or max(1, min(os.cpu_count() or 1, n_frames))
+    ctx = mp.get_context("spawn")
+    barrier = ctx.Barrier(n_workers + 1)
+    q = ctx.Queue()
+    shards = [list(range(w, n_frames, n_workers)) for w in range(n_workers)]
+    procs = [ctx.Process(target=_ref_worker, args=(w, shards[w], n_steps, barrier, q), daemon=True)
+             for w in range(n_workers)]
+    for p in procs:
+        p.start()
+    times = []
+    for _ in range(n_steps):
+        barrier.wait()
+        res = [q.get() for _ in range(n_workers)]
+        for r in res:
+            if r[1] == "error":
+                raise RuntimeError(f"reference worker failed: {r[2]}")
+        times.append(max(r[2] for r in res) - min(r[1] for r in res))
+    for p in procs:
+        p.join(timeout=30)
+    return times, n_workers, n_frames
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    n_frames = max(64, 4 * cores)                   # bounded sample: ~4 frames per core per step
+    n_frames = min(n_frames, FRAMES_PER_GPU)
+    times, workers, n_frames = run_reference_cpu(n_frames, args.warmup + args.steps)
+    timed = times[args.warmup:]
+    total = sum(timed)
+    fps = n_frames * len(timed) / total
+    import cv2
+    line = {
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(timed),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "gpu_launches": 0,
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": workers, "kind": "port",
+                         "sample": f"{n_frames} frames of the workload per step, {len(timed)} steps; "
+                                   f"oracle/ref_callsites.eval_frame = real cv2 {cv2.__version__} solvePnPRansac(EPNP) "
+                                   "on 256 random masked px + numpy ADD/ADD-S; one process per host core"},
+        "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n_gpus):
+    return {"workload": "C2: 13-object LineMOD-shaped eval pass, 1024 synthetic frames per GPU, 480x640 "
+                        "coordinate map + mask, P~U{800..1200} masked px, 256 RANSAC hypotheses, 500-pt models "
+                        "(ADD; ADD-S for eggbox/glue)",
+            "frames_per_gpu": FRAMES_PER_GPU, "n_hyp": N_HYP, "model_points": N_MODEL,
+            "map": [480, 640], "parallelism": f"frames sharded over {n_gpus} rank(s); one all-reduce of the [24,13] table",
+            "l2_policy": "inputs (4.09 GB per step per GPU) exceed the 126 MB L2; no flush needed"}
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            p = [x.strip() for x in r.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1])); smax.append(float(p[2])); pw.append(float(p[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def build_inputs(torch, dev, first_frame, n_frames):
+    """Synthetic frames [first_frame, first_frame+n) -> device tensors (generation is untimed)."""
+    import numpy as np
+    from concurrent.futures import ThreadPoolExecutor
+    from pose_estimation_b200 import synth
+    H, W = synth.IMG_H, synth.IMG_W
+    with ThreadPoolExecutor(max_workers=min(16, os.cpu_count() or 1)) as ex:
+        sps = list(ex.map(lambda f: synth.make_frame_sparse(SEED, CONFIG_ID, f), range(first_frame, first_frame + n_frames)))
+    xyz = torch.zeros((n_frames, 3, H, W), dtype=torch.float32, device=dev)
+    mask = torch.zeros((n_frames, H, W), dtype=torch.uint8, device=dev)
+    fidx = np.concatenate([np.full(s["rows"].shape[0], i, np.int64) for i, s in enumerate(sps)])
+    rows = np.concatenate([s["rows"] for s in sps]).astype(np.int64)
+    cols = np.concatenate([s["cols"] for s in sps]).astype(np.int64)
+    vals = np.concatenate([s["xyzn"] for s in sps]).astype(np.float32)
+    fi, ri, ci = (torch.from_numpy(a).to(dev) for a in (fidx, rows, cols))
+    v = torch.from_numpy(vals).to(dev)
+    for c in range(3):
+        xyz[fi, c, ri, ci] = v[:, c]
+    mask[fi, ri, ci] = 1
+    cls = np.array([s["cls"] for s in sps], np.int32)
+    out = dict(xyz=xyz, mask=mask, cls=torch.from_numpy(cls).to(dev),
+               extent=torch.from_numpy(synth.EXTENT[cls].astype(np.float32)).to(dev),
+               lfborder=torch.from_numpy(synth.LFBORDER[cls].astype(np.float32)).to(dev),
+               K4=torch.from_numpy(np.tile(synth.LINEMOD_K4, (n_frames, 1))).to(dev),
+               R_gt=torch.from_numpy(np.stack([s["R_gt"] for s in sps])).to(dev),
+               t_gt=torch.from_numpy(np.stack([s["t_gt"] for s in sps])).to(dev),
+               n_px=int(rows.shape[0]))
+    return out
+
+
+def ours_arm(args):
+    import torch
+    import torch.distributed as dist
+    import pose_estimation_b200 as pb
+    from pose_estimation_b200 import _lib, ops, synth, sweep
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (pose_estimation_b200 has no CPU path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    _lib.load()                                     # fail loudly if libposeb200.so is missing
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    F = FRAMES_PER_GPU
+    H, W = synth.IMG_H, synth.IMG_W
+    inp = build_inputs(torch, dev, rank * F, F)
+    models = torch.from_numpy(synth.class_models(N_MODEL))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    cfg = ops.RansacConfig(n_hyp=N_HYP, seed=SEED)
+    sw = pb.EvalSweep(models, diam, sym, F, H, W, CAP, cfg, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def one_step(events=None):
+        sw.table.zero_()
+        sw.step(inp["xyz"], inp["mask"], inp["extent"], inp["lfborder"], inp["K4"], inp["cls"], inp["R_gt"],
+                inp["t_gt"], frame0=rank * F, events=events)
+        sw.finish()
+
+    # ---- device-resident throughput ------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        one_step()
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    evs = []
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        one_step(evs)
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+    tmax = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms_total = float(tmax.item())
+    table = sw.table.clone()
+    value = world * F * args.steps / (ms_total * 1e-3)
+    stage_ms = [statistics.fmean(ev[i].elapsed_time(ev[i + 1]) for ev in evs) for i in range(4)]
+    k0_ms = stage_ms[0]
+    algo_bytes = F * MAP_BYTES_PER_FRAME + inp["n_px"] * 20
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    else:
+        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+    achieved = algo_bytes / (k0_ms * 1e-3) / 1e9
+
+    # ---- end to end from pinned host memory --------------------------------------------------------
+    chunk = 128
+    hs = sweep.HostEvalSweep(models, diam, sym, H, W, CAP, chunk=chunk, cfg=cfg, device=dev)
+    xyz_h = torch.empty((F, 3, H, W), dtype=torch.float32).pin_memory()
+    mask_h = torch.empty((F, H, W), dtype=torch.uint8).pin_memory()
+    xyz_h.copy_(inp["xyz"]); mask_h.copy_(inp["mask"])
+    small_h = sweep.pack_small(inp["extent"].cpu(), inp["lfborder"].cpu(), inp["K4"].cpu(), inp["R_gt"].cpu(),
+                               inp["t_gt"].cpu(), chunk).pin_memory()
+    cls_h = inp["cls"].cpu().pin_memory()
+    torch.cuda.synchronize(dev)
+
+    def e2e_step():
+        hs.table.zero_()
+        return hs.run(xyz_h, mask_h, small_h, cls_h, frame0=rank * F)
+
+    for _ in range(max(args.warmup, 3)):
+        e2e_step()
+    barrier()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record()
+    for _ in range(args.steps):
+        tb_host = e2e_step()
+    g1.record()
+    barrier()
+    e2e_ms = torch.tensor([g0.elapsed_time(g1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_value = world * F * args.steps / (float(e2e_ms.item()) * 1e-3)
+    same = bool(torch.equal(tb_host, table.cpu()))
+
+    if rank == 0:
+        summ = pb.summarize(table, synth.OBJLIST)
+        cpu_base = None
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            n_frames = min(FRAMES_PER_GPU, max(64, 8 * cores))
+            times, workers, n_frames = run_reference_cpu(n_frames, 3)
+            t = min(times[1:])
+            import cv2
+            cpu_base = {"value": n_frames / t, "unit": UNIT, "cores": workers, "kind": "port",
+                        "sample": f"{n_frames} frames of the workload (best of 2 timed passes after 1 warm-up); "
+                                  f"oracle/ref_callsites.eval_frame around real cv2 {cv2.__version__} "
+                                  "solvePnPRansac(EPNP, 256 px) + numpy ADD/ADD-S; one process per host core"}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(world),
+            "hyp_pts_per_s": world * N_HYP * inp["n_px"] * args.steps / (ms_total * 1e-3),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": hs.h2d_bytes,
+                    "d2h_bytes_per_step": tb_host.numel() * tb_host.element_size(),
+                    "api": "HostEvalSweep.run (pinned host maps -> chunked H2D overlapped with K0..K6 -> table D2H)",
+                    "table_equals_device_path": same},
+            "gpu_launches": args.steps * sw.launches_per_step,
+            "kernels_per_step": ["compact_kernel", "ransac_score_kernel", "ransac_finalize_kernel",
+                                 "pose_metrics_kernel", "accumulate_kernel"],
+            "stage_ms": dict(zip(sw.STAGES, stage_ms)),
+            "roofline": {"kernel": "compact_kernel (K0: map stream + mask compaction + de-normalise)",
+                         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": algo_bytes, "launch_ms": k0_ms},
+            "cpu_baseline": cpu_base,
+            "clocks": clocks,
+            "accuracy": {"succ_add": summ["succ_base_rt"], "succ_r5deg": summ["succ_base_r"],
+                         "succ_t5cm": summ["succ_base_t"], "failed": summ["failed"], "frames": summ["frames"]},
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        ours_arm(args)
+
+
+if __name__ == "__main__":
+    main()

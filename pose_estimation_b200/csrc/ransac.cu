@@ -265,7 +265,11 @@ __global__ void resample_inliers_kernel(const uint32_t* bitmap, const int32_t* c
     const int P = min(count[f], cap);
     int32_t* o = out + (size_t)f * n;
     int m = 0;
-    for (int w = 0; w < (P + 31) / 32; ++w) m += __popc(bm[w]);
+    for (int w = 0; w < (P + 31) / 32; ++w) {
+        uint32_t bits = bm[w];
+        if (32 * w + 32 > P) bits &= (1u << (P - 32 * w)) - 1u;  // bits at and beyond count[f] are ignored
+        m += __popc(bits);
+    }
     if (m == 0) { for (int k = 0; k < n; ++k) o[k] = -1; return; }
     if (m > n) {
         int sel = 0, j = 0;

@@ -128,6 +128,51 @@ def pnp_ransac_pts(pts, count, K4, cfg: RansacConfig | None = None, frame0=0, sa
     return out
 
 
+class MapCompactor:
+    """Reusable K0 launcher: persistent pts [F,5,cap] / count [F] / workspace."""
+
+    def __init__(self, F, H, W, cap, device="cuda"):
+        self.F, self.H, self.W, self.cap = F, H, W, cap
+        dev = torch.device(device)
+        nb = _lib.load().pb_compact_workspace_bytes(F, H, W, cap)
+        self.launches = 2 if nb else 1
+        self.ws = _ws(nb, dev)
+        self.pts = torch.empty((F, 5, cap), dtype=torch.float32, device=dev)
+        self.count = torch.empty((F,), dtype=torch.int32, device=dev)
+
+    def __call__(self, xyz, mask, extent, lfborder, roi=None):
+        if tuple(xyz.shape) != (self.F, 3, self.H, self.W) or not xyz.is_contiguous() or xyz.dtype != torch.float32:
+            raise ValueError("xyz must be a contiguous float32 [F,3,H,W] CUDA tensor of the planned shape")
+        call("pb_compact_map", _ptr(xyz), _ptr(mask), _ptr(roi), _ptr(extent), _ptr(lfborder), self.F, self.H,
+             self.W, self.cap, _ptr(self.pts), _ptr(self.count), None, _ptr(self.ws), self.ws.numel(), _stream())
+        return self.pts, self.count
+
+
+class PtsRansac:
+    """Reusable K1-K4 launcher with persistent outputs and workspace."""
+
+    launches = 2
+
+    def __init__(self, F, cap, cfg: RansacConfig | None = None, device="cuda"):
+        self.F, self.cap = F, cap
+        self.cfg = cfg or RansacConfig()
+        self.prm = self.cfg.c_struct()
+        dev = torch.device(device)
+        self.ws = _ws(_lib.load().pb_ransac_workspace_bytes(F, cap, C.byref(self.prm)), dev)
+        self.R = torch.empty((F, 3, 3), dtype=torch.float32, device=dev)
+        self.t = torch.empty((F, 3), dtype=torch.float32, device=dev)
+        self.n_inl = torch.empty((F,), dtype=torch.int32, device=dev)
+        self.best_hyp = torch.empty((F,), dtype=torch.int32, device=dev)
+        self.n_inl_refined = torch.empty((F,), dtype=torch.int32, device=dev)
+        self.status = torch.empty((F,), dtype=torch.int32, device=dev)
+
+    def __call__(self, pts, count, K4, frame0=0):
+        call("pb_pnp_ransac_pts", _ptr(pts), _ptr(count), _ptr(K4), self.F, self.cap, frame0, C.byref(self.prm),
+             None, _ptr(self.R), _ptr(self.t), _ptr(self.n_inl), _ptr(self.best_hyp), _ptr(self.n_inl_refined),
+             _ptr(self.status), None, None, None, None, _ptr(self.ws), self.ws.numel(), _stream())
+        return self
+
+
 class MapRansac:
     """Reusable map -> pose launcher (K0 + K1-K4) with a persistent workspace and outputs."""
 

@@ -53,29 +53,132 @@ def summarize(table: torch.Tensor, objlist):
 
 
 class EvalSweep:
-    """map -> pose -> ADD(-S)/r/t -> accuracy table, all on one stream, no host sync per batch."""
+    """map -> pose -> ADD(-S)/r/t -> accuracy table, all on one stream, no host sync per batch.
+
+    Four ABI calls per batch of F frames: pb_compact_map (K0), pb_pnp_ransac_pts (K1-K4: score +
+    finalize kernels), pb_pose_metrics (K6), pb_accumulate_results.  All buffers are persistent."""
+
+    STAGES = ("compact", "ransac", "metrics", "accumulate")
 
     def __init__(self, model_points, diameter, is_sym, F, H, W, cap, cfg: RansacConfig | None = None,
                  device="cuda", add_frac=0.1, r_thr_deg=5.0, t_thr_m=0.05):
         dev = torch.device(device)
+        self.dev = dev
+        self.F, self.H, self.W, self.cap = F, H, W, cap
+        self.cfg = cfg or RansacConfig()
         self.model = model_points.to(dev, torch.float32).contiguous()        # [C,N,3]
         self.diameter = diameter.to(dev, torch.float32).contiguous()          # [C]
         self.is_sym = is_sym.to(dev, torch.uint8).contiguous()                # [C]
         self.n_cls = self.model.shape[0]
-        self.ransac = ops.MapRansac(F, H, W, cap, cfg, device=dev)
+        self.compact = ops.MapCompactor(F, H, W, cap, device=dev)
+        self.ransac = ops.PtsRansac(F, cap, self.cfg, device=dev)
         self.table = ops_metric.new_table(self.n_cls, dev)
         self.add_frac, self.r_thr_deg, self.t_thr_m = add_frac, r_thr_deg, t_thr_m
-        self.launches_per_step = None
+        self.launches_per_step = self.compact.launches + self.ransac.launches + 2
 
-    def step(self, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=0, roi=None):
-        """One batch of F frames (device tensors).  Returns (add, r_deg, t_m) [F] device tensors."""
-        rs = self.ransac(xyz, mask, extent, lfborder, K4, roi=roi, frame0=frame0)
+    def step(self, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=0, roi=None, events=None):
+        """One batch of F frames (device tensors).  Returns (add, r_deg, t_m) [F] device tensors.
+        ``events``: optional list that receives one (name, start, end) CUDA-event triple per stage
+        (recorded on the current stream; used by bench.py for the per-kernel roofline)."""
+        def mark():
+            if events is None:
+                return None
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            return e
+        e0 = mark()
+        pts, count = self.compact(xyz, mask, extent, lfborder, roi=roi)
+        e1 = mark()
+        rs = self.ransac(pts, count, K4, frame0=frame0)
+        e2 = mark()
         add, r_deg, t_m = ops_metric.pose_metrics(rs.R, rs.t, R_gt, t_gt, self.model, cls, self.is_sym)
+        e3 = mark()
         ops_metric.accumulate_results(self.table, add, r_deg, t_m, cls, self.diameter, status=rs.status,
                                       variant=0, add_frac=self.add_frac, r_thr_deg=self.r_thr_deg,
                                       t_thr_m=self.t_thr_m, count_frames=True)
+        e4 = mark()
+        if events is not None:
+            events.append((e0, e1, e2, e3, e4))
         return add, r_deg, t_m
 
     def finish(self, group=None):
         """All-reduce the table across ranks (on the compute stream) and return it."""
         return reduce_table(self.table, group)
+
+
+SMALL_WIDTHS = (3, 3, 4, 9, 3)          # extent | lfborder | K4 | R_gt | t_gt
+SMALL_COLS = sum(SMALL_WIDTHS)
+
+
+def pack_small(extent, lfborder, K4, R_gt, t_gt, chunk):
+    """Per-frame small inputs -> [F/chunk, 22*chunk] f32: one H2D copy per chunk, and every field is
+    a contiguous view after it (extent [chunk,3] | lfborder [chunk,3] | K4 | R_gt | t_gt)."""
+    F = extent.shape[0]
+    parts = [torch.as_tensor(a, dtype=torch.float32).reshape(F // chunk, chunk * w)
+             for a, w in zip((extent, lfborder, K4, R_gt, t_gt), SMALL_WIDTHS)]
+    return torch.cat(parts, dim=1).contiguous()
+
+
+def unpack_small(flat, chunk):
+    out, off = [], 0
+    for w in SMALL_WIDTHS:
+        out.append(flat[off:off + chunk * w].view(chunk, w))
+        off += chunk * w
+    out[3] = out[3].view(chunk, 3, 3)
+    return out
+
+
+class HostEvalSweep:
+    """The same pass for inputs that live in (pinned) HOST memory -- what a caller holding the
+    network output on the host would run.  The batch is cut into chunks of ``chunk`` frames; the
+    H2D copy of chunk i+1 (copy stream) overlaps K0..K6 of chunk i (compute stream) through two
+    device staging buffers; the only D2H traffic is the [24,C] accuracy table at the end."""
+
+    def __init__(self, model_points, diameter, is_sym, H, W, cap, chunk=128, cfg: RansacConfig | None = None,
+                 device="cuda", **kw):
+        dev = torch.device(device)
+        self.dev, self.chunk, self.H, self.W = dev, chunk, H, W
+        self.sweep = EvalSweep(model_points, diameter, is_sym, chunk, H, W, cap, cfg, device=dev, **kw)
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.stage = [dict(xyz=torch.empty((chunk, 3, H, W), dtype=torch.float32, device=dev),
+                           mask=torch.empty((chunk, H, W), dtype=torch.uint8, device=dev),
+                           small=torch.empty((SMALL_COLS * chunk,), dtype=torch.float32, device=dev),
+                           cls=torch.empty((chunk,), dtype=torch.int32, device=dev),
+                           ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
+        self.table_host = torch.empty((ops_metric.TABLE_ROWS, self.sweep.n_cls), dtype=torch.float64).pin_memory()
+        self.h2d_bytes = 0
+
+    @property
+    def table(self):
+        return self.sweep.table
+
+    def run(self, xyz_h, mask_h, small_h, cls_h, frame0=0, group=None):
+        """xyz_h [F,3,H,W] f32, mask_h [F,H,W] u8, small_h = pack_small(...) [F/chunk, 22*chunk] f32,
+        cls_h [F] i32 -- pinned host tensors; F a multiple of ``chunk``.  Returns the table on the
+        host (this call synchronises once, at the end)."""
+        F = xyz_h.shape[0]
+        if F % self.chunk:
+            raise ValueError("F must be a multiple of the chunk size")
+        comp = torch.cuda.current_stream(self.dev)
+        n = F // self.chunk
+        self.h2d_bytes = 0
+        for i in range(n):
+            st = self.stage[i & 1]
+            lo, hi = i * self.chunk, (i + 1) * self.chunk
+            with torch.cuda.stream(self.copy_stream):
+                if i >= 2:
+                    self.copy_stream.wait_event(st["free"])
+                st["xyz"].copy_(xyz_h[lo:hi], non_blocking=True)
+                st["mask"].copy_(mask_h[lo:hi], non_blocking=True)
+                st["small"].copy_(small_h[i], non_blocking=True)
+                st["cls"].copy_(cls_h[lo:hi], non_blocking=True)
+                st["ready"].record(self.copy_stream)
+            self.h2d_bytes += sum(st[k].numel() * st[k].element_size() for k in ("xyz", "mask", "small", "cls"))
+            comp.wait_event(st["ready"])
+            ext, lfb, K4, Rg, tg = unpack_small(st["small"], self.chunk)
+            self.sweep.step(st["xyz"], st["mask"], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
+            st["free"].record(comp)
+        reduce_table(self.sweep.table, group)
+        self.table_host.copy_(self.sweep.table, non_blocking=True)
+        comp.synchronize()
+        return self.table_host

@@ -135,14 +135,28 @@ class MapCompactor:
         self.F, self.H, self.W, self.cap = F, H, W, cap
         dev = torch.device(device)
         nb = _lib.load().pb_compact_workspace_bytes(F, H, W, cap)
-        self.launches = 2 if nb else 1
+        self.sparse_ok = (H * W) % 32 == 0 and (H * W) // 8 <= 200 * 1024
+        self.launches_dense = 2 if nb else 1
         self.ws = _ws(nb, dev)
         self.pts = torch.empty((F, 5, cap), dtype=torch.float32, device=dev)
         self.count = torch.empty((F,), dtype=torch.int32, device=dev)
 
+    def launches(self, has_mask=True):
+        """Kernels launched per call: the mask-first kernel is one launch; the maskless stream adds a
+        merge launch when frames are split into row bands."""
+        return 1 if (has_mask and self.sparse_ok) else self.launches_dense
+
     def __call__(self, xyz, mask, extent, lfborder, roi=None):
+        """xyz / mask may be CUDA tensors or PINNED host tensors (mapped under UVA): with a mask the
+        mask-first kernel then reads only the mask and the foreground pixels' sectors across PCIe."""
         if tuple(xyz.shape) != (self.F, 3, self.H, self.W) or not xyz.is_contiguous() or xyz.dtype != torch.float32:
-            raise ValueError("xyz must be a contiguous float32 [F,3,H,W] CUDA tensor of the planned shape")
+            raise ValueError("xyz must be a contiguous float32 [F,3,H,W] tensor of the planned shape")
+        for name, t in (("xyz", xyz), ("mask", mask)):
+            if t is not None and not (t.is_cuda or t.is_pinned()):
+                raise _lib.PoseB200Error(f"{name} must be a CUDA tensor or a pinned host tensor (no CPU path)")
+        if mask is not None and (tuple(mask.shape) != (self.F, self.H, self.W) or mask.dtype != torch.uint8
+                                 or not mask.is_contiguous()):
+            raise ValueError("mask must be a contiguous uint8 [F,H,W] tensor")
         call("pb_compact_map", _ptr(xyz), _ptr(mask), _ptr(roi), _ptr(extent), _ptr(lfborder), self.F, self.H,
              self.W, self.cap, _ptr(self.pts), _ptr(self.count), None, _ptr(self.ws), self.ws.numel(), _stream())
         return self.pts, self.count

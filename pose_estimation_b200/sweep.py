@@ -74,7 +74,7 @@ class EvalSweep:
         self.ransac = ops.PtsRansac(F, cap, self.cfg, device=dev)
         self.table = ops_metric.new_table(self.n_cls, dev)
         self.add_frac, self.r_thr_deg, self.t_thr_m = add_frac, r_thr_deg, t_thr_m
-        self.launches_per_step = self.compact.launches + self.ransac.launches + 2
+        self.launches_per_step = self.compact.launches(True) + self.ransac.launches + 2
 
     def step(self, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=0, roi=None, events=None):
         """One batch of F frames (device tensors).  Returns (add, r_deg, t_m) [F] device tensors.
@@ -135,13 +135,18 @@ class HostEvalSweep:
     device staging buffers; the only D2H traffic is the [24,C] accuracy table at the end."""
 
     def __init__(self, model_points, diameter, is_sym, H, W, cap, chunk=128, cfg: RansacConfig | None = None,
-                 device="cuda", **kw):
+                 device="cuda", zero_copy=False, **kw):
+        """zero_copy=True (needs a mask): no staging copy of the maps at all -- the mask-first K0
+        kernel reads the pinned host maps through their mapped (UVA) addresses, so only the mask
+        bytes and the foreground pixels' 32-byte sectors cross PCIe (csrc/compact.cu)."""
         dev = torch.device(device)
         self.dev, self.chunk, self.H, self.W = dev, chunk, H, W
+        self.zero_copy = zero_copy
         self.sweep = EvalSweep(model_points, diameter, is_sym, chunk, H, W, cap, cfg, device=dev, **kw)
         self.copy_stream = torch.cuda.Stream(device=dev)
-        self.stage = [dict(xyz=torch.empty((chunk, 3, H, W), dtype=torch.float32, device=dev),
-                           mask=torch.empty((chunk, H, W), dtype=torch.uint8, device=dev),
+        zc = zero_copy
+        self.stage = [dict(xyz=None if zc else torch.empty((chunk, 3, H, W), dtype=torch.float32, device=dev),
+                           mask=None if zc else torch.empty((chunk, H, W), dtype=torch.uint8, device=dev),
                            small=torch.empty((SMALL_COLS * chunk,), dtype=torch.float32, device=dev),
                            cls=torch.empty((chunk,), dtype=torch.int32, device=dev),
                            ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
@@ -168,15 +173,23 @@ class HostEvalSweep:
             with torch.cuda.stream(self.copy_stream):
                 if i >= 2:
                     self.copy_stream.wait_event(st["free"])
-                st["xyz"].copy_(xyz_h[lo:hi], non_blocking=True)
-                st["mask"].copy_(mask_h[lo:hi], non_blocking=True)
+                if not self.zero_copy:
+                    st["xyz"].copy_(xyz_h[lo:hi], non_blocking=True)
+                    st["mask"].copy_(mask_h[lo:hi], non_blocking=True)
                 st["small"].copy_(small_h[i], non_blocking=True)
                 st["cls"].copy_(cls_h[lo:hi], non_blocking=True)
                 st["ready"].record(self.copy_stream)
-            self.h2d_bytes += sum(st[k].numel() * st[k].element_size() for k in ("xyz", "mask", "small", "cls"))
+            self.h2d_bytes += sum(st[k].numel() * st[k].element_size() for k in ("xyz", "mask", "small", "cls")
+                                  if st[k] is not None)
             comp.wait_event(st["ready"])
             ext, lfb, K4, Rg, tg = unpack_small(st["small"], self.chunk)
-            self.sweep.step(st["xyz"], st["mask"], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
+            if self.zero_copy:
+                if mask_h is None:
+                    raise ValueError("zero_copy needs a mask (without one every pixel must be streamed)")
+                self.h2d_bytes += mask_h[lo:hi].numel()          # + the gathered sectors, added by the caller
+                self.sweep.step(xyz_h[lo:hi], mask_h[lo:hi], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
+            else:
+                self.sweep.step(st["xyz"], st["mask"], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
             st["free"].record(comp)
         reduce_table(self.sweep.table, group)
         self.table_host.copy_(self.sweep.table, non_blocking=True)

@@ -124,6 +124,28 @@ def test_eval_sweep_table(dev):
     assert (pb.batch_intrinsic_transform(pb.batch_intrinsic_transform(t(b["K4"]))) == t(b["K4"])).all()
 
 
+def test_host_eval_sweep_staged_and_zero_copy_equal_device(dev):
+    """HostEvalSweep (pinned host maps; staged H2D or zero-copy) gives the device path's table bit for bit."""
+    from pose_estimation_b200 import sweep
+    F, chunk = 16, 8
+    sps = synth.make_batch_sparse(0x5EED, 2, F)
+    b = batch_arrays(sps)
+    models = torch.from_numpy(synth.class_models(500))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    t = lambda a: torch.from_numpy(a).to(dev)
+    sw = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev)
+    sw.step(t(b["xyz"]), t(b["mask"]), t(b["extent"]), t(b["lfborder"]), t(b["K4"]), t(b["cls"]), t(b["R_gt"]), t(b["t_gt"]))
+    want = sw.finish().cpu()
+    xyz_h, mask_h = torch.from_numpy(b["xyz"]).pin_memory(), torch.from_numpy(b["mask"]).pin_memory()
+    cls_h = torch.from_numpy(b["cls"]).pin_memory()
+    for zc in (False, True):
+        hs = sweep.HostEvalSweep(models, diam, sym, synth.IMG_H, synth.IMG_W, 1280, chunk=chunk, device=dev, zero_copy=zc)
+        small_h = sweep.pack_small(b["extent"], b["lfborder"], b["K4"], b["R_gt"], b["t_gt"], chunk).pin_memory()
+        got = hs.run(xyz_h, mask_h, small_h, cls_h)
+        assert torch.equal(got, want), zc
+        assert hs.h2d_bytes > 0
+
+
 def test_cpu_tensors_have_no_fallback():
     from pose_estimation_b200 import ops_metric
     from pose_estimation_b200._lib import PoseB200Error

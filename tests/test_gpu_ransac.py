@@ -63,6 +63,37 @@ def test_compact_truncation_roi_and_odd_shape(cref, dev):
         assert np.array_equal(pts[f, :, :ref.shape[1]].cpu().numpy(), ref)
 
 
+def test_compact_mask_first_kernel_edges_and_pinned_host(cref, dev):
+    """Mask-first (sparse) K0: any non-zero mask byte is foreground, dense masks truncate at cap in
+    pixel order, ROI offsets, empty frames; the same kernel reading PINNED HOST maps (zero-copy
+    over PCIe) is bit-identical."""
+    rng = np.random.default_rng(7)
+    F, H, W, cap = 6, 64, 96, 300
+    xyz = rng.random((F, 3, H, W)).astype(np.float32)
+    mask = (rng.random((F, H, W)) < 0.03).astype(np.uint8) * rng.integers(1, 256, (F, H, W)).astype(np.uint8)
+    mask[1] = 0                       # empty
+    mask[2] = 255                     # full frame -> truncated at cap
+    mask[3] = 0; mask[3, -1, -1] = 7  # only the very last pixel
+    mask[4] = 0; mask[4, 0, 0] = 128; mask[4, 0, 31] = 1; mask[4, 0, 32] = 1
+    ext = rng.random((F, 3)).astype(np.float32) + 0.1
+    lfb = -rng.random((F, 3)).astype(np.float32)
+    roi = rng.integers(0, 100, (F, 2)).astype(np.int32)
+    refs = [cref.compact_map(xyz[f], mask[f], ext[f], lfb[f], rmin=int(roi[f, 0]), cmin=int(roi[f, 1]), cap=cap)
+            for f in range(F)]
+    xyz_p, mask_p = torch.from_numpy(xyz).pin_memory(), torch.from_numpy(mask).pin_memory()
+    comp = ops.MapCompactor(F, H, W, cap, device=dev)
+    assert comp.launches(True) == 1
+    for src_xyz, src_mask in ((_t(xyz, dev), _t(mask, dev)), (xyz_p, mask_p)):
+        pts, count = comp(src_xyz, src_mask, _t(ext, dev), _t(lfb, dev), roi=_t(roi, dev))
+        pts, count = pts.cpu().numpy(), count.cpu().numpy()
+        for f in range(F):
+            ref, tot = refs[f]
+            assert count[f] == ref.shape[1] == min(tot, cap)
+            assert np.array_equal(pts[f, :, :count[f]], ref)
+    with pytest.raises(Exception):    # pageable host memory is rejected (no CPU path)
+        comp(torch.from_numpy(xyz), _t(mask, dev), _t(ext, dev), _t(lfb, dev))
+
+
 def _check_ransac(cref, dev, sps, cfg, cap, frame0=0, sample_idx=None):
     pts_list = [synth.compact_points(s) for s in sps]
     pts, cnt = pack_pts(pts_list, cap)
@@ -110,16 +141,19 @@ def test_ransac_forced_minimal_sets_and_large_P(cref, dev):
     _check_ransac(cref, dev, sps, ops.RansacConfig(n_hyp=H, lo_rounds=1), cap=cap, sample_idx=sidx)
 
 
-def test_ransac_failure_status(dev):
+def test_ransac_failure_status(dev, cref):
     F, cap = 3, 64
     pts = np.zeros((F, 5, cap), np.float32)
     cnt = np.array([0, 3, 40], np.int32)
     rng = np.random.default_rng(0)
     pts[2, :, :40] = rng.random((5, 40))         # garbage correspondences: no consensus
+    pts[2, 3:5, :40] *= 600.0                    # image points spread over the frame (not all within 1 px)
     K4 = np.tile(synth.LINEMOD_K4, (F, 1))
     out = ops.pnp_ransac_pts(_t(pts, dev), _t(cnt, dev), _t(K4, dev), ops.RansacConfig(n_hyp=32, min_inliers=30))
     st = out["status"].cpu().numpy()
     assert st[0] == 1 and st[1] == 1 and st[2] == 2
+    o = cref.ransac_frame(pts[2, :, :40], K4[2], frame=2, n_hyp=32, min_inliers=30)
+    assert o["status"] == 2
     assert np.array_equal(out["R"][0].cpu().numpy(), np.eye(3, dtype=np.float32))
     assert np.all(out["t"].cpu().numpy()[:2] == 0)
 

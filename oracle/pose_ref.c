@@ -298,15 +298,25 @@ static inline void make_proj(const float K4[4], const float R[9], const float t[
     M[8] = R[6]; M[9] = R[7]; M[10] = R[8]; M[11] = t[2];
 }
 
-static inline int inlier_test(const float M[12], float X, float Y, float Z, float u, float v, float thr2) {
-    float x = fmaf(M[0], X, fmaf(M[1], Y, fmaf(M[2], Z, M[3])));
-    float y = fmaf(M[4], X, fmaf(M[5], Y, fmaf(M[6], Z, M[7])));
-    float w = fmaf(M[8], X, fmaf(M[9], Y, fmaf(M[10], Z, M[11])));
-    float dx = fmaf(-u, w, x);
-    float dy = fmaf(-v, w, y);
-    float e = fmaf(dx, dx, dy * dy);
-    float lim = thr2 * (w * w);
-    return (w > 0.0f) && (e <= lim);
+/* Inlier test in threshold units (division-free; cv2 tests |proj - uv|^2 <= thr^2):
+ *   Ms = K[R|t] with rows 0,1 multiplied by inv_thr = 1/thr; (us,vs) = (u,v)*inv_thr;
+ *   s  = (x - us*w)^2 + (y - vs*w)^2 - w*|w|      inlier  <=>  s < 0
+ * (w <= 0 makes -w*|w| >= 0, so points behind the camera never pass; NaN never passes).
+ * The operation order below is the contract shared with csrc/common.cuh::inlier_s. */
+static inline void scale_proj(const float M[12], float inv_thr, float Ms[12]) {
+    for (int k = 0; k < 8; ++k) Ms[k] = M[k] * inv_thr;
+    for (int k = 8; k < 12; ++k) Ms[k] = M[k];
+}
+static inline int inlier_test(const float Ms[12], float X, float Y, float Z, float us, float vs) {
+    float x = fmaf(Ms[0], X, fmaf(Ms[1], Y, fmaf(Ms[2], Z, Ms[3])));
+    float y = fmaf(Ms[4], X, fmaf(Ms[5], Y, fmaf(Ms[6], Z, Ms[7])));
+    float w = fmaf(Ms[8], X, fmaf(Ms[9], Y, fmaf(Ms[10], Z, Ms[11])));
+    float dx = fmaf(-us, w, x);
+    float dy = fmaf(-vs, w, y);
+    float q = w * fabsf(w);
+    float t = fmaf(dy, dy, -q);
+    float s = fmaf(dx, dx, t);
+    return s < 0.0f;
 }
 
 int ref_hypothesis(const float* X, const float* Y, const float* Z, const float* U, const float* V,
@@ -345,11 +355,13 @@ int ref_hypothesis(const float* X, const float* Y, const float* Z, const float* 
 }
 
 int ref_score(const float M[12], const float* X, const float* Y, const float* Z, const float* U,
-              const float* V, int P, float thr2, uint32_t* bitmap) {
+              const float* V, int P, float inv_thr, uint32_t* bitmap) {
     int n = 0;
+    float Ms[12];
+    scale_proj(M, inv_thr, Ms);
     if (bitmap) memset(bitmap, 0, sizeof(uint32_t) * (size_t)((P + 31) / 32));
     for (int i = 0; i < P; ++i) {
-        int in = inlier_test(M, X[i], Y[i], Z[i], U[i], V[i], thr2);
+        int in = inlier_test(Ms, X[i], Y[i], Z[i], U[i] * inv_thr, V[i] * inv_thr);
         n += in;
         if (bitmap && in) bitmap[i >> 5] |= 1u << (i & 31);
     }
@@ -526,7 +538,7 @@ int ref_ransac_frame(const float* X, const float* Y, const float* Z, const float
     int H = prm->n_hyp;
     if (hyp_counts) for (int h = 0; h < H; ++h) hyp_counts[h] = -1;
     if (P < 4) return 1;
-    float thr2 = prm->thresh_px * prm->thresh_px;
+    float inv_thr = 1.0f / prm->thresh_px;
     int bc = -1, bh = -1;
     float bR[9], bt[3], bM[12];
     for (int h = 0; h < H; ++h) {
@@ -541,7 +553,7 @@ int ref_ransac_frame(const float* X, const float* Y, const float* Z, const float
         }
         float M[12], Rh[9], th[3];
         if (!ref_hypothesis(X, Y, Z, U, V, K4, idx, M, Rh, th)) continue;
-        int c = ref_score(M, X, Y, Z, U, V, P, thr2, NULL);
+        int c = ref_score(M, X, Y, Z, U, V, P, inv_thr, NULL);
         if (hyp_counts) hyp_counts[h] = c;
         if (c > bc) { bc = c; bh = h; memcpy(bR, Rh, sizeof(bR)); memcpy(bt, th, sizeof(bt)); memcpy(bM, M, sizeof(bM)); }
     }
@@ -550,7 +562,7 @@ int ref_ransac_frame(const float* X, const float* Y, const float* Z, const float
     if (R0) memcpy(R0, bR, sizeof(bR));
     if (t0) memcpy(t0, bt, sizeof(bt));
     uint32_t* bm = (uint32_t*)malloc(sizeof(uint32_t) * (size_t)words);
-    ref_score(bM, X, Y, Z, U, V, P, thr2, bm);
+    ref_score(bM, X, Y, Z, U, V, P, inv_thr, bm);
     if (bitmap) memcpy(bitmap, bm, sizeof(uint32_t) * (size_t)words);
     float q[4], tt[3] = {bt[0], bt[1], bt[2]};
     ref_rot_to_quat(bR, q);
@@ -560,7 +572,7 @@ int ref_ransac_frame(const float* X, const float* Y, const float* Z, const float
         float Rq[9], Mq[12];
         quat_to_rot(q, Rq);
         make_proj(K4, Rq, tt, Mq);
-        nref = ref_score(Mq, X, Y, Z, U, V, P, thr2, bm);
+        nref = ref_score(Mq, X, Y, Z, U, V, P, inv_thr, bm);
     }
     quat_to_rot(q, R);
     t[0] = tt[0]; t[1] = tt[1]; t[2] = tt[2];

@@ -52,9 +52,9 @@ int ref_p3p(const float x[3][3], const float y[3][3], float R[4][9], float t[4][
 int ref_hypothesis(const float* X, const float* Y, const float* Z, const float* U, const float* V,
                    const float K4[4], const int32_t idx[4], float M[12], float R[9], float t[3]);
 
-/* inlier count of one projection matrix (bitmap optional, ceil(P/32) words) */
+/* inlier count of one projection matrix (bitmap optional, ceil(P/32) words); inv_thr = 1/thresh_px */
 int ref_score(const float M[12], const float* X, const float* Y, const float* Z, const float* U,
-              const float* V, int P, float thr2, uint32_t* bitmap);
+              const float* V, int P, float inv_thr, uint32_t* bitmap);
 
 /* Full per-frame RANSAC.  sample_idx optional [H,4].  hyp_counts optional [H] (-1 = invalid).
  * status: 0 ok, 1 too few points, 2 no valid hypothesis / too few inliers. */

@@ -71,17 +71,31 @@ __device__ __forceinline__ void make_proj(float fx, float fy, float cx, float cy
     M[8] = R[6]; M[9] = R[7]; M[10] = R[8]; M[11] = t[2];
 }
 
-// division-free reprojection test: |proj - uv|^2 <= thr^2  <=>  (x-u w)^2+(y-v w)^2 <= thr^2 w^2, w>0
-__device__ __forceinline__ bool inlier_test(const float M[12], float X, float Y, float Z, float u, float v,
-                                            float thr2) {
-    float x = fmaf(M[0], X, fmaf(M[1], Y, fmaf(M[2], Z, M[3])));
-    float y = fmaf(M[4], X, fmaf(M[5], Y, fmaf(M[6], Z, M[7])));
-    float w = fmaf(M[8], X, fmaf(M[9], Y, fmaf(M[10], Z, M[11])));
-    float dx = fmaf(-u, w, x);
-    float dy = fmaf(-v, w, y);
-    float e = fmaf(dx, dx, dy * dy);
-    float lim = thr2 * (w * w);
-    return (w > 0.0f) && (e <= lim);
+// Projection matrix in threshold units: rows 0,1 of K[R|t] times inv_thr = 1/thr (thr = 1: unchanged).
+__device__ __forceinline__ void make_proj_s(float fx, float fy, float cx, float cy, const float R[9],
+                                            const float t[3], float inv_thr, float M[12]) {
+    make_proj(fx, fy, cx, cy, R, t, M);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) M[k] = M[k] * inv_thr;
+}
+
+// Division-free reprojection test in threshold units (cv2: |proj - uv|^2 <= thr^2):
+//   s = (x - us w)^2 + (y - vs w)^2 - w|w|,  (us,vs) = (u,v)*inv_thr;   inlier <=> s < 0.
+// w <= 0 gives -w|w| >= 0, so points behind the camera never pass; NaN never passes (the GPU's
+// canonical NaN has a clear sign bit).  14 FMA-pipe instructions; the sign bit of s is the verdict.
+// Operation order is a contract with oracle/pose_ref.c::inlier_test (bit-exact inlier sets).
+__device__ __forceinline__ float inlier_s(const float M[12], float X, float Y, float Z, float us, float vs) {
+    const float x = fmaf(M[0], X, fmaf(M[1], Y, fmaf(M[2], Z, M[3])));
+    const float y = fmaf(M[4], X, fmaf(M[5], Y, fmaf(M[6], Z, M[7])));
+    const float w = fmaf(M[8], X, fmaf(M[9], Y, fmaf(M[10], Z, M[11])));
+    const float dx = fmaf(-us, w, x);
+    const float dy = fmaf(-vs, w, y);
+    const float q = w * fabsf(w);
+    const float t = fmaf(dy, dy, -q);
+    return fmaf(dx, dx, t);
+}
+__device__ __forceinline__ bool inlier_test(const float M[12], float X, float Y, float Z, float us, float vs) {
+    return __float_as_int(inlier_s(M, X, Y, Z, us, vs)) < 0;
 }
 
 __device__ __forceinline__ void quat_to_rot(const float q[4], float R[9]) {

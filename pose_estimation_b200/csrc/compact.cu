@@ -167,18 +167,20 @@ __device__ __forceinline__ uint32_t nz4(uint32_t w) {
 
 constexpr int SP_UNROLL = 4;   // 128-bit mask loads in flight per thread
 
-// One CTA per frame.  Phase 1: mask -> shared bitmap (1 bit/px).  Phase 2: each warp owns a
-// contiguous run of bitmap words: count, block prefix, then emit (pixel index, u, v) in pixel
-// order.  Phase 3: all threads gather xyz at the emitted pixels and de-normalise.
+// One CTA per frame.  Phase 1: mask -> shared bitmap (1 bit/px).  Phase 2: per-tile (32 words)
+// counts, exclusive prefix, then every warp emits (pixel index, u, v) for its round-robin tiles at
+// the tile's offset, i.e. in pixel order.  Phase 3: all threads gather xyz at the emitted pixels
+// and de-normalise.
 __global__ void __launch_bounds__(CT) compact_sparse_kernel(CompactArgs a) {
-    extern __shared__ __align__(16) uint32_t sbm[];             // [HW/32]
-    __shared__ int wcnt[CT / 32];
+    extern __shared__ __align__(16) uint32_t sbm[];             // [HW/32] bitmap, then [ntiles] tile offsets
+    __shared__ int stotal;
     const int f = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nwords = a.HW >> 5;
     const int nv = a.HW >> 4;                                   // 16-px groups (one uint4 of mask each)
     const uint4* pm = reinterpret_cast<const uint4*>(a.mask + (size_t)f * a.HW);
     uint16_t* sb16 = reinterpret_cast<uint16_t*>(sbm);
+    int* stile = reinterpret_cast<int*>(sbm + nwords);
 
     // ---- phase 1
     for (int g0 = 0; g0 < nv; g0 += CT * SP_UNROLL) {
@@ -197,49 +199,61 @@ __global__ void __launch_bounds__(CT) compact_sparse_kernel(CompactArgs a) {
     }
     __syncthreads();
 
-    // ---- phase 2: per-warp contiguous runs of words
-    const int wpw = (nwords + CT / 32 - 1) / (CT / 32);
-    const int w0 = warp * wpw, w1 = min(nwords, w0 + wpw);
-    int c = 0;
-    for (int w = w0 + lane; w < w1; w += 32) c += __popc(sbm[w]);
-    c = __reduce_add_sync(0xffffffffu, c);
-    if (lane == 0) wcnt[warp] = c;
-    __syncthreads();
-    int base = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < CT / 32; ++w) {
-        const int v = wcnt[w];
-        if (w < warp) base += v;
-        total += v;
+    // ---- phase 2: tiles of 32 bitmap words (1024 px) dealt round-robin to the warps, so a compact
+    // foreground blob (a few dozen image rows) is spread over all warps
+    const int ntiles = (nwords + 31) >> 5;
+    for (int k = warp; k < ntiles; k += CT / 32) {
+        const int w = (k << 5) + lane;
+        const int c = __reduce_add_sync(0xffffffffu, w < nwords ? __popc(sbm[w]) : 0);
+        if (lane == 0) stile[k] = c;
     }
-    const int rmin = a.roi ? a.roi[2 * f] : 0, cmin = a.roi ? a.roi[2 * f + 1] : 0;
-    float* oX = a.pts + (size_t)f * 5 * a.cap;
-    float* oY = oX + a.cap; float* oZ = oY + a.cap; float* oU = oZ + a.cap; float* oV = oU + a.cap;
-    if (c > 0) {
-        for (int wb = w0; wb < w1 && base < a.cap; wb += 32) {
-            const int w = wb + lane;
-            uint32_t bits = w < w1 ? sbm[w] : 0u;
-            const int n = __popc(bits);
-            int incl = n;
+    __syncthreads();
+    if (warp == 0) {   // exclusive prefix over the tile counts (in place), total -> stotal
+        int run = 0;
+        for (int k0 = 0; k0 < ntiles; k0 += 32) {
+            const int k = k0 + lane;
+            const int c = k < ntiles ? stile[k] : 0;
+            int incl = c;
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) {
                 const int o = __shfl_up_sync(0xffffffffu, incl, off);
                 if (lane >= off) incl += o;
             }
-            int pos = base + incl - n;
-            while (bits) {
-                const int b = __ffs(bits) - 1;
-                bits &= bits - 1u;
-                if (pos < a.cap) {
-                    const int p = (w << 5) + b;
-                    const int row = p / a.Ww, col = p - row * a.Ww;
-                    oX[pos] = __int_as_float(p);
-                    oU[pos] = (float)(col + cmin);
-                    oV[pos] = (float)(row + rmin);
-                }
-                ++pos;
+            if (k < ntiles) stile[k] = run + incl - c;
+            run += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (lane == 0) stotal = run;
+    }
+    __syncthreads();
+    const int total = stotal;
+    const int rmin = a.roi ? a.roi[2 * f] : 0, cmin = a.roi ? a.roi[2 * f + 1] : 0;
+    float* oX = a.pts + (size_t)f * 5 * a.cap;
+    float* oY = oX + a.cap; float* oZ = oY + a.cap; float* oU = oZ + a.cap; float* oV = oU + a.cap;
+    for (int k = warp; k < ntiles; k += CT / 32) {
+        const int base = stile[k];
+        const int next = (k + 1 < ntiles) ? stile[k + 1] : total;
+        if (next == base || base >= a.cap) continue;          // empty tile / beyond cap (warp-uniform)
+        const int w = (k << 5) + lane;
+        uint32_t bits = w < nwords ? sbm[w] : 0u;
+        const int n = __popc(bits);
+        int incl = n;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += o;
+        }
+        int pos = base + incl - n;
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1u;
+            if (pos < a.cap) {
+                const int p = (w << 5) + b;
+                const int row = p / a.Ww, col = p - row * a.Ww;
+                oX[pos] = __int_as_float(p);
+                oU[pos] = (float)(col + cmin);
+                oV[pos] = (float)(row + rmin);
             }
-            base += __shfl_sync(0xffffffffu, incl, 31);
+            ++pos;
         }
     }
     __syncthreads();   // pixel indices written by this CTA are visible to all of its threads
@@ -365,7 +379,7 @@ CPlan make_cplan(int F, int Hh, int Ww, int cap, bool has_mask) {
     CPlan p;
     const long long HW = (long long)Hh * Ww;
     p.vec = (HW % 4) == 0;
-    p.smem_sparse = (size_t)(HW / 32) * 4;
+    p.smem_sparse = (size_t)(HW / 32) * 4 + (size_t)((HW / 32 + 31) / 32) * 4;
     p.sparse = has_mask && (HW % 32) == 0 && p.smem_sparse <= 200 * 1024;
     if (p.sparse) { p.S = 1; p.quads_per_split = 0; p.segcap = cap; p.off_tot = 0; p.total = 0; return p; }
     int S = 1;

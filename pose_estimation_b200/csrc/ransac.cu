@@ -25,7 +25,7 @@ struct FinalArgs {
     float* R; float* t; int32_t* n_inl; int32_t* best_hyp; int32_t* n_inl_refined; int32_t* status;
     uint32_t* inl_bitmap; float* R0; float* t0;
     int cap, H, HS, gn_iters, lo_rounds, min_inliers;
-    float thr2;
+    float inv_thr;
 };
 
 // fixed-shape block sum of K floats per thread: butterfly inside each warp, then warps in order.
@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a
     float q[4], tt[3] = {tb[0], tb[1], tb[2]};
     rot_to_quat(Rb, q);
     float M[12];
-    make_proj(fx, fy, cx, cy, Rb, tb, M);
+    make_proj_s(fx, fy, cx, cy, Rb, tb, a.inv_thr, M);
 
     int nref = bc;
     for (int w = tid; w < (a.cap + PB_THREADS - 1) / PB_THREADS * (PB_THREADS / 32); w += PB_THREADS) bm[w] = 0u;
@@ -225,14 +225,14 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a
 #pragma unroll
             for (int i = 0; i < 3; ++i)
                 tt[i] = tc[i] - fmaf(R[3 * i], cb[0], fmaf(R[3 * i + 1], cb[1], R[3 * i + 2] * cb[2]));
-            make_proj(fx, fy, cx, cy, R, tt, M);
+            make_proj_s(fx, fy, cx, cy, R, tt, a.inv_thr, M);
         }
         // ---- (re-)score: inlier bitmap by warp ballot
         __syncthreads();
         int cn = 0;
         for (int base = 0; base < P; base += PB_THREADS) {
             const int i = base + tid;
-            bool in = i < P && inlier_test(M, X[i], Y[i], Z[i], U[i], V[i], a.thr2);
+            bool in = i < P && inlier_test(M, X[i], Y[i], Z[i], U[i] * a.inv_thr, V[i] * a.inv_thr);
             unsigned b = __ballot_sync(0xffffffffu, in);
             if (lane == 0) { bm[(base >> 5) + warp] = b; cn += __popc(b); }
         }
@@ -321,14 +321,14 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     sa.slice_best = reinterpret_cast<unsigned long long*>(static_cast<char*>(ws) + p.off_best);
     sa.cap = cap; sa.H = prm->n_hyp; sa.HS = p.HS; sa.Hs = p.Hs; sa.CH = p.CH; sa.PP = p.PP;
     sa.frame0 = frame0; sa.seed_lo = prm->seed_lo; sa.seed_hi = prm->seed_hi;
-    sa.thr2 = prm->thresh_px * prm->thresh_px;
+    sa.inv_thr = 1.0f / prm->thresh_px; sa.F = F;
     if (pb_launch_score(sa, p, F, st)) return -2;
     FinalArgs fa;
     fa.pts = pts; fa.count = count; fa.K4 = K4; fa.hypRt = sa.hypRt; fa.slice_best = sa.slice_best;
     fa.R = R; fa.t = t; fa.n_inl = n_inl; fa.best_hyp = best_hyp; fa.n_inl_refined = n_inl_refined;
     fa.status = status; fa.inl_bitmap = inl_bitmap; fa.R0 = R0; fa.t0 = t0;
     fa.cap = cap; fa.H = prm->n_hyp; fa.HS = p.HS; fa.gn_iters = prm->gn_iters; fa.lo_rounds = prm->lo_rounds;
-    fa.min_inliers = prm->min_inliers; fa.thr2 = sa.thr2;
+    fa.min_inliers = prm->min_inliers; fa.inv_thr = sa.inv_thr;
     cudaFuncSetAttribute(ransac_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_final);
     ransac_finalize_kernel<<<F, PB_THREADS, p.smem_final, st>>>(fa);
     if (pb_check_launch("ransac_finalize_kernel")) return -2;

@@ -7,12 +7,13 @@ struct ScoreArgs {
     const int32_t* count;
     const float* K4;
     const int32_t* sample_idx;
-    float* hypRt;                    // [F,H,12] R|t of every valid hypothesis
+    float* hypRt;                    // [F,H,12] R|t of every hypothesis (t_z = NaN: no model)
     int32_t* hyp_counts;             // optional [F,H]
     unsigned long long* slice_best;  // [F,HS] packed (count+1, ~hyp)
     int cap, H, HS, Hs, CH, PP;      // Hs hypotheses per slice (power of two >= 32); PP point parts
     uint32_t frame0, seed_lo, seed_hi;
-    float thr2;
+    float inv_thr;
+    int F;
 };
 
 struct Plan {
@@ -38,7 +39,7 @@ static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm) {
     int CH = (cap + 127) / 128 * 128;
     if (CH > 2048) CH = 2048;
     p.CH = CH;
-    p.smem_score = (size_t)Hs * 13 * 4 + (size_t)CH * 5 * 4;
+    p.smem_score = (size_t)CH * 5 * 4 + (size_t)Hs * 4;
     p.smem_final = (size_t)((cap + PB_THREADS - 1) / PB_THREADS) * (PB_THREADS / 32) * 4;
     size_t hyp = (size_t)F * H * 12 * sizeof(float);
     p.off_best = (hyp + 255) / 256 * 256;

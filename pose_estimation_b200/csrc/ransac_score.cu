@@ -1,28 +1,79 @@
-// ransac_score.cu -- K1 + K2 + K3 of PnP-RANSAC (sm_100a): sample, solve, score.
+// ransac_score.cu -- K1 + K2 (sample, solve) and K3 (score) of PnP-RANSAC (sm_100a).
 //
-// One CTA per (frame, hypothesis slice).  Replaces the iteration loop inside cv2.solvePnPRansac
-// (tools/trainer.py:423-427): cv::RNG subset draw -> Philox4x32-10 keyed (seed, frame, hyp);
-// 5-point EPnP -> P3P + 4th-point disambiguation (p3p.cuh); PnPRansacCallback::computeError +
-// findInliers -> division-free reprojection test of EVERY correspondence.
+// Replaces the iteration loop inside cv2.solvePnPRansac (tools/trainer.py:423-427): cv::RNG subset
+// draw -> Philox4x32-10 keyed (seed, frame, hyp); 5-point EPnP -> P3P + 4th-point disambiguation
+// (p3p.cuh); PnPRansacCallback::computeError + findInliers -> division-free reprojection test of
+// EVERY correspondence.
 //
-// K3 layout: thread <-> hypothesis (its 3x4 projection matrix lives in 12 registers per
-// hypothesis, NHL hypotheses per thread), correspondences staged once per chunk in shared memory
-// as float4(X,Y,Z,U)+float(V) and read as warp-broadcast LDS.128 + LDS.32, so one shared-memory
-// wavefront feeds 32*NHL hypothesis*point tests and the inlier counter is a private register (no
-// ballot, no reduction).  FP32-pipe bound: 15 FMA-pipe + 2 ALU ops per hypothesis*point.
+//   ransac_hypothesis_kernel  one THREAD per (frame, hypothesis): Philox sample, P3P, R|t -> hypRt.
+//       Register-heavy and divergent, but only F*H threads of ~4k instructions; kept apart so that
+//       the scoring kernel stays lean (high occupancy, no solver registers).
+//   ransac_score_kernel       one CTA per (frame, hypothesis slice): thread <-> hypothesis (3x4
+//       projection matrix in 12 registers, NHL hypotheses per thread), correspondences staged per
+//       chunk in shared memory as float4(X,Y,Z,U') + float(V') and read as warp-broadcast LDS.128,
+//       so one shared-memory wavefront feeds 32*NHL tests.  Per hypothesis*point: 14 FMA-pipe
+//       instructions + one funnel shift that pushes the verdict's sign bit into a 32-bit window
+//       (popcount every 8 points) -- no compare, no select, no reduction in the loop.  Chunks are
+//       padded to a multiple of 8 with never-inlier sentinels so the loop has no tail test.
+//       FP32-pipe bound.
 #include "p3p.cuh"
 #include "ransac_plan.h"
 
 namespace {
 
+constexpr int HT = 128;  // threads per CTA of the hypothesis kernel
+
+__global__ void __launch_bounds__(HT) ransac_hypothesis_kernel(ScoreArgs a) {
+    const long long gid = (long long)blockIdx.x * HT + threadIdx.x;
+    if (gid >= (long long)a.F * a.H) return;
+    const int f = (int)(gid / a.H), h = (int)(gid - (long long)f * a.H);
+    const int P = min(a.count[f], a.cap);
+    const float* X = a.pts + (size_t)f * 5 * a.cap;
+    const float* Y = X + a.cap;
+    const float* Z = Y + a.cap;
+    const float* U = Z + a.cap;
+    const float* V = U + a.cap;
+    float* o = a.hypRt + (size_t)gid * 12;
+    bool valid = false;
+    float R[9], t[3];
+    if (P >= 4) {
+        int idx[4];
+        bool have;
+        if (a.sample_idx) {
+            const int32_t* si = a.sample_idx + (size_t)gid * 4;
+            have = true;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { idx[k] = si[k]; have = have && idx[k] >= 0 && idx[k] < P; }
+        } else {
+            have = sample4(a.seed_lo, a.seed_hi, a.frame0 + (uint32_t)f, (uint32_t)h, P, idx);
+        }
+        if (have) {
+            const float fx = a.K4[4 * f], fy = a.K4[4 * f + 1], cx = a.K4[4 * f + 2], cy = a.K4[4 * f + 3];
+            float x[4][3], uv[4][2];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                x[k][0] = X[idx[k]]; x[k][1] = Y[idx[k]]; x[k][2] = Z[idx[k]];
+                uv[k][0] = U[idx[k]]; uv[k][1] = V[idx[k]];
+            }
+            valid = p3p::solve(x, uv, fx, fy, cx, cy, R, t);
+        }
+    }
+    if (valid) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) o[k] = R[k];
+        o[9] = t[0]; o[10] = t[1]; o[11] = t[2];
+    } else {
+        o[11] = __int_as_float(0x7fffffff);  // t_z = NaN marks "no model"
+    }
+}
+
 template <int NHL>
 __global__ void __launch_bounds__(PB_THREADS) ransac_score_kernel(ScoreArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int CH = a.CH, Hs = a.Hs;
-    float4* sp4 = reinterpret_cast<float4*>(smem_raw);          // [CH] X,Y,Z,U
-    float* spv = reinterpret_cast<float*>(sp4 + CH);            // [CH] V
-    float* Msm = spv + CH;                                      // [Hs][12]
-    int* cnt = reinterpret_cast<int*>(Msm + Hs * 12);           // [Hs]
+    float4* sp4 = reinterpret_cast<float4*>(smem_raw);          // [CH] X,Y,Z,U'
+    float* spv = reinterpret_cast<float*>(sp4 + CH);            // [CH] V'
+    int* cnt = reinterpret_cast<int*>(spv + CH);                // [Hs]
     __shared__ unsigned long long wkey[PB_THREADS / 32];
 
     const int f = blockIdx.x / a.HS, s = blockIdx.x % a.HS;
@@ -35,82 +86,77 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_score_kernel(ScoreArgs a) {
     const float* V = U + a.cap;
     const float fx = a.K4[4 * f], fy = a.K4[4 * f + 1], cx = a.K4[4 * f + 2], cy = a.K4[4 * f + 3];
     const int h0 = s * Hs;
-
-    // ---- K1 + K2: one hypothesis per thread
-    for (int hl = tid; hl < Hs; hl += PB_THREADS) {
-        const int h = h0 + hl;
-        float M[12];
-#pragma unroll
-        for (int k = 0; k < 12; ++k) M[k] = 0.0f;
-        M[11] = -1.0f;  // w < 0 for every point: never an inlier
-        bool valid = false;
-        if (h < a.H && P >= 4) {
-            int idx[4];
-            bool have;
-            if (a.sample_idx) {
-                const int32_t* si = a.sample_idx + ((size_t)f * a.H + h) * 4;
-                have = true;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) { idx[k] = si[k]; have = have && idx[k] >= 0 && idx[k] < P; }
-            } else {
-                have = sample4(a.seed_lo, a.seed_hi, a.frame0 + (uint32_t)f, (uint32_t)h, P, idx);
-            }
-            if (have) {
-                float x[4][3], uv[4][2];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    x[k][0] = X[idx[k]]; x[k][1] = Y[idx[k]]; x[k][2] = Z[idx[k]];
-                    uv[k][0] = U[idx[k]]; uv[k][1] = V[idx[k]];
-                }
-                float R[9], t[3];
-                valid = p3p::solve(x, uv, fx, fy, cx, cy, R, t);
-                if (valid) {
-                    make_proj(fx, fy, cx, cy, R, t, M);
-                    float* o = a.hypRt + ((size_t)f * a.H + h) * 12;
-#pragma unroll
-                    for (int k = 0; k < 9; ++k) o[k] = R[k];
-                    o[9] = t[0]; o[10] = t[1]; o[11] = t[2];
-                }
-            }
-        }
-#pragma unroll
-        for (int k = 0; k < 12; ++k) Msm[hl * 12 + k] = M[k];
-        cnt[hl] = valid ? 0 : -1;
-    }
-    __syncthreads();
-
-    // ---- K3: every correspondence against this thread's hypotheses
     const int PP = a.PP;                       // >1 only when Hs < PB_THREADS (then NHL == 1)
     const int part = (PP > 1) ? tid / Hs : 0;  // warp-uniform: Hs is a multiple of 32
+
+    // ---- this thread's hypotheses: K[R|t] in threshold units, 12 registers each
     float m[NHL][12];
     int c[NHL];
 #pragma unroll
     for (int j = 0; j < NHL; ++j) {
         const int hl = (PP > 1) ? (tid % Hs) : (tid + j * PB_THREADS);
+        const int h = h0 + hl;
         c[j] = 0;
+        bool valid = false;
+        if (h < a.H) {
+            const float4* o = reinterpret_cast<const float4*>(a.hypRt + ((size_t)f * a.H + h) * 12);
+            const float4 r0 = o[0], r1 = o[1], r2 = o[2];
+            valid = (r2.w == r2.w);
+            if (valid) {
+                const float R[9] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x};
+                const float t[3] = {r2.y, r2.z, r2.w};
+                make_proj_s(fx, fy, cx, cy, R, t, a.inv_thr, m[j]);
+            }
+        }
+        if (!valid) {
 #pragma unroll
-        for (int k = 0; k < 12; ++k) m[j][k] = Msm[hl * 12 + k];
+            for (int k = 0; k < 12; ++k) m[j][k] = 0.0f;
+            m[j][11] = -1.0f;  // w < 0 for every point: never an inlier
+        }
+        if (part == 0 && hl < Hs) cnt[hl] = valid ? 0 : -1;
     }
+
+    // ---- K3: every correspondence against this thread's hypotheses
+    const float inf = __int_as_float(0x7f800000);
     for (int c0 = 0; c0 < P; c0 += CH) {
         const int n = min(CH, P - c0);
-        if (c0 > 0) __syncthreads();           // previous chunk fully consumed
-        for (int i = tid; i < n; i += PB_THREADS) {
-            sp4[i] = make_float4(X[c0 + i], Y[c0 + i], Z[c0 + i], U[c0 + i]);
-            spv[i] = V[c0 + i];
+        const int npp = ((n + 8 * PP - 1) / (8 * PP)) * 8;   // points per partition, multiple of 8
+        __syncthreads();                                     // previous chunk consumed / cnt initialised
+        for (int i = tid; i < npp * PP; i += PB_THREADS) {
+            if (i < n) {
+                sp4[i] = make_float4(X[c0 + i], Y[c0 + i], Z[c0 + i], U[c0 + i] * a.inv_thr);
+                spv[i] = V[c0 + i] * a.inv_thr;
+            } else {                                         // sentinel: s = +inf or NaN, never an inlier
+                sp4[i] = make_float4(0.0f, 0.0f, 0.0f, inf);
+                spv[i] = inf;
+            }
         }
         __syncthreads();
-#pragma unroll 4
-        for (int i = part; i < n; i += PP) {
-            const float4 p = sp4[i];
-            const float pv = spv[i];
+        const float4* s4 = sp4 + part * npp;
+        const float4* sv = reinterpret_cast<const float4*>(spv + part * npp);
+#pragma unroll 1
+        for (int i = 0; i < npp; i += 8) {
+            const float4 v0 = sv[i >> 2], v1 = sv[(i >> 2) + 1];
+            const float vs[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+            uint32_t acc[NHL];
 #pragma unroll
-            for (int j = 0; j < NHL; ++j) c[j] += inlier_test(m[j], p.x, p.y, p.z, p.w, pv, a.thr2) ? 1 : 0;
+            for (int j = 0; j < NHL; ++j) acc[j] = 0u;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float4 p = s4[i + k];
+#pragma unroll
+                for (int j = 0; j < NHL; ++j)
+                    acc[j] = __funnelshift_l(__float_as_uint(inlier_s(m[j], p.x, p.y, p.z, p.w, vs[k])), acc[j], 1);
+            }
+#pragma unroll
+            for (int j = 0; j < NHL; ++j) c[j] += __popc(acc[j]);
         }
     }
+    if (P <= 0) __syncthreads();               // cnt initialised even when there was no chunk
 #pragma unroll
     for (int j = 0; j < NHL; ++j) {
         const int hl = (PP > 1) ? (tid % Hs) : (tid + j * PB_THREADS);
-        if (hl < Hs && cnt[hl] >= 0 && c[j] > 0) atomicAdd(&cnt[hl], c[j]);
+        if (hl < Hs && c[j] > 0) atomicAdd(&cnt[hl], c[j]);   // c > 0 only for valid hypotheses
     }
     __syncthreads();
 
@@ -150,6 +196,9 @@ int launch(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
 }  // namespace
 
 int pb_launch_score(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
+    const long long nh = (long long)F * a.H;
+    ransac_hypothesis_kernel<<<(unsigned)((nh + HT - 1) / HT), HT, 0, st>>>(a);
+    if (pb_check_launch("ransac_hypothesis_kernel")) return 1;
     switch (p.NHL) {
         case 1: return launch<1>(a, p, F, st);
         case 2: return launch<2>(a, p, F, st);

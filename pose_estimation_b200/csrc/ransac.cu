@@ -1,15 +1,16 @@
 // ransac.cu -- K1..K4: PnP-RANSAC on compacted correspondences (sm_100a).
 //
 // Replaces cv2.solvePnPRansac at tools/trainer.py:423-427 / lib/utils/utlis.py:59-63.
-//   ransac_score_kernel    one CTA per (frame, hypothesis slice):
-//       K1 Philox minimal-set sampling + K2 P3P solve, one hypothesis per thread;
-//       K3 reprojection scoring of EVERY correspondence: points staged in shared memory (SoA,
-//          conflict-free), lanes <-> points, NH hypotheses register-tiled per warp, per-lane
-//          counters + redux.sync; FP32-pipe bound (15 FMA-pipe ops per hypothesis*point).
-//   ransac_finalize_kernel one CTA per frame:
-//       K4 argmax over slices (lowest hypothesis index on ties), inlier bitmap by warp ballot,
-//          Gauss-Newton refit on the inliers with a fixed reduction tree (bit-reproducible on the
-//          CPU oracle), optional re-score -> refit rounds.
+//   ransac_hypothesis_kernel / ransac_score_kernel   K1-K3, see ransac_score.cu.
+//   K4 argmax over slices (lowest hypothesis index on ties), inlier bitmap by warp ballot,
+//      Gauss-Newton refit on the inliers, optional re-score -> refit rounds.  The refit's sums have
+//      ONE canonical order (256 virtual threads striding the points, xor-butterfly over each group
+//      of 32, groups added in order) that the CPU oracle reproduces bit for bit; two kernels
+//      realise it:
+//        ransac_finalize_kernel       one CTA (256 threads) per frame  -- few frames / many points
+//        ransac_finalize_warp_kernel  one WARP per frame (8 frames per CTA, no block barriers; the
+//                                     warp walks the 8 virtual groups, each reduced with a
+//                                     31-shuffle transpose-reduce) -- many frames (the eval sweep).
 #include "common.cuh"
 #include "ransac_plan.h"
 
@@ -49,36 +50,105 @@ __device__ __forceinline__ void block_tree_sum(float* v, float (*red)[28], float
 }
 
 __device__ __forceinline__ bool chol6_solve(const double A21[21], const double g[6], double d[6]) {
+    // every loop is fully unrolled (constant indices) so A/L stay in registers, no local memory
     double A[6][6], L[6][6];
     int k = 0;
+#pragma unroll
     for (int i = 0; i < 6; ++i)
+#pragma unroll
         for (int j = i; j < 6; ++j) { A[i][j] = A21[k]; A[j][i] = A21[k]; ++k; }
+#pragma unroll
     for (int i = 0; i < 6; ++i)
+#pragma unroll
         for (int j = 0; j < 6; ++j) L[i][j] = 0.0;
+    bool spd = true;
+#pragma unroll
     for (int j = 0; j < 6; ++j) {
         double s = A[j][j];
+#pragma unroll
         for (int m = 0; m < j; ++m) s = s - L[j][m] * L[j][m];
-        if (!(s > 0.0)) return false;
+        spd = spd && (s > 0.0);
         double ljj = sqrt(s);
         L[j][j] = ljj;
+#pragma unroll
         for (int i = j + 1; i < 6; ++i) {
             double v = A[i][j];
+#pragma unroll
             for (int m = 0; m < j; ++m) v = v - L[i][m] * L[j][m];
             L[i][j] = v / ljj;
         }
     }
+    if (!spd) return false;
     double z[6];
+#pragma unroll
     for (int i = 0; i < 6; ++i) {
         double v = g[i];
+#pragma unroll
         for (int m = 0; m < i; ++m) v = v - L[i][m] * z[m];
         z[i] = v / L[i][i];
     }
+#pragma unroll
     for (int i = 5; i >= 0; --i) {
         double v = z[i];
+#pragma unroll
         for (int m = i + 1; m < 6; ++m) v = v - L[m][i] * d[m];
         d[i] = v / L[i][i];
     }
     return true;
+}
+
+// one inlier's contribution to the normal equations (21 upper-triangle terms of J^T J, 6 of J^T r)
+__device__ __forceinline__ void gn_accumulate(float* acc, const float R[9], const float cb[3], const float tc[3],
+                                              float fx, float fy, float cx, float cy, float Xi, float Yi, float Zi,
+                                              float Ui, float Vi) {
+    float xo = Xi - cb[0], yo = Yi - cb[1], zo = Zi - cb[2];
+    float xr = fmaf(R[0], xo, fmaf(R[1], yo, R[2] * zo));
+    float yr = fmaf(R[3], xo, fmaf(R[4], yo, R[5] * zo));
+    float zr = fmaf(R[6], xo, fmaf(R[7], yo, R[8] * zo));
+    float xc = xr + tc[0], yc = yr + tc[1], zc = zr + tc[2];
+    float iz = 1.0f / zc;
+    float un = xc * iz, vn = yc * iz;
+    float ru = fmaf(fx, un, cx) - Ui;
+    float rv = fmaf(fy, vn, cy) - Vi;
+    float ja = fx * iz, jb = fy * iz;
+    float jc = -(ja * un), jd = -(jb * vn);
+    float ju[6] = {yr * jc, fmaf(zr, ja, -(xr * jc)), -(yr * ja), ja, 0.0f, jc};
+    float jv[6] = {fmaf(yr, jd, -(zr * jb)), -(xr * jd), xr * jb, 0.0f, jb, jd};
+    int k = 0;
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int s2 = r; s2 < 6; ++s2) { acc[k] = fmaf(ju[r], ju[s2], fmaf(jv[r], jv[s2], acc[k])); ++k; }
+#pragma unroll
+    for (int r = 0; r < 6; ++r) acc[21 + r] = fmaf(ju[r], ru, fmaf(jv[r], rv, acc[21 + r]));
+}
+
+// solve the 6x6 normal equations (FP64 Cholesky) -> FP32 step; false if not SPD / not finite
+__device__ __forceinline__ bool gn_solve(const float* tot, float dl[6]) {
+    double A21[21], g[6], d[6];
+#pragma unroll
+    for (int k = 0; k < 21; ++k) A21[k] = (double)tot[k];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) g[k] = -(double)tot[21 + k];
+    bool ok = chol6_solve(A21, g, d);
+    if (ok) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) { dl[k] = (float)d[k]; ok = ok && isfinite(dl[k]); }
+    }
+    return ok;
+}
+
+// q <- normalise(q + 0.5 * (0, d_rot) * q), tc += d_trans
+__device__ __forceinline__ void gn_apply(float q[4], float tc[3], const float dl[6]) {
+    const float hx = 0.5f * dl[0], hy = 0.5f * dl[1], hz = 0.5f * dl[2];
+    const float w0 = q[0], x0 = q[1], y0 = q[2], z0 = q[3];
+    float nw = w0 - fmaf(hx, x0, fmaf(hy, y0, hz * z0));
+    float nx = x0 + fmaf(hx, w0, fmaf(hy, z0, -(hz * y0)));
+    float ny = y0 + fmaf(hy, w0, fmaf(hz, x0, -(hx * z0)));
+    float nz = z0 + fmaf(hz, w0, fmaf(hx, y0, -(hy * x0)));
+    float in = 1.0f / sqrtf(fmaf(nw, nw, fmaf(nx, nx, fmaf(ny, ny, nz * nz))));
+    q[0] = nw * in; q[1] = nx * in; q[2] = ny * in; q[3] = nz * in;
+    tc[0] += dl[3]; tc[1] += dl[4]; tc[2] += dl[5];
 }
 
 __global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a) {
@@ -175,51 +245,20 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a
                 for (int k = 0; k < 27; ++k) acc[k] = 0.0f;
                 for (int i = tid; i < P; i += PB_THREADS) {
                     if (!((bm[i >> 5] >> (i & 31)) & 1u)) continue;
-                    float xo = X[i] - cb[0], yo = Y[i] - cb[1], zo = Z[i] - cb[2];
-                    float xr = fmaf(R[0], xo, fmaf(R[1], yo, R[2] * zo));
-                    float yr = fmaf(R[3], xo, fmaf(R[4], yo, R[5] * zo));
-                    float zr = fmaf(R[6], xo, fmaf(R[7], yo, R[8] * zo));
-                    float xc = xr + tc[0], yc = yr + tc[1], zc = zr + tc[2];
-                    float iz = 1.0f / zc;
-                    float un = xc * iz, vn = yc * iz;
-                    float ru = fmaf(fx, un, cx) - U[i];
-                    float rv = fmaf(fy, vn, cy) - V[i];
-                    float ja = fx * iz, jb = fy * iz;
-                    float jc = -(ja * un), jd = -(jb * vn);
-                    float ju[6] = {yr * jc, fmaf(zr, ja, -(xr * jc)), -(yr * ja), ja, 0.0f, jc};
-                    float jv[6] = {fmaf(yr, jd, -(zr * jb)), -(xr * jd), xr * jb, 0.0f, jb, jd};
-                    int k = 0;
-#pragma unroll
-                    for (int r = 0; r < 6; ++r)
-#pragma unroll
-                        for (int s2 = r; s2 < 6; ++s2) { acc[k] = fmaf(ju[r], ju[s2], fmaf(jv[r], jv[s2], acc[k])); ++k; }
-#pragma unroll
-                    for (int r = 0; r < 6; ++r) acc[21 + r] = fmaf(ju[r], ru, fmaf(jv[r], rv, acc[21 + r]));
+                    gn_accumulate(acc, R, cb, tc, fx, fy, cx, cy, X[i], Y[i], Z[i], U[i], V[i]);
                 }
                 block_tree_sum<27>(acc, red, tot, tid);
                 if (tid == 0) {
-                    double A21[21], g[6], d[6];
-                    for (int k = 0; k < 21; ++k) A21[k] = (double)tot[k];
-                    for (int k = 0; k < 6; ++k) g[k] = -(double)tot[21 + k];
-                    bool ok = chol6_solve(A21, g, d);
                     float dl[6];
-                    if (ok)
-                        for (int k = 0; k < 6; ++k) { dl[k] = (float)d[k]; ok = ok && isfinite(dl[k]); }
+                    const bool ok = gn_solve(tot, dl);
                     if (ok)
                         for (int k = 0; k < 6; ++k) sdelta[k] = dl[k];
                     sflag = ok ? 1 : 0;
                 }
                 __syncthreads();
                 if (!sflag) break;  // uniform
-                const float hx = 0.5f * sdelta[0], hy = 0.5f * sdelta[1], hz = 0.5f * sdelta[2];
-                const float w0 = q[0], x0 = q[1], y0 = q[2], z0 = q[3];
-                float nw = w0 - fmaf(hx, x0, fmaf(hy, y0, hz * z0));
-                float nx = x0 + fmaf(hx, w0, fmaf(hy, z0, -(hz * y0)));
-                float ny = y0 + fmaf(hy, w0, fmaf(hz, x0, -(hx * z0)));
-                float nz = z0 + fmaf(hz, w0, fmaf(hx, y0, -(hy * x0)));
-                float in = 1.0f / sqrtf(fmaf(nw, nw, fmaf(nx, nx, fmaf(ny, ny, nz * nz))));
-                q[0] = nw * in; q[1] = nx * in; q[2] = ny * in; q[3] = nz * in;
-                tc[0] += sdelta[3]; tc[1] += sdelta[4]; tc[2] += sdelta[5];
+                const float dl[6] = {sdelta[0], sdelta[1], sdelta[2], sdelta[3], sdelta[4], sdelta[5]};
+                gn_apply(q, tc, dl);
             }
             quat_to_rot(q, R);
 #pragma unroll
@@ -253,6 +292,161 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a
     if (tid < 9) a.R[9 * f + tid] = R[tid];
     if (tid < 3) a.t[3 * f + tid] = tt[tid];
     if (tid == 0) { a.n_inl[f] = bc; a.best_hyp[f] = bh; a.n_inl_refined[f] = nref; a.status[f] = PB_STATUS_OK; }
+}
+
+// ------------------------------------------------------------------------------------------
+// Warp-per-frame K4.  Same arithmetic and the same summation order as ransac_finalize_kernel: the
+// warp plays the CTA's 8 warps ("virtual groups") one after the other.  A 32-value transpose-
+// reduce (16+8+4+2+1 shuffles; lane k ends with the butterfly sum of value k) replaces 27 separate
+// butterflies; float add is commutative, so every partial sum is bit-identical to the butterfly's.
+constexpr int FW = 8;  // frames (warps) per CTA
+
+__device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+        const bool up = (lane & half) != 0;
+#pragma unroll
+        for (int k = 0; k < half; ++k) {
+            const float send = up ? v[k] : v[k + half];
+            const float keep = up ? v[k + half] : v[k];
+            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+        }
+    }
+    return v[0];
+}
+
+__global__ void __launch_bounds__(32 * FW) ransac_finalize_warp_kernel(FinalArgs a, int F) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int f = blockIdx.x * FW + warp;
+    if (f >= F) return;                              // whole warp; no block-level barrier below
+    const int words = (a.cap + 31) / 32;
+    uint32_t* bm = reinterpret_cast<uint32_t*>(smem_raw) + (size_t)warp * words;
+    const int P = min(a.count[f], a.cap);
+    const float* X = a.pts + (size_t)f * 5 * a.cap;
+    const float* Y = X + a.cap;
+    const float* Z = Y + a.cap;
+    const float* U = Z + a.cap;
+    const float* V = U + a.cap;
+    const float fx = a.K4[4 * f], fy = a.K4[4 * f + 1], cx = a.K4[4 * f + 2], cy = a.K4[4 * f + 3];
+
+    unsigned long long key = a.slice_best[(size_t)f * a.HS];
+    for (int s = 1; s < a.HS; ++s) {
+        unsigned long long k = a.slice_best[(size_t)f * a.HS + s];
+        key = k > key ? k : key;
+    }
+    const int bc = (int)(uint32_t)(key >> 32) - 1;
+    const int bh = (int)(0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull));
+    const bool fail_pts = P < 4;
+    const bool fail_model = !fail_pts && (bc < 0 || bc < a.min_inliers);
+    if (fail_pts || fail_model) {
+        if (lane < 9) {
+            float v = (lane % 4 == 0) ? 1.0f : 0.0f;
+            a.R[9 * f + lane] = v;
+            if (a.R0) a.R0[9 * f + lane] = v;
+        }
+        if (lane < 3) { a.t[3 * f + lane] = 0.0f; if (a.t0) a.t0[3 * f + lane] = 0.0f; }
+        if (lane == 0) {
+            a.n_inl[f] = 0; a.best_hyp[f] = -1; a.n_inl_refined[f] = 0;
+            a.status[f] = fail_pts ? PB_STATUS_TOO_FEW_POINTS : PB_STATUS_NO_MODEL;
+        }
+        if (a.inl_bitmap)
+            for (int w = lane; w < words; w += 32) a.inl_bitmap[(size_t)f * words + w] = 0u;
+        return;
+    }
+    float Rb[9], tb[3];
+    {
+        const float* o = a.hypRt + ((size_t)f * a.H + bh) * 12;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) Rb[k] = o[k];
+        tb[0] = o[9]; tb[1] = o[10]; tb[2] = o[11];
+    }
+    if (lane < 9 && a.R0) a.R0[9 * f + lane] = Rb[lane];
+    if (lane < 3 && a.t0) a.t0[3 * f + lane] = tb[lane];
+    float q[4], tt[3] = {tb[0], tb[1], tb[2]};
+    rot_to_quat(Rb, q);
+    float M[12];
+    make_proj_s(fx, fy, cx, cy, Rb, tb, a.inv_thr, M);
+    int nref = bc;
+    const int pwords = (P + 31) / 32;
+    for (int round = -1; round <= a.lo_rounds; ++round) {
+        bool stop = false;
+        if (round >= 0) {
+            // ---- centroid of the inlier object points (canonical order: 8 virtual groups)
+            float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
+            int cn = 0;
+#pragma unroll 1
+            for (int vw = 0; vw < PB_THREADS / 32; ++vw) {
+                float cs[3] = {0.0f, 0.0f, 0.0f};
+                for (int i = vw * 32 + lane; i < P; i += PB_THREADS)
+                    if ((bm[i >> 5] >> (i & 31)) & 1u) { cs[0] += X[i]; cs[1] += Y[i]; cs[2] += Z[i]; ++cn; }
+#pragma unroll
+                for (int k = 0; k < 3; ++k) cs[k] = warp_sum_bfly(cs[k]);
+                if (vw == 0) { c0 = cs[0]; c1 = cs[1]; c2 = cs[2]; }
+                else { c0 = c0 + cs[0]; c1 = c1 + cs[1]; c2 = c2 + cs[2]; }
+            }
+            const int cnt_all = __reduce_add_sync(0xffffffffu, cn);
+            if (cnt_all < 4) break;  // warp-uniform
+            const float fn = (float)cnt_all;
+            const float cb[3] = {c0 / fn, c1 / fn, c2 / fn};
+            float R[9];
+            quat_to_rot(q, R);
+            float tc[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+                tc[i] = fmaf(R[3 * i], cb[0], fmaf(R[3 * i + 1], cb[1], fmaf(R[3 * i + 2], cb[2], tt[i])));
+            for (int it = 0; it < a.gn_iters; ++it) {
+                quat_to_rot(q, R);
+                float totl = 0.0f;                   // lane k: running sum of normal-equation term k
+#pragma unroll 1
+                for (int vw = 0; vw < PB_THREADS / 32; ++vw) {
+                    float acc[32];
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) acc[k] = 0.0f;
+                    for (int i = vw * 32 + lane; i < P; i += PB_THREADS) {
+                        if (!((bm[i >> 5] >> (i & 31)) & 1u)) continue;
+                        gn_accumulate(acc, R, cb, tc, fx, fy, cx, cy, X[i], Y[i], Z[i], U[i], V[i]);
+                    }
+                    const float v = warp_transpose_reduce32(acc, lane);
+                    totl = (vw == 0) ? v : totl + v;
+                }
+                float tot[27];
+#pragma unroll
+                for (int k = 0; k < 27; ++k) tot[k] = __shfl_sync(0xffffffffu, totl, k);
+                float dl[6];
+                if (!gn_solve(tot, dl)) { stop = true; break; }   // every lane holds the same tot: uniform
+                gn_apply(q, tc, dl);
+            }
+            (void)stop;
+            quat_to_rot(q, R);
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+                tt[i] = tc[i] - fmaf(R[3 * i], cb[0], fmaf(R[3 * i + 1], cb[1], R[3 * i + 2] * cb[2]));
+            make_proj_s(fx, fy, cx, cy, R, tt, a.inv_thr, M);
+        }
+        // ---- (re-)score: inlier bitmap by warp ballot
+        __syncwarp();
+        int cn = 0;
+        for (int base = 0; base < P; base += 32) {
+            const int i = base + lane;
+            bool in = i < P && inlier_test(M, X[i], Y[i], Z[i], U[i] * a.inv_thr, V[i] * a.inv_thr);
+            unsigned b = __ballot_sync(0xffffffffu, in);
+            if (lane == 0) bm[base >> 5] = b;
+            cn += __popc(b);
+        }
+        __syncwarp();
+        if (round < 0) {
+            if (a.inl_bitmap)
+                for (int w = lane; w < words; w += 32) a.inl_bitmap[(size_t)f * words + w] = w < pwords ? bm[w] : 0u;
+        } else {
+            nref = cn;
+        }
+    }
+    float R[9];
+    quat_to_rot(q, R);
+    if (lane < 9) a.R[9 * f + lane] = R[lane];
+    if (lane < 3) a.t[3 * f + lane] = tt[lane];
+    if (lane == 0) { a.n_inl[f] = bc; a.best_hyp[f] = bh; a.n_inl_refined[f] = nref; a.status[f] = PB_STATUS_OK; }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -329,9 +523,16 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     fa.status = status; fa.inl_bitmap = inl_bitmap; fa.R0 = R0; fa.t0 = t0;
     fa.cap = cap; fa.H = prm->n_hyp; fa.HS = p.HS; fa.gn_iters = prm->gn_iters; fa.lo_rounds = prm->lo_rounds;
     fa.min_inliers = prm->min_inliers; fa.inv_thr = sa.inv_thr;
-    cudaFuncSetAttribute(ransac_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_final);
-    ransac_finalize_kernel<<<F, PB_THREADS, p.smem_final, st>>>(fa);
-    if (pb_check_launch("ransac_finalize_kernel")) return -2;
+    // many frames of moderate size: one warp per frame; otherwise one CTA per frame (same results)
+    const size_t smem_warp = (size_t)FW * ((cap + 31) / 32) * sizeof(uint32_t);
+    if (F >= 4 * 148 && smem_warp <= 48 * 1024) {
+        ransac_finalize_warp_kernel<<<(F + FW - 1) / FW, 32 * FW, smem_warp, st>>>(fa, F);
+        if (pb_check_launch("ransac_finalize_warp_kernel")) return -2;
+    } else {
+        cudaFuncSetAttribute(ransac_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_final);
+        ransac_finalize_kernel<<<F, PB_THREADS, p.smem_final, st>>>(fa);
+        if (pb_check_launch("ransac_finalize_kernel")) return -2;
+    }
     return 0;
 }
 

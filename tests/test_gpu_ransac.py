@@ -130,6 +130,23 @@ def test_ransac_bit_exact_vs_oracle(cref, dev, n_hyp, F, lo):
     _check_ransac(cref, dev, sps[:F] if F <= 12 else sps, cfg, cap=1280, frame0=7)
 
 
+@pytest.mark.parametrize("lo", [0, 2])
+def test_ransac_warp_per_frame_finalize_matches_oracle_and_cta_path(cref, dev, lo):
+    """F >= 592 frames take the warp-per-frame K4 kernel; fewer take the CTA-per-frame one.  Both
+    must agree with the oracle (integers bit-exact) and with EACH OTHER bit for bit (R, t included):
+    results may not depend on launch geometry."""
+    F = 640
+    base = synth.make_batch_sparse(0x5EED, 2, 16)
+    base[3] = dict(base[3]); base[3]["rows"] = base[3]["rows"][:3]; base[3]["cols"] = base[3]["cols"][:3]
+    base[3]["xyzn"] = base[3]["xyzn"][:3]                          # a too-few-points frame in the mix
+    sps = (base * (F // 16))[:F]
+    cfg = ops.RansacConfig(n_hyp=64, lo_rounds=lo)
+    big = _check_ransac(cref, dev, sps, cfg, cap=1280, frame0=11)
+    small = _check_ransac(cref, dev, sps[:40], cfg, cap=1280, frame0=11)
+    for k in ("R", "t", "n_inl_refined", "status", "best_hyp", "inl_bitmap"):
+        assert np.array_equal(big[k][:40], small[k]), k
+
+
 def test_ransac_forced_minimal_sets_and_large_P(cref, dev):
     sps = synth.make_batch_sparse(0x5EED, 4, 2, p_range=(5000, 6000), outlier_frac=0.3)
     cap = 6144

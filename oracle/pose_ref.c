@@ -429,23 +429,23 @@ static int chol6_solve(const double A21[21], const double g[6], double d[6]) {
         for (int m = 0; m < j; ++m) s = s - L[j][m] * L[j][m];
         if (!(s > 0.0)) return 0;
         double ljj = sqrt(s);
-        L[j][j] = ljj;
+        L[j][j] = 1.0 / ljj;    /* the diagonal holds the RECIPROCAL (one division per column) */
         for (int i = j + 1; i < 6; ++i) {
             double v = A[i][j];
             for (int m = 0; m < j; ++m) v = v - L[i][m] * L[j][m];
-            L[i][j] = v / ljj;
+            L[i][j] = v * L[j][j];
         }
     }
     double z[6];
     for (int i = 0; i < 6; ++i) {
         double v = g[i];
         for (int m = 0; m < i; ++m) v = v - L[i][m] * z[m];
-        z[i] = v / L[i][i];
+        z[i] = v * L[i][i];
     }
     for (int i = 5; i >= 0; --i) {
         double v = z[i];
         for (int m = i + 1; m < 6; ++m) v = v - L[m][i] * d[m];
-        d[i] = v / L[i][i];
+        d[i] = v * L[i][i];
     }
     return 1;
 }

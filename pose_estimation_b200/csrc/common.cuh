@@ -83,7 +83,7 @@ __device__ __forceinline__ void make_proj_s(float fx, float fy, float cx, float 
 //   s = (x - us w)^2 + (y - vs w)^2 - w|w|,  (us,vs) = (u,v)*inv_thr;   inlier <=> s < 0.
 // w <= 0 gives -w|w| >= 0, so points behind the camera never pass; NaN never passes (the GPU's
 // canonical NaN has a clear sign bit).  14 FMA-pipe instructions; the sign bit of s is the verdict.
-// Operation order is a contract with oracle/pose_ref.c::inlier_test (bit-exact inlier sets).
+// Operation order is a contract with the CPU oracle (its inlier_test): bit-exact inlier sets.
 __device__ __forceinline__ float inlier_s(const float M[12], float X, float Y, float Z, float us, float vs) {
     const float x = fmaf(M[0], X, fmaf(M[1], Y, fmaf(M[2], Z, M[3])));
     const float y = fmaf(M[4], X, fmaf(M[5], Y, fmaf(M[6], Z, M[7])));

@@ -5,12 +5,9 @@
 //   K4 argmax over slices (lowest hypothesis index on ties), inlier bitmap by warp ballot,
 //      Gauss-Newton refit on the inliers, optional re-score -> refit rounds.  The refit's sums have
 //      ONE canonical order (256 virtual threads striding the points, xor-butterfly over each group
-//      of 32, groups added in order) that the CPU oracle reproduces bit for bit; two kernels
-//      realise it:
-//        ransac_finalize_kernel       one CTA (256 threads) per frame  -- few frames / many points
-//        ransac_finalize_warp_kernel  one WARP per frame (8 frames per CTA, no block barriers; the
-//                                     warp walks the 8 virtual groups, each reduced with a
-//                                     31-shuffle transpose-reduce) -- many frames (the eval sweep).
+//      of 32, groups added in order) that the CPU oracle reproduces bit for bit;
+//      ransac_finalize_kernel<G> realises it with G = 1, 2, 4 or 8 warps per frame (one CTA per
+//      frame), G chosen from the frame count so that enough warps are in flight.
 #include "common.cuh"
 #include "ransac_plan.h"
 
@@ -28,26 +25,6 @@ struct FinalArgs {
     int cap, H, HS, gn_iters, lo_rounds, min_inliers;
     float inv_thr;
 };
-
-// fixed-shape block sum of K floats per thread: butterfly inside each warp, then warps in order.
-template <int K>
-__device__ __forceinline__ void block_tree_sum(float* v, float (*red)[28], float* tot, int tid) {
-    const int lane = tid & 31, warp = tid >> 5;
-#pragma unroll
-    for (int k = 0; k < K; ++k) v[k] = warp_sum_bfly(v[k]);
-    __syncthreads();  // previous readers of red/tot are done
-    if (lane == 0) {
-#pragma unroll
-        for (int k = 0; k < K; ++k) red[warp][k] = v[k];
-    }
-    __syncthreads();
-    if (tid < K) {
-        float s = red[0][tid];
-        for (int w = 1; w < PB_THREADS / 32; ++w) s = s + red[w][tid];
-        tot[tid] = s;
-    }
-    __syncthreads();
-}
 
 __device__ __forceinline__ bool chol6_solve(const double A21[21], const double g[6], double d[6]) {
     // every loop is fully unrolled (constant indices) so A/L stay in registers, no local memory
@@ -69,13 +46,13 @@ __device__ __forceinline__ bool chol6_solve(const double A21[21], const double g
         for (int m = 0; m < j; ++m) s = s - L[j][m] * L[j][m];
         spd = spd && (s > 0.0);
         double ljj = sqrt(s);
-        L[j][j] = ljj;
+        L[j][j] = 1.0 / ljj;    // the diagonal holds the RECIPROCAL (one division per column)
 #pragma unroll
         for (int i = j + 1; i < 6; ++i) {
             double v = A[i][j];
 #pragma unroll
             for (int m = 0; m < j; ++m) v = v - L[i][m] * L[j][m];
-            L[i][j] = v / ljj;
+            L[i][j] = v * L[j][j];
         }
     }
     if (!spd) return false;
@@ -85,14 +62,14 @@ __device__ __forceinline__ bool chol6_solve(const double A21[21], const double g
         double v = g[i];
 #pragma unroll
         for (int m = 0; m < i; ++m) v = v - L[i][m] * z[m];
-        z[i] = v / L[i][i];
+        z[i] = v * L[i][i];
     }
 #pragma unroll
     for (int i = 5; i >= 0; --i) {
         double v = z[i];
 #pragma unroll
         for (int m = i + 1; m < 6; ++m) v = v - L[m][i] * d[m];
-        d[i] = v / L[i][i];
+        d[i] = v * L[i][i];
     }
     return true;
 }
@@ -151,16 +128,39 @@ __device__ __forceinline__ void gn_apply(float q[4], float tc[3], const float dl
     tc[0] += dl[3]; tc[1] += dl[4]; tc[2] += dl[5];
 }
 
-__global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint32_t* bm = reinterpret_cast<uint32_t*>(smem_raw);  // [ceil(cap/32)]
-    __shared__ float red[PB_THREADS / 32][28];
-    __shared__ float tot[28];
-    __shared__ int ired[PB_THREADS / 32];
-    __shared__ float sdelta[8];
-    __shared__ int sflag;
+// 32-value transpose-reduce: lane k ends with the xor-butterfly sum (offsets 16,8,4,2,1) of value
+// k over the warp.  16+8+4+2+1 shuffles instead of 27 separate butterflies; float add is
+// commutative, so every partial sum has the butterfly's bits.
+__device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+        const bool up = (lane & half) != 0;
+#pragma unroll
+        for (int k = 0; k < half; ++k) {
+            const float send = up ? v[k] : v[k + half];
+            const float keep = up ? v[k + half] : v[k];
+            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+        }
+    }
+    return v[0];
+}
 
-    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+constexpr int NVG = PB_THREADS / 32;  // virtual groups of the canonical summation order
+
+// K4, one CTA of G warps per frame (G = 1, 2, 4, 8).  The refit's sums have ONE canonical order --
+// 256 virtual threads stride the points, each group of 32 is xor-butterfly reduced, the 8 group
+// sums are added in order -- whatever G is: warp w plays groups w, w+G, ...; the per-group sums
+// meet in shared memory and every thread adds them in group order, then solves the 6x6 system
+// redundantly (no broadcast).  So results do not depend on G, and the CPU oracle reproduces them.
+template <int G>
+__global__ void __launch_bounds__(32 * G) ransac_finalize_kernel(FinalArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* bm = reinterpret_cast<uint32_t*>(smem_raw);  // [ceil(cap/256)*8] inlier bitmap
+    __shared__ float red[2][NVG][32];
+    __shared__ int ired[NVG];
+    constexpr int NT = 32 * G;
+
+    const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int P = min(a.count[f], a.cap);
     const int words = (a.cap + 31) / 32;
     const float* X = a.pts + (size_t)f * 5 * a.cap;
@@ -181,10 +181,10 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a
     const bool fail_pts = P < 4;
     const bool fail_model = !fail_pts && (bc < 0 || bc < a.min_inliers);
     if (fail_pts || fail_model) {
-        if (tid < 9) {
-            float v = (tid % 4 == 0) ? 1.0f : 0.0f;
-            a.R[9 * f + tid] = v;
-            if (a.R0) a.R0[9 * f + tid] = v;
+        for (int k = tid; k < 9; k += NT) {
+            float v = (k % 4 == 0) ? 1.0f : 0.0f;
+            a.R[9 * f + k] = v;
+            if (a.R0) a.R0[9 * f + k] = v;
         }
         if (tid < 3) { a.t[3 * f + tid] = 0.0f; if (a.t0) a.t0[3 * f + tid] = 0.0f; }
         if (tid == 0) {
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a
             a.status[f] = fail_pts ? PB_STATUS_TOO_FEW_POINTS : PB_STATUS_NO_MODEL;
         }
         if (a.inl_bitmap)
-            for (int w = tid; w < words; w += PB_THREADS) a.inl_bitmap[(size_t)f * words + w] = 0u;
+            for (int w = tid; w < words; w += NT) a.inl_bitmap[(size_t)f * words + w] = 0u;
         return;
     }
 
@@ -212,25 +212,37 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a
     make_proj_s(fx, fy, cx, cy, Rb, tb, a.inv_thr, M);
 
     int nref = bc;
-    for (int w = tid; w < (a.cap + PB_THREADS - 1) / PB_THREADS * (PB_THREADS / 32); w += PB_THREADS) bm[w] = 0u;
-    __syncthreads();
     // round -1: bitmap of the best minimal hypothesis; rounds 0..lo_rounds: refit then re-score
     for (int round = -1; round <= a.lo_rounds; ++round) {
         if (round >= 0) {
             // ---- centroid of the inlier object points
-            float cs[3] = {0.0f, 0.0f, 0.0f};
             int cn = 0;
-            for (int i = tid; i < P; i += PB_THREADS)
-                if ((bm[i >> 5] >> (i & 31)) & 1u) { cs[0] += X[i]; cs[1] += Y[i]; cs[2] += Z[i]; ++cn; }
+            for (int vw = wid; vw < NVG; vw += G) {
+                float cs[3] = {0.0f, 0.0f, 0.0f};
+                for (int i = vw * 32 + lane; i < P; i += PB_THREADS)
+                    if ((bm[i >> 5] >> (i & 31)) & 1u) { cs[0] += X[i]; cs[1] += Y[i]; cs[2] += Z[i]; ++cn; }
+#pragma unroll
+                for (int k = 0; k < 3; ++k) cs[k] = warp_sum_bfly(cs[k]);
+                if (lane < 3) red[0][vw][lane] = lane == 0 ? cs[0] : (lane == 1 ? cs[1] : cs[2]);
+            }
             cn = __reduce_add_sync(0xffffffffu, cn);
-            block_tree_sum<3>(cs, red, tot, tid);
-            if (lane == 0) ired[warp] = cn;
+            if (lane == 0) ired[wid] = cn;
             __syncthreads();
+            float cb[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                float sacc = red[0][0][k];
+#pragma unroll
+                for (int vw = 1; vw < NVG; ++vw) sacc = sacc + red[0][vw][k];
+                cb[k] = sacc;
+            }
             int cnt_all = 0;
-            for (int w = 0; w < PB_THREADS / 32; ++w) cnt_all += ired[w];
+#pragma unroll
+            for (int w = 0; w < G; ++w) cnt_all += ired[w];
+            __syncthreads();         // red / ired may be rewritten
             if (cnt_all < 4) break;  // uniform
             const float fn = (float)cnt_all;
-            const float cb[3] = {tot[0] / fn, tot[1] / fn, tot[2] / fn};
+            cb[0] = cb[0] / fn; cb[1] = cb[1] / fn; cb[2] = cb[2] / fn;
             float R[9];
             quat_to_rot(q, R);
             float tc[3];
@@ -240,166 +252,9 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_finalize_kernel(FinalArgs a
             // ---- Gauss-Newton on the reprojection error of the inliers
             for (int it = 0; it < a.gn_iters; ++it) {
                 quat_to_rot(q, R);
-                float acc[27];
-#pragma unroll
-                for (int k = 0; k < 27; ++k) acc[k] = 0.0f;
-                for (int i = tid; i < P; i += PB_THREADS) {
-                    if (!((bm[i >> 5] >> (i & 31)) & 1u)) continue;
-                    gn_accumulate(acc, R, cb, tc, fx, fy, cx, cy, X[i], Y[i], Z[i], U[i], V[i]);
-                }
-                block_tree_sum<27>(acc, red, tot, tid);
-                if (tid == 0) {
-                    float dl[6];
-                    const bool ok = gn_solve(tot, dl);
-                    if (ok)
-                        for (int k = 0; k < 6; ++k) sdelta[k] = dl[k];
-                    sflag = ok ? 1 : 0;
-                }
-                __syncthreads();
-                if (!sflag) break;  // uniform
-                const float dl[6] = {sdelta[0], sdelta[1], sdelta[2], sdelta[3], sdelta[4], sdelta[5]};
-                gn_apply(q, tc, dl);
-            }
-            quat_to_rot(q, R);
-#pragma unroll
-            for (int i = 0; i < 3; ++i)
-                tt[i] = tc[i] - fmaf(R[3 * i], cb[0], fmaf(R[3 * i + 1], cb[1], R[3 * i + 2] * cb[2]));
-            make_proj_s(fx, fy, cx, cy, R, tt, a.inv_thr, M);
-        }
-        // ---- (re-)score: inlier bitmap by warp ballot
-        __syncthreads();
-        int cn = 0;
-        for (int base = 0; base < P; base += PB_THREADS) {
-            const int i = base + tid;
-            bool in = i < P && inlier_test(M, X[i], Y[i], Z[i], U[i] * a.inv_thr, V[i] * a.inv_thr);
-            unsigned b = __ballot_sync(0xffffffffu, in);
-            if (lane == 0) { bm[(base >> 5) + warp] = b; cn += __popc(b); }
-        }
-        if (lane == 0) ired[warp] = cn;
-        __syncthreads();
-        int tot_in = 0;
-        for (int w = 0; w < PB_THREADS / 32; ++w) tot_in += ired[w];
-        if (round < 0) {
-            if (a.inl_bitmap)
-                for (int w = tid; w < words; w += PB_THREADS) a.inl_bitmap[(size_t)f * words + w] = bm[w];
-        } else {
-            nref = tot_in;
-        }
-        __syncthreads();
-    }
-    float R[9];
-    quat_to_rot(q, R);
-    if (tid < 9) a.R[9 * f + tid] = R[tid];
-    if (tid < 3) a.t[3 * f + tid] = tt[tid];
-    if (tid == 0) { a.n_inl[f] = bc; a.best_hyp[f] = bh; a.n_inl_refined[f] = nref; a.status[f] = PB_STATUS_OK; }
-}
-
-// ------------------------------------------------------------------------------------------
-// Warp-per-frame K4.  Same arithmetic and the same summation order as ransac_finalize_kernel: the
-// warp plays the CTA's 8 warps ("virtual groups") one after the other.  A 32-value transpose-
-// reduce (16+8+4+2+1 shuffles; lane k ends with the butterfly sum of value k) replaces 27 separate
-// butterflies; float add is commutative, so every partial sum is bit-identical to the butterfly's.
-constexpr int FW = 8;  // frames (warps) per CTA
-
-__device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {
-#pragma unroll
-    for (int half = 16; half >= 1; half >>= 1) {
-        const bool up = (lane & half) != 0;
-#pragma unroll
-        for (int k = 0; k < half; ++k) {
-            const float send = up ? v[k] : v[k + half];
-            const float keep = up ? v[k + half] : v[k];
-            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, half);
-        }
-    }
-    return v[0];
-}
-
-__global__ void __launch_bounds__(32 * FW) ransac_finalize_warp_kernel(FinalArgs a, int F) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int f = blockIdx.x * FW + warp;
-    if (f >= F) return;                              // whole warp; no block-level barrier below
-    const int words = (a.cap + 31) / 32;
-    uint32_t* bm = reinterpret_cast<uint32_t*>(smem_raw) + (size_t)warp * words;
-    const int P = min(a.count[f], a.cap);
-    const float* X = a.pts + (size_t)f * 5 * a.cap;
-    const float* Y = X + a.cap;
-    const float* Z = Y + a.cap;
-    const float* U = Z + a.cap;
-    const float* V = U + a.cap;
-    const float fx = a.K4[4 * f], fy = a.K4[4 * f + 1], cx = a.K4[4 * f + 2], cy = a.K4[4 * f + 3];
-
-    unsigned long long key = a.slice_best[(size_t)f * a.HS];
-    for (int s = 1; s < a.HS; ++s) {
-        unsigned long long k = a.slice_best[(size_t)f * a.HS + s];
-        key = k > key ? k : key;
-    }
-    const int bc = (int)(uint32_t)(key >> 32) - 1;
-    const int bh = (int)(0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull));
-    const bool fail_pts = P < 4;
-    const bool fail_model = !fail_pts && (bc < 0 || bc < a.min_inliers);
-    if (fail_pts || fail_model) {
-        if (lane < 9) {
-            float v = (lane % 4 == 0) ? 1.0f : 0.0f;
-            a.R[9 * f + lane] = v;
-            if (a.R0) a.R0[9 * f + lane] = v;
-        }
-        if (lane < 3) { a.t[3 * f + lane] = 0.0f; if (a.t0) a.t0[3 * f + lane] = 0.0f; }
-        if (lane == 0) {
-            a.n_inl[f] = 0; a.best_hyp[f] = -1; a.n_inl_refined[f] = 0;
-            a.status[f] = fail_pts ? PB_STATUS_TOO_FEW_POINTS : PB_STATUS_NO_MODEL;
-        }
-        if (a.inl_bitmap)
-            for (int w = lane; w < words; w += 32) a.inl_bitmap[(size_t)f * words + w] = 0u;
-        return;
-    }
-    float Rb[9], tb[3];
-    {
-        const float* o = a.hypRt + ((size_t)f * a.H + bh) * 12;
-#pragma unroll
-        for (int k = 0; k < 9; ++k) Rb[k] = o[k];
-        tb[0] = o[9]; tb[1] = o[10]; tb[2] = o[11];
-    }
-    if (lane < 9 && a.R0) a.R0[9 * f + lane] = Rb[lane];
-    if (lane < 3 && a.t0) a.t0[3 * f + lane] = tb[lane];
-    float q[4], tt[3] = {tb[0], tb[1], tb[2]};
-    rot_to_quat(Rb, q);
-    float M[12];
-    make_proj_s(fx, fy, cx, cy, Rb, tb, a.inv_thr, M);
-    int nref = bc;
-    const int pwords = (P + 31) / 32;
-    for (int round = -1; round <= a.lo_rounds; ++round) {
-        bool stop = false;
-        if (round >= 0) {
-            // ---- centroid of the inlier object points (canonical order: 8 virtual groups)
-            float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
-            int cn = 0;
+                const int buf = it & 1;
 #pragma unroll 1
-            for (int vw = 0; vw < PB_THREADS / 32; ++vw) {
-                float cs[3] = {0.0f, 0.0f, 0.0f};
-                for (int i = vw * 32 + lane; i < P; i += PB_THREADS)
-                    if ((bm[i >> 5] >> (i & 31)) & 1u) { cs[0] += X[i]; cs[1] += Y[i]; cs[2] += Z[i]; ++cn; }
-#pragma unroll
-                for (int k = 0; k < 3; ++k) cs[k] = warp_sum_bfly(cs[k]);
-                if (vw == 0) { c0 = cs[0]; c1 = cs[1]; c2 = cs[2]; }
-                else { c0 = c0 + cs[0]; c1 = c1 + cs[1]; c2 = c2 + cs[2]; }
-            }
-            const int cnt_all = __reduce_add_sync(0xffffffffu, cn);
-            if (cnt_all < 4) break;  // warp-uniform
-            const float fn = (float)cnt_all;
-            const float cb[3] = {c0 / fn, c1 / fn, c2 / fn};
-            float R[9];
-            quat_to_rot(q, R);
-            float tc[3];
-#pragma unroll
-            for (int i = 0; i < 3; ++i)
-                tc[i] = fmaf(R[3 * i], cb[0], fmaf(R[3 * i + 1], cb[1], fmaf(R[3 * i + 2], cb[2], tt[i])));
-            for (int it = 0; it < a.gn_iters; ++it) {
-                quat_to_rot(q, R);
-                float totl = 0.0f;                   // lane k: running sum of normal-equation term k
-#pragma unroll 1
-                for (int vw = 0; vw < PB_THREADS / 32; ++vw) {
+                for (int vw = wid; vw < NVG; vw += G) {
                     float acc[32];
 #pragma unroll
                     for (int k = 0; k < 32; ++k) acc[k] = 0.0f;
@@ -407,46 +262,61 @@ __global__ void __launch_bounds__(32 * FW) ransac_finalize_warp_kernel(FinalArgs
                         if (!((bm[i >> 5] >> (i & 31)) & 1u)) continue;
                         gn_accumulate(acc, R, cb, tc, fx, fy, cx, cy, X[i], Y[i], Z[i], U[i], V[i]);
                     }
-                    const float v = warp_transpose_reduce32(acc, lane);
-                    totl = (vw == 0) ? v : totl + v;
+                    red[buf][vw][lane] = warp_transpose_reduce32(acc, lane);
                 }
+                __syncthreads();
+                float totl = red[buf][0][lane];      // lane k: normal-equation term k
+#pragma unroll
+                for (int vw = 1; vw < NVG; ++vw) totl = totl + red[buf][vw][lane];
                 float tot[27];
 #pragma unroll
                 for (int k = 0; k < 27; ++k) tot[k] = __shfl_sync(0xffffffffu, totl, k);
                 float dl[6];
-                if (!gn_solve(tot, dl)) { stop = true; break; }   // every lane holds the same tot: uniform
+                if (!gn_solve(tot, dl)) break;       // every thread holds the same tot: uniform
                 gn_apply(q, tc, dl);
             }
-            (void)stop;
             quat_to_rot(q, R);
 #pragma unroll
             for (int i = 0; i < 3; ++i)
                 tt[i] = tc[i] - fmaf(R[3 * i], cb[0], fmaf(R[3 * i + 1], cb[1], R[3 * i + 2] * cb[2]));
             make_proj_s(fx, fy, cx, cy, R, tt, a.inv_thr, M);
+            __syncthreads();         // every warp is done reading bm and red
         }
         // ---- (re-)score: inlier bitmap by warp ballot
-        __syncwarp();
         int cn = 0;
-        for (int base = 0; base < P; base += 32) {
-            const int i = base + lane;
+        for (int base = 0; base < P; base += NT) {
+            const int i = base + tid;
             bool in = i < P && inlier_test(M, X[i], Y[i], Z[i], U[i] * a.inv_thr, V[i] * a.inv_thr);
             unsigned b = __ballot_sync(0xffffffffu, in);
-            if (lane == 0) bm[base >> 5] = b;
-            cn += __popc(b);
+            if (lane == 0) { bm[(base >> 5) + wid] = b; cn += __popc(b); }
         }
-        __syncwarp();
+        if (lane == 0) ired[wid] = cn;
+        __syncthreads();
+        int tot_in = 0;
+#pragma unroll
+        for (int w = 0; w < G; ++w) tot_in += ired[w];
         if (round < 0) {
-            if (a.inl_bitmap)
-                for (int w = lane; w < words; w += 32) a.inl_bitmap[(size_t)f * words + w] = w < pwords ? bm[w] : 0u;
+            if (a.inl_bitmap) {
+                const int pw = (P + 31) / 32;
+                for (int w = tid; w < words; w += NT) a.inl_bitmap[(size_t)f * words + w] = w < pw ? bm[w] : 0u;
+            }
         } else {
-            nref = cn;
+            nref = tot_in;
         }
+        __syncthreads();
     }
     float R[9];
     quat_to_rot(q, R);
-    if (lane < 9) a.R[9 * f + lane] = R[lane];
-    if (lane < 3) a.t[3 * f + lane] = tt[lane];
-    if (lane == 0) { a.n_inl[f] = bc; a.best_hyp[f] = bh; a.n_inl_refined[f] = nref; a.status[f] = PB_STATUS_OK; }
+    for (int k = tid; k < 9; k += NT) a.R[9 * f + k] = R[k];
+    if (tid < 3) a.t[3 * f + tid] = tt[tid];
+    if (tid == 0) { a.n_inl[f] = bc; a.best_hyp[f] = bh; a.n_inl_refined[f] = nref; a.status[f] = PB_STATUS_OK; }
+}
+
+template <int G>
+int launch_finalize(const FinalArgs& fa, int F, size_t smem, cudaStream_t st) {
+    cudaFuncSetAttribute(ransac_finalize_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ransac_finalize_kernel<G><<<F, 32 * G, smem, st>>>(fa);
+    return pb_check_launch("ransac_finalize_kernel");
 }
 
 // ------------------------------------------------------------------------------------------
@@ -523,16 +393,14 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     fa.status = status; fa.inl_bitmap = inl_bitmap; fa.R0 = R0; fa.t0 = t0;
     fa.cap = cap; fa.H = prm->n_hyp; fa.HS = p.HS; fa.gn_iters = prm->gn_iters; fa.lo_rounds = prm->lo_rounds;
     fa.min_inliers = prm->min_inliers; fa.inv_thr = sa.inv_thr;
-    // many frames of moderate size: one warp per frame; otherwise one CTA per frame (same results)
-    const size_t smem_warp = (size_t)FW * ((cap + 31) / 32) * sizeof(uint32_t);
-    if (F >= 4 * 148 && smem_warp <= 48 * 1024) {
-        ransac_finalize_warp_kernel<<<(F + FW - 1) / FW, 32 * FW, smem_warp, st>>>(fa, F);
-        if (pb_check_launch("ransac_finalize_warp_kernel")) return -2;
-    } else {
-        cudaFuncSetAttribute(ransac_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_final);
-        ransac_finalize_kernel<<<F, PB_THREADS, p.smem_final, st>>>(fa);
-        if (pb_check_launch("ransac_finalize_kernel")) return -2;
-    }
+    // warps per frame: enough warps in flight to hide latency (>= ~16 per SM), results identical
+    const long long want_warps = 148ll * 16;
+    int rcf;
+    if ((long long)F * 1 >= want_warps * 2) rcf = launch_finalize<1>(fa, F, p.smem_final, st);
+    else if ((long long)F * 2 >= want_warps) rcf = launch_finalize<2>(fa, F, p.smem_final, st);
+    else if ((long long)F * 4 >= want_warps) rcf = launch_finalize<4>(fa, F, p.smem_final, st);
+    else rcf = launch_finalize<8>(fa, F, p.smem_final, st);
+    if (rcf) return -2;
     return 0;
 }
 

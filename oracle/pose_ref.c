@@ -369,6 +369,7 @@ int ref_score(const float M[12], const float* X, const float* Y, const float* Z,
 }
 
 /* ------------------------------------------------------------------ refine (Gauss-Newton) */
+#define GN_EPS 1e-6f /* Gauss-Newton stops early once a step is this small (rad / m) */
 #define RT 256 /* threads of the finalize CTA whose reduction tree is emulated */
 
 /* emulate: per-thread strided partials -> xor-butterfly per warp -> sequential sum over warps */
@@ -516,6 +517,9 @@ static int refine_pose(const float* X, const float* Y, const float* Z, const flo
         float in = 1.0f / sqrtf(fmaf(nw, nw, fmaf(nx, nx, fmaf(ny, ny, nz * nz))));
         q[0] = nw * in; q[1] = nx * in; q[2] = ny * in; q[3] = nz * in;
         tc[0] += dt[0]; tc[1] += dt[1]; tc[2] += dt[2];
+        /* converged: the step just applied is below 1e-6 rad and 1e-6 m in every component */
+        if (fmaxf(fmaxf(fabsf(dw[0]), fabsf(dw[1])), fabsf(dw[2])) < GN_EPS &&
+            fmaxf(fmaxf(fabsf(dt[0]), fabsf(dt[1])), fabsf(dt[2])) < GN_EPS) break;
     }
     quat_to_rot(q, R);
     for (int i = 0; i < 3; ++i)

@@ -9,6 +9,7 @@
 #define PB_SAMPLE_TAG 0x50335031u   /* Philox counter word 3 for minimal-set sampling */
 #define PB_RESAMPLE_TAG 0x52534d50u /* ... for inlier resampling                       */
 #define PB_SAMPLE_ATTEMPTS 16
+#define PB_GN_EPS 1e-6f            /* Gauss-Newton stops once a step is below this (rad and m)        */
 #define PB_THREADS 256              /* CTA size of the RANSAC kernels (fixes the refit reduction tree) */
 
 void pb_set_error(const char* fmt, ...);

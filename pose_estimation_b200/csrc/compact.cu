@@ -159,10 +159,10 @@ __device__ __forceinline__ float ldg_stream_f32(const float* p) {
     asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
     return r;
 }
-// 4 mask bytes -> 4 bits (byte != 0)
+// 4 mask bytes -> 4 bits (byte != 0): per-byte compare (0xFF per non-zero byte), keep one bit per
+// byte, gather the four bits with a multiply (bit k of the result's top byte <- byte k)
 __device__ __forceinline__ uint32_t nz4(uint32_t w) {
-    const uint32_t t = (((w & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | w) & 0x80808080u;   // bit 7 of each non-zero byte
-    return ((t >> 7) | (t >> 14) | (t >> 21) | (t >> 28)) & 0xFu;
+    return ((__vcmpne4(w, 0u) & 0x01010101u) * 0x10204080u) >> 28;
 }
 
 constexpr int SP_UNROLL = 4;   // 128-bit mask loads in flight per thread
@@ -193,8 +193,12 @@ __global__ void __launch_bounds__(CT) compact_sparse_kernel(CompactArgs a) {
 #pragma unroll
         for (int k = 0; k < SP_UNROLL; ++k) {
             const int g = g0 + k * CT + tid;
-            if (g < nv)
-                sb16[g] = (uint16_t)(nz4(m[k].x) | (nz4(m[k].y) << 4) | (nz4(m[k].z) << 8) | (nz4(m[k].w) << 12));
+            if (g < nv) {
+                uint32_t bits = 0u;
+                if (m[k].x | m[k].y | m[k].z | m[k].w)          // most of a frame is background
+                    bits = nz4(m[k].x) | (nz4(m[k].y) << 4) | (nz4(m[k].z) << 8) | (nz4(m[k].w) << 12);
+                sb16[g] = (uint16_t)bits;
+            }
         }
     }
     __syncthreads();

@@ -274,6 +274,8 @@ __global__ void __launch_bounds__(32 * G) ransac_finalize_kernel(FinalArgs a) {
                 float dl[6];
                 if (!gn_solve(tot, dl)) break;       // every thread holds the same tot: uniform
                 gn_apply(q, tc, dl);
+                if (fmaxf(fmaxf(fabsf(dl[0]), fabsf(dl[1])), fabsf(dl[2])) < PB_GN_EPS &&
+                    fmaxf(fmaxf(fabsf(dl[3]), fabsf(dl[4])), fabsf(dl[5])) < PB_GN_EPS) break;   // converged (uniform)
             }
             quat_to_rot(q, R);
 #pragma unroll
@@ -393,13 +395,14 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     fa.status = status; fa.inl_bitmap = inl_bitmap; fa.R0 = R0; fa.t0 = t0;
     fa.cap = cap; fa.H = prm->n_hyp; fa.HS = p.HS; fa.gn_iters = prm->gn_iters; fa.lo_rounds = prm->lo_rounds;
     fa.min_inliers = prm->min_inliers; fa.inv_thr = sa.inv_thr;
-    // warps per frame: enough warps in flight to hide latency (>= ~16 per SM), results identical
-    const long long want_warps = 148ll * 16;
+    // warps per frame: the largest G whose CTAs are ALL resident at once (120 registers per thread:
+    // 2 / 4 / 8 / 17 CTAs per SM for G = 8 / 4 / 2 / 1), so a batch is one wave with no tail; results
+    // do not depend on G.
     int rcf;
-    if ((long long)F * 1 >= want_warps * 2) rcf = launch_finalize<1>(fa, F, p.smem_final, st);
-    else if ((long long)F * 2 >= want_warps) rcf = launch_finalize<2>(fa, F, p.smem_final, st);
-    else if ((long long)F * 4 >= want_warps) rcf = launch_finalize<4>(fa, F, p.smem_final, st);
-    else rcf = launch_finalize<8>(fa, F, p.smem_final, st);
+    if (F <= 148 * 2) rcf = launch_finalize<8>(fa, F, p.smem_final, st);
+    else if (F <= 148 * 4) rcf = launch_finalize<4>(fa, F, p.smem_final, st);
+    else if (F <= 148 * 8) rcf = launch_finalize<2>(fa, F, p.smem_final, st);
+    else rcf = launch_finalize<1>(fa, F, p.smem_final, st);
     if (rcf) return -2;
     return 0;
 }

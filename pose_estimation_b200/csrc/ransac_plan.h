@@ -23,19 +23,21 @@ struct Plan {
 
 // Hypotheses of a frame are cut into HS slices of Hs (power of two) so that few-frame launches
 // still fill 148 SMs; a slice narrower than the CTA splits the points PP ways instead.
+#define PB_SCORE_THREADS 128     /* CTA size of the scoring kernel (ST in ransac_score.cu) */
+
 static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm) {
     Plan p;
     const int H = prm->n_hyp;
     int Hs = 32;
-    while (Hs < H && Hs < 1024) Hs <<= 1;              // whole frame in one slice if it fits
+    while (Hs < H && Hs < 2 * PB_SCORE_THREADS) Hs <<= 1;   // up to 2 hypotheses per thread
     if (F < 296) {                                     // few frames: more, narrower slices
         int want = (296 + F - 1) / F;
         while (Hs > 64 && (H + Hs - 1) / Hs < want) Hs >>= 1;
     }
     p.Hs = Hs;
     p.HS = (H + Hs - 1) / Hs;
-    p.NHL = Hs > PB_THREADS ? Hs / PB_THREADS : 1;
-    p.PP = Hs < PB_THREADS ? PB_THREADS / Hs : 1;
+    p.NHL = Hs > PB_SCORE_THREADS ? Hs / PB_SCORE_THREADS : 1;
+    p.PP = Hs < PB_SCORE_THREADS ? PB_SCORE_THREADS / Hs : 1;
     int CH = (cap + 127) / 128 * 128;
     if (CH > 2048) CH = 2048;
     p.CH = CH;

@@ -11,11 +11,13 @@
 //   ransac_score_kernel       one CTA per (frame, hypothesis slice): thread <-> hypothesis (3x4
 //       projection matrix in 12 registers, NHL hypotheses per thread), correspondences staged per
 //       chunk in shared memory as float4(X,Y,Z,U') + float(V') and read as warp-broadcast LDS.128,
-//       so one shared-memory wavefront feeds 32*NHL tests.  Per hypothesis*point: 14 FMA-pipe
-//       instructions + one funnel shift that pushes the verdict's sign bit into a 32-bit window
-//       (popcount every 8 points) -- no compare, no select, no reduction in the loop.  Chunks are
-//       padded to a multiple of 8 with never-inlier sentinels so the loop has no tail test.
-//       FP32-pipe bound.
+//       so one shared-memory wavefront feeds 32*NHL tests.  The arithmetic is PACKED FP32x2
+//       (Blackwell FFMA2/FMUL2, fma.rn.f32x2): two points per instruction, IEEE-rn per half, so
+//       the bits equal the scalar contract in common.cuh::inlier_s.  Per hypothesis*point: 7 packed
+//       FMA-pipe instructions, one LOP (-|w|) and one funnel shift that pushes the verdict's sign
+//       bit into a 32-bit window (popcount every 8 points) -- no compare, no select, no reduction
+//       in the loop.  Chunks are padded to a multiple of 8 with never-inlier sentinels so the loop
+//       has no tail test.  FP32-pipe bound.
 #include "p3p.cuh"
 #include "ransac_plan.h"
 
@@ -67,14 +69,50 @@ __global__ void __launch_bounds__(HT) ransac_hypothesis_kernel(ScoreArgs a) {
     }
 }
 
+typedef unsigned long long f32x2;   // two packed binary32 values (lo = even point, hi = odd point)
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 fmul2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+// opaque to the optimiser on purpose: a (v,v) pair must live in its own aligned register pair,
+// otherwise the compiler keeps one copy and rebuilds the pair with moves inside the hot loop
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+    return d;
+}
+// inlier_s (common.cuh) for two points at once; nus/nvs are the NEGATED scaled pixel coordinates.
+// q = w*|w| enters as  w * (-|w|) = -q  (sign flips are exact), so every half has inlier_s' bits.
+__device__ __forceinline__ f32x2 inlier_s2(const f32x2 m[12], f32x2 X, f32x2 Y, f32x2 Z, f32x2 nus, f32x2 nvs) {
+    const f32x2 x = ffma2(m[0], X, ffma2(m[1], Y, ffma2(m[2], Z, m[3])));
+    const f32x2 y = ffma2(m[4], X, ffma2(m[5], Y, ffma2(m[6], Z, m[7])));
+    const f32x2 w = ffma2(m[8], X, ffma2(m[9], Y, ffma2(m[10], Z, m[11])));
+    const f32x2 dx = ffma2(nus, w, x);
+    const f32x2 dy = ffma2(nvs, w, y);
+    const f32x2 nq = fmul2(w, w | 0x8000000080000000ull);
+    const f32x2 t = ffma2(dy, dy, nq);
+    return ffma2(dx, dx, t);
+}
+
+constexpr int ST = 128;  // threads per scoring CTA: 128 x 64 regs x ~26 KB smem -> 8 CTAs per SM, so the
+                         // 1024 CTAs of a 1024-frame batch are all resident (one wave, no tail)
+
 template <int NHL>
-__global__ void __launch_bounds__(PB_THREADS) ransac_score_kernel(ScoreArgs a) {
+__global__ void __launch_bounds__(ST) ransac_score_kernel(ScoreArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int CH = a.CH, Hs = a.Hs;
-    float4* sp4 = reinterpret_cast<float4*>(smem_raw);          // [CH] X,Y,Z,U'
-    float* spv = reinterpret_cast<float*>(sp4 + CH);            // [CH] V'
-    int* cnt = reinterpret_cast<int*>(spv + CH);                // [Hs]
-    __shared__ unsigned long long wkey[PB_THREADS / 32];
+    // points are staged as PAIRS (2i, 2i+1): sA[i] = (X0,X1,Y0,Y1), sB[i] = (Z0,Z1,-U0',-U1'), sC[i] = (-V0',-V1')
+    float4* sA = reinterpret_cast<float4*>(smem_raw);            // [CH/2]
+    float4* sB = sA + CH / 2;                                    // [CH/2]
+    float2* sC = reinterpret_cast<float2*>(sB + CH / 2);         // [CH/2]
+    int* cnt = reinterpret_cast<int*>(sC + CH / 2);              // [Hs]
+    __shared__ unsigned long long wkey[ST / 32];
 
     const int f = blockIdx.x / a.HS, s = blockIdx.x % a.HS;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -86,18 +124,19 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_score_kernel(ScoreArgs a) {
     const float* V = U + a.cap;
     const float fx = a.K4[4 * f], fy = a.K4[4 * f + 1], cx = a.K4[4 * f + 2], cy = a.K4[4 * f + 3];
     const int h0 = s * Hs;
-    const int PP = a.PP;                       // >1 only when Hs < PB_THREADS (then NHL == 1)
+    const int PP = a.PP;                       // >1 only when Hs < ST (then NHL == 1)
     const int part = (PP > 1) ? tid / Hs : 0;  // warp-uniform: Hs is a multiple of 32
 
-    // ---- this thread's hypotheses: K[R|t] in threshold units, 12 registers each
-    float m[NHL][12];
+    // ---- this thread's hypotheses: K[R|t] in threshold units, each entry duplicated into both halves
+    f32x2 m[NHL][12];
     int c[NHL];
 #pragma unroll
     for (int j = 0; j < NHL; ++j) {
-        const int hl = (PP > 1) ? (tid % Hs) : (tid + j * PB_THREADS);
+        const int hl = (PP > 1) ? (tid % Hs) : (tid + j * ST);
         const int h = h0 + hl;
         c[j] = 0;
         bool valid = false;
+        float mj[12];
         if (h < a.H) {
             const float4* o = reinterpret_cast<const float4*>(a.hypRt + ((size_t)f * a.H + h) * 12);
             const float4 r0 = o[0], r1 = o[1], r2 = o[2];
@@ -105,48 +144,61 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_score_kernel(ScoreArgs a) {
             if (valid) {
                 const float R[9] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x};
                 const float t[3] = {r2.y, r2.z, r2.w};
-                make_proj_s(fx, fy, cx, cy, R, t, a.inv_thr, m[j]);
+                make_proj_s(fx, fy, cx, cy, R, t, a.inv_thr, mj);
             }
         }
         if (!valid) {
 #pragma unroll
-            for (int k = 0; k < 12; ++k) m[j][k] = 0.0f;
-            m[j][11] = -1.0f;  // w < 0 for every point: never an inlier
+            for (int k = 0; k < 12; ++k) mj[k] = 0.0f;
+            mj[11] = -1.0f;  // w < 0 for every point: never an inlier
         }
+#pragma unroll
+        for (int k = 0; k < 12; ++k) m[j][k] = pack2(mj[k], mj[k]);
         if (part == 0 && hl < Hs) cnt[hl] = valid ? 0 : -1;
     }
 
     // ---- K3: every correspondence against this thread's hypotheses
-    const float inf = __int_as_float(0x7f800000);
+    const float ninf = __int_as_float(0xff800000);
+    float* sAf = reinterpret_cast<float*>(sA);
+    float* sBf = reinterpret_cast<float*>(sB);
+    float* sCf = reinterpret_cast<float*>(sC);
     for (int c0 = 0; c0 < P; c0 += CH) {
         const int n = min(CH, P - c0);
         const int npp = ((n + 8 * PP - 1) / (8 * PP)) * 8;   // points per partition, multiple of 8
         __syncthreads();                                     // previous chunk consumed / cnt initialised
-        for (int i = tid; i < npp * PP; i += PB_THREADS) {
+        for (int i = tid; i < npp * PP; i += ST) {
+            const int o4 = (i >> 1) * 4 + (i & 1);
             if (i < n) {
-                sp4[i] = make_float4(X[c0 + i], Y[c0 + i], Z[c0 + i], U[c0 + i] * a.inv_thr);
-                spv[i] = V[c0 + i] * a.inv_thr;
+                sAf[o4] = X[c0 + i]; sAf[o4 + 2] = Y[c0 + i];
+                sBf[o4] = Z[c0 + i]; sBf[o4 + 2] = -(U[c0 + i] * a.inv_thr);
+                sCf[i] = -(V[c0 + i] * a.inv_thr);
             } else {                                         // sentinel: s = +inf or NaN, never an inlier
-                sp4[i] = make_float4(0.0f, 0.0f, 0.0f, inf);
-                spv[i] = inf;
+                sAf[o4] = 0.0f; sAf[o4 + 2] = 0.0f;
+                sBf[o4] = 0.0f; sBf[o4 + 2] = ninf;
+                sCf[i] = ninf;
             }
         }
         __syncthreads();
-        const float4* s4 = sp4 + part * npp;
-        const float4* sv = reinterpret_cast<const float4*>(spv + part * npp);
+        const int pb = (part * npp) >> 1;                    // first pair of this partition
+        const ulonglong2* a2 = reinterpret_cast<const ulonglong2*>(sA) + pb;
+        const ulonglong2* b2 = reinterpret_cast<const ulonglong2*>(sB) + pb;
+        const ulonglong2* c2 = reinterpret_cast<const ulonglong2*>(sC + pb);   // two pairs per 16 bytes
 #pragma unroll 1
-        for (int i = 0; i < npp; i += 8) {
-            const float4 v0 = sv[i >> 2], v1 = sv[(i >> 2) + 1];
-            const float vs[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+        for (int i = 0; i < (npp >> 1); i += 4) {            // 4 pairs = 8 points per iteration
+            const ulonglong2 v01 = c2[i >> 1], v23 = c2[(i >> 1) + 1];
+            const f32x2 nvs[4] = {v01.x, v01.y, v23.x, v23.y};
             uint32_t acc[NHL];
 #pragma unroll
             for (int j = 0; j < NHL; ++j) acc[j] = 0u;
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const float4 p = s4[i + k];
+            for (int k = 0; k < 4; ++k) {
+                const ulonglong2 pa = a2[i + k], pbv = b2[i + k];
 #pragma unroll
-                for (int j = 0; j < NHL; ++j)
-                    acc[j] = __funnelshift_l(__float_as_uint(inlier_s(m[j], p.x, p.y, p.z, p.w, vs[k])), acc[j], 1);
+                for (int j = 0; j < NHL; ++j) {
+                    const f32x2 sv = inlier_s2(m[j], pa.x, pa.y, pbv.x, pbv.y, nvs[k]);
+                    acc[j] = __funnelshift_l((uint32_t)sv, acc[j], 1);
+                    acc[j] = __funnelshift_l((uint32_t)(sv >> 32), acc[j], 1);
+                }
             }
 #pragma unroll
             for (int j = 0; j < NHL; ++j) c[j] += __popc(acc[j]);
@@ -155,14 +207,14 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_score_kernel(ScoreArgs a) {
     if (P <= 0) __syncthreads();               // cnt initialised even when there was no chunk
 #pragma unroll
     for (int j = 0; j < NHL; ++j) {
-        const int hl = (PP > 1) ? (tid % Hs) : (tid + j * PB_THREADS);
+        const int hl = (PP > 1) ? (tid % Hs) : (tid + j * ST);
         if (hl < Hs && c[j] > 0) atomicAdd(&cnt[hl], c[j]);   // c > 0 only for valid hypotheses
     }
     __syncthreads();
 
     // ---- slice argmax: max count, lowest hypothesis index on ties
     unsigned long long key = 0ull;
-    for (int hl = tid; hl < Hs; hl += PB_THREADS) {
+    for (int hl = tid; hl < Hs; hl += ST) {
         const int h = h0 + hl;
         if (h < a.H) {
             const int cv = cnt[hl];
@@ -181,7 +233,7 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_score_kernel(ScoreArgs a) {
     __syncthreads();
     if (tid == 0) {
         unsigned long long k = wkey[0];
-        for (int w = 1; w < PB_THREADS / 32; ++w) k = wkey[w] > k ? wkey[w] : k;
+        for (int w = 1; w < ST / 32; ++w) k = wkey[w] > k ? wkey[w] : k;
         a.slice_best[(size_t)f * a.HS + s] = k;
     }
 }
@@ -189,7 +241,7 @@ __global__ void __launch_bounds__(PB_THREADS) ransac_score_kernel(ScoreArgs a) {
 template <int NHL>
 int launch(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
     cudaFuncSetAttribute(ransac_score_kernel<NHL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_score);
-    ransac_score_kernel<NHL><<<F * p.HS, PB_THREADS, p.smem_score, st>>>(a);
+    ransac_score_kernel<NHL><<<F * p.HS, ST, p.smem_score, st>>>(a);
     return pb_check_launch("ransac_score_kernel");
 }
 
@@ -202,7 +254,6 @@ int pb_launch_score(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
     switch (p.NHL) {
         case 1: return launch<1>(a, p, F, st);
         case 2: return launch<2>(a, p, F, st);
-        case 4: return launch<4>(a, p, F, st);
         default: pb_set_error("ransac_score: unsupported NHL=%d", p.NHL); return 1;
     }
 }

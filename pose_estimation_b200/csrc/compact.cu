@@ -167,100 +167,113 @@ __device__ __forceinline__ uint32_t nz4(uint32_t w) {
 
 constexpr int SP_UNROLL = 4;   // 128-bit mask loads in flight per thread
 
-// One CTA per frame.  Phase 1: mask -> shared bitmap (1 bit/px).  Phase 2: per-tile (32 words)
-// counts, exclusive prefix, then every warp emits (pixel index, u, v) for its round-robin tiles at
-// the tile's offset, i.e. in pixel order.  Phase 3: all threads gather xyz at the emitted pixels
-// and de-normalise.
+// One CTA per frame, the frame walked in bands of SP_BAND_WORDS bitmap words (76,800 px) so the
+// bitmap is ~10 KB and 8 CTAs fit per SM: a 1024-frame batch is ONE resident wave.  Per band:
+// phase 1 mask -> shared bitmap (1 bit/px); phase 2 per-tile (32 words) counts, exclusive prefix,
+// then every warp emits (pixel index, u, v) for its round-robin tiles at the tile's offset, i.e.
+// in pixel order.  After the last band, phase 3: all threads gather xyz at the emitted pixels and
+// de-normalise.
+constexpr int SP_BAND_WORDS = 2400;
+constexpr int SP_BAND_TILES = (SP_BAND_WORDS + 31) / 32;
+
 __global__ void __launch_bounds__(CT) compact_sparse_kernel(CompactArgs a) {
-    extern __shared__ __align__(16) uint32_t sbm[];             // [HW/32] bitmap, then [ntiles] tile offsets
+    __shared__ __align__(16) uint32_t sbm[SP_BAND_WORDS];
+    __shared__ int stile[SP_BAND_TILES];
     __shared__ int stotal;
     const int f = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nwords = a.HW >> 5;
-    const int nv = a.HW >> 4;                                   // 16-px groups (one uint4 of mask each)
     const uint4* pm = reinterpret_cast<const uint4*>(a.mask + (size_t)f * a.HW);
     uint16_t* sb16 = reinterpret_cast<uint16_t*>(sbm);
-    int* stile = reinterpret_cast<int*>(sbm + nwords);
-
-    // ---- phase 1
-    for (int g0 = 0; g0 < nv; g0 += CT * SP_UNROLL) {
-        uint4 m[SP_UNROLL];
-#pragma unroll
-        for (int k = 0; k < SP_UNROLL; ++k) {
-            const int g = g0 + k * CT + tid;
-            m[k] = g < nv ? ldg_stream_u4(pm + g) : make_uint4(0u, 0u, 0u, 0u);
-        }
-#pragma unroll
-        for (int k = 0; k < SP_UNROLL; ++k) {
-            const int g = g0 + k * CT + tid;
-            if (g < nv) {
-                uint32_t bits = 0u;
-                if (m[k].x | m[k].y | m[k].z | m[k].w)          // most of a frame is background
-                    bits = nz4(m[k].x) | (nz4(m[k].y) << 4) | (nz4(m[k].z) << 8) | (nz4(m[k].w) << 12);
-                sb16[g] = (uint16_t)bits;
-            }
-        }
-    }
-    __syncthreads();
-
-    // ---- phase 2: tiles of 32 bitmap words (1024 px) dealt round-robin to the warps, so a compact
-    // foreground blob (a few dozen image rows) is spread over all warps
-    const int ntiles = (nwords + 31) >> 5;
-    for (int k = warp; k < ntiles; k += CT / 32) {
-        const int w = (k << 5) + lane;
-        const int c = __reduce_add_sync(0xffffffffu, w < nwords ? __popc(sbm[w]) : 0);
-        if (lane == 0) stile[k] = c;
-    }
-    __syncthreads();
-    if (warp == 0) {   // exclusive prefix over the tile counts (in place), total -> stotal
-        int run = 0;
-        for (int k0 = 0; k0 < ntiles; k0 += 32) {
-            const int k = k0 + lane;
-            const int c = k < ntiles ? stile[k] : 0;
-            int incl = c;
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const int o = __shfl_up_sync(0xffffffffu, incl, off);
-                if (lane >= off) incl += o;
-            }
-            if (k < ntiles) stile[k] = run + incl - c;
-            run += __shfl_sync(0xffffffffu, incl, 31);
-        }
-        if (lane == 0) stotal = run;
-    }
-    __syncthreads();
-    const int total = stotal;
     const int rmin = a.roi ? a.roi[2 * f] : 0, cmin = a.roi ? a.roi[2 * f + 1] : 0;
     float* oX = a.pts + (size_t)f * 5 * a.cap;
     float* oY = oX + a.cap; float* oZ = oY + a.cap; float* oU = oZ + a.cap; float* oV = oU + a.cap;
-    for (int k = warp; k < ntiles; k += CT / 32) {
-        const int base = stile[k];
-        const int next = (k + 1 < ntiles) ? stile[k + 1] : total;
-        if (next == base || base >= a.cap) continue;          // empty tile / beyond cap (warp-uniform)
-        const int w = (k << 5) + lane;
-        uint32_t bits = w < nwords ? sbm[w] : 0u;
-        const int n = __popc(bits);
-        int incl = n;
+
+    int total = 0;                                              // foreground pixels before this band
+    for (int wb0 = 0; wb0 < nwords; wb0 += SP_BAND_WORDS) {
+        const int bw = min(SP_BAND_WORDS, nwords - wb0);        // words in this band
+        const int nv = bw * 2;                                  // 16-px groups (one uint4 of mask each)
+        const uint4* pmb = pm + (size_t)wb0 * 2;
+        // ---- phase 1
+        for (int g0 = 0; g0 < nv; g0 += CT * SP_UNROLL) {
+            uint4 m[SP_UNROLL];
 #pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const int o = __shfl_up_sync(0xffffffffu, incl, off);
-            if (lane >= off) incl += o;
-        }
-        int pos = base + incl - n;
-        while (bits) {
-            const int b = __ffs(bits) - 1;
-            bits &= bits - 1u;
-            if (pos < a.cap) {
-                const int p = (w << 5) + b;
-                const int row = p / a.Ww, col = p - row * a.Ww;
-                oX[pos] = __int_as_float(p);
-                oU[pos] = (float)(col + cmin);
-                oV[pos] = (float)(row + rmin);
+            for (int k = 0; k < SP_UNROLL; ++k) {
+                const int g = g0 + k * CT + tid;
+                m[k] = g < nv ? ldg_stream_u4(pmb + g) : make_uint4(0u, 0u, 0u, 0u);
             }
-            ++pos;
+#pragma unroll
+            for (int k = 0; k < SP_UNROLL; ++k) {
+                const int g = g0 + k * CT + tid;
+                if (g < nv) {
+                    uint32_t bits = 0u;
+                    if (m[k].x | m[k].y | m[k].z | m[k].w)      // most of a frame is background
+                        bits = nz4(m[k].x) | (nz4(m[k].y) << 4) | (nz4(m[k].z) << 8) | (nz4(m[k].w) << 12);
+                    sb16[g] = (uint16_t)bits;
+                }
+            }
         }
+        __syncthreads();
+        // ---- phase 2: tiles of 32 bitmap words (1024 px) dealt round-robin to the warps, so a
+        // compact foreground blob (a few dozen image rows) is spread over all warps
+        const int ntiles = (bw + 31) >> 5;
+        for (int k = warp; k < ntiles; k += CT / 32) {
+            const int w = (k << 5) + lane;
+            const int c = __reduce_add_sync(0xffffffffu, w < bw ? __popc(sbm[w]) : 0);
+            if (lane == 0) stile[k] = c;
+        }
+        __syncthreads();
+        if (warp == 0) {   // exclusive prefix over the tile counts (in place), running total -> stotal
+            int run = total;
+            for (int k0 = 0; k0 < ntiles; k0 += 32) {
+                const int k = k0 + lane;
+                const int c = k < ntiles ? stile[k] : 0;
+                int incl = c;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) {
+                    const int o = __shfl_up_sync(0xffffffffu, incl, off);
+                    if (lane >= off) incl += o;
+                }
+                if (k < ntiles) stile[k] = run + incl - c;
+                run += __shfl_sync(0xffffffffu, incl, 31);
+            }
+            if (lane == 0) stotal = run;
+        }
+        __syncthreads();
+        const int btotal = stotal;
+        if (btotal > total && total < a.cap) {                  // uniform: this band has foreground below cap
+            for (int k = warp; k < ntiles; k += CT / 32) {
+                const int base = stile[k];
+                const int next = (k + 1 < ntiles) ? stile[k + 1] : btotal;
+                if (next == base || base >= a.cap) continue;    // empty tile / beyond cap (warp-uniform)
+                const int w = (k << 5) + lane;
+                uint32_t bits = w < bw ? sbm[w] : 0u;
+                const int n = __popc(bits);
+                int incl = n;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) {
+                    const int o = __shfl_up_sync(0xffffffffu, incl, off);
+                    if (lane >= off) incl += o;
+                }
+                int pos = base + incl - n;
+                while (bits) {
+                    const int b = __ffs(bits) - 1;
+                    bits &= bits - 1u;
+                    if (pos < a.cap) {
+                        const int p = ((wb0 + w) << 5) + b;
+                        const int row = p / a.Ww, col = p - row * a.Ww;
+                        oX[pos] = __int_as_float(p);
+                        oU[pos] = (float)(col + cmin);
+                        oV[pos] = (float)(row + rmin);
+                    }
+                    ++pos;
+                }
+            }
+        }
+        total = btotal;
+        __syncthreads();   // bitmap / tile offsets are rewritten by the next band; also publishes the
+                           // pixel indices written by this CTA to all of its threads
     }
-    __syncthreads();   // pixel indices written by this CTA are visible to all of its threads
 
     // ---- phase 3: gather + de-normalise
     const int n = min(total, a.cap);
@@ -383,8 +396,8 @@ CPlan make_cplan(int F, int Hh, int Ww, int cap, bool has_mask) {
     CPlan p;
     const long long HW = (long long)Hh * Ww;
     p.vec = (HW % 4) == 0;
-    p.smem_sparse = (size_t)(HW / 32) * 4 + (size_t)((HW / 32 + 31) / 32) * 4;
-    p.sparse = has_mask && (HW % 32) == 0 && p.smem_sparse <= 200 * 1024;
+    p.smem_sparse = 0;
+    p.sparse = has_mask && (HW % 32) == 0;
     if (p.sparse) { p.S = 1; p.quads_per_split = 0; p.segcap = cap; p.off_tot = 0; p.total = 0; return p; }
     int S = 1;
     if (p.vec && F < 592) {
@@ -432,8 +445,7 @@ extern "C" int pb_compact_map(const float* xyz, const uint8_t* mask, const int32
     a.HW = Hh * Ww; a.Ww = Ww; a.cap = cap; a.S = p.S; a.quads_per_split = p.quads_per_split; a.segcap = p.segcap;
     if (p.sparse) {
         a.pts = pts; a.S = 1; a.seg_total = nullptr;
-        cudaFuncSetAttribute(compact_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_sparse);
-        compact_sparse_kernel<<<F, CT, p.smem_sparse, st>>>(a);
+        compact_sparse_kernel<<<F, CT, 0, st>>>(a);
         return pb_check_launch("compact_sparse_kernel") ? -2 : 0;
     }
     const bool aligned = (reinterpret_cast<uintptr_t>(xyz) % 16 == 0) &&

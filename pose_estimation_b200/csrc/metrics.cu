@@ -11,15 +11,23 @@
 
 namespace {
 
-__global__ void __launch_bounds__(KT) pose_metrics_kernel(const float* __restrict__ R, const float* __restrict__ t,
-                                                          const float* __restrict__ R_gt, const float* __restrict__ t_gt,
-                                                          const float* __restrict__ model, const float* __restrict__ target,
-                                                          const int32_t* __restrict__ cls, const uint8_t* __restrict__ is_sym,
-                                                          int N, int C, float* __restrict__ add, float* __restrict__ r_deg,
-                                                          float* __restrict__ t_m) {
+constexpr int PM_T = 512;            // threads per frame
+constexpr int PM_PARTS = PM_T / KT;  // database parts scanned side by side by groups of KT threads
+
+// One CTA of 512 threads per frame.  ADD frames: threads stride the model points.  ADD-S frames
+// (N x N pairs): the CTA is KT query lanes (QPT queries each) x PM_PARTS database parts, so the
+// serial scan per thread is N / PM_PARTS long; partial minima meet in shared memory (min is
+// order-independent), sums use a fixed tree.
+__global__ void __launch_bounds__(PM_T) pose_metrics_kernel(const float* __restrict__ R, const float* __restrict__ t,
+                                                            const float* __restrict__ R_gt, const float* __restrict__ t_gt,
+                                                            const float* __restrict__ model, const float* __restrict__ target,
+                                                            const int32_t* __restrict__ cls, const uint8_t* __restrict__ is_sym,
+                                                            int N, int C, float* __restrict__ add, float* __restrict__ r_deg,
+                                                            float* __restrict__ t_m) {
     __shared__ float4 tile[TY];
-    __shared__ float red[KT / 32];
-    const int f = blockIdx.x;
+    __shared__ float smin[PM_PARTS][KT * QPT];
+    __shared__ float red[PM_T / 32];
+    const int f = blockIdx.x, tid = threadIdx.x;
     int c = cls[f];
     c = c < 0 ? 0 : (c >= C ? C - 1 : c);
     const float* m = model + (size_t)c * N * 3;
@@ -33,33 +41,61 @@ __global__ void __launch_bounds__(KT) pose_metrics_kernel(const float* __restric
     const bool sym = is_sym && is_sym[c] != 0;
     float s = 0.0f;
     if (!sym) {
-        for (int i = threadIdx.x; i < N; i += KT) {
+        for (int i = tid; i < N; i += PM_T) {
             const float4 p = Lp(i);
             const float4 g = tg ? make_float4(tg[3 * (size_t)i], tg[3 * (size_t)i + 1], tg[3 * (size_t)i + 2], 0.0f) : Lg(i);
             s += sqrtf(sqdist3(p.x, p.y, p.z, g.x, g.y, g.z));
         }
     } else {
         // ADD-S: for every target point the closest predicted point (metric.py:27-31)
+        const int ql = tid % KT, part = tid / KT;   // part is warp-uniform
         for (int base = 0; base < N; base += KT * QPT) {
             float qx[QPT], qy[QPT], qz[QPT], best[QPT];
-            int bidx[QPT];
 #pragma unroll
             for (int q = 0; q < QPT; ++q) {
-                const int i = base + q * KT + threadIdx.x;
+                const int i = base + q * KT + ql;
                 float4 g = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 if (i < N) g = tg ? make_float4(tg[3 * (size_t)i], tg[3 * (size_t)i + 1], tg[3 * (size_t)i + 2], 0.0f) : Lg(i);
                 qx[q] = g.x; qy[q] = g.y; qz[q] = g.z;
-                best[q] = INFINITY; bidx[q] = 0;
+                best[q] = INFINITY;
             }
-            nn_scan<false>(Lp, N, tile, qx, qy, qz, best, bidx);
+            for (int j0 = 0; j0 < N; j0 += TY) {
+                const int n = min(TY, N - j0);
+                __syncthreads();
+                for (int j = tid; j < n; j += PM_T) tile[j] = Lp(j0 + j);
+                __syncthreads();
+                const int per = (n + PM_PARTS - 1) / PM_PARTS;
+                const int j1 = min(n, (part + 1) * per);
+#pragma unroll 4
+                for (int j = part * per; j < j1; ++j) {
+                    const float4 p = tile[j];
 #pragma unroll
-            for (int q = 0; q < QPT; ++q)
-                if (base + q * KT + threadIdx.x < N) s += sqrtf(best[q]);
+                    for (int q = 0; q < QPT; ++q) best[q] = fminf(best[q], sqdist3(qx[q], qy[q], qz[q], p.x, p.y, p.z));
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < QPT; ++q) smin[part][q * KT + ql] = best[q];
+            __syncthreads();
+            if (part == 0) {
+#pragma unroll
+                for (int q = 0; q < QPT; ++q) {
+                    float b = smin[0][q * KT + ql];
+#pragma unroll
+                    for (int pp = 1; pp < PM_PARTS; ++pp) b = fminf(b, smin[pp][q * KT + ql]);
+                    if (base + q * KT + ql < N) s += sqrtf(b);
+                }
+            }
         }
     }
-    const float v = block_sum_kt(s, red) / (float)N;
-    if (threadIdx.x == 0) {
-        add[f] = v;
+    // deterministic block sum: butterfly per warp, then warps in order
+    s = warp_sum_bfly(s);
+    __syncthreads();
+    if ((tid & 31) == 0) red[tid >> 5] = s;
+    __syncthreads();
+    if (tid == 0) {
+        float tot = red[0];
+        for (int w = 1; w < PM_T / 32; ++w) tot = tot + red[w];
+        add[f] = tot / (float)N;
         float q1[4], q2[4];
         rot_to_quat(Lp.R, q1);
         rot_to_quat(Lg.R, q2);
@@ -243,7 +279,7 @@ extern "C" int pb_pose_metrics(const float* R, const float* t, const float* R_gt
     PB_REQUIRE(F >= 0 && N > 0 && C > 0, "pb_pose_metrics: bad sizes F=%d N=%d C=%d", F, N, C);
     if (F == 0) return 0;
     PB_REQUIRE(R && t && R_gt && t_gt && model && cls && add && r_deg && t_m, "pb_pose_metrics: null pointer argument");
-    pose_metrics_kernel<<<F, KT, 0, static_cast<cudaStream_t>(stream)>>>(R, t, R_gt, t_gt, model, target, cls, is_sym, N, C,
+    pose_metrics_kernel<<<F, PM_T, 0, static_cast<cudaStream_t>(stream)>>>(R, t, R_gt, t_gt, model, target, cls, is_sym, N, C,
                                                                        add, r_deg, t_m);
     return pb_check_launch("pose_metrics_kernel") ? -2 : 0;
 }

@@ -135,7 +135,7 @@ class MapCompactor:
         self.F, self.H, self.W, self.cap = F, H, W, cap
         dev = torch.device(device)
         nb = _lib.load().pb_compact_workspace_bytes(F, H, W, cap)
-        self.sparse_ok = (H * W) % 32 == 0 and (H * W) // 8 <= 200 * 1024
+        self.sparse_ok = (H * W) % 32 == 0
         self.launches_dense = 2 if nb else 1
         self.ws = _ws(nb, dev)
         self.pts = torch.empty((F, 5, cap), dtype=torch.float32, device=dev)

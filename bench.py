@@ -11,7 +11,9 @@ hypotheses, ADD with 500-pt models, ADD-S for eggbox/glue), ending with the all-
   value     whole-job frames/s with the maps already resident in HBM (CUDA events, max over ranks)
   e2e       the same pass through HostEvalSweep.run with PINNED HOST inputs: every step copies its
             maps host->device inside the timed region and reads the accuracy table back
-  roofline  the dominant kernel (K0 map stream + compaction, HBM-bound) timed live with CUDA events
+  roofline  the dominant kernel of the step (K3 hypothesis scoring, FP32-pipe bound) timed live with
+            CUDA events against an FFMA probe run in the same process; roofline_all adds the HBM-bound
+            K0 kernels (mask-first as used in the step, and the maskless full stream)
   cpu_baseline / --impl reference
             the reference's own per-frame CPU path (tools/trainer.py:166-191: 256-point
             cv2.solvePnPRansac + ADD(-S)) restated in oracle/ref_callsites.py around the real cv2,
@@ -22,6 +24,7 @@ Nothing here reads /root/reference at run time.
 from __future__ import annotations
 
 import argparse
+import ctypes as C
 import json
 import multiprocessing as mp
 import os
@@ -262,12 +265,18 @@ def ours_arm(args):
     barrier()
     evs = []
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    lib = _lib.load()
+    lib.pb_stage_timing(1)                          # CUDA events around the three RANSAC launches
     barrier()
     e0.record()
     for _ in range(args.steps):
         one_step(evs)
     e1.record()
     barrier()
+    ms3, ncalls = (C.c_float * 3)(), C.c_int(0)
+    lib.pb_stage_timing_read(ms3, C.byref(ncalls))
+    lib.pb_stage_timing(0)
+    hyp_ms, score_ms, final_ms = float(ms3[0]), float(ms3[1]), float(ms3[2])
     ms_total = e0.elapsed_time(e1)
     tmax = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
@@ -277,13 +286,63 @@ def ours_arm(args):
     value = world * F * args.steps / (ms_total * 1e-3)
     stage_ms = [statistics.fmean(ev[i].elapsed_time(ev[i + 1]) for ev in evs) for i in range(4)]
     k0_ms = stage_ms[0]
-    algo_bytes = F * MAP_BYTES_PER_FRAME + inp["n_px"] * 20
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
-        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+        hbm_peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
     else:
-        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
-    achieved = algo_bytes / (k0_ms * 1e-3) / 1e9
+        hbm_peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+    traffic = {}
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath))
+
+    def timed(fn, n):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize(dev)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(n):
+            fn()
+        a1.record()
+        torch.cuda.synchronize(dev)
+        return a0.elapsed_time(a1) / n
+
+    # FP32 FMA peak of this GPU right now (scalar FFMA and packed FFMA2 probes; the larger one is the peak)
+    probe_out = torch.zeros(4, dtype=torch.float32, device=dev)
+    stream_ptr = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    ctas, iters = 148 * 8, 4096
+    fp32_peak = 0.0
+    fp32_probe = {}
+    for packed in (0, 1):
+        ms = timed(lambda: lib.pb_probe_fma(ctas, iters, packed, C.c_void_p(probe_out.data_ptr()), stream_ptr), 5)
+        tf = ctas * 256 * iters * 8 * 2 * (2 if packed else 1) / (ms * 1e-3) / 1e12
+        fp32_probe["ffma2" if packed else "ffma"] = tf
+        fp32_peak = max(fp32_peak, tf)
+    # maskless K0 (every pixel streamed: the HBM-roofline kernel of SURVEY.md 8(d)), timed on the same maps
+    dense = ops.MapCompactor(F, H, W, CAP, device=dev)
+    dense_ms = timed(lambda: dense(inp["xyz"], None, inp["extent"], inp["lfborder"]), 10)
+    dense_bytes = F * 480 * 640 * 12 + inp["n_px"] * 20
+    sparse_bytes = F * 480 * 640 + inp["n_px"] * (3 * 32 + 20)
+    score_flop = 27.0 * N_HYP * inp["n_px"]
+    roof_score = {"kernel": "ransac_score_kernel (K3: reprojection scoring of every masked pixel x 256 hypotheses)",
+                  "bound": "fp32", "achieved": score_flop / (score_ms * 1e-3) / 1e12, "peak": fp32_peak,
+                  "unit": "TFLOP/s", "frac": score_flop / (score_ms * 1e-3) / 1e12 / fp32_peak,
+                  "traffic": traffic.get("ransac_score_kernel"),
+                  "peak_source": "FFMA/FFMA2 probe kernel timed in this run (MEASURED_PEAKS.json has no FP32 entry); "
+                                 "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4",
+                  "algorithmic_flop_per_launch": score_flop, "flop_per_hyp_pt": 27, "launch_ms": score_ms,
+                  "note": "FP32-pipe bound (SURVEY.md 8(d)); the kernel executes 14 FMA-pipe instructions per "
+                          "hypothesis*point = 28 flop-slots, so its pipe occupancy is frac*28/27"}
+    roof_k0 = {"kernel": "compact_sparse_kernel (K0 mask-first: mask stream + foreground sector gather)",
+               "bound": "hbm", "achieved": sparse_bytes / (k0_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+               "frac": sparse_bytes / (k0_ms * 1e-3) / 1e9 / hbm_peak, "traffic": traffic.get("compact_sparse_kernel"),
+               "peak_source": peak_src, "algorithmic_bytes_per_launch": sparse_bytes, "launch_ms": k0_ms,
+               "note": "algorithmic bytes = 1 B/px mask + per foreground px 3 x 32 B sectors read + 20 B written"}
+    roof_dense = {"kernel": "compact_kernel (K0 maskless: all three planes streamed; not part of the timed step)",
+                  "bound": "hbm", "achieved": dense_bytes / (dense_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                  "frac": dense_bytes / (dense_ms * 1e-3) / 1e9 / hbm_peak, "traffic": traffic.get("compact_kernel"),
+                  "peak_source": peak_src, "algorithmic_bytes_per_launch": dense_bytes, "launch_ms": dense_ms}
 
     # ---- end to end from pinned host memory --------------------------------------------------------
     xyz_h = torch.empty((F, 3, H, W), dtype=torch.float32).pin_memory()
@@ -350,13 +409,15 @@ def ours_arm(args):
                                             "api": "HostEvalSweep.run(zero_copy=False): whole maps copied H2D in "
                                                    "128-frame chunks overlapped with compute"}},
             "gpu_launches": args.steps * sw.launches_per_step,
-            "kernels_per_step": ["compact_kernel", "ransac_score_kernel", "ransac_finalize_kernel",
-                                 "pose_metrics_kernel", "accumulate_kernel"],
+            "kernels_per_step": ["compact_sparse_kernel", "ransac_hypothesis_kernel", "ransac_score_kernel",
+                                 "ransac_finalize_kernel", "pose_metrics_kernel", "accumulate_kernel"],
             "stage_ms": dict(zip(sw.STAGES, stage_ms)),
-            "roofline": {"kernel": "compact_kernel (K0: map stream + mask compaction + de-normalise)",
-                         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": algo_bytes, "launch_ms": k0_ms},
+            "kernel_ms": {"compact_sparse_kernel": k0_ms, "ransac_hypothesis_kernel": hyp_ms,
+                          "ransac_score_kernel": score_ms, "ransac_finalize_kernel": final_ms,
+                          "pose_metrics_kernel": stage_ms[2], "accumulate_kernel": stage_ms[3]},
+            "roofline": roof_score,                 # the dominant kernel of the step
+            "roofline_all": [roof_score, roof_k0, roof_dense],
+            "fp32_probe_tflops": fp32_probe,
             "cpu_baseline": cpu_base,
             "clocks": clocks,
             "accuracy": {"succ_add": summ["succ_base_rt"], "succ_r5deg": summ["succ_base_r"],

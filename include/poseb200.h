@@ -153,6 +153,18 @@ int pb_pose_loss_bwd(const float* pred, const float* model, const float* target,
  * t[b,:] = mean_i (cloud[b,i,:] + t_res[b,:,i]);  cloud [B,NP,3], t_res [B,3,NP].               */
 int pb_vote_translation(const float* cloud, const float* t_res, int B, int NP, float* t, void* stream);
 
+/* ---- measurement probe (no reference counterpart) ----------------------------------------------
+ * Sustained FP32 FMA rate: ctas CTAs x 256 threads x iters x 8 independent FMAs (x2 lanes when
+ * packed != 0, FFMA2).  Timed by the caller with CUDA events; bench.py uses it as the denominator
+ * of the scoring kernel's FP32 roofline (MEASURED_PEAKS.json has HBM and bf16 peaks only).        */
+int pb_probe_fma(int ctas, int iters, int packed, float* out, void* stream);
+
+/* Per-kernel timing of pb_pnp_ransac_pts: while enabled, every call records CUDA events on its
+ * stream around its three launches (hypotheses | scoring | finalize; up to 256 calls).
+ * pb_stage_timing_read waits for them and returns the mean milliseconds per call (host pointers). */
+int pb_stage_timing(int enable);
+int pb_stage_timing_read(float* ms3 /*host [3]*/, int* calls /*host*/);
+
 #ifdef __cplusplus
 }
 #endif

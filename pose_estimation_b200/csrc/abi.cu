@@ -23,6 +23,50 @@ int pb_check_launch(const char* what) {
     return 0;
 }
 
+// ---- optional per-kernel timing of the RANSAC call (CUDA events recorded on the caller's stream) ----
+namespace {
+constexpr int TIM_SLOTS = 256, TIM_MARKS = 4;     // marks: before hyp | before score | before finalize | after
+bool g_tim_on = false;
+int g_tim_calls = 0;
+cudaEvent_t g_tim_ev[TIM_SLOTS][TIM_MARKS];
+bool g_tim_made = false;
+}
+
+void pb_stage_mark(int mark, cudaStream_t st) {
+    if (!g_tim_on || g_tim_calls >= TIM_SLOTS) return;
+    cudaEventRecord(g_tim_ev[g_tim_calls][mark], st);
+    if (mark == TIM_MARKS - 1) ++g_tim_calls;
+}
+
+extern "C" int pb_stage_timing(int enable) {
+    if (enable && !g_tim_made) {
+        for (int i = 0; i < TIM_SLOTS; ++i)
+            for (int k = 0; k < TIM_MARKS; ++k)
+                if (cudaEventCreate(&g_tim_ev[i][k]) != cudaSuccess) { pb_set_error("pb_stage_timing: cudaEventCreate failed"); return -2; }
+        g_tim_made = true;
+    }
+    g_tim_on = enable != 0;
+    g_tim_calls = 0;
+    return 0;
+}
+
+extern "C" int pb_stage_timing_read(float* ms3, int* calls) {
+    PB_REQUIRE(ms3 && calls, "pb_stage_timing_read: null pointer argument");
+    double acc[TIM_MARKS - 1] = {0, 0, 0};
+    const int n = g_tim_calls;
+    for (int i = 0; i < n; ++i) {
+        if (cudaEventSynchronize(g_tim_ev[i][TIM_MARKS - 1]) != cudaSuccess) { pb_set_error("pb_stage_timing_read: sync failed"); return -2; }
+        for (int k = 0; k + 1 < TIM_MARKS; ++k) {
+            float ms = 0.0f;
+            cudaEventElapsedTime(&ms, g_tim_ev[i][k], g_tim_ev[i][k + 1]);
+            acc[k] += ms;
+        }
+    }
+    for (int k = 0; k + 1 < TIM_MARKS; ++k) ms3[k] = n ? (float)(acc[k] / n) : 0.0f;
+    *calls = n;
+    return 0;
+}
+
 extern "C" const char* pb_last_error(void) { return g_err; }
 extern "C" int pb_abi_version(void) { return PB_ABI_VERSION; }
 

@@ -14,6 +14,7 @@
 
 void pb_set_error(const char* fmt, ...);
 int pb_check_launch(const char* what);
+void pb_stage_mark(int mark, cudaStream_t st);   // no-op unless pb_stage_timing(1) (abi.cu)
 
 #define PB_REQUIRE(cond, ...)                 \
     do {                                      \

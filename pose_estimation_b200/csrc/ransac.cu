@@ -395,6 +395,7 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     fa.status = status; fa.inl_bitmap = inl_bitmap; fa.R0 = R0; fa.t0 = t0;
     fa.cap = cap; fa.H = prm->n_hyp; fa.HS = p.HS; fa.gn_iters = prm->gn_iters; fa.lo_rounds = prm->lo_rounds;
     fa.min_inliers = prm->min_inliers; fa.inv_thr = sa.inv_thr;
+    pb_stage_mark(2, st);
     // warps per frame: the largest G whose CTAs are ALL resident at once (120 registers per thread:
     // 2 / 4 / 8 / 17 CTAs per SM for G = 8 / 4 / 2 / 1), so a batch is one wave with no tail; results
     // do not depend on G.
@@ -404,6 +405,7 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     else if (F <= 148 * 8) rcf = launch_finalize<2>(fa, F, p.smem_final, st);
     else rcf = launch_finalize<1>(fa, F, p.smem_final, st);
     if (rcf) return -2;
+    pb_stage_mark(3, st);
     return 0;
 }
 

@@ -249,8 +249,10 @@ int launch(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
 
 int pb_launch_score(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
     const long long nh = (long long)F * a.H;
+    pb_stage_mark(0, st);
     ransac_hypothesis_kernel<<<(unsigned)((nh + HT - 1) / HT), HT, 0, st>>>(a);
     if (pb_check_launch("ransac_hypothesis_kernel")) return 1;
+    pb_stage_mark(1, st);
     switch (p.NHL) {
         case 1: return launch<1>(a, p, F, st);
         case 2: return launch<2>(a, p, F, st);

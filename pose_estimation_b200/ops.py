@@ -165,7 +165,7 @@ class MapCompactor:
 class PtsRansac:
     """Reusable K1-K4 launcher with persistent outputs and workspace."""
 
-    launches = 2
+    launches = 3      # hypotheses, scoring, finalize
 
     def __init__(self, F, cap, cfg: RansacConfig | None = None, device="cuda"):
         self.F, self.cap = F, cap

@@ -1,0 +1,99 @@
+#!/usr/bin/env python
+"""bench_configs.py -- the other BASELINE.json configs (C3 KNN / ADD-S / symmetric-KNN loss, C4 dense
+correspondences + T-vote), measured with CUDA events on one B200.  bench.py stays the contract
+benchmark (C2); this script only fills BASELINE.md's table.  One JSON line per config."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+from pose_estimation_b200 import ops, ops_metric, synth  # noqa: E402
+
+
+def timed(fn, n, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(n):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / n
+
+
+def c3(args, dev):
+    """eggbox / glue: B pose pairs, N = M = 2620 model points: KNN indices, ADD-S, PoseLoss value."""
+    B, N = args.c3_batch, 2620
+    rng = np.random.default_rng(3)
+    models = synth.class_models(N)
+    cls = np.where(np.arange(B) % 2 == 0, 7, 8)
+    model = torch.from_numpy(models[cls]).to(dev)                        # [B,N,3]
+    q = rng.normal(size=(B, 4)); q /= np.linalg.norm(q, axis=1, keepdims=True)
+    Rg = np.stack([synth.random_rotation(np.random.default_rng(i)) for i in range(B)]).astype(np.float32)
+    tg = (rng.normal(size=(B, 3)) * 0.05 + [0, 0, 0.9]).astype(np.float32)
+    ang = np.radians(rng.uniform(0, 10, B)); ax = rng.normal(size=(B, 3)); ax /= np.linalg.norm(ax, axis=1, keepdims=True)
+    Kx = np.zeros((B, 3, 3)); Kx[:, 0, 1] = -ax[:, 2]; Kx[:, 0, 2] = ax[:, 1]; Kx[:, 1, 0] = ax[:, 2]
+    Kx[:, 1, 2] = -ax[:, 0]; Kx[:, 2, 0] = -ax[:, 1]; Kx[:, 2, 1] = ax[:, 0]
+    dR = np.eye(3)[None] + np.sin(ang)[:, None, None] * Kx + (1 - np.cos(ang))[:, None, None] * (Kx @ Kx)
+    R = (dR @ Rg).astype(np.float32)
+    t = (tg + rng.normal(size=(B, 3)) * 0.005).astype(np.float32)
+    Rt, tt, Rgt, tgt = (torch.from_numpy(a).to(dev) for a in (R, t, Rg, tg))
+    pred = ops_metric.transform_points(model, Rt, tt)
+    target = ops_metric.transform_points(model, Rgt, tgt)
+    sym = torch.ones(B, dtype=torch.uint8, device=dev)
+    out = {}
+    ms = timed(lambda: ops_metric.knn1(pred, target), args.iters)
+    out["knn1"] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3)}
+    ms = timed(lambda: ops_metric.add_adds(pred, target, None), args.iters)
+    out["add_adds"] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3)}
+    ms = timed(lambda: ops_metric.pose_loss_fwd(Rt, tt, model, target, sym), args.iters)
+    out["pose_loss_fwd"] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3)}
+    print(json.dumps({"config": "C3", "batch": B, "N": N, "pairs": B * N * N, **out}), flush=True)
+
+
+def c4(args, dev):
+    """F frames, P = 10k correspondences, H = 1024 hypotheses, 5 re-score/refit rounds, T-vote on 10k points."""
+    F, cap, H = args.c4_frames, 10240, 1024
+    sps = synth.make_batch_sparse(0x5EED, 4, min(F, 16), p_range=(10000, 10000), outlier_frac=0.3)
+    pts = np.zeros((F, 5, cap), np.float32); cnt = np.zeros(F, np.int32)
+    for f in range(F):
+        p = synth.compact_points(sps[f % len(sps)])
+        n = min(p.shape[1], cap); pts[f, :, :n] = p[:, :n]; cnt[f] = n
+    K4 = torch.from_numpy(np.tile(synth.LINEMOD_K4, (F, 1))).to(dev)
+    pts_d, cnt_d = torch.from_numpy(pts).to(dev), torch.from_numpy(cnt).to(dev)
+    rs = ops.PtsRansac(F, cap, ops.RansacConfig(n_hyp=H, lo_rounds=5), device=dev)
+    ms = timed(lambda: rs(pts_d, cnt_d, K4), args.iters)
+    hp = float(H) * float(cnt.sum())
+    NP = 10000
+    cloud = torch.randn(F, NP, 3, device=dev); tres = torch.randn(F, 3, NP, device=dev)
+    ms_v = timed(lambda: ops_metric.vote_translation(cloud, tres), args.iters)
+    print(json.dumps({"config": "C4", "frames": F, "P_mean": float(cnt.mean()), "n_hyp": H, "lo_rounds": 5,
+                      "ransac_ms": ms, "frames_per_s": F / (ms * 1e-3), "hyp_pts_per_s": hp / (ms * 1e-3),
+                      "vote_ms": ms_v, "vote_GBps": F * NP * 24 / (ms_v * 1e-3) / 1e9}), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--c3-batch", type=int, default=4096)
+    ap.add_argument("--c4-frames", type=int, default=256)
+    ap.add_argument("--only", default="")
+    args = ap.parse_args()
+    dev = torch.device("cuda:0")
+    if args.only in ("", "c3"):
+        c3(args, dev)
+    if args.only in ("", "c4"):
+        c4(args, dev)
+
+
+if __name__ == "__main__":
+    main()

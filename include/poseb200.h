@@ -159,6 +159,11 @@ int pb_vote_translation(const float* cloud, const float* t_res, int B, int NP, f
  * of the scoring kernel's FP32 roofline (MEASURED_PEAKS.json has HBM and bf16 peaks only).        */
 int pb_probe_fma(int ctas, int iters, int packed, float* out, void* stream);
 
+/* tcgen05 self test: D[128,128] f32 = A[128,32] * B[128,32]^T for bf16 operands given in the canonical
+ * no-swizzle K-major tile layout [kc 0..3][row 0..127][8 bf16] (the layout pb_knn1's tensor-core
+ * path stages); err (device int) is set when the completion barrier timed out.                     */
+int pb_tc_selftest(const void* A, const void* B, float* D, int* err, void* stream);
+
 /* Per-kernel timing of pb_pnp_ransac_pts: while enabled, every call records CUDA events on its
  * stream around its three launches (hypotheses | scoring | finalize; up to 256 calls).
  * pb_stage_timing_read waits for them and returns the mean milliseconds per call (host pointers). */

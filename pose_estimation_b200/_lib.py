@@ -47,6 +47,7 @@ SIGNATURES = {
     "pb_pose_loss_bwd": (I, [P, P, P, P, I, I, F32, P, P, P]),
     "pb_vote_translation": (I, [P, P, I, I, P, P]),
     "pb_probe_fma": (I, [I, I, I, P, P]),
+    "pb_tc_selftest": (I, [P, P, P, P, P]),
     "pb_stage_timing": (I, [I]),
     "pb_stage_timing_read": (I, [P, P]),
 }

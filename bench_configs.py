@@ -51,8 +51,14 @@ def c3(args, dev):
     target = ops_metric.transform_points(model, Rgt, tgt)
     sym = torch.ones(B, dtype=torch.uint8, device=dev)
     out = {}
-    ms = timed(lambda: ops_metric.knn1(pred, target), args.iters)
-    out["knn1"] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3)}
+    ms = timed(lambda: ops_metric.knn1(pred, target, impl="simt"), args.iters)
+    out["knn1_simt"] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3)}
+    ms = timed(lambda: ops_metric.knn1(pred, target, impl="tc"), args.iters)
+    st = ops_metric.LAST_TC_STATS.cpu().tolist()
+    out["knn1_tc"] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3), "fallback_rows": st[1],
+                      "exact_evals_per_row": st[2] / (B * N), "timeout": st[0]}
+    same = bool(torch.equal(ops_metric.knn1(pred, target, impl="tc"), ops_metric.knn1(pred, target, impl="simt")))
+    out["tc_equals_simt"] = same
     ms = timed(lambda: ops_metric.add_adds(pred, target, None), args.iters)
     out["add_adds"] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3)}
     ms = timed(lambda: ops_metric.pose_loss_fwd(Rt, tt, model, target, sym), args.iters)

@@ -111,6 +111,13 @@ int pb_resample_inliers(const uint32_t* inl_bitmap, const int32_t* count, int F,
 int pb_knn1(const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx, float* d2,
             void* stream);
 
+/* Tensor-core path of the same handle: tiled tcgen05 contraction (|q|^2 - 2 p.q from exact 3-way
+ * bf16 splits, FP32 accumulate in TMEM) + exact FP32 re-rank of the candidates, so idx / d2 are
+ * identical to pb_knn1's (csrc/knn_tc.cu).  ws: pb_knn1_tc_workspace_bytes(B,N,M), 128-byte aligned. */
+size_t pb_knn1_tc_workspace_bytes(int B, int N, int M);
+int pb_knn1_tc(const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx, float* d2,
+               void* ws, size_t ws_bytes, void* stream);
+
 /* replaces Metric.cal_adds_cuda (lib/utils/metric.py:17-36): add[b] = mean_i |pred_i - tgt_i|;
  * adds[b] = mean_i min_j |pred_j - tgt_i| computed where want_adds[b] != 0 (NULL -> all),
  * else adds[b] = add[b].  pred/target [B,N,3].                                                  */

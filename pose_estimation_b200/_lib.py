@@ -39,6 +39,8 @@ SIGNATURES = {
     "pb_pnp_ransac_map": (I, [P, P, P, P, P, P, I, I, I, I, U32, PRM, P, P, P, P, P, P, P, SZ, P]),
     "pb_resample_inliers": (I, [P, P, I, I, I, U32, U32, U32, P, P]),
     "pb_knn1": (I, [P, P, I, I, I, I, P, P, P]),
+    "pb_knn1_tc_workspace_bytes": (SZ, [I, I, I]),
+    "pb_knn1_tc": (I, [P, P, I, I, I, I, P, P, P, SZ, P]),
     "pb_add_adds": (I, [P, P, I, I, P, P, P, P]),
     "pb_transform_points": (I, [P, I, P, P, I, I, P, P]),
     "pb_pose_metrics": (I, [P, P, P, P, P, P, P, P, I, I, I, P, P, P, P]),

@@ -14,8 +14,16 @@ VARIANTS = ("base", "reg", "final")
 VARIANT_COLS = ("succ_{}_rt", "dis_{}_rt", "succ_{}_r", "dis_{}_r", "succ_{}_t", "dis_{}_t")
 
 
-def knn1(x, y, want_d2=False):
-    """x [B,N,3] or [N,3]; y [B,M,3], [M,3] (shared) -> idx int64 [B,N] (and d2 f32)."""
+TC_MIN_PAIRS = 1 << 18     # below this many pairs per problem the SIMT kernel wins (tile padding, prepare pass)
+
+
+LAST_TC_STATS = None       # device int32 [4] of the last tensor-core call: timeout flag, fallback rows, exact evaluations
+
+
+def knn1(x, y, want_d2=False, impl="auto"):
+    """x [B,N,3] or [N,3]; y [B,M,3], [M,3] (shared) -> idx int64 [B,N] (and d2 f32).
+    impl: "tc" = tcgen05 contraction + exact FP32 re-rank, "simt" = exact FP32 scan, "auto" picks by
+    size; both return identical indices."""
     x = _chk(x, torch.float32, "x")
     y = _chk(y, torch.float32, "y")
     squeeze = x.dim() == 2
@@ -30,7 +38,23 @@ def knn1(x, y, want_d2=False):
     M = y.shape[-2]
     idx = torch.empty((B, N), dtype=torch.int64, device=x.device)
     d2 = torch.empty((B, N), dtype=torch.float32, device=x.device) if want_d2 else None
-    call("pb_knn1", _ptr(x), _ptr(y), B, N, M, y_shared, _ptr(idx), _ptr(d2), _stream())
+    if impl not in ("auto", "tc", "simt"):
+        raise ValueError("impl must be auto, tc or simt")
+    use_tc = impl == "tc" or (impl == "auto" and N * M >= TC_MIN_PAIRS)
+    if use_tc:
+        from . import _lib
+        nb = _lib.load().pb_knn1_tc_workspace_bytes(B, N, M)
+        ws = torch.empty(nb + 128, dtype=torch.uint8, device=x.device)
+        off = (-ws.data_ptr()) % 128
+        import ctypes as C
+        call("pb_knn1_tc", _ptr(x), _ptr(y), B, N, M, y_shared, _ptr(idx), _ptr(d2),
+             C.c_void_p(ws.data_ptr() + off), nb, _stream())
+        global LAST_TC_STATS
+        nbm = min(B, 256)
+        tiles = ((N + 127) // 128 + (M + 127) // 128) * 8192
+        LAST_TC_STATS = ws[off + nbm * tiles + nbm * 16: off + nbm * tiles + nbm * 16 + 16].view(torch.int32)
+    else:
+        call("pb_knn1", _ptr(x), _ptr(y), B, N, M, y_shared, _ptr(idx), _ptr(d2), _stream())
     if squeeze:
         idx = idx[0]
         d2 = d2[0] if want_d2 else None

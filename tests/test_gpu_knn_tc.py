@@ -29,3 +29,51 @@ def test_tcgen05_selftest_matches_numpy(dev):
     torch.cuda.synchronize()
     assert int(err.item()) == 0
     assert torch.allclose(D.cpu().double(), want, atol=1e-4, rtol=1e-5)
+
+
+def _brute(x, y):
+    """FP32 SqDist argmin with the oracle's operation order (dx*dx, fma dy, fma dz), lowest j on ties."""
+    from oracle import cref
+    return cref.knn1(x, y)
+
+
+@pytest.mark.parametrize("B,N,M,scale", [(3, 500, 500, 0.1), (2, 2620, 2620, 0.1), (1, 1000, 130, 1.0),
+                                         (4, 37, 1, 0.1), (1, 129, 257, 5.0)])
+def test_knn_tc_indices_equal_exact_fp32(dev, B, N, M, scale):
+    from pose_estimation_b200 import ops_metric
+    rng = np.random.default_rng(N * 7 + M)
+    x = (rng.random((B, N, 3)) * scale + 0.7).astype(np.float32)          # offset: the centring must cope
+    y = (rng.random((B, M, 3)) * scale + 0.7).astype(np.float32)
+    if N > 10 and M > 10:
+        y[0, 5] = y[0, 3]                       # exact duplicate database points: lowest index wins
+        x[0, 1] = y[0, 3]                       # a query sitting exactly on them
+        y[0, 9] = y[0, 3] + np.float32(1e-7)    # and a near tie
+    xt, yt = torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev)
+    idx_tc, d2_tc = ops_metric.knn1(xt, yt, want_d2=True, impl="tc")
+    idx_si, d2_si = ops_metric.knn1(xt, yt, want_d2=True, impl="simt")
+    stats = ops_metric.LAST_TC_STATS.cpu().numpy()
+    assert stats[0] == 0                                                 # no barrier timeout
+    if M >= 100 and scale <= 1.0:                                        # the tensor path did the work:
+        assert stats[1] <= 0.01 * B * N                                  #   hardly any exact-scan fallback rows
+        assert stats[2] <= 3 * B * N                                     #   and a few exact evaluations per row
+    assert torch.equal(idx_tc, idx_si) and torch.equal(d2_tc, d2_si)     # the two device paths: bit-identical
+    for b in range(B):
+        ref_idx, ref_d2 = _brute(x[b], y[b])
+        assert np.array_equal(idx_tc[b].cpu().numpy(), ref_idx)
+        assert np.array_equal(d2_tc[b].cpu().numpy(), ref_d2)
+
+
+def test_knn_tc_shared_database_and_adversarial_order(dev):
+    """y shared by all batch elements; database sorted by decreasing distance from the queries (every
+    column a new running minimum: candidate lists overflow and rows fall back to the exact scan)."""
+    from pose_estimation_b200 import ops_metric
+    rng = np.random.default_rng(5)
+    N, M = 300, 1500
+    y = np.zeros((M, 3), np.float32)
+    y[:, 0] = np.linspace(2.0, 0.01, M)
+    x = (rng.normal(size=(2, N, 3)) * 1e-3).astype(np.float32)
+    xt, yt = torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev)
+    idx_tc = ops_metric.knn1(xt, yt, impl="tc")
+    idx_si = ops_metric.knn1(xt, yt, impl="simt")
+    assert torch.equal(idx_tc, idx_si)
+    assert (idx_tc == M - 1).float().mean() > 0.9

@@ -48,7 +48,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if not os.path.exists(src):
             continue
         obj = os.path.join(HERE, "build", s.replace(".cu", ".o"))
-        cmd = [nvcc, *NVCC_FLAGS, "-c", src, "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("PB_EXTRA_NVCC", "").split(), "-c", src, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

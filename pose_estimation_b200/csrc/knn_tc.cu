@@ -10,10 +10,10 @@
 //            row carries the 27 cross products of the three coordinates plus |q|^2 (three bf16),
 //            so two K=16 tcgen05.mma (kind::f16, M=128, N=128, FP32 accumulate in TMEM) give s~ to
 //            within E ~ 1e-5 R^2 (R = cloud radius), dominated by the accumulation, not by bf16.
-//   epilogue one thread per query row reads its 128 scores per tile with tcgen05.ld (32x32b.x32),
-//            reduces each chunk of 32 with 3-input minima (FMNMX3, 0.56 ALU op per pair) and only
-//            when a chunk dips below  running-min + T  (T = 2^-13 R^2 >> 2E) looks at single
-//            columns; those candidates go to a short per-row list in shared memory.
+//   epilogue two threads per query row (64 columns of the tile each) read their scores with
+//            tcgen05.ld (32x32b.x32), reduce each chunk of 32 with 3-input minima (FMNMX3, 0.56 ALU
+//            op per pair) and only when a group of 8 dips below  running-min + T  (T = 2^-13 R^2 >> 2E)
+//            look at single columns; those candidates go to a short per-thread list in shared memory.
 //   re-rank  after the sweep the candidates within T of the final minimum (a provable superset of
 //            the FP32 argmin) are re-evaluated with the exact FP32 formula; rows whose list
 //            overflowed fall back to an exact scan.
@@ -156,169 +156,248 @@ struct MainArgs {
     int* err;
 };
 
-constexpr int CAND = 24;   // candidate slots per query row
+constexpr int CAND = 8;            // ring slots of flagged chunks per epilogue thread
+constexpr int NWG = 2;             // epilogue warpgroups = TMEM accumulators: warpgroup g owns the tiles v = g (mod NWG)
+constexpr int EPI_T = NWG * TM;    // 256 epilogue threads: thread = (query row tid & 127, warpgroup tid >> 7)
+constexpr int KT2 = EPI_T + 64;    // + warp 8 (MMA issuer, TMEM owner) + warp 9 (bulk-copy producer)
+constexpr int NACC = NWG;
+constexpr int NSTG = 6;            // shared-memory stages of database tiles (48 KB in flight per CTA)
+constexpr int TMEM_COLS = NACC * TM;   // 256 columns: two CTAs share an SM's 512
 
 __device__ __forceinline__ float fmin3(float a, float b, float c) {
     float d;
     asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
     return d;
 }
+// minimum of 8 consecutive scores: four 3-input minima (FMNMX3)
+__device__ __forceinline__ float group_min(const uint32_t* r) {
+    const float* v = reinterpret_cast<const float*>(r);
+    return fmin3(fmin3(v[0], v[1], v[2]), fmin3(v[3], v[4], v[5]), fminf(v[6], v[7]));
+}
 
-// grid (row tiles, batch elements of the chunk); 128 threads: thread <-> query row of the tile
-__global__ void __launch_bounds__(TM) knn_tc_kernel(MainArgs a) {
+#ifdef PB_TC_DEBUG
+__device__ unsigned long long g_tcdbg[256 * 8];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define TCDBG(slot) do { if (blockIdx.x == 0 && blockIdx.y < 256) g_tcdbg[blockIdx.y * 8 + (slot)] = gtime(); } while (0)
+#else
+#define TCDBG(slot) do {} while (0)
+#endif
+
+// One flagged group (8 consecutive columns from j0) of a query row: exact FP32 distances, lowest index on ties.
+__device__ __forceinline__ void exact_group(const float* __restrict__ yb, int M, int j0, float qx, float qy, float qz,
+                                            float& best, int& bidx, int& nexact) {
+    float p[8][3];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const int j = j0 + c < M ? j0 + c : M - 1;                 // clamped loads, all in flight together
+#pragma unroll
+        for (int k = 0; k < 3; ++k) p[c][k] = yb[3 * (size_t)j + k];
+    }
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const int j = j0 + c;
+        if (j < M) {
+            const float d = sqdist3(qx, qy, qz, p[c][0], p[c][1], p[c][2]);
+            ++nexact;
+            if (d < best || (d == best && j < bidx)) { best = d; bidx = j; }
+        }
+    }
+}
+
+// grid (row tiles, batch elements of the chunk), 320 threads, two CTAs per SM.  Warp-specialised:
+//   warps 0-7  epilogue: warpgroup g = warp / 4 reads accumulator g (its thread t owns query row t & 127);
+//   warp 8     issues the MMAs of tile v into accumulator v % NACC, owns the TMEM allocation;
+//   warp 9     streams the database tiles through NSTG shared-memory stages with 1-D TMA bulk copies.
+// All hand-offs are mbarriers; the tile loop has no CTA-wide barrier.
+__global__ void __launch_bounds__(KT2, 2) knn_tc_kernel(MainArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint4* sA = reinterpret_cast<uint4*>(smem_raw);                    // [TILE_U4]
-    uint4* sB = sA + TILE_U4;                                          // [2][TILE_U4]
-    float* cval = reinterpret_cast<float*>(sB + 2 * TILE_U4);          // [CAND][TM] candidate scores
-    int* ccol = reinterpret_cast<int*>(cval + CAND * TM);              // [CAND][TM] candidate columns
-    __shared__ __align__(8) uint64_t bar_load[2], bar_mma[2], bar_a;
+    uint4* sB = sA + TILE_U4;                                          // [NSTG][TILE_U4]
+    float* lval_all = reinterpret_cast<float*>(sB + NSTG * TILE_U4);   // [CAND][EPI_T] chunk minimum
+    uint32_t* lid_all = reinterpret_cast<uint32_t*>(lval_all + CAND * EPI_T);   // [CAND][EPI_T] chunk << 4 | group mask
+    __shared__ __align__(8) uint64_t bar_load[NSTG], bar_sfree[NSTG], bar_mma[NACC], bar_free[NACC], bar_a;
     __shared__ uint32_t tmem_base;
+    __shared__ float s_mrun[EPI_T];
+    __shared__ float s_best[EPI_T];
+    __shared__ int s_bidx[EPI_T];
+    __shared__ int s_rowbad[EPI_T];
+    __shared__ int s_bad;
 
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int rt = blockIdx.x, bl = blockIdx.y, b = a.b0 + bl;
     const uint4* Ag = a.Aop + ((size_t)bl * a.ntN + rt) * TILE_U4;
     const uint4* Bg = a.Bop + (size_t)bl * a.ntM * TILE_U4;
     const int ntM = a.ntM;
 
     if (tid == 0) {
-        tc::mbar_init(&bar_load[0], 1); tc::mbar_init(&bar_load[1], 1);
-        tc::mbar_init(&bar_mma[0], 1); tc::mbar_init(&bar_mma[1], 1);
+        TCDBG(0);
+        for (int i = 0; i < NSTG; ++i) { tc::mbar_init(&bar_load[i], 1); tc::mbar_init(&bar_sfree[i], 1); }
+        for (int i = 0; i < NACC; ++i) { tc::mbar_init(&bar_mma[i], 1); tc::mbar_init(&bar_free[i], 4); }
         tc::mbar_init(&bar_a, 1);
+        s_bad = 0;
         tc::fence_mbar_init();
     }
-    if (warp == 0) tc::tmem_alloc<256>(&tmem_base);
+    if (warp == 8) tc::tmem_alloc<TMEM_COLS>(&tmem_base);
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem = tmem_base;
-    const uint32_t idesc = tc::idesc_bf16_f32(TM, TM);
     bool ok = true;
+    if (tid == 0) TCDBG(1);
 
-    auto issue_mma = [&](int tile) {       // thread 0: D[acc tile&1] = A * B[tile&1]^T  (two K=16 steps)
-        const uint32_t acc = tmem + (uint32_t)(tile & 1) * TM;
-        const uint32_t sb = tc::smem_u32(sB + (tile & 1) * TILE_U4);
-#pragma unroll
-        for (int k = 0; k < 2; ++k)
-            tc::mma_bf16(acc, tc::smem_desc(tc::smem_u32(sA) + k * 2 * TM * 16, TM * 16, 128),
-                         tc::smem_desc(sb + k * 2 * TM * 16, TM * 16, 128), idesc, k > 0);
-        tc::mma_commit(&bar_mma[tile & 1]);
-    };
-    auto issue_load = [&](int tile) {      // thread 0: bulk copy of database tile `tile`
-        tc::mbar_expect_tx(&bar_load[tile & 1], TILE_BYTES);
-        tc::bulk_g2s(sB + (tile & 1) * TILE_U4, Bg + (size_t)tile * TILE_U4, TILE_BYTES, &bar_load[tile & 1]);
-    };
-
-    if (tid == 0) {
-        tc::mbar_expect_tx(&bar_a, TILE_BYTES);
-        tc::bulk_g2s(sA, Ag, TILE_BYTES, &bar_a);
-        issue_load(0);
-        if (ntM > 1) issue_load(1);
-        ok = tc::mbar_wait(&bar_a, 0) && tc::mbar_wait(&bar_load[0], 0);
-        tc::fence_after_sync();
-        issue_mma(0);
-    }
-
-    const int row = rt * TM + tid;
-    const float T = a.tol[bl];
-    float m_run = INFINITY, thr = INFINITY;    // running minimum of s~ and m_run + T
-    int ncand = 0;
-    const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-
-    for (int n = 0; n < ntM; ++n) {
-        ok = tc::mbar_wait(&bar_mma[n & 1], (uint32_t)(n >> 1) & 1u) && ok;
-        tc::fence_after_sync();
-        if (tid == 0) {
-            if (n + 1 < ntM) {
-                ok = tc::mbar_wait(&bar_load[(n + 1) & 1], (uint32_t)((n + 1) >> 1) & 1u) && ok;
+    if (warp == 9) {
+        // ===== producer
+        if (lane == 0) {
+            tc::mbar_expect_tx(&bar_a, TILE_BYTES);
+            tc::bulk_g2s(sA, Ag, TILE_BYTES, &bar_a);
+            for (int v = 0; v < ntM; ++v) {
+                const int s = v % NSTG;
+                if (v >= NSTG) ok = tc::mbar_wait(&bar_sfree[s], (uint32_t)(v / NSTG - 1) & 1u) && ok;
+                tc::mbar_expect_tx(&bar_load[s], TILE_BYTES);
+                tc::bulk_g2s(sB + s * TILE_U4, Bg + (size_t)v * TILE_U4, TILE_BYTES, &bar_load[s]);
+            }
+            if (!ok) s_bad = 1;
+        }
+    } else if (warp == 8) {
+        // ===== MMA issuer: D[acc v % NACC] = A * B[v % NSTG]^T, two K=16 steps per tile
+        if (lane == 0) {
+            const uint32_t idesc = tc::idesc_bf16_f32(TM, TM);
+            ok = tc::mbar_wait(&bar_a, 0);
+            TCDBG(2);
+            for (int v = 0; v < ntM; ++v) {
+                const int s = v % NSTG, acc = v % NACC;
+                ok = tc::mbar_wait(&bar_load[s], (uint32_t)(v / NSTG) & 1u) && ok;
+                if (v >= NACC) ok = tc::mbar_wait(&bar_free[acc], (uint32_t)(v / NACC - 1) & 1u) && ok;
                 tc::fence_after_sync();
-                issue_mma(n + 1);
+                const uint32_t sb = tc::smem_u32(sB + s * TILE_U4);
+#pragma unroll
+                for (int k = 0; k < 2; ++k)
+                    tc::mma_bf16(tmem + (uint32_t)acc * TM, tc::smem_desc(tc::smem_u32(sA) + k * 2 * TM * 16, TM * 16, 128),
+                                 tc::smem_desc(sb + k * 2 * TM * 16, TM * 16, 128), idesc, k > 0);
+                tc::mma_commit(&bar_mma[acc]);       // accumulator ready -> epilogue
+                tc::mma_commit(&bar_sfree[s]);       // stage consumed     -> producer
+                if (v == 0) TCDBG(3);
             }
-            if (n + 2 < ntM) issue_load(n + 2);    // sB[n&1] is free: MMA n has completed
+            TCDBG(4);
+            // the epilogue has read the last tile of every accumulator -> the TMEM columns can go
+            for (int acc = 0; acc < NACC; ++acc) {
+                const int uses = (ntM - acc + NACC - 1) / NACC;           // tiles that used this accumulator
+                if (uses > 0) ok = tc::mbar_wait(&bar_free[acc], (uint32_t)(uses - 1) & 1u) && ok;
+            }
+            if (!ok) s_bad = 1;
         }
-        // ---- epilogue of tile n: this thread's 128 scores, 32 at a time
-        const uint32_t acc = lane_base + (uint32_t)(n & 1) * TM;
-#pragma unroll 1
-        for (int c0 = 0; c0 < TM; c0 += 32) {
-            uint32_t r[32];
-            tc::tmem_ld32(acc + c0, r);
-            tc::tmem_ld_wait();
-            float g[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const float* v = reinterpret_cast<const float*>(r) + 8 * q;
-                g[q] = fmin3(fmin3(v[0], v[1], v[2]), fmin3(v[3], v[4], v[5]), fminf(v[6], v[7]));
-            }
-            const float cmin = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
-            if (cmin < thr) {
-                // a chunk reaches below running-min + T: tighten the running minimum first, then keep
-                // the single columns below the (new) threshold -- always a superset of "within T of
-                // the final minimum" because the running minimum never drops below the final one
-                if (cmin < m_run) { m_run = cmin; thr = cmin + T; }
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    if (g[q] < thr) {
-#pragma unroll
-                        for (int k = 0; k < 8; ++k) {
-                            const float v = __uint_as_float(r[8 * q + k]);
-                            if (v < thr) {
-                                if (ncand == CAND) {             // full: drop entries the threshold has overtaken
-                                    int w = 0;
-                                    for (int e = 0; e < CAND; ++e) {
-                                        const float cv = cval[e * TM + tid];
-                                        if (cv < thr) { cval[w * TM + tid] = cv; ccol[w * TM + tid] = ccol[e * TM + tid]; ++w; }
-                                    }
-                                    ncand = w;
-                                }
-                                if (ncand < CAND) { cval[ncand * TM + tid] = v; ccol[ncand * TM + tid] = n * TM + c0 + 8 * q + k; ++ncand; }
-                                else ncand = CAND + 1;           // still full: overflow -> exact scan for this row
-                            }
-                        }
-                    }
-                }
-            }
-        }
-        tc::fence_before_sync();
-        __syncthreads();                          // accumulator n&1 may be overwritten by MMA n+2
-    }
-
-    // ---- exact FP32 re-rank of the candidates within T of the minimum (lowest index on ties)
-    if (row < a.N) {
+        __syncwarp();
+        tc::fence_after_sync();
+        tc::tmem_dealloc<TMEM_COLS>(tmem);
+    } else {
+        // ===== epilogue: one sweep.  Per 32-column chunk: minimum by 3-input minima; a chunk whose minimum
+        // is below  running minimum + T  is remembered (ring of CAND) with the mask of its 8-column groups.
+        const int wg = tid >> 7, rloc = tid & (TM - 1);
+        const int row = rt * TM + rloc;
+        float* lval = lval_all + tid;
+        uint32_t* lid = lid_all + tid;
+        const float T = a.tol[bl];
         const float* xb = a.x + (size_t)b * a.N * 3;
         const float* yb = a.y + (a.y_shared ? 0 : (size_t)b * a.M * 3);
-        const float qx = xb[3 * (size_t)row], qy = xb[3 * (size_t)row + 1], qz = xb[3 * (size_t)row + 2];
+        float qx = 0.0f, qy = 0.0f, qz = 0.0f;
+        if (row < a.N) { qx = xb[3 * (size_t)row]; qy = xb[3 * (size_t)row + 1]; qz = xb[3 * (size_t)row + 2]; }
+        float m_run = INFINITY;        // minimum of s~ over the chunks this thread has seen
+        float lost = INFINITY;         // smallest chunk minimum that fell out of the ring
+        int cnt = 0;
+        const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)wg * TM;
+        uint32_t ph = 0;
+        for (int v = wg; v < ntM; v += NWG) {
+            if (tid == 0 && v == NWG) TCDBG(5);
+            ok = tc::mbar_wait(&bar_mma[wg], ph) && ok;
+            ph ^= 1u;
+            tc::fence_after_sync();
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                uint32_t r[64];
+                tc::tmem_ld64(taddr + half * 64, r);
+                tc::tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    float g[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) g[q] = group_min(r + c * 32 + q * 8);
+                    const float cm = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
+                    const float lim_run = m_run + T;
+                    if (cm < lim_run) {
+                        const uint32_t mask = (g[0] < lim_run ? 1u : 0u) | (g[1] < lim_run ? 2u : 0u) |
+                                              (g[2] < lim_run ? 4u : 0u) | (g[3] < lim_run ? 8u : 0u);
+                        const int slot = cnt & (CAND - 1);
+                        if (cnt >= CAND) lost = fminf(lost, lval[slot * EPI_T]);
+                        lval[slot * EPI_T] = cm;
+                        lid[slot * EPI_T] = ((uint32_t)(v * 4 + half * 2 + c) << 4) | mask;
+                        ++cnt;
+                    }
+                    m_run = fminf(m_run, cm);
+                }
+            }
+            tc::fence_before_sync();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&bar_free[wg]);      // this warp is done with the accumulator
+        }
+        if (tid == 0) TCDBG(6);
+        if (!ok) s_bad = 1;
+        s_mrun[tid] = m_run;
+        asm volatile("bar.sync 1, %0;" ::"n"(EPI_T) : "memory");
+        const bool sweep_ok = s_bad == 0;      // written before the barrier by any epilogue thread that timed out
+        // ---- exact FP32 re-rank of the flagged chunks within T of the row minimum (lowest index on ties)
+        float lim = s_mrun[rloc];
+#pragma unroll
+        for (int g = 1; g < NWG; ++g) lim = fminf(lim, s_mrun[rloc + g * TM]);
+        lim += T;
         float best = INFINITY;
-        int bidx = 0;
-        int nexact = 0;
-        if (ncand <= CAND && ok) {
-            for (int k = 0; k < ncand; ++k) {
-                if (!(cval[k * TM + tid] < thr)) continue;      // thr = final minimum + T
-                ++nexact;
-                const int j = ccol[k * TM + tid];
-                if (j >= a.M) continue;
-                const float d = sqdist3(qx, qy, qz, yb[3 * (size_t)j], yb[3 * (size_t)j + 1], yb[3 * (size_t)j + 2]);
+        int bidx = 0, nexact = 0;
+        const bool rowbad = !sweep_ok || lost < lim;
+        if (row < a.N && !rowbad) {
+            const int n = cnt < CAND ? cnt : CAND;
+            uint32_t flag = 0;                  // bit 4k+q: group q of ring entry k is within T of the row minimum
+            for (int k = 0; k < n; ++k)
+                if (lval[k * EPI_T] < lim) flag |= (lid[k * EPI_T] & 15u) << (4 * k);
+            while (flag) {                      // lanes walk their own flagged groups together
+                const int pos = __ffs(flag) - 1;
+                flag &= flag - 1;
+                const int chunk = (int)(lid[(pos >> 2) * EPI_T] >> 4);
+                exact_group(yb, a.M, chunk * 32 + (pos & 3) * 8, qx, qy, qz, best, bidx, nexact);
+            }
+        }
+        s_best[tid] = best; s_bidx[tid] = bidx; s_rowbad[tid] = rowbad ? 1 : 0;
+        asm volatile("bar.sync 1, %0;" ::"n"(EPI_T) : "memory");
+        if (wg == 0 && row < a.N) {
+            bool bad = rowbad;
+#pragma unroll
+            for (int g = 1; g < NWG; ++g) {
+                const float d = s_best[rloc + g * TM];
+                const int j = s_bidx[rloc + g * TM];
                 if (d < best || (d == best && j < bidx)) { best = d; bidx = j; }
+                bad = bad || s_rowbad[rloc + g * TM] != 0;
             }
-        }
-        if (ncand > CAND || !ok || best == INFINITY) {          // list overflow / NaN input: exact scan
-            best = INFINITY; bidx = 0;
-            atomicAdd(a.err + 1, 1);                            // statistics: rows that fell back
-            for (int j = 0; j < a.M; ++j) {
-                const float d = sqdist3(qx, qy, qz, yb[3 * (size_t)j], yb[3 * (size_t)j + 1], yb[3 * (size_t)j + 2]);
-                if (d < best) { best = d; bidx = j; }
+            if (bad || best == INFINITY) {                          // ring overflow / timeout / NaN input: exact scan
+                best = INFINITY; bidx = 0;
+                atomicAdd(a.err + 1, 1);                            // statistics: rows that fell back
+                for (int j = 0; j < a.M; ++j) {
+                    const float d = sqdist3(qx, qy, qz, yb[3 * (size_t)j], yb[3 * (size_t)j + 1], yb[3 * (size_t)j + 2]);
+                    if (d < best) { best = d; bidx = j; }
+                }
             }
+            a.idx[(size_t)b * a.N + row] = bidx;
+            if (a.d2) a.d2[(size_t)b * a.N + row] = best;
         }
-        nexact = __reduce_add_sync(__activemask(), nexact);
-        if ((tid & 31) == (__ffs(__activemask()) - 1)) atomicAdd(a.err + 2, nexact);   // statistics: exact evaluations
-        a.idx[(size_t)b * a.N + row] = bidx;
-        if (a.d2) a.d2[(size_t)b * a.N + row] = best;
+        nexact = __reduce_add_sync(0xffffffffu, nexact);
+        if (lane == 0 && nexact) atomicAdd(a.err + 2, nexact);      // statistics: exact evaluations
     }
-    if (!ok && tid == 0) *a.err = 1;
     __syncthreads();
-    if (warp == 0) tc::tmem_dealloc<256>(tmem);
+    if (tid == 0) {
+        if (s_bad) *a.err = 1;
+        TCDBG(7);
+    }
 }
 
 constexpr int TC_CHUNK = 256;      // batch elements per prepare/main pair: operands (~90 MB for C3) stay in L2
-constexpr size_t MAIN_SMEM = (size_t)3 * TILE_BYTES + (size_t)CAND * TM * 8;
+constexpr size_t MAIN_SMEM = (size_t)(1 + NSTG) * TILE_BYTES + (size_t)CAND * EPI_T * 8;
 
 size_t tc_ws_bytes(int B, int N, int M) {
     const int nb = B < TC_CHUNK ? B : TC_CHUNK;
@@ -377,6 +456,12 @@ extern "C" int pb_tc_selftest(const void* A, const void* B, float* D, int* err, 
     return pb_check_launch("tc_selftest_kernel") ? -2 : 0;
 }
 
+#ifdef PB_TC_DEBUG
+extern "C" int pb_tc_debug_read(unsigned long long* host) {
+    return (int)cudaMemcpyFromSymbol(host, g_tcdbg, sizeof(unsigned long long) * 256 * 8);
+}
+#endif
+
 extern "C" size_t pb_knn1_tc_workspace_bytes(int B, int N, int M) {
     if (B <= 0 || N <= 0 || M <= 0) return 0;
     return tc_ws_bytes(B, N, M);
@@ -409,7 +494,7 @@ extern "C" int pb_knn1_tc(const float* x, const float* y, int B, int N, int M, i
         knn_tc_prepare_kernel<<<nb, 256, 0, st>>>(pa);
         if (pb_check_launch("knn_tc_prepare_kernel")) return -2;
         MainArgs ma{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, idx, d2, b0, err};
-        knn_tc_kernel<<<dim3(ntN, nb), TM, MAIN_SMEM, st>>>(ma);
+        knn_tc_kernel<<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);
         if (pb_check_launch("knn_tc_kernel")) return -2;
     }
     return 0;

@@ -55,7 +55,7 @@ def test_knn_tc_indices_equal_exact_fp32(dev, B, N, M, scale):
     assert stats[0] == 0                                                 # no barrier timeout
     if M >= 100 and scale <= 1.0:                                        # the tensor path did the work:
         assert stats[1] <= 0.01 * B * N                                  #   hardly any exact-scan fallback rows
-        assert stats[2] <= 3 * B * N                                     #   and a few exact evaluations per row
+        assert stats[2] <= 32 * B * N                                    #   and a few 8-column groups of exact evaluations per row
     assert torch.equal(idx_tc, idx_si) and torch.equal(d2_tc, d2_si)     # the two device paths: bit-identical
     for b in range(B):
         ref_idx, ref_d2 = _brute(x[b], y[b])

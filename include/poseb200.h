@@ -111,9 +111,12 @@ int pb_resample_inliers(const uint32_t* inl_bitmap, const int32_t* count, int F,
 int pb_knn1(const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx, float* d2,
             void* stream);
 
-/* Tensor-core path of the same handle: tiled tcgen05 contraction (|q|^2 - 2 p.q from exact 3-way
- * bf16 splits, FP32 accumulate in TMEM) + exact FP32 re-rank of the candidates, so idx / d2 are
- * identical to pb_knn1's (csrc/knn_tc.cu).  ws: pb_knn1_tc_workspace_bytes(B,N,M), 128-byte aligned. */
+/* Tensor-core path of the same handle: tiled tcgen05 contraction (|q|^2 - 2 p.q from two-way bf16
+ * splits of the centred coordinates, K = 16, FP32 accumulate in TMEM) + exact FP32 re-rank of every
+ * column group within the proven error bound of the row minimum, so idx / d2 are identical to
+ * pb_knn1's (csrc/knn_tc.cu).  ws: pb_knn1_tc_workspace_bytes(B,N,M), 128-byte aligned; after the
+ * call its first 16 bytes hold int stats[4] = {barrier timeout, rows that fell back to the exact
+ * scan, exact evaluations, 0}.                                                                  */
 size_t pb_knn1_tc_workspace_bytes(int B, int N, int M);
 int pb_knn1_tc(const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx, float* d2,
                void* ws, size_t ws_bytes, void* stream);

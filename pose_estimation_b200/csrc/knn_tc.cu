@@ -25,7 +25,7 @@
 namespace {
 
 constexpr int TM = 128;              // rows / columns per operand tile
-constexpr int TILE_U4 = 4 * TM;      // uint4 per operand tile: [kc 0..3][row][8 bf16] = 8 KB
+constexpr int TILE_U4 = 2 * TM;      // uint4 per operand tile: [kc 0..1][row][8 bf16] = 4 KB (K = 16)
 constexpr int TILE_BYTES = TILE_U4 * 16;
 constexpr float TC_TOL_REL = 1.0f / 8192.0f;   // T = 2^-13 * R^2
 
@@ -50,39 +50,34 @@ struct PrepArgs {
     int b0;
 };
 
-// K = 32 operand row of one point.  Query rows (IS_A): -2*(h,h,h,m,m,m,l,l,l) per coordinate, then 1,1,1,0,0.
-// Database rows: (h,m,l,h,m,l,h,m,l) per coordinate, then |q|^2 as three bf16, 0, 0.
+// K = 16 operand row of one point.  Query rows (IS_A): per coordinate (h, h, m, m) of -2p, then 1, 1, 1, 0.
+// Database rows: per coordinate (h, m, h, m) of q, then |q|^2 as three bf16, 0.  h + m carries 16 mantissa bits
+// of a coordinate, so the twelve cross products give -2 p.q to 2^-16 R^2.
 template <bool IS_A>
 __device__ __forceinline__ void write_row(uint4* tile_base, int r, float px, float py, float pz, bool pad) {
-    __nv_bfloat16 e[32];
+    __nv_bfloat16 e[16];
     const __nv_bfloat16 zero = __float2bfloat16_rn(0.0f), one = __float2bfloat16_rn(1.0f);
 #pragma unroll
-    for (int k = 0; k < 32; ++k) e[k] = zero;
+    for (int k = 0; k < 16; ++k) e[k] = zero;
     if (!pad) {
         const float pc[3] = {px, py, pz};
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             const Split3 s = split3(IS_A ? -2.0f * pc[c] : pc[c]);
-            if (IS_A) {
-                e[9 * c + 0] = s.h; e[9 * c + 1] = s.h; e[9 * c + 2] = s.h;
-                e[9 * c + 3] = s.m; e[9 * c + 4] = s.m; e[9 * c + 5] = s.m;
-                e[9 * c + 6] = s.l; e[9 * c + 7] = s.l; e[9 * c + 8] = s.l;
-            } else {
-#pragma unroll
-                for (int g = 0; g < 3; ++g) { e[9 * c + 3 * g] = s.h; e[9 * c + 3 * g + 1] = s.m; e[9 * c + 3 * g + 2] = s.l; }
-            }
+            if (IS_A) { e[4 * c] = s.h; e[4 * c + 1] = s.h; e[4 * c + 2] = s.m; e[4 * c + 3] = s.m; }
+            else      { e[4 * c] = s.h; e[4 * c + 1] = s.m; e[4 * c + 2] = s.h; e[4 * c + 3] = s.m; }
         }
-        if (IS_A) { e[27] = one; e[28] = one; e[29] = one; }
+        if (IS_A) { e[12] = one; e[13] = one; e[14] = one; }
         else {
             const float n = fmaf(pz, pz, fmaf(py, py, px * px));
             const Split3 s = split3(n);
-            e[27] = s.h; e[28] = s.m; e[29] = s.l;
+            e[12] = s.h; e[13] = s.m; e[14] = s.l;
         }
     } else if (!IS_A) {
-        e[27] = __float2bfloat16_rn(1.0e30f);          // padded database row: never a candidate
+        e[12] = __float2bfloat16_rn(1.0e30f);          // padded database row: never a candidate
     }
 #pragma unroll
-    for (int kc = 0; kc < 4; ++kc)
+    for (int kc = 0; kc < 2; ++kc)
         tile_base[kc * TM + r] = make_uint4(pk(e[8 * kc], e[8 * kc + 1]), pk(e[8 * kc + 2], e[8 * kc + 3]),
                                             pk(e[8 * kc + 4], e[8 * kc + 5]), pk(e[8 * kc + 6], e[8 * kc + 7]));
 }
@@ -160,9 +155,15 @@ constexpr int CAND = 8;            // ring slots of flagged chunks per epilogue 
 constexpr int NWG = 2;             // epilogue warpgroups = TMEM accumulators: warpgroup g owns the tiles v = g (mod NWG)
 constexpr int EPI_T = NWG * TM;    // 256 epilogue threads: thread = (query row tid & 127, warpgroup tid >> 7)
 constexpr int KT2 = EPI_T + 64;    // + warp 8 (MMA issuer, TMEM owner) + warp 9 (bulk-copy producer)
-constexpr int NACC = NWG;
-constexpr int NSTG = 6;            // shared-memory stages of database tiles (48 KB in flight per CTA)
-constexpr int TMEM_COLS = NACC * TM;   // 256 columns: two CTAs share an SM's 512
+#ifndef PB_TC_NH
+#define PB_TC_NH 1
+#endif
+constexpr int NH = PB_TC_NH;       // accumulators per warpgroup: the tile is issued as NH MMAs of TM / NH columns, so the
+                                   // MMA of the next tile's part overlaps the epilogue of the other part
+constexpr int NACC = NH * NWG;
+constexpr int TH = TM / NH;        // columns per accumulator
+constexpr int NSTG = 8;            // shared-memory stages of database tiles (32 KB in flight per CTA)
+constexpr int TMEM_COLS = NACC * TH;   // 256 columns: two CTAs' main loops share an SM's 512
 
 __device__ __forceinline__ float fmin3(float a, float b, float c) {
     float d;
@@ -179,7 +180,12 @@ __device__ __forceinline__ float group_min(const uint32_t* r) {
 __device__ unsigned long long g_tcdbg[256 * 8];
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 #define TCDBG(slot) do { if (blockIdx.x == 0 && blockIdx.y < 256) g_tcdbg[blockIdx.y * 8 + (slot)] = gtime(); } while (0)
+__device__ unsigned long long g_tccyc[256 * 8];
+#define TCCLK(var) const long long var = clock64()
+#define TCACC(k, t0, t1) cyc[k] += (t1) - (t0)
 #else
+#define TCCLK(var) do {} while (0)
+#define TCACC(k, t0, t1) do {} while (0)
 #define TCDBG(slot) do {} while (0)
 #endif
 
@@ -209,7 +215,7 @@ __device__ __forceinline__ void exact_group(const float* __restrict__ yb, int M,
 //   warp 8     issues the MMAs of tile v into accumulator v % NACC, owns the TMEM allocation;
 //   warp 9     streams the database tiles through NSTG shared-memory stages with 1-D TMA bulk copies.
 // All hand-offs are mbarriers; the tile loop has no CTA-wide barrier.
-__global__ void __launch_bounds__(KT2, 2) knn_tc_kernel(MainArgs a) {
+__global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint4* sA = reinterpret_cast<uint4*>(smem_raw);                    // [TILE_U4]
     uint4* sB = sA + TILE_U4;                                          // [NSTG][TILE_U4]
@@ -259,33 +265,54 @@ __global__ void __launch_bounds__(KT2, 2) knn_tc_kernel(MainArgs a) {
             if (!ok) s_bad = 1;
         }
     } else if (warp == 8) {
-        // ===== MMA issuer: D[acc v % NACC] = A * B[v % NSTG]^T, two K=16 steps per tile
-        if (lane == 0) {
-            const uint32_t idesc = tc::idesc_bf16_f32(TM, TM);
-            ok = tc::mbar_wait(&bar_a, 0);
-            TCDBG(2);
-            for (int v = 0; v < ntM; ++v) {
-                const int s = v % NSTG, acc = v % NACC;
-                ok = tc::mbar_wait(&bar_load[s], (uint32_t)(v / NSTG) & 1u) && ok;
-                if (v >= NACC) ok = tc::mbar_wait(&bar_free[acc], (uint32_t)(v / NACC - 1) & 1u) && ok;
-                tc::fence_after_sync();
-                const uint32_t sb = tc::smem_u32(sB + s * TILE_U4);
+        // ===== MMA issuer: D[acc] = A * B[stage, half]^T, two K=16 steps per half tile.  The whole warp runs
+        // the loop (waits and descriptor arithmetic stay warp-uniform); one lane issues.
+        const uint32_t idesc = tc::idesc_bf16_f32(TM, TH);
+        const uint64_t ad0 = tc::smem_desc(tc::smem_u32(sA), TM * 16, 128);
+        const uint64_t bd0 = tc::smem_desc(tc::smem_u32(sB), TM * 16, 128);
+        ok = tc::mbar_wait(&bar_a, 0);
+        if (lane == 0) TCDBG(2);
+#ifdef PB_TC_DEBUG
+        long long cyc[5] = {0, 0, 0, 0, 0};
+#endif
+        int s = 0;
+        uint32_t lph = 0;
+        for (int v = 0; v < ntM; ++v) {
+            const int wg = v % NWG, use = v / NWG;
+            TCCLK(t0);
+            ok = tc::mbar_wait(&bar_load[s], lph) && ok;
+            TCCLK(t1);
+            TCACC(0, t0, t1);
 #pragma unroll
-                for (int k = 0; k < 2; ++k)
-                    tc::mma_bf16(tmem + (uint32_t)acc * TM, tc::smem_desc(tc::smem_u32(sA) + k * 2 * TM * 16, TM * 16, 128),
-                                 tc::smem_desc(sb + k * 2 * TM * 16, TM * 16, 128), idesc, k > 0);
-                tc::mma_commit(&bar_mma[acc]);       // accumulator ready -> epilogue
-                tc::mma_commit(&bar_sfree[s]);       // stage consumed     -> producer
-                if (v == 0) TCDBG(3);
+            for (int h = 0; h < NH; ++h) {                     // database rows TH*h .. of the tile
+                const int acc = wg * NH + h;
+                TCCLK(t2);
+                if (use > 0) ok = tc::mbar_wait(&bar_free[acc], (uint32_t)(use - 1) & 1u) && ok;
+                tc::fence_after_sync();
+                TCCLK(t3);
+                const uint64_t bd = bd0 + (uint64_t)((s * TILE_BYTES + h * TH * 16) >> 4);
+                if (lane == 0) {
+                    tc::mma_bf16(tmem + (uint32_t)acc * TH, ad0, bd, idesc, 0);      // the whole K = 16 in one MMA
+                    tc::mma_commit(&bar_mma[acc]);             // accumulator ready -> epilogue
+                }
+                TCCLK(t4);
+                TCACC(1, t2, t3); TCACC(2, t3, t4);
             }
-            TCDBG(4);
-            // the epilogue has read the last tile of every accumulator -> the TMEM columns can go
-            for (int acc = 0; acc < NACC; ++acc) {
-                const int uses = (ntM - acc + NACC - 1) / NACC;           // tiles that used this accumulator
-                if (uses > 0) ok = tc::mbar_wait(&bar_free[acc], (uint32_t)(uses - 1) & 1u) && ok;
-            }
-            if (!ok) s_bad = 1;
+            if (lane == 0) tc::mma_commit(&bar_sfree[s]);      // stage consumed -> producer
+            if (v == 0 && lane == 0) TCDBG(3);
+            if (++s == NSTG) { s = 0; lph ^= 1u; }
         }
+        if (lane == 0) TCDBG(4);
+#ifdef PB_TC_DEBUG
+        if (lane == 0 && blockIdx.x == 0 && blockIdx.y < 256)
+            for (int k = 0; k < 4; ++k) g_tccyc[blockIdx.y * 8 + 4 + k] = (unsigned long long)cyc[k];
+#endif
+        // the epilogue has read the last tile of every accumulator -> the TMEM columns can go
+        for (int acc = 0; acc < NACC; ++acc) {
+            const int uses = (ntM - acc / NH + NWG - 1) / NWG;            // tiles that used this accumulator
+            if (uses > 0) ok = tc::mbar_wait(&bar_free[acc], (uint32_t)(uses - 1) & 1u) && ok;
+        }
+        if (!ok) s_bad = 1;
         __syncwarp();
         tc::fence_after_sync();
         tc::tmem_dealloc<TMEM_COLS>(tmem);
@@ -306,21 +333,29 @@ __global__ void __launch_bounds__(KT2, 2) knn_tc_kernel(MainArgs a) {
         int cnt = 0;
         const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)wg * TM;
         uint32_t ph = 0;
+#ifdef PB_TC_DEBUG
+        long long cyc[5] = {0, 0, 0, 0, 0};
+#endif
         for (int v = wg; v < ntM; v += NWG) {
             if (tid == 0 && v == NWG) TCDBG(5);
-            ok = tc::mbar_wait(&bar_mma[wg], ph) && ok;
-            ph ^= 1u;
-            tc::fence_after_sync();
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                uint32_t r[64];
-                tc::tmem_ld64(taddr + half * 64, r);
-                tc::tmem_ld_wait();
+            for (int half = 0; half < NH; ++half) {
+                TCCLK(t0);
+                ok = tc::mbar_wait(&bar_mma[wg * NH + half], ph) && ok;
+                TCCLK(t1);
+                tc::fence_after_sync();
+                TCCLK(t2);
+                TCACC(0, t0, t1); TCACC(1, t1, t2);
 #pragma unroll
-                for (int c = 0; c < 2; ++c) {
+                for (int c = 0; c < 4 / NH; ++c) {
+                    TCCLK(t3);
+                    uint32_t r[32];
+                    tc::tmem_ld32(taddr + half * TH + c * 32, r);
+                    tc::tmem_ld_wait();
+                    TCCLK(t4);
                     float g[4];
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) g[q] = group_min(r + c * 32 + q * 8);
+                    for (int q = 0; q < 4; ++q) g[q] = group_min(r + q * 8);
                     const float cm = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
                     const float lim_run = m_run + T;
                     if (cm < lim_run) {
@@ -329,16 +364,26 @@ __global__ void __launch_bounds__(KT2, 2) knn_tc_kernel(MainArgs a) {
                         const int slot = cnt & (CAND - 1);
                         if (cnt >= CAND) lost = fminf(lost, lval[slot * EPI_T]);
                         lval[slot * EPI_T] = cm;
-                        lid[slot * EPI_T] = ((uint32_t)(v * 4 + half * 2 + c) << 4) | mask;
+                        lid[slot * EPI_T] = ((uint32_t)(v * 4 + half * (4 / NH) + c) << 4) | mask;
                         ++cnt;
                     }
                     m_run = fminf(m_run, cm);
+                    TCCLK(t5);
+                    TCACC(2, t3, t4); TCACC(3, t4, t5);
                 }
+                TCCLK(t6);
+                tc::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(&bar_free[wg * NH + half]);  // this warp is done with the part
+                TCCLK(t7);
+                TCACC(4, t6, t7);
             }
-            tc::fence_before_sync();
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&bar_free[wg]);      // this warp is done with the accumulator
+            ph ^= 1u;
         }
+#ifdef PB_TC_DEBUG
+        if (tid == 0 && blockIdx.x == 0 && blockIdx.y < 256)
+            for (int k = 0; k < 4; ++k) g_tccyc[blockIdx.y * 8 + k] = (unsigned long long)cyc[k == 3 ? 4 : k] + (k == 2 ? cyc[3] : 0);
+#endif
         if (tid == 0) TCDBG(6);
         if (!ok) s_bad = 1;
         s_mrun[tid] = m_run;
@@ -402,7 +447,7 @@ constexpr size_t MAIN_SMEM = (size_t)(1 + NSTG) * TILE_BYTES + (size_t)CAND * EP
 size_t tc_ws_bytes(int B, int N, int M) {
     const int nb = B < TC_CHUNK ? B : TC_CHUNK;
     const size_t ntN = (N + TM - 1) / TM, ntM = (M + TM - 1) / TM;
-    return (size_t)nb * (ntN + ntM) * TILE_BYTES + (size_t)nb * 4 * sizeof(float) + 256;   // tail: int stats[4]
+    return 128 + (size_t)nb * (ntN + ntM) * TILE_BYTES + (size_t)nb * 4 * sizeof(float) + 128;   // head: int stats[4]
 }
 
 // ---- self test: D[128x128] = A[128x32] * B[128x32]^T, operands given in the canonical tile layout
@@ -457,8 +502,57 @@ extern "C" int pb_tc_selftest(const void* A, const void* B, float* D, int* err, 
 }
 
 #ifdef PB_TC_DEBUG
+// MMA issue-rate probe: reps x (two K=16 MMAs, M=128, N=n) on garbage operands, one commit at the end.
+__global__ void __launch_bounds__(128) tc_mma_probe_kernel(int n, uint32_t layout, uint32_t lbo, uint32_t sbo, uint32_t kstep,
+                                                            int reps, int nacc, long long* out) {
+    extern __shared__ __align__(1024) unsigned char sm[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < 64 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(sm)[i] = 0x3c003c00u;
+    if (tid == 0) { tc::mbar_init(&bar, 1); tc::fence_mbar_init(); }
+    if (warp == 0) tc::tmem_alloc<512>(&tmem_base);
+    tc::fence_proxy_async();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = tmem_base;
+    if (tid == 0) {
+        const uint32_t idesc = tc::idesc_bf16_f32(128, n);
+        const uint64_t ad = tc::smem_desc(tc::smem_u32(sm), lbo, sbo) | ((uint64_t)layout << 61);
+        const uint64_t bd = tc::smem_desc(tc::smem_u32(sm) + 32768, lbo, sbo) | ((uint64_t)layout << 61);
+        const long long t0 = clock64();
+        for (int r = 0; r < reps; ++r) {
+            const uint32_t d = tmem + (uint32_t)(r % nacc) * (uint32_t)n;
+            tc::mma_bf16(d, ad, bd, idesc, 0);
+            tc::mma_bf16(d, ad + (kstep >> 4), bd + (kstep >> 4), idesc, 1);
+        }
+        const long long t1 = clock64();
+        tc::mma_commit(&bar);
+        tc::mbar_wait(&bar, 0);
+        const long long t2 = clock64();
+        if (blockIdx.x == 0) { out[0] = t1 - t0; out[1] = t2 - t0; }
+    } 
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc<512>(tmem);
+}
+extern "C" int pb_tc_probe_mma(int ctas, int n, unsigned layout, unsigned lbo, unsigned sbo, unsigned kstep, int reps, int nacc,
+                               long long* host_out) {
+    long long* d;
+    cudaMalloc(&d, 16);
+    cudaFuncSetAttribute(tc_mma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    tc_mma_probe_kernel<<<ctas, 128, 64 * 1024>>>(n, layout, lbo, sbo, kstep, reps, nacc, d);
+    int rc = (int)cudaDeviceSynchronize();
+    cudaMemcpy(host_out, d, 16, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    return rc;
+}
 extern "C" int pb_tc_debug_read(unsigned long long* host) {
     return (int)cudaMemcpyFromSymbol(host, g_tcdbg, sizeof(unsigned long long) * 256 * 8);
+}
+extern "C" int pb_tc_debug_read_cycles(unsigned long long* host) {
+    return (int)cudaMemcpyFromSymbol(host, g_tccyc, sizeof(unsigned long long) * 256 * 8);
 }
 #endif
 
@@ -481,11 +575,11 @@ extern "C" int pb_knn1_tc(const float* x, const float* y, int B, int N, int M, i
     const int ntN = (N + TM - 1) / TM, ntM = (M + TM - 1) / TM;
     PB_REQUIRE(ntN <= 65535 * 32, "pb_knn1_tc: N too large");
     char* base = static_cast<char*>(ws);
-    uint4* Aop = reinterpret_cast<uint4*>(base);
+    int* err = reinterpret_cast<int*>(base);                          // int stats[4] at the head of the workspace
+    uint4* Aop = reinterpret_cast<uint4*>(base + 128);
     uint4* Bop = Aop + (size_t)nb_max * ntN * TILE_U4;
     float* tol = reinterpret_cast<float*>(Bop + (size_t)nb_max * ntM * TILE_U4);
     float* centre = tol + nb_max;
-    int* err = reinterpret_cast<int*>(centre + 3 * nb_max);          // last word of the float block (+pad)
     cudaFuncSetAttribute(knn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAIN_SMEM);
     cudaMemsetAsync(err, 0, 4 * sizeof(int), st);   // [0] barrier timeout, [1] fallback rows, [2] exact evaluations
     for (int b0 = 0; b0 < B; b0 += TC_CHUNK) {

@@ -50,9 +50,7 @@ def knn1(x, y, want_d2=False, impl="auto"):
         call("pb_knn1_tc", _ptr(x), _ptr(y), B, N, M, y_shared, _ptr(idx), _ptr(d2),
              C.c_void_p(ws.data_ptr() + off), nb, _stream())
         global LAST_TC_STATS
-        nbm = min(B, 256)
-        tiles = ((N + 127) // 128 + (M + 127) // 128) * 8192
-        LAST_TC_STATS = ws[off + nbm * tiles + nbm * 16: off + nbm * tiles + nbm * 16 + 16].view(torch.int32)
+        LAST_TC_STATS = ws[off: off + 16].view(torch.int32)       # the workspace starts with int stats[4]
     else:
         call("pb_knn1", _ptr(x), _ptr(y), B, N, M, y_shared, _ptr(idx), _ptr(d2), _stream())
     if squeeze:

@@ -20,3 +20,10 @@ for i, n in enumerate(names): print(f"  {n:16s} {np.median(d[:, i]):9.0f}   p10 
 print("kernel span of sampled CTAs (us)", (t[:, 7].max() - t0) / 1e3)
 o = np.argsort(t[:, 0])
 for k in o[:6].tolist() + o[-3:].tolist(): print(k, (t[k] - t0).tolist())
+
+if hasattr(lib, "pb_tc_debug_read_cycles"):
+    lib.pb_tc_debug_read_cycles.argtypes = [C.c_void_p]; lib.pb_tc_debug_read_cycles.restype = C.c_int
+    lib.pb_tc_debug_read_cycles(buf)
+    c = np.frombuffer(buf, dtype=np.uint64).reshape(256, 8).astype(np.int64)
+    print("warp 0 cycles over the tile loop [mbar_wait, fence_after, tmem ld+wait+min/push, fence+arrive]:", np.median(c[:, :4], axis=0).tolist())
+    print("issuer cycles [wait load, wait free, mma+commit issue, first commit->barrier latency]:", np.median(c[:, 4:8], axis=0).tolist())

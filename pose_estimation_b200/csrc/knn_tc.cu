@@ -151,7 +151,7 @@ struct MainArgs {
     int* err;
 };
 
-constexpr int CAND = 8;            // ring slots of flagged chunks per epilogue thread
+constexpr int CAND = 8;            // ring slots per epilogue thread: the CAND - 1 latest flagged chunks + one scratch slot
 constexpr int NWG = 2;             // epilogue warpgroups = TMEM accumulators: warpgroup g owns the tiles v = g (mod NWG)
 constexpr int EPI_T = NWG * TM;    // 256 epilogue threads: thread = (query row tid & 127, warpgroup tid >> 7)
 constexpr int KT2 = EPI_T + 64;    // + warp 8 (MMA issuer, TMEM owner) + warp 9 (bulk-copy producer)
@@ -162,7 +162,7 @@ constexpr int NH = PB_TC_NH;       // accumulators per warpgroup: the tile is is
                                    // MMA of the next tile's part overlaps the epilogue of the other part
 constexpr int NACC = NH * NWG;
 constexpr int TH = TM / NH;        // columns per accumulator
-constexpr int NSTG = 8;            // shared-memory stages of database tiles (32 KB in flight per CTA)
+constexpr int NSTG = 6;            // shared-memory stages of database tiles (24 KB in flight per CTA)
 constexpr int TMEM_COLS = NACC * TH;   // 256 columns: two CTAs' main loops share an SM's 512
 
 __device__ __forceinline__ float fmin3(float a, float b, float c) {
@@ -192,20 +192,22 @@ __device__ unsigned long long g_tccyc[256 * 8];
 // One flagged group (8 consecutive columns from j0) of a query row: exact FP32 distances, lowest index on ties.
 __device__ __forceinline__ void exact_group(const float* __restrict__ yb, int M, int j0, float qx, float qy, float qz,
                                             float& best, int& bidx, int& nexact) {
-    float p[8][3];
+    const float* __restrict__ yp = yb + 3 * (size_t)j0;
+    if (j0 + 8 <= M) {                                   // all 24 loads in flight, immediate offsets
+        float p[24];
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
-        const int j = j0 + c < M ? j0 + c : M - 1;                 // clamped loads, all in flight together
+        for (int k = 0; k < 24; ++k) p[k] = yp[k];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) p[c][k] = yb[3 * (size_t)j + k];
-    }
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-        const int j = j0 + c;
-        if (j < M) {
-            const float d = sqdist3(qx, qy, qz, p[c][0], p[c][1], p[c][2]);
+        for (int c = 0; c < 8; ++c) {
+            const float d = sqdist3(qx, qy, qz, p[3 * c], p[3 * c + 1], p[3 * c + 2]);
+            if (d < best || (d == best && j0 + c < bidx)) { best = d; bidx = j0 + c; }
+        }
+        nexact += 8;
+    } else {
+        for (int c = 0; j0 + c < M; ++c) {
+            const float d = sqdist3(qx, qy, qz, yp[3 * c], yp[3 * c + 1], yp[3 * c + 2]);
             ++nexact;
-            if (d < best || (d == best && j < bidx)) { best = d; bidx = j; }
+            if (d < best || (d == best && j0 + c < bidx)) { best = d; bidx = j0 + c; }
         }
     }
 }
@@ -219,8 +221,8 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint4* sA = reinterpret_cast<uint4*>(smem_raw);                    // [TILE_U4]
     uint4* sB = sA + TILE_U4;                                          // [NSTG][TILE_U4]
-    float* lval_all = reinterpret_cast<float*>(sB + NSTG * TILE_U4);   // [CAND][EPI_T] chunk minimum
-    uint32_t* lid_all = reinterpret_cast<uint32_t*>(lval_all + CAND * EPI_T);   // [CAND][EPI_T] chunk << 4 | group mask
+    float4* lgrp_all = reinterpret_cast<float4*>(sB + NSTG * TILE_U4);          // [CAND][EPI_T] minima of the four 8-column groups
+    int* lid_all = reinterpret_cast<int*>(lgrp_all + CAND * EPI_T);             // [CAND][EPI_T] chunk index
     __shared__ __align__(8) uint64_t bar_load[NSTG], bar_sfree[NSTG], bar_mma[NACC], bar_free[NACC], bar_a;
     __shared__ uint32_t tmem_base;
     __shared__ float s_mrun[EPI_T];
@@ -318,11 +320,12 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
         tc::tmem_dealloc<TMEM_COLS>(tmem);
     } else {
         // ===== epilogue: one sweep.  Per 32-column chunk: minimum by 3-input minima; a chunk whose minimum
-        // is below  running minimum + T  is remembered (ring of CAND) with the mask of its 8-column groups.
+        // is below  running minimum + T  is remembered with the minima of its 8-column groups.  The ring is
+        // written without a branch: every chunk lands in the scratch slot cnt % CAND, a flagged one keeps it.
         const int wg = tid >> 7, rloc = tid & (TM - 1);
         const int row = rt * TM + rloc;
-        float* lval = lval_all + tid;
-        uint32_t* lid = lid_all + tid;
+        float4* lgrp = lgrp_all + tid;
+        int* lid = lid_all + tid;
         const float T = a.tol[bl];
         const float* xb = a.x + (size_t)b * a.N * 3;
         const float* yb = a.y + (a.y_shared ? 0 : (size_t)b * a.M * 3);
@@ -357,15 +360,15 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
 #pragma unroll
                     for (int q = 0; q < 4; ++q) g[q] = group_min(r + q * 8);
                     const float cm = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
-                    const float lim_run = m_run + T;
-                    if (cm < lim_run) {
-                        const uint32_t mask = (g[0] < lim_run ? 1u : 0u) | (g[1] < lim_run ? 2u : 0u) |
-                                              (g[2] < lim_run ? 4u : 0u) | (g[3] < lim_run ? 8u : 0u);
-                        const int slot = cnt & (CAND - 1);
-                        if (cnt >= CAND) lost = fminf(lost, lval[slot * EPI_T]);
-                        lval[slot * EPI_T] = cm;
-                        lid[slot * EPI_T] = ((uint32_t)(v * 4 + half * (4 / NH) + c) << 4) | mask;
-                        ++cnt;
+                    const int slot = cnt & (CAND - 1);
+                    lgrp[slot * EPI_T] = make_float4(g[0], g[1], g[2], g[3]);
+                    lid[slot * EPI_T] = v * 4 + half * (4 / NH) + c;
+                    if (cm < m_run + T) {
+                        ++cnt;                                  // keep it; the next slot becomes scratch
+                        if (cnt >= CAND) {                      // ... and the flagged chunk it still holds is dropped
+                            const float4 o = lgrp[(cnt & (CAND - 1)) * EPI_T];
+                            lost = fminf(lost, fminf(fminf(o.x, o.y), fminf(o.z, o.w)));
+                        }
                     }
                     m_run = fminf(m_run, cm);
                     TCCLK(t5);
@@ -398,14 +401,17 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
         int bidx = 0, nexact = 0;
         const bool rowbad = !sweep_ok || lost < lim;
         if (row < a.N && !rowbad) {
-            const int n = cnt < CAND ? cnt : CAND;
-            uint32_t flag = 0;                  // bit 4k+q: group q of ring entry k is within T of the row minimum
-            for (int k = 0; k < n; ++k)
-                if (lval[k * EPI_T] < lim) flag |= (lid[k * EPI_T] & 15u) << (4 * k);
+            uint32_t flag = 0;                  // bit 4*slot+q: group q of that ring slot is within T of the row minimum
+            for (int i = cnt > CAND - 1 ? cnt - (CAND - 1) : 0; i < cnt; ++i) {
+                const int slot = i & (CAND - 1);
+                const float4 g = lgrp[slot * EPI_T];
+                const uint32_t mask = (g.x < lim ? 1u : 0u) | (g.y < lim ? 2u : 0u) | (g.z < lim ? 4u : 0u) | (g.w < lim ? 8u : 0u);
+                flag |= mask << (4 * slot);
+            }
             while (flag) {                      // lanes walk their own flagged groups together
                 const int pos = __ffs(flag) - 1;
                 flag &= flag - 1;
-                const int chunk = (int)(lid[(pos >> 2) * EPI_T] >> 4);
+                const int chunk = lid[(pos >> 2) * EPI_T];
                 exact_group(yb, a.M, chunk * 32 + (pos & 3) * 8, qx, qy, qz, best, bidx, nexact);
             }
         }
@@ -442,7 +448,7 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
 }
 
 constexpr int TC_CHUNK = 256;      // batch elements per prepare/main pair: operands (~90 MB for C3) stay in L2
-constexpr size_t MAIN_SMEM = (size_t)(1 + NSTG) * TILE_BYTES + (size_t)CAND * EPI_T * 8;
+constexpr size_t MAIN_SMEM = (size_t)(1 + NSTG) * TILE_BYTES + (size_t)CAND * EPI_T * 20;
 
 size_t tc_ws_bytes(int B, int N, int M) {
     const int nb = B < TC_CHUNK ? B : TC_CHUNK;

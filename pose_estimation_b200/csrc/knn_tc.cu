@@ -82,12 +82,15 @@ __device__ __forceinline__ void write_row(uint4* tile_base, int r, float px, flo
                                             pk(e[8 * kc + 4], e[8 * kc + 5]), pk(e[8 * kc + 6], e[8 * kc + 7]));
 }
 
-// one CTA per batch element: bounding-box centre of y, operand tiles of x and y, tolerance
+constexpr int PREP_SPLIT = 4;   // CTAs per batch element: each finds the centre, then writes every PREP_SPLIT-th slab of rows
+
+// grid (batch elements, PREP_SPLIT): bounding-box centre of y, operand tiles of x and y, squared cloud radius
 __global__ void __launch_bounds__(256) knn_tc_prepare_kernel(PrepArgs a) {
     __shared__ float red[6][8];
     __shared__ float cen[3];
     __shared__ float rmax[8];
     const int bl = blockIdx.x, b = a.b0 + bl, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int part = blockIdx.y;
     const float* xb = a.x + (size_t)b * a.N * 3;
     const float* yb = a.y + (a.y_shared ? 0 : (size_t)b * a.M * 3);
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -116,14 +119,14 @@ __global__ void __launch_bounds__(256) knn_tc_prepare_kernel(PrepArgs a) {
     float r2 = 0.0f;
     uint4* At = a.Aop + (size_t)bl * a.ntN * TILE_U4;
     uint4* Bt = a.Bop + (size_t)bl * a.ntM * TILE_U4;
-    for (int i = tid; i < a.ntN * TM; i += 256) {
+    for (int i = part * 256 + tid; i < a.ntN * TM; i += 256 * PREP_SPLIT) {
         const bool pad = i >= a.N;
         float px = 0.0f, py = 0.0f, pz = 0.0f;
         if (!pad) { px = xb[3 * (size_t)i] - c0; py = xb[3 * (size_t)i + 1] - c1; pz = xb[3 * (size_t)i + 2] - c2; }
         r2 = fmaxf(r2, fmaf(pz, pz, fmaf(py, py, px * px)));
         write_row<true>(At + (size_t)(i / TM) * TILE_U4, i % TM, px, py, pz, pad);
     }
-    for (int j = tid; j < a.ntM * TM; j += 256) {
+    for (int j = part * 256 + tid; j < a.ntM * TM; j += 256 * PREP_SPLIT) {
         const bool pad = j >= a.M;
         float px = 0.0f, py = 0.0f, pz = 0.0f;
         if (!pad) { px = yb[3 * (size_t)j] - c0; py = yb[3 * (size_t)j + 1] - c1; pz = yb[3 * (size_t)j + 2] - c2; }
@@ -137,8 +140,9 @@ __global__ void __launch_bounds__(256) knn_tc_prepare_kernel(PrepArgs a) {
     if (tid == 0) {
         float r = rmax[0];
         for (int w = 1; w < 8; ++w) r = fmaxf(r, rmax[w]);
-        a.tol[bl] = isfinite(r) ? r * TC_TOL_REL : INFINITY;   // non-finite input: everything is a candidate
-        a.centre[3 * bl] = c0; a.centre[3 * bl + 1] = c1; a.centre[3 * bl + 2] = c2;
+        // squared radius R^2 >= 0 as ordered bits (zeroed before the launch); non-finite input -> +inf: everything is a candidate
+        atomicMax(reinterpret_cast<unsigned int*>(a.tol + bl), __float_as_uint(isfinite(r) ? r : INFINITY));
+        if (part == 0) { a.centre[3 * bl] = c0; a.centre[3 * bl + 1] = c1; a.centre[3 * bl + 2] = c2; }
     }
 }
 
@@ -326,7 +330,7 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
         const int row = rt * TM + rloc;
         float4* lgrp = lgrp_all + tid;
         int* lid = lid_all + tid;
-        const float T = a.tol[bl];
+        const float T = a.tol[bl] * TC_TOL_REL;         // T = 2^-13 R^2
         const float* xb = a.x + (size_t)b * a.N * 3;
         const float* yb = a.y + (a.y_shared ? 0 : (size_t)b * a.M * 3);
         float qx = 0.0f, qy = 0.0f, qz = 0.0f;
@@ -591,7 +595,8 @@ extern "C" int pb_knn1_tc(const float* x, const float* y, int B, int N, int M, i
     for (int b0 = 0; b0 < B; b0 += TC_CHUNK) {
         const int nb = (B - b0) < TC_CHUNK ? (B - b0) : TC_CHUNK;
         PrepArgs pa{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, centre, b0};
-        knn_tc_prepare_kernel<<<nb, 256, 0, st>>>(pa);
+        cudaMemsetAsync(tol, 0, (size_t)nb * sizeof(float), st);
+        knn_tc_prepare_kernel<<<dim3(nb, PREP_SPLIT), 256, 0, st>>>(pa);
         if (pb_check_launch("knn_tc_prepare_kernel")) return -2;
         MainArgs ma{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, idx, d2, b0, err};
         knn_tc_kernel<<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);

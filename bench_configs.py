@@ -59,10 +59,16 @@ def c3(args, dev):
                       "exact_evals_per_row": st[2] / (B * N), "timeout": st[0]}
     same = bool(torch.equal(ops_metric.knn1(pred, target, impl="tc"), ops_metric.knn1(pred, target, impl="simt")))
     out["tc_equals_simt"] = same
-    ms = timed(lambda: ops_metric.add_adds(pred, target, None), args.iters)
-    out["add_adds"] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3)}
-    ms = timed(lambda: ops_metric.pose_loss_fwd(Rt, tt, model, target, sym), args.iters)
-    out["pose_loss_fwd"] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3)}
+    for impl in ("simt", "tc"):
+        ms = timed(lambda: ops_metric.add_adds(pred, target, None, impl=impl), args.iters)
+        out["add_adds_" + impl] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3)}
+        ms = timed(lambda: ops_metric.pose_loss_fwd(Rt, tt, model, target, sym, impl=impl, sym_host=[1] * B), args.iters)
+        out["pose_loss_fwd_" + impl] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3)}
+    a_s = ops_metric.add_adds(pred, target, None, impl="simt"); a_t = ops_metric.add_adds(pred, target, None, impl="tc")
+    l_s = ops_metric.pose_loss_fwd(Rt, tt, model, target, sym, impl="simt")
+    l_t = ops_metric.pose_loss_fwd(Rt, tt, model, target, sym, impl="tc", sym_host=[1] * B)
+    out["adds_tc_equals_simt"] = bool(torch.equal(a_s[1], a_t[1]) and torch.equal(a_s[0], a_t[0]))
+    out["loss_tc_equals_simt"] = bool(torch.equal(l_s[0], l_t[0]) and torch.equal(l_s[2], l_t[2]))
     print(json.dumps({"config": "C3", "batch": B, "N": N, "pairs": B * N * N, **out}), flush=True)
 
 

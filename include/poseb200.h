@@ -126,6 +126,13 @@ int pb_knn1_tc(const float* x, const float* y, int B, int N, int M, int y_shared
  * else adds[b] = add[b].  pred/target [B,N,3].                                                  */
 int pb_add_adds(const float* pred, const float* target, int B, int N, const uint8_t* want_adds,
                 float* add, float* adds, void* stream);
+/* The same metric with the N x N search on the tensor cores (pb_knn1_tc's kernels); add / adds are
+ * bit-identical to pb_add_adds.  sym_list: device list of the n_sym batch elements with
+ * want_adds[b] != 0 (want_adds NULL -> every element, list ignored).  ws: 128-byte aligned.     */
+size_t pb_add_adds_tc_workspace_bytes(int B, int N);
+int pb_add_adds_tc(const float* pred, const float* target, int B, int N, const uint8_t* want_adds,
+                   const int* sym_list, int n_sym, float* add, float* adds, void* ws, size_t ws_bytes,
+                   void* stream);
 
 /* out[b,i,:] = R[b] * model[b or 0,i,:] + t[b]   (tools/trainer.py:376, lib/network/loss.py:26) */
 int pb_transform_points(const float* model, int model_shared, const float* R, const float* t, int B,
@@ -155,6 +162,12 @@ int pb_accumulate_results(const float* add, const float* r_deg, const float* t_m
 int pb_pose_loss_fwd(const float* R, const float* t, const float* model, const float* target,
                      const uint8_t* sym /*[B]*/, int B, int N, float* pred /*[B,N,3]*/, int64_t* nn_idx,
                      float* loss_b /*[B]*/, void* stream);
+/* forward with the symmetric samples' search on the tensor cores; sym_list = device list of the
+ * n_sym elements with sym[b] != 0 (sym NULL -> all symmetric, list ignored);
+ * ws = pb_knn1_tc_workspace_bytes(B,N,N), 128-byte aligned.                                     */
+int pb_pose_loss_fwd_tc(const float* R, const float* t, const float* model, const float* target,
+                        const uint8_t* sym, const int* sym_list, int n_sym, int B, int N, float* pred,
+                        int64_t* nn_idx, float* loss_b, void* ws, size_t ws_bytes, void* stream);
 int pb_pose_loss_bwd(const float* pred, const float* model, const float* target, const int64_t* nn_idx,
                      int B, int N, float gscale, float* grad_R /*[B,9]*/, float* grad_t /*[B,3]*/,
                      void* stream);

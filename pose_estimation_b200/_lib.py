@@ -42,10 +42,13 @@ SIGNATURES = {
     "pb_knn1_tc_workspace_bytes": (SZ, [I, I, I]),
     "pb_knn1_tc": (I, [P, P, I, I, I, I, P, P, P, SZ, P]),
     "pb_add_adds": (I, [P, P, I, I, P, P, P, P]),
+    "pb_add_adds_tc_workspace_bytes": (SZ, [I, I]),
+    "pb_add_adds_tc": (I, [P, P, I, I, P, P, I, P, P, P, SZ, P]),
     "pb_transform_points": (I, [P, I, P, P, I, I, P, P]),
     "pb_pose_metrics": (I, [P, P, P, P, P, P, P, P, I, I, I, P, P, P, P]),
     "pb_accumulate_results": (I, [P, P, P, P, P, P, I, I, I, F32, F32, F32, I, P, P]),
     "pb_pose_loss_fwd": (I, [P, P, P, P, P, I, I, P, P, P, P]),
+    "pb_pose_loss_fwd_tc": (I, [P, P, P, P, P, P, I, I, I, P, P, P, P, SZ, P]),
     "pb_pose_loss_bwd": (I, [P, P, P, P, I, I, F32, P, P, P]),
     "pb_vote_translation": (I, [P, P, I, I, P, P]),
     "pb_probe_fma": (I, [I, I, I, P, P]),

@@ -157,9 +157,10 @@ def knn(x, y):
 
 class _PoseLossFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, pred_r, pred_t, targets, model_points, sym):
+    def forward(ctx, pred_r, pred_t, targets, model_points, sym, sym_host=None):
         loss_b, pred, nn_idx = ops_metric.pose_loss_fwd(pred_r.contiguous(), pred_t.reshape(-1, 3).contiguous(),
-                                                        model_points.contiguous(), targets.contiguous(), sym)
+                                                        model_points.contiguous(), targets.contiguous(), sym,
+                                                        sym_host=sym_host)
         ctx.save_for_backward(pred, model_points, targets, nn_idx)
         ctx.t_shape = pred_t.shape
         return loss_b.mean()
@@ -168,7 +169,7 @@ class _PoseLossFn(torch.autograd.Function):
     def backward(ctx, gout):
         pred, model_points, targets, nn_idx = ctx.saved_tensors
         gR, gt = ops_metric.pose_loss_bwd(pred, model_points.contiguous(), targets.contiguous(), nn_idx, 1.0)
-        return gR * gout, (gt * gout).reshape(ctx.t_shape), None, None, None
+        return gR * gout, (gt * gout).reshape(ctx.t_shape), None, None, None, None
 
 
 class PoseLoss(torch.nn.Module):
@@ -183,9 +184,9 @@ class PoseLoss(torch.nn.Module):
 
     def forward(self, pred_r, pred_t, targets, model_points, idxs):
         ids = torch.as_tensor(idxs).reshape(-1).tolist()
-        sym = torch.tensor([1 if int(i) in self.sym_list else 0 for i in ids], dtype=torch.uint8,
-                           device=pred_r.device)
-        return _PoseLossFn.apply(pred_r.float(), pred_t.float(), targets.float(), model_points.float(), sym)
+        flags = [1 if int(i) in self.sym_list else 0 for i in ids]
+        sym = torch.tensor(flags, dtype=torch.uint8, device=pred_r.device)
+        return _PoseLossFn.apply(pred_r.float(), pred_t.float(), targets.float(), model_points.float(), sym, flags)
 
 
 class _VoteFn(torch.autograd.Function):

@@ -9,6 +9,8 @@
 #include "common.cuh"
 #include "nn.cuh"
 
+extern "C" size_t pb_knn1_tc_workspace_bytes(int B, int N, int M);
+
 namespace {
 
 __global__ void __launch_bounds__(KT) knn1_kernel(const float* __restrict__ x, const float* __restrict__ y, int N,
@@ -119,6 +121,68 @@ extern "C" int pb_add_adds(const float* pred, const float* target, int B, int N,
     PB_REQUIRE(pred && target && (add || adds), "pb_add_adds: null pointer argument");
     add_adds_kernel<<<B, KT, 0, static_cast<cudaStream_t>(stream)>>>(pred, target, N, want_adds, add, adds);
     return pb_check_launch("add_adds_kernel") ? -2 : 0;
+}
+
+// ADD as in add_adds_kernel; ADD-S from the nearest-neighbour squared distances of the tensor path, summed in
+// add_adds_kernel's order (thread-strided, then the deterministic block sum) so both paths return the same bits.
+__global__ void __launch_bounds__(KT) add_adds_finish_kernel(const float* __restrict__ pred, const float* __restrict__ target,
+                                                             int N, const uint8_t* __restrict__ want_adds,
+                                                             const float* __restrict__ d2, float* __restrict__ add,
+                                                             float* __restrict__ adds) {
+    __shared__ float red[KT / 32];
+    const int b = blockIdx.x;
+    const float* pb = pred + (size_t)b * N * 3;
+    const float* tb = target + (size_t)b * N * 3;
+    float s = 0.0f;
+    for (int i = threadIdx.x; i < N; i += KT)
+        s += sqrtf(sqdist3(pb[3 * (size_t)i], pb[3 * (size_t)i + 1], pb[3 * (size_t)i + 2], tb[3 * (size_t)i],
+                           tb[3 * (size_t)i + 1], tb[3 * (size_t)i + 2]));
+    const float add_v = block_sum_kt(s, red) / (float)N;
+    if (threadIdx.x == 0 && add) add[b] = add_v;
+    if (!adds) return;
+    const bool want = want_adds ? (want_adds[b] != 0) : true;
+    if (!want) {
+        if (threadIdx.x == 0) adds[b] = add_v;
+        return;
+    }
+    float s2 = 0.0f;
+    for (int base = 0; base < N; base += KT * QPT)
+#pragma unroll
+        for (int q = 0; q < QPT; ++q) {
+            const int i = base + q * KT + threadIdx.x;
+            if (i < N) s2 += sqrtf(d2[(size_t)b * N + i]);
+        }
+    const float adds_v = block_sum_kt(s2, red) / (float)N;
+    if (threadIdx.x == 0) adds[b] = adds_v;
+}
+
+static size_t d2_bytes(int B, int N) { return (((size_t)B * N * sizeof(float)) + 127) / 128 * 128; }
+
+extern "C" size_t pb_add_adds_tc_workspace_bytes(int B, int N) {
+    if (B <= 0 || N <= 0) return 0;
+    return d2_bytes(B, N) + pb_knn1_tc_workspace_bytes(B, N, N);
+}
+
+extern "C" int pb_add_adds_tc(const float* pred, const float* target, int B, int N, const uint8_t* want_adds,
+                              const int* sym_list, int n_sym, float* add, float* adds, void* ws, size_t ws_bytes,
+                              void* stream) {
+    PB_REQUIRE(B >= 0 && N > 0, "pb_add_adds_tc: bad sizes B=%d N=%d", B, N);
+    if (B == 0) return 0;
+    PB_REQUIRE(pred && target && adds, "pb_add_adds_tc: null pointer argument");
+    PB_REQUIRE(!want_adds || (n_sym >= 0 && n_sym <= B && (sym_list || n_sym == 0)), "pb_add_adds_tc: want_adds needs its list of set elements");
+    PB_REQUIRE(ws && ws_bytes >= pb_add_adds_tc_workspace_bytes(B, N), "pb_add_adds_tc: workspace too small");
+    PB_REQUIRE(reinterpret_cast<uintptr_t>(ws) % 128 == 0, "pb_add_adds_tc: workspace must be 128-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    float* d2 = static_cast<float*>(ws);
+    char* kws = static_cast<char*>(ws) + d2_bytes(B, N);
+    // ADD-S: for every target point the nearest predicted point (lib/utils/metric.py:26-33)
+    if (!want_adds || n_sym > 0) {
+        const int rc = pb_internal_knn1_tc("pb_add_adds_tc", target, pred, B, N, N, 0, nullptr, d2, kws,
+                                           ws_bytes - d2_bytes(B, N), want_adds ? sym_list : nullptr, n_sym, st);
+        if (rc) return rc;
+    }
+    add_adds_finish_kernel<<<B, KT, 0, st>>>(pred, target, N, want_adds, d2, add, adds);
+    return pb_check_launch("add_adds_finish_kernel") ? -2 : 0;
 }
 
 extern "C" int pb_transform_points(const float* model, int model_shared, const float* R, const float* t, int B, int N,

@@ -48,6 +48,7 @@ struct PrepArgs {
     int N, M, y_shared, ntN, ntM;
     uint4* Aop; uint4* Bop; float* tol; float* centre;   // per chunk-local batch element
     int b0;
+    const int* blist;                                     // optional: batch element of list position b0 + bl
 };
 
 // K = 16 operand row of one point.  Query rows (IS_A): per coordinate (h, h, m, m) of -2p, then 1, 1, 1, 0.
@@ -89,8 +90,8 @@ __global__ void __launch_bounds__(256) knn_tc_prepare_kernel(PrepArgs a) {
     __shared__ float red[6][8];
     __shared__ float cen[3];
     __shared__ float rmax[8];
-    const int bl = blockIdx.x, b = a.b0 + bl, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int part = blockIdx.y;
+    const int bl = blockIdx.x, b = a.blist ? a.blist[a.b0 + bl] : a.b0 + bl;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, part = blockIdx.y;
     const float* xb = a.x + (size_t)b * a.N * 3;
     const float* yb = a.y + (a.y_shared ? 0 : (size_t)b * a.M * 3);
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -153,6 +154,7 @@ struct MainArgs {
     int64_t* idx; float* d2;
     int b0;
     int* err;
+    const int* blist;
 };
 
 constexpr int CAND = 8;            // ring slots per epilogue thread: the CAND - 1 latest flagged chunks + one scratch slot
@@ -236,7 +238,7 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
     __shared__ int s_bad;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int rt = blockIdx.x, bl = blockIdx.y, b = a.b0 + bl;
+    const int rt = blockIdx.x, bl = blockIdx.y, b = a.blist ? a.blist[a.b0 + bl] : a.b0 + bl;
     const uint4* Ag = a.Aop + ((size_t)bl * a.ntN + rt) * TILE_U4;
     const uint4* Bg = a.Bop + (size_t)bl * a.ntM * TILE_U4;
     const int ntM = a.ntM;
@@ -438,7 +440,7 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
                     if (d < best) { best = d; bidx = j; }
                 }
             }
-            a.idx[(size_t)b * a.N + row] = bidx;
+            if (a.idx) a.idx[(size_t)b * a.N + row] = bidx;
             if (a.d2) a.d2[(size_t)b * a.N + row] = best;
         }
         nexact = __reduce_add_sync(0xffffffffu, nexact);
@@ -571,19 +573,18 @@ extern "C" size_t pb_knn1_tc_workspace_bytes(int B, int N, int M) {
     return tc_ws_bytes(B, N, M);
 }
 
-extern "C" int pb_knn1_tc(const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx, float* d2,
-                          void* ws, size_t ws_bytes, void* stream) {
-    PB_REQUIRE(B >= 0 && N >= 0 && M > 0, "pb_knn1_tc: bad sizes B=%d N=%d M=%d", B, N, M);
-    if (B == 0 || N == 0) return 0;
-    PB_REQUIRE(x && y && idx, "pb_knn1_tc: null pointer argument");
-    PB_REQUIRE(M <= (1 << 24), "pb_knn1_tc: M too large");
+// shared by pb_knn1_tc, pb_add_adds_tc and pb_pose_loss_fwd_tc: nearest y[b] point of every x[b] point for the
+// batch elements b = blist[0..nlist) (device array; NULL = all of 0..B)
+int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx,
+                        float* d2, void* ws, size_t ws_bytes, const int* blist, int nlist, cudaStream_t st) {
+    const int nl = blist ? nlist : B;
+    PB_REQUIRE(M <= (1 << 24), "%s: M too large", who);
     const size_t need = tc_ws_bytes(B, N, M);
-    PB_REQUIRE(ws && ws_bytes >= need, "pb_knn1_tc: workspace too small (%zu < %zu)", ws_bytes, need);
-    PB_REQUIRE(reinterpret_cast<uintptr_t>(ws) % 128 == 0, "pb_knn1_tc: workspace must be 128-byte aligned");
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    PB_REQUIRE(ws && ws_bytes >= need, "%s: workspace too small (%zu < %zu)", who, ws_bytes, need);
+    PB_REQUIRE(reinterpret_cast<uintptr_t>(ws) % 128 == 0, "%s: workspace must be 128-byte aligned", who);
     const int nb_max = B < TC_CHUNK ? B : TC_CHUNK;
     const int ntN = (N + TM - 1) / TM, ntM = (M + TM - 1) / TM;
-    PB_REQUIRE(ntN <= 65535 * 32, "pb_knn1_tc: N too large");
+    PB_REQUIRE(ntN <= 65535 * 32, "%s: N too large", who);
     char* base = static_cast<char*>(ws);
     int* err = reinterpret_cast<int*>(base);                          // int stats[4] at the head of the workspace
     uint4* Aop = reinterpret_cast<uint4*>(base + 128);
@@ -592,15 +593,24 @@ extern "C" int pb_knn1_tc(const float* x, const float* y, int B, int N, int M, i
     float* centre = tol + nb_max;
     cudaFuncSetAttribute(knn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAIN_SMEM);
     cudaMemsetAsync(err, 0, 4 * sizeof(int), st);   // [0] barrier timeout, [1] fallback rows, [2] exact evaluations
-    for (int b0 = 0; b0 < B; b0 += TC_CHUNK) {
-        const int nb = (B - b0) < TC_CHUNK ? (B - b0) : TC_CHUNK;
-        PrepArgs pa{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, centre, b0};
+    for (int b0 = 0; b0 < nl; b0 += TC_CHUNK) {
+        const int nb = (nl - b0) < TC_CHUNK ? (nl - b0) : TC_CHUNK;
+        PrepArgs pa{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, centre, b0, blist};
         cudaMemsetAsync(tol, 0, (size_t)nb * sizeof(float), st);
         knn_tc_prepare_kernel<<<dim3(nb, PREP_SPLIT), 256, 0, st>>>(pa);
         if (pb_check_launch("knn_tc_prepare_kernel")) return -2;
-        MainArgs ma{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, idx, d2, b0, err};
+        MainArgs ma{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, idx, d2, b0, err, blist};
         knn_tc_kernel<<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);
         if (pb_check_launch("knn_tc_kernel")) return -2;
     }
     return 0;
+}
+
+extern "C" int pb_knn1_tc(const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx, float* d2,
+                          void* ws, size_t ws_bytes, void* stream) {
+    PB_REQUIRE(B >= 0 && N >= 0 && M > 0, "pb_knn1_tc: bad sizes B=%d N=%d M=%d", B, N, M);
+    if (B == 0 || N == 0) return 0;
+    PB_REQUIRE(x && y && idx, "pb_knn1_tc: null pointer argument");
+    return pb_internal_knn1_tc("pb_knn1_tc", x, y, B, N, M, y_shared, idx, d2, ws, ws_bytes, nullptr, 0,
+                               static_cast<cudaStream_t>(stream));
 }

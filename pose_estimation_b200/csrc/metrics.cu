@@ -313,6 +313,37 @@ extern "C" int pb_pose_loss_fwd(const float* R, const float* t, const float* mod
     return pb_check_launch("gather_mean_l2_kernel") ? -2 : 0;
 }
 
+__global__ void identity_index_kernel(int64_t* __restrict__ nn_idx, int N) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) nn_idx[(size_t)blockIdx.y * N + i] = i;
+}
+
+// pb_pose_loss_fwd with the nearest-neighbour search of the symmetric samples on the tensor cores; sym_list is the
+// device list of the n_sym batch elements with sym != 0 (sym NULL = every element is symmetric).  Same bits out.
+extern "C" int pb_pose_loss_fwd_tc(const float* R, const float* t, const float* model, const float* target,
+                                   const uint8_t* sym, const int* sym_list, int n_sym, int B, int N, float* pred,
+                                   int64_t* nn_idx, float* loss_b, void* ws, size_t ws_bytes, void* stream) {
+    PB_REQUIRE(B >= 0 && N > 0, "pb_pose_loss_fwd_tc: bad sizes");
+    PB_REQUIRE(B <= 65535, "pb_pose_loss_fwd_tc: B too large (<= 65535)");
+    if (B == 0) return 0;
+    PB_REQUIRE(R && t && model && target && pred && nn_idx && loss_b, "pb_pose_loss_fwd_tc: null pointer argument");
+    PB_REQUIRE(!sym || (n_sym >= 0 && n_sym <= B && (sym_list || n_sym == 0)), "pb_pose_loss_fwd_tc: sym needs its list of set elements");
+    int rc = pb_transform_points(model, 0, R, t, B, N, pred, stream);
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (sym) {
+        identity_index_kernel<<<dim3((N + 255) / 256, B), 256, 0, st>>>(nn_idx, N);
+        if (pb_check_launch("identity_index_kernel")) return -2;
+    }
+    if (!sym || n_sym > 0) {
+        rc = pb_internal_knn1_tc("pb_pose_loss_fwd_tc", pred, target, B, N, N, 0, nn_idx, nullptr, ws, ws_bytes,
+                                 sym ? sym_list : nullptr, n_sym, st);
+        if (rc) return rc;
+    }
+    gather_mean_l2_kernel<<<B, KT, 0, st>>>(pred, target, nn_idx, N, loss_b);
+    return pb_check_launch("gather_mean_l2_kernel") ? -2 : 0;
+}
+
 extern "C" int pb_pose_loss_bwd(const float* pred, const float* model, const float* target, const int64_t* nn_idx, int B,
                                 int N, float gscale, float* grad_R, float* grad_t, void* stream) {
     PB_REQUIRE(B >= 0 && N > 0, "pb_pose_loss_bwd: bad sizes");

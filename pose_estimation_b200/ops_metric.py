@@ -59,17 +59,46 @@ def knn1(x, y, want_d2=False, impl="auto"):
     return (idx, d2) if want_d2 else idx
 
 
-def add_adds(pred, target, want_adds=None):
-    """pred/target [B,N,3] -> add [B], adds [B]; want_adds u8 [B] or None (all)."""
+def _aligned_ws(nbytes, device):
+    """128-byte aligned device workspace -> (owner tensor, ctypes pointer)."""
+    import ctypes as C
+    ws = torch.empty(nbytes + 128, dtype=torch.uint8, device=device)
+    off = (-ws.data_ptr()) % 128
+    return ws, off, C.c_void_p(ws.data_ptr() + off)
+
+
+def _sym_list(flags):
+    """u8 [B] device flags -> (int32 device list of the set elements, count); one host sync."""
+    lst = torch.nonzero(flags, as_tuple=False).flatten().to(torch.int32)
+    return lst, int(lst.numel())
+
+
+def add_adds(pred, target, want_adds=None, impl="auto"):
+    """pred/target [B,N,3] -> add [B], adds [B]; want_adds u8 [B] or None (all).
+    impl: "simt" exact FP32 scan, "tc" = N x N search on the tensor cores (same bits out), "auto" uses
+    "tc" for large problems when every element wants ADD-S (no flag list to build)."""
     pred = _chk(pred, torch.float32, "pred")
     target = _chk(target, torch.float32, "target")
     want_adds = _chk(want_adds, torch.uint8, "want_adds", True)
     if pred.shape != target.shape:
         raise ValueError("pred and target must have the same shape")
+    if impl not in ("auto", "tc", "simt"):
+        raise ValueError("impl must be auto, tc or simt")
     B, N, _ = pred.shape
     add = torch.empty((B,), dtype=torch.float32, device=pred.device)
     adds = torch.empty((B,), dtype=torch.float32, device=pred.device)
-    call("pb_add_adds", _ptr(pred), _ptr(target), B, N, _ptr(want_adds), _ptr(add), _ptr(adds), _stream())
+    if impl == "tc" or (impl == "auto" and want_adds is None and N * N >= TC_MIN_PAIRS):
+        from . import _lib
+        global LAST_TC_STATS
+        lst, n = (None, 0) if want_adds is None else _sym_list(want_adds)
+        nb = _lib.load().pb_add_adds_tc_workspace_bytes(B, N)
+        ws, off, wptr = _aligned_ws(nb, pred.device)
+        call("pb_add_adds_tc", _ptr(pred), _ptr(target), B, N, _ptr(want_adds), _ptr(lst), n, _ptr(add), _ptr(adds),
+             wptr, nb, _stream())
+        d2b = (B * N * 4 + 127) // 128 * 128
+        LAST_TC_STATS = ws[off + d2b: off + d2b + 16].view(torch.int32)
+    else:
+        call("pb_add_adds", _ptr(pred), _ptr(target), B, N, _ptr(want_adds), _ptr(add), _ptr(adds), _stream())
     return add, adds
 
 
@@ -144,18 +173,40 @@ def table_to_result(table, objlist):
     return res
 
 
-def pose_loss_fwd(R, t, model, target, sym):
-    """-> loss_b [B], pred [B,N,3], nn_idx [B,N] (lib/network/loss.py:25-41)."""
+def pose_loss_fwd(R, t, model, target, sym, impl="auto", sym_host=None):
+    """-> loss_b [B], pred [B,N,3], nn_idx [B,N] (lib/network/loss.py:25-41).
+    impl "tc": the symmetric samples' nearest-neighbour search runs on the tensor cores (same bits out);
+    "auto" picks it for large N when the caller also passes the flags as a host list (sym_host), so the
+    list of symmetric samples needs no device sync."""
     R = _chk(R, torch.float32, "R"); t = _chk(t, torch.float32, "t")
     model = _chk(model, torch.float32, "model"); target = _chk(target, torch.float32, "target")
     sym = _chk(sym, torch.uint8, "sym")
+    if impl not in ("auto", "tc", "simt"):
+        raise ValueError("impl must be auto, tc or simt")
     B, N, _ = model.shape
     dev = model.device
     pred = torch.empty((B, N, 3), dtype=torch.float32, device=dev)
     nn_idx = torch.empty((B, N), dtype=torch.int64, device=dev)
     loss_b = torch.empty((B,), dtype=torch.float32, device=dev)
-    call("pb_pose_loss_fwd", _ptr(R), _ptr(t), _ptr(model), _ptr(target), _ptr(sym), B, N, _ptr(pred),
-         _ptr(nn_idx), _ptr(loss_b), _stream())
+    if impl == "tc" or (impl == "auto" and sym_host is not None and any(sym_host) and N * N >= TC_MIN_PAIRS):
+        from . import _lib
+        global LAST_TC_STATS
+        sym_arg = sym
+        if sym_host is None:
+            lst, n = _sym_list(sym)
+        elif all(sym_host):
+            lst, n, sym_arg = None, 0, None
+        else:
+            ids = [i for i, f in enumerate(sym_host) if f]
+            lst, n = torch.tensor(ids, dtype=torch.int32, device=dev), len(ids)
+        nb = _lib.load().pb_knn1_tc_workspace_bytes(B, N, N)
+        ws, off, wptr = _aligned_ws(nb, dev)
+        call("pb_pose_loss_fwd_tc", _ptr(R), _ptr(t), _ptr(model), _ptr(target), _ptr(sym_arg), _ptr(lst), n, B, N,
+             _ptr(pred), _ptr(nn_idx), _ptr(loss_b), wptr, nb, _stream())
+        LAST_TC_STATS = ws[off: off + 16].view(torch.int32)
+    else:
+        call("pb_pose_loss_fwd", _ptr(R), _ptr(t), _ptr(model), _ptr(target), _ptr(sym), B, N, _ptr(pred),
+             _ptr(nn_idx), _ptr(loss_b), _stream())
     return loss_b, pred, nn_idx
 
 

@@ -77,3 +77,34 @@ def test_knn_tc_shared_database_and_adversarial_order(dev):
     idx_si = ops_metric.knn1(xt, yt, impl="simt")
     assert torch.equal(idx_tc, idx_si)
     assert (idx_tc == M - 1).float().mean() > 0.9
+
+
+def test_add_adds_and_pose_loss_on_tensor_cores_equal_simt_bits(dev):
+    """pb_add_adds_tc / pb_pose_loss_fwd_tc: mixed symmetric flags, results bit-identical to the SIMT entries
+    and to the CPU oracle's ADD-S."""
+    from pose_estimation_b200 import ops_metric
+    from oracle import cref
+    rng = np.random.default_rng(11)
+    B, N = 5, 700
+    model = (rng.normal(size=(B, N, 3)) * 0.05).astype(np.float32)
+    R = np.stack([np.linalg.qr(rng.normal(size=(3, 3)))[0] for _ in range(B)]).astype(np.float32)
+    t = (rng.normal(size=(B, 3)) * 0.02 + [0, 0, 0.8]).astype(np.float32)
+    Rg = np.stack([np.linalg.qr(rng.normal(size=(3, 3)))[0] for _ in range(B)]).astype(np.float32)
+    mt, Rt, tt, Rgt = (torch.from_numpy(a).to(dev) for a in (model, R, t, Rg))
+    pred = ops_metric.transform_points(mt, Rt, tt)
+    target = ops_metric.transform_points(mt, Rgt, tt)
+    for flags in ([1, 0, 1, 1, 0], [1, 1, 1, 1, 1], [0, 0, 0, 0, 0]):
+        want = torch.tensor(flags, dtype=torch.uint8, device=dev)
+        a_s, s_s = ops_metric.add_adds(pred, target, want, impl="simt")
+        a_t, s_t = ops_metric.add_adds(pred, target, want, impl="tc")
+        assert torch.equal(a_s, a_t) and torch.equal(s_s, s_t)
+        l_s, p_s, i_s = ops_metric.pose_loss_fwd(Rt, tt, mt, target, want, impl="simt")
+        l_t, p_t, i_t = ops_metric.pose_loss_fwd(Rt, tt, mt, target, want, impl="tc")
+        assert torch.equal(i_s, i_t) and torch.equal(l_s, l_t) and torch.equal(p_s, p_t)
+        l_h, _, i_h = ops_metric.pose_loss_fwd(Rt, tt, mt, target, want, impl="tc", sym_host=flags)
+        assert torch.equal(i_s, i_h) and torch.equal(l_s, l_h)
+    a_all, s_all = ops_metric.add_adds(pred, target, None, impl="tc")
+    a_ref, s_ref = ops_metric.add_adds(pred, target, None, impl="simt")
+    assert torch.equal(a_all, a_ref) and torch.equal(s_all, s_ref)
+    ra, rs = cref.add_adds(pred[0].cpu().numpy(), target[0].cpu().numpy())
+    assert np.isclose(float(a_all[0]), ra, rtol=1e-5) and np.isclose(float(s_all[0]), rs, rtol=1e-5)

@@ -75,7 +75,8 @@ def c3(args, dev):
 def c4(args, dev):
     """F frames, P = 10k correspondences, H = 1024 hypotheses, 5 re-score/refit rounds, T-vote on 10k points."""
     F, cap, H = args.c4_frames, 10240, 1024
-    sps = synth.make_batch_sparse(0x5EED, 4, min(F, 16), p_range=(10000, 10000), outlier_frac=0.3)
+    sps = synth.make_batch_sparse(0x5EED, 4, min(F, 16), p_range=(10000, 10000), outlier_frac=0.3,
+                                  z_range=(0.30, 0.40), xy_frac=0.25)       # close-ups: silhouettes >= 10k px
     pts = np.zeros((F, 5, cap), np.float32); cnt = np.zeros(F, np.int32)
     for f in range(F):
         p = synth.compact_points(sps[f % len(sps)])

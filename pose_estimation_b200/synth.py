@@ -63,7 +63,7 @@ def random_rotation(rng) -> np.ndarray:
 
 def make_frame_sparse(seed: int, config_id: int, frame: int, cls: int | None = None,
                       p_range=(800, 1200), outlier_frac=0.25, noise_m=1e-3,
-                      K4=LINEMOD_K4, H=IMG_H, W=IMG_W, outlier_min_px=0.0):
+                      K4=LINEMOD_K4, H=IMG_H, W=IMG_W, outlier_min_px=0.0, z_range=(0.6, 1.2), xy_frac=1.0):
     """One frame in sparse form.  Returns dict with
        rows,cols [P] int32 (row-major sorted), xyzn [P,3] f32 (normalised map values, never 0),
        cls, R_gt [3,3] f32, t_gt [3] f32, inlier [P] bool (ground truth of the injected outliers)."""
@@ -73,7 +73,8 @@ def make_frame_sparse(seed: int, config_id: int, frame: int, cls: int | None = N
     ext, lfb = EXTENT[cls], LFBORDER[cls]
     fx, fy, cx, cy = [float(v) for v in K4]
     R = random_rotation(rng)
-    t = np.array([rng.uniform(-0.15, 0.15), rng.uniform(-0.1, 0.1), rng.uniform(0.6, 1.2)])
+    t = np.array([rng.uniform(-0.15, 0.15) * xy_frac, rng.uniform(-0.1, 0.1) * xy_frac,
+                  rng.uniform(z_range[0], z_range[1])])      # close-up frames (C4) shrink z_range / xy_frac
     P = int(rng.integers(p_range[0], p_range[1] + 1))
     uc, vc = fx * t[0] / t[2] + cx, fy * t[1] / t[2] + cy
     smax = 0.49 * float(ext.max())

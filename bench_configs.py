@@ -1,6 +1,6 @@
 #!/usr/bin/env python
-"""bench_configs.py -- the other BASELINE.json configs (C3 KNN / ADD-S / symmetric-KNN loss, C4 dense
-correspondences + T-vote), measured with CUDA events on one B200.  bench.py stays the contract
+"""bench_configs.py -- the other BASELINE.json configs (C1 ape batch, C3 KNN / ADD-S / symmetric-KNN loss, C4 dense
+correspondences + T-vote, C5 65,536-frame sweep), measured with CUDA events on one B200.  bench.py stays the contract
 benchmark (C2); this script only fills BASELINE.md's table.  One JSON line per config."""
 from __future__ import annotations
 
@@ -94,18 +94,76 @@ def c4(args, dev):
                       "vote_ms": ms_v, "vote_GBps": F * NP * 24 / (ms_v * 1e-3) / 1e9}), flush=True)
 
 
+def c1(args, dev):
+    """LineMOD 'ape' batch: F = 1 and 64 frames of object 1, P ~ 1k masked px, 500-point model, H = 256."""
+    import pose_estimation_b200 as pb
+    out = {"config": "C1", "n_hyp": 256, "model_points": 500}
+    H, W = synth.IMG_H, synth.IMG_W
+    models = torch.from_numpy(synth.class_models(500))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    for F in (1, 64):
+        sps = [synth.make_frame_sparse(0x5EED, 1, f, cls=0) for f in range(F)]
+        xyz = np.zeros((F, 3, H, W), np.float32); mask = np.zeros((F, H, W), np.uint8)
+        for i, sp in enumerate(sps):
+            xyz[i], mask[i] = synth.dense_from_sparse(sp)
+        cls = np.zeros(F, np.int32)
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        inp = dict(xyz=t(xyz), mask=t(mask), cls=t(cls), extent=t(synth.EXTENT[cls].astype(np.float32)),
+                   lfborder=t(synth.LFBORDER[cls].astype(np.float32)), K4=t(np.tile(synth.LINEMOD_K4, (F, 1))),
+                   R_gt=t(np.stack([s["R_gt"] for s in sps])), t_gt=t(np.stack([s["t_gt"] for s in sps])))
+        sw = pb.EvalSweep(models, diam, sym, F, H, W, 4096, ops.RansacConfig(n_hyp=256, seed=0x5EED), device=dev)
+        def step():
+            sw.reset()
+            sw.step(inp["xyz"], inp["mask"], inp["extent"], inp["lfborder"], inp["K4"], inp["cls"], inp["R_gt"], inp["t_gt"])
+        ms = timed(step, max(args.iters, 20), warm=5)
+        tb = sw.table.cpu().numpy()
+        out[f"F{F}"] = {"ms_per_batch": ms, "frames_per_s": F / (ms * 1e-3), "P_mean": float(np.mean([len(s["rows"]) for s in sps])),
+                        "add_success": float(tb[ops_metric.ROW_VARIANT0, 0] / max(tb[ops_metric.ROW_OBJ_NUM, 0], 1))}
+    print(json.dumps(out), flush=True)
+
+
+def c5(args, dev):
+    """65,536-frame sweep as C2, streamed in chunks of 2048 frames per GPU; the same 2048 synthetic frames are
+    re-used for every chunk (frame0 differs, so the hypothesis streams differ); ends with the table reduction."""
+    import bench
+    import pose_estimation_b200 as pb
+    F, total = 2048, args.c5_frames
+    H, W = synth.IMG_H, synth.IMG_W
+    inp = bench.build_inputs(torch, dev, 0, F)
+    models = torch.from_numpy(synth.class_models(bench.N_MODEL))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    sw = pb.EvalSweep(models, diam, sym, F, H, W, bench.CAP, ops.RansacConfig(n_hyp=bench.N_HYP, seed=bench.SEED), device=dev)
+    def sweep():
+        sw.reset()
+        for c in range(total // F):
+            sw.step(inp["xyz"], inp["mask"], inp["extent"], inp["lfborder"], inp["K4"], inp["cls"], inp["R_gt"], inp["t_gt"],
+                    frame0=c * F)
+        return sw.finish()
+    ms = timed(sweep, 2, warm=1)
+    tb = sw.table.cpu().numpy()
+    print(json.dumps({"config": "C5", "frames": total, "chunk": F, "n_gpus": 1, "sweep_ms": ms,
+                      "frames_per_s": total / (ms * 1e-3), "map_bytes_streamed": total * (3 * H * W * 4 + H * W),
+                      "frames_counted": float(tb[ops_metric.ROW_ALL_NUM].sum()),
+                      "data": "synthetic; 2048 distinct frames re-used for each of the chunks"}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--c5-frames", type=int, default=65536)
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--c3-batch", type=int, default=4096)
     ap.add_argument("--c4-frames", type=int, default=256)
     ap.add_argument("--only", default="")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
+    if args.only in ("", "c1"):
+        c1(args, dev)
     if args.only in ("", "c3"):
         c3(args, dev)
     if args.only in ("", "c4"):
         c4(args, dev)
+    if args.only in ("", "c5"):
+        c5(args, dev)
 
 
 if __name__ == "__main__":

@@ -115,9 +115,9 @@ def transform_points(model, R, t):
     return out
 
 
-def pose_metrics(R, t, R_gt, t_gt, model, cls, is_sym, target=None):
+def pose_metrics(R, t, R_gt, t_gt, model, cls, is_sym, target=None, out=None):
     """R,R_gt [F,3,3]; t,t_gt [F,3]; model [C,N,3]; cls i32 [F]; is_sym u8 [C]; target [F,N,3]|None
-    -> add [F] (ADD-S for symmetric classes), r_deg [F], t_m [F]."""
+    -> add [F] (ADD-S for symmetric classes), r_deg [F], t_m [F] (written into ``out`` if given)."""
     R = _chk(R, torch.float32, "R"); t = _chk(t, torch.float32, "t")
     R_gt = _chk(R_gt, torch.float32, "R_gt"); t_gt = _chk(t_gt, torch.float32, "t_gt")
     model = _chk(model, torch.float32, "model")
@@ -127,9 +127,12 @@ def pose_metrics(R, t, R_gt, t_gt, model, cls, is_sym, target=None):
     F = R.shape[0]
     Cn, N, _ = model.shape
     dev = R.device
-    add = torch.empty((F,), dtype=torch.float32, device=dev)
-    r_deg = torch.empty((F,), dtype=torch.float32, device=dev)
-    t_m = torch.empty((F,), dtype=torch.float32, device=dev)
+    if out is not None:
+        add, r_deg, t_m = (_chk(o, torch.float32, "out") for o in out)
+    else:
+        add = torch.empty((F,), dtype=torch.float32, device=dev)
+        r_deg = torch.empty((F,), dtype=torch.float32, device=dev)
+        t_m = torch.empty((F,), dtype=torch.float32, device=dev)
     call("pb_pose_metrics", _ptr(R), _ptr(t), _ptr(R_gt), _ptr(t_gt), _ptr(model), _ptr(target), _ptr(cls),
          _ptr(is_sym), F, N, Cn, _ptr(add), _ptr(r_deg), _ptr(t_m), _stream())
     return add, r_deg, t_m

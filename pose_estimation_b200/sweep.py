@@ -61,7 +61,10 @@ class EvalSweep:
     STAGES = ("compact", "ransac", "metrics", "accumulate")
 
     def __init__(self, model_points, diameter, is_sym, F, H, W, cap, cfg: RansacConfig | None = None,
-                 device="cuda", add_frac=0.1, r_thr_deg=5.0, t_thr_m=0.05):
+                 device="cuda", add_frac=0.1, r_thr_deg=5.0, t_thr_m=0.05, lanes=1):
+        """lanes > 1: the batch is cut into ``lanes`` contiguous parts that run on their own streams, so the
+        HBM-bound K0 of one part overlaps the FP32-bound scoring and the latency-bound refit of another
+        (results are identical: frames are independent and the per-lane tables are summed)."""
         dev = torch.device(device)
         self.dev = dev
         self.F, self.H, self.W, self.cap = F, H, W, cap
@@ -70,16 +73,61 @@ class EvalSweep:
         self.diameter = diameter.to(dev, torch.float32).contiguous()          # [C]
         self.is_sym = is_sym.to(dev, torch.uint8).contiguous()                # [C]
         self.n_cls = self.model.shape[0]
+        self.add_frac, self.r_thr_deg, self.t_thr_m = add_frac, r_thr_deg, t_thr_m
+        self.lanes = []
+        if lanes > 1:
+            if F % lanes:
+                raise ValueError("F must be a multiple of lanes")
+            self.lanes = [EvalSweep(self.model, self.diameter, self.is_sym, F // lanes, H, W, cap, self.cfg, dev,
+                                    add_frac, r_thr_deg, t_thr_m) for _ in range(lanes)]
+            self.lane_streams = [torch.cuda.Stream(device=dev) for _ in range(lanes)]
+            self.ev_in = torch.cuda.Event()
+            self.ev_out = [torch.cuda.Event() for _ in range(lanes)]
+            self.out = torch.empty((3, F), dtype=torch.float32, device=dev)
+            self.launches_per_step = sum(l.launches_per_step for l in self.lanes)
+            return
         self.compact = ops.MapCompactor(F, H, W, cap, device=dev)
         self.ransac = ops.PtsRansac(F, cap, self.cfg, device=dev)
-        self.table = ops_metric.new_table(self.n_cls, dev)
-        self.add_frac, self.r_thr_deg, self.t_thr_m = add_frac, r_thr_deg, t_thr_m
+        self._table = ops_metric.new_table(self.n_cls, dev)
         self.launches_per_step = self.compact.launches(True) + self.ransac.launches + 2
 
-    def step(self, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=0, roi=None, events=None):
+    def reset(self):
+        """Zero the accuracy table(s)."""
+        for l in self.lanes:
+            l.reset()
+        if not self.lanes:
+            self._table.zero_()
+
+    @property
+    def table(self):
+        if self.lanes:
+            t = self.lanes[0].table.clone()
+            for l in self.lanes[1:]:
+                t += l.table
+            return t
+        return self._table
+
+    def step(self, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=0, roi=None, events=None, out=None):
         """One batch of F frames (device tensors).  Returns (add, r_deg, t_m) [F] device tensors.
         ``events``: optional list that receives one (name, start, end) CUDA-event triple per stage
         (recorded on the current stream; used by bench.py for the per-kernel roofline)."""
+        if self.lanes:
+            main = torch.cuda.current_stream(self.dev)
+            self.ev_in.record(main)
+            Fl = self.F // len(self.lanes)
+            for k, lane in enumerate(self.lanes):
+                s = self.lane_streams[k]
+                s.wait_event(self.ev_in)
+                lo, hi = k * Fl, (k + 1) * Fl
+                with torch.cuda.stream(s):
+                    lane.step(xyz[lo:hi], None if mask is None else mask[lo:hi], extent[lo:hi], lfborder[lo:hi],
+                              K4[lo:hi], cls[lo:hi], R_gt[lo:hi], t_gt[lo:hi], frame0=frame0 + lo,
+                              roi=None if roi is None else roi[lo:hi], out=tuple(self.out[j, lo:hi] for j in range(3)))
+                    self.ev_out[k].record(s)
+            for e in self.ev_out:
+                main.wait_event(e)
+            return self.out[0], self.out[1], self.out[2]
+
         def mark():
             if events is None:
                 return None
@@ -91,9 +139,9 @@ class EvalSweep:
         e1 = mark()
         rs = self.ransac(pts, count, K4, frame0=frame0)
         e2 = mark()
-        add, r_deg, t_m = ops_metric.pose_metrics(rs.R, rs.t, R_gt, t_gt, self.model, cls, self.is_sym)
+        add, r_deg, t_m = ops_metric.pose_metrics(rs.R, rs.t, R_gt, t_gt, self.model, cls, self.is_sym, out=out)
         e3 = mark()
-        ops_metric.accumulate_results(self.table, add, r_deg, t_m, cls, self.diameter, status=rs.status,
+        ops_metric.accumulate_results(self._table, add, r_deg, t_m, cls, self.diameter, status=rs.status,
                                       variant=0, add_frac=self.add_frac, r_thr_deg=self.r_thr_deg,
                                       t_thr_m=self.t_thr_m, count_frames=True)
         e4 = mark()

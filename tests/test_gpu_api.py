@@ -146,6 +146,37 @@ def test_host_eval_sweep_staged_and_zero_copy_equal_device(dev):
         assert hs.h2d_bytes > 0
 
 
+def test_eval_sweep_stream_lanes_and_graph_replay_equal_single_stream(dev):
+    """EvalSweep(lanes=2) (two streams) and a CUDA-graph replay of the step give the single-stream table and
+    per-frame outputs bit for bit."""
+    F = 16
+    sps = synth.make_batch_sparse(0x5EED, 2, F)
+    b = batch_arrays(sps)
+    models = torch.from_numpy(synth.class_models(500))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    t = lambda a: torch.from_numpy(a).to(dev)
+    args = [t(b[k]) for k in ("xyz", "mask", "extent", "lfborder", "K4", "cls", "R_gt", "t_gt")]
+    sw1 = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev)
+    add1, r1, t1 = (x.clone() for x in sw1.step(*args))
+    want = sw1.finish().clone()
+    sw2 = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev, lanes=2)
+    add2, r2, t2 = sw2.step(*args)
+    torch.cuda.synchronize()
+    assert torch.equal(sw2.finish(), want)
+    assert torch.equal(add2, add1) and torch.equal(r2, r1) and torch.equal(t2, t1)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        sw2.reset(); sw2.step(*args)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=s):
+        sw2.reset()
+        sw2.step(*args)
+    g.replay(); g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(sw2.table, want)
+
+
 def test_cpu_tensors_have_no_fallback():
     from pose_estimation_b200 import ops_metric
     from pose_estimation_b200._lib import PoseB200Error

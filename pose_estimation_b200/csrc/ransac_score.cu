@@ -13,8 +13,9 @@
 //       chunk in shared memory as float4(X,Y,Z,U') + float(V') and read as warp-broadcast LDS.128,
 //       so one shared-memory wavefront feeds 32*NHL tests.  The arithmetic is PACKED FP32x2
 //       (Blackwell FFMA2/FMUL2, fma.rn.f32x2): two points per instruction, IEEE-rn per half, so
-//       the bits equal the scalar contract in common.cuh::inlier_s.  Per hypothesis*point: 7 packed
-//       FMA-pipe instructions, one LOP (-|w|) and one funnel shift that pushes the verdict's sign
+//       the bits equal the scalar contract in common.cuh::inlier_s.  Per hypothesis*point: 4.5 packed
+//       + 5 scalar FMA-pipe instructions (the tail reads three 64-bit operands when packed, which costs
+//       register-file bandwidth, so it is scalar) and one funnel shift that pushes the verdict's sign
 //       bit into a 32-bit window (popcount every 8 points) -- no compare, no select, no reduction
 //       in the loop.  Chunks are padded to a multiple of 8 with never-inlier sentinels so the loop
 //       has no tail test.  FP32-pipe bound.
@@ -89,15 +90,36 @@ __device__ __forceinline__ f32x2 pack2(float lo, float hi) {
 }
 // inlier_s (common.cuh) for two points at once; nus/nvs are the NEGATED scaled pixel coordinates.
 // q = w*|w| enters as  w * (-|w|) = -q  (sign flips are exact), so every half has inlier_s' bits.
-__device__ __forceinline__ f32x2 inlier_s2(const f32x2 m[12], f32x2 X, f32x2 Y, f32x2 Z, f32x2 nus, f32x2 nvs) {
+#ifndef PB_SCORE_TAIL
+#define PB_SCORE_TAIL 1
+#endif
+__device__ __forceinline__ float lo32(f32x2 v) { return __uint_as_float((uint32_t)v); }
+__device__ __forceinline__ float hi32(f32x2 v) { return __uint_as_float((uint32_t)(v >> 32)); }
+// Returns the two verdict words (sign bit = inlier).  The nine matrix FMAs are packed (scalar-broadcast matrix
+// entry x packed point coordinate: 2-3 register reads per FFMA2); the five tail operations read three full
+// 64-bit operands as FFMA2 (6 register reads, 3 issue cycles), so they are issued as scalar FFMA instead.
+__device__ __forceinline__ void inlier_s2(const f32x2 m[12], f32x2 X, f32x2 Y, f32x2 Z, f32x2 nus, f32x2 nvs,
+                                          uint32_t& s0, uint32_t& s1) {
     const f32x2 x = ffma2(m[0], X, ffma2(m[1], Y, ffma2(m[2], Z, m[3])));
     const f32x2 y = ffma2(m[4], X, ffma2(m[5], Y, ffma2(m[6], Z, m[7])));
     const f32x2 w = ffma2(m[8], X, ffma2(m[9], Y, ffma2(m[10], Z, m[11])));
+#if PB_SCORE_TAIL == 0
     const f32x2 dx = ffma2(nus, w, x);
     const f32x2 dy = ffma2(nvs, w, y);
     const f32x2 nq = fmul2(w, w | 0x8000000080000000ull);
     const f32x2 t = ffma2(dy, dy, nq);
-    return ffma2(dx, dx, t);
+    const f32x2 sv = ffma2(dx, dx, t);
+    s0 = (uint32_t)sv; s1 = (uint32_t)(sv >> 32);
+#else
+    {
+        const float w0 = lo32(w), dx0 = fmaf(lo32(nus), w0, lo32(x)), dy0 = fmaf(lo32(nvs), w0, lo32(y));
+        const float nq0 = w0 * -fabsf(w0);
+        s0 = __float_as_uint(fmaf(dx0, dx0, fmaf(dy0, dy0, nq0)));
+        const float w1 = hi32(w), dx1 = fmaf(hi32(nus), w1, hi32(x)), dy1 = fmaf(hi32(nvs), w1, hi32(y));
+        const float nq1 = w1 * -fabsf(w1);
+        s1 = __float_as_uint(fmaf(dx1, dx1, fmaf(dy1, dy1, nq1)));
+    }
+#endif
 }
 
 constexpr int ST = 128;  // threads per scoring CTA: 128 x 64 regs x ~26 KB smem -> 8 CTAs per SM, so the
@@ -195,9 +217,10 @@ __global__ void __launch_bounds__(ST) ransac_score_kernel(ScoreArgs a) {
                 const ulonglong2 pa = a2[i + k], pbv = b2[i + k];
 #pragma unroll
                 for (int j = 0; j < NHL; ++j) {
-                    const f32x2 sv = inlier_s2(m[j], pa.x, pa.y, pbv.x, pbv.y, nvs[k]);
-                    acc[j] = __funnelshift_l((uint32_t)sv, acc[j], 1);
-                    acc[j] = __funnelshift_l((uint32_t)(sv >> 32), acc[j], 1);
+                    uint32_t s0, s1;
+                    inlier_s2(m[j], pa.x, pa.y, pbv.x, pbv.y, nvs[k], s0, s1);
+                    acc[j] = __funnelshift_l(s0, acc[j], 1);
+                    acc[j] = __funnelshift_l(s1, acc[j], 1);
                 }
             }
 #pragma unroll

@@ -52,6 +52,13 @@ typedef struct pb_ransac_params {
     uint32_t seed_lo, seed_hi; /* Philox key; replaces cv::RNG inside solvePnPRansac                          */
 } pb_ransac_params;
 
+typedef struct pb_sim3_params {
+    int32_t  n_iter;           /* maxIter = 128 (lib/transform/umeyama.py:21)                                     */
+    float    confidence;       /* 0.99 (:22): stop once 1 - (1 - ratio^5)^i exceeds it                            */
+    float    min_inlier_ratio; /* 0.1 (:50): below it the reference returns None -> PB_STATUS_NO_MODEL            */
+    uint32_t seed_lo, seed_hi; /* Philox key; replaces np.random.randint(nPoints, size=5) (:32)                   */
+} pb_sim3_params;
+
 const char* pb_last_error(void);
 int pb_abi_version(void);
 
@@ -102,6 +109,22 @@ int pb_pnp_ransac_map(const float* xyz, const uint8_t* mask, const int32_t* roi,
  * replaces lib/utils/utlis.py:64-71.  out [F,n] int32 (-1 if the frame has no inliers).       */
 int pb_resample_inliers(const uint32_t* inl_bitmap, const int32_t* count, int F, int cap, int n,
                         uint32_t frame0, uint32_t seed_lo, uint32_t seed_hi, int32_t* out, void* stream);
+
+/* ---- 3D-3D RANSAC + Umeyama similarity fit (lib/transform/umeyama.py:8-97; trans.py:9-123) --------
+ * For each of B problems: target ~ scale * R * source + t from `count[b]` corresponding pairs
+ * src/dst [B,cap,3].  n_iter hypotheses of 5 pairs drawn WITH replacement (sample_idx [B,n_iter,5]
+ * overrides the RNG), Umeyama per hypothesis, inlier iff |dst - (sR src + t)| < scale * diameter/10,
+ * the reference's sequential best-ratio / confidence-break rule replayed over the counts, then the
+ * Umeyama refit on the inliers.  Outputs: scale [B], R [B,9], t [B,3], n_inl, best_hyp (iteration
+ * index), status; optional hyp_counts [B,n_iter], inl_bitmap [B,ceil(cap/32)].                   */
+size_t pb_sim3_ransac_workspace_bytes(int B, const pb_sim3_params* prm);
+int pb_sim3_ransac(const float* src, const float* dst, const int32_t* count, int B, int cap,
+                   uint32_t prob0, const pb_sim3_params* prm /*host*/, const int32_t* sample_idx,
+                   float* scale, float* R, float* t, int32_t* n_inl, int32_t* best_hyp, int32_t* status,
+                   int32_t* hyp_counts, uint32_t* inl_bitmap, void* ws, size_t ws_bytes, void* stream);
+/* batched estimateSimilarityUmeyama (umeyama.py:65-97): least-squares similarity over all pairs. */
+int pb_umeyama_fit(const float* src, const float* dst, const int32_t* count, int B, int cap, float* scale,
+                   float* R, float* t, int32_t* status, void* stream);
 
 /* ---- K5: nearest neighbour / ADD-S -----------------------------------------------------------
  * pb_knn1 replaces the KeOps handle generic_argkmin('SqDist(x, y)','a = Vi(1)','x = Vi(3)',

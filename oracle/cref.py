@@ -16,8 +16,8 @@ _SO = os.path.join(_HERE, "libpose_ref.so")
 
 
 def build(force: bool = False) -> str:
-    src = os.path.join(_HERE, "pose_ref.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("pose_ref.c", "sim3_ref.c", "pose_ref.h")]
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s", "CC=gcc"])
     return _SO
 
@@ -34,8 +34,7 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
-        if not os.path.exists(_SO):
-            build()
+        build()
         _lib = C.CDLL(_SO)
         _lib.ref_ransac_frame.restype = C.c_int
         _lib.ref_compact_map.restype = C.c_int
@@ -44,6 +43,10 @@ def lib():
         _lib.ref_score.restype = C.c_int
         _lib.ref_hypothesis.restype = C.c_int
         _lib.ref_angular_deg.restype = C.c_float
+        _lib.ref_sim3_ransac.restype = C.c_int
+        _lib.ref_umeyama_fit.restype = C.c_int
+        _lib.ref_sim3_inlier_t.restype = C.c_double
+        _lib.ref_umeyama_core.restype = C.c_int
     return _lib
 
 
@@ -161,3 +164,34 @@ def resample_inliers(bitmap, P, n, seed=0x5EED, frame=0):
     lib().ref_resample_inliers(_p(bitmap), C.c_int(P), C.c_int(n), C.c_uint32(seed & 0xFFFFFFFF),
                                C.c_uint32(seed >> 32), C.c_uint32(frame), _p(out))
     return out
+
+
+def sim3_ransac(src, dst, n_iter=128, confidence=0.99, min_ratio=0.1, seed=0x5EED, prob=0, sample_idx=None):
+    """3D-3D RANSAC + Umeyama of ONE problem (sim3_ref.c) -> dict(status, scale, R, t, n_inl, best_hyp,
+    hyp_counts [n_iter], bitmap)."""
+    src = _f32(src); dst = _f32(dst)
+    n = src.shape[0]
+    si = None if sample_idx is None else np.ascontiguousarray(sample_idx, dtype=np.int32).reshape(n_iter, 5)
+    scale = C.c_float(); n_inl = C.c_int32(); best = C.c_int32()
+    R = np.zeros(9, np.float32); t = np.zeros(3, np.float32)
+    counts = np.zeros(n_iter, np.int32)
+    bitmap = np.zeros(max((n + 31) // 32, 1), np.uint32)
+    st = lib().ref_sim3_ransac(_p(src), _p(dst), C.c_int(n), C.c_int(n_iter), C.c_float(confidence), C.c_float(min_ratio),
+                               C.c_uint32(seed & 0xFFFFFFFF), C.c_uint32(seed >> 32), C.c_uint32(prob), _p(si),
+                               C.byref(scale), _p(R), _p(t), C.byref(n_inl), C.byref(best), _p(counts), _p(bitmap))
+    return dict(status=int(st), scale=float(scale.value), R=R.reshape(3, 3), t=t, n_inl=int(n_inl.value),
+                best_hyp=int(best.value), hyp_counts=counts, bitmap=bitmap)
+
+
+def sim3_sample5(seed, prob, hyp, n):
+    idx = np.zeros(5, np.int32)
+    lib().ref_sim3_sample5(C.c_uint32(seed & 0xFFFFFFFF), C.c_uint32(seed >> 32), C.c_uint32(prob), C.c_uint32(hyp),
+                           C.c_int(n), _p(idx))
+    return idx
+
+
+def umeyama_fit(src, dst):
+    src = _f32(src); dst = _f32(dst)
+    scale = C.c_float(); R = np.zeros(9, np.float32); t = np.zeros(3, np.float32)
+    st = lib().ref_umeyama_fit(_p(src), _p(dst), C.c_int(src.shape[0]), C.byref(scale), _p(R), _p(t))
+    return int(st), float(scale.value), R.reshape(3, 3), t

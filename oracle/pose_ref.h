@@ -93,6 +93,17 @@ void ref_vote_translation(const float* cloud, const float* t_res, int NP, float 
 void ref_resample_inliers(const uint32_t* bitmap, int P, int n, uint32_t seed_lo, uint32_t seed_hi,
                           uint32_t frame, int32_t* out);
 
+/* ---- 3D-3D RANSAC + Umeyama (sim3_ref.c; lib/transform/umeyama.py:8-97) ---- */
+int ref_umeyama_core(const double ms[3], const double mt[3], const double C[3][3], double varp, double* scale,
+                     double R[9], double T[3]);
+double ref_sim3_inlier_t(const float* src, int n);
+int ref_sim3_hypothesis(const float* src, const float* dst, int n, const int32_t idx[5], double inlier_t, float hyp[16]);
+void ref_sim3_sample5(uint32_t seed_lo, uint32_t seed_hi, uint32_t prob, uint32_t hyp, int n, int32_t idx[5]);
+int ref_sim3_ransac(const float* src, const float* dst, int n, int H, float confidence, float min_ratio, uint32_t seed_lo,
+                    uint32_t seed_hi, uint32_t prob, const int32_t* sample_idx, float* scale_out, float R_out[9],
+                    float t_out[3], int32_t* n_inl, int32_t* best_hyp, int32_t* hyp_counts, uint32_t* bitmap);
+int ref_umeyama_fit(const float* src, const float* dst, int n, float* scale_out, float R_out[9], float t_out[3]);
+
 #ifdef __cplusplus
 }
 #endif

@@ -51,6 +51,9 @@ SIGNATURES = {
     "pb_pose_loss_fwd_tc": (I, [P, P, P, P, P, P, I, I, I, P, P, P, P, SZ, P]),
     "pb_pose_loss_bwd": (I, [P, P, P, P, I, I, F32, P, P, P]),
     "pb_vote_translation": (I, [P, P, I, I, P, P]),
+    "pb_sim3_ransac_workspace_bytes": (SZ, [I, P]),
+    "pb_sim3_ransac": (I, [P, P, P, I, I, U32, P, P, P, P, P, P, P, P, P, P, P, SZ, P]),
+    "pb_umeyama_fit": (I, [P, P, P, I, I, P, P, P, P, P]),
     "pb_probe_fma": (I, [I, I, I, P, P]),
     "pb_tc_selftest": (I, [P, P, P, P, P]),
     "pb_stage_timing": (I, [I]),

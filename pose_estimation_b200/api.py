@@ -21,7 +21,7 @@ from __future__ import annotations
 import numpy as np
 import torch
 
-from . import ops, ops_metric
+from . import ops, ops_metric, ops_sim3
 from .ops import RansacConfig
 
 DEFAULT_RANSAC = RansacConfig()
@@ -219,3 +219,44 @@ def choose_ransac_batch(coor_emb, uv_emb, K_matrix, n=125, cfg: RansacConfig | N
     out = ops.pnp_ransac_pts(pts, count, batch_intrinsic_transform(K).contiguous(), cfg, want_bitmap=True)
     sel = ops.resample_inliers(out['inl_bitmap'], count, m, n, seed=cfg.seed)
     return sel.cpu().numpy().astype(np.int32).reshape(bs, 1, n)
+
+
+# ---- lib/transform/umeyama.py ---------------------------------------------------------------------------
+def _sim3_out(scale, R, t):
+    """(Scale, Rotation, Translation, OutTransform) as the reference returns them (float64 numpy)."""
+    S = float(scale)
+    Rn = R.double().cpu().numpy()
+    Tn = t.double().cpu().numpy()
+    M = np.identity(4)
+    M[:3, :3] = S * Rn
+    M[:3, 3] = Tn
+    return S, Rn, Tn, M
+
+
+def estimateSimilarityTransform(source, target, verbose=False, cfg: ops_sim3.Sim3Config | None = None, device="cuda"):
+    """lib/transform/umeyama.py:8-62: RANSAC similarity fit target ~ Scale * Rotation @ source + Translation.
+    source / target: (N,3) arrays.  Returns (Scale, Rotation, Translation, OutTransform), or four ``None`` when the
+    best inlier ratio is below 0.1 (the reference's failure return, :50-52).  The 5-point draws come from the
+    counter RNG of ``cfg.seed`` instead of numpy's global state."""
+    src = torch.as_tensor(np.asarray(source), dtype=torch.float32, device=device).reshape(1, -1, 3).contiguous()
+    dst = torch.as_tensor(np.asarray(target), dtype=torch.float32, device=device).reshape(1, -1, 3).contiguous()
+    if src.shape != dst.shape:
+        raise AssertionError("Source and Target must have same number of points.")      # umeyama.py:13
+    res = ops_sim3.sim3_ransac(src, dst, cfg=cfg)
+    if int(res.status.item()) != 0:
+        if verbose:
+            print("[ WARN ] - Something is wrong. Small BestInlierRatio")
+        return None, None, None, None
+    return _sim3_out(res.scale[0], res.R[0], res.t[0])
+
+
+def estimateSimilarityUmeyama(SourceHom, TargetHom, device="cuda"):
+    """lib/transform/umeyama.py:65-97: least-squares similarity over all columns of the (4,N) homogeneous arrays."""
+    s = np.ascontiguousarray(np.asarray(SourceHom)[:3].T)
+    t = np.ascontiguousarray(np.asarray(TargetHom)[:3].T)
+    src = torch.as_tensor(s, dtype=torch.float32, device=device).reshape(1, -1, 3)
+    dst = torch.as_tensor(t, dtype=torch.float32, device=device).reshape(1, -1, 3)
+    scale, R, tt, status = ops_sim3.umeyama_fit(src, dst)
+    if int(status.item()) != 0:
+        raise RuntimeError("estimateSimilarityUmeyama: degenerate input")
+    return _sim3_out(scale[0], R[0], tt[0])

@@ -143,3 +143,56 @@ def test_compaction_oracle_matches_reference_gather(cref):
     assert np.array_equal(pts, pts2)                     # xyz != 0 convention gives the same set
     e, _ = cref.compact_map(np.zeros((3, 8, 8), np.float32), None, np.ones(3), np.zeros(3))
     assert e.shape == (5, 0)
+
+
+# ---- 3D-3D RANSAC + Umeyama: the oracle against vectors produced by RUNNING the reference
+# (tests/golden/gen_golden_sim3.py imports /root/reference/lib/transform/umeyama.py) ---------------------
+def _sim3_golden():
+    import os
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sim3_ref.npz"))
+
+
+def test_sim3_oracle_matches_reference_run_iteration_by_iteration():
+    """With the reference's own np.random index sets: every iteration's inlier count, the chosen iteration (so
+    the confidence break fired at the same place), the refit set size and the final transform."""
+    from oracle import cref
+    g = _sim3_golden()
+    for k in range(5):
+        src, dst, idx, counts = g[f"src{k}"], g[f"dst{k}"], g[f"idx{k}"], g[f"counts{k}"]
+        it = idx.shape[0]                                   # iterations the reference ran before its break
+        si = np.concatenate([idx, np.repeat(idx[-1:], 128 - it, 0)]) if it < 128 else idx
+        r = cref.sim3_ransac(src, dst, sample_idx=si)
+        assert r["status"] == 0
+        assert np.array_equal(r["hyp_counts"][:it], counts)                 # integer work: exact
+        assert r["best_hyp"] == int(np.argmax(counts))                      # first maximum = strict '>' update
+        assert r["n_inl"] == int(counts.max())
+        assert abs(r["scale"] - float(g[f"scale{k}"])) <= 2e-7 * max(1.0, float(g[f"scale{k}"]))
+        assert np.abs(r["R"] - g[f"R{k}"]).max() <= 1e-6                    # FP32 outputs of an FP64 fit
+        assert np.abs(r["t"] - g[f"t{k}"]).max() <= 1e-6
+
+
+def test_umeyama_oracle_matches_reference_fit_including_reflection():
+    from oracle import cref
+    g = _sim3_golden()
+    for k in range(4):
+        st, sc, R, t = cref.umeyama_fit(g[f"u_src{k}"], g[f"u_dst{k}"])
+        assert st == 0
+        assert abs(sc - float(g[f"u_scale{k}"])) <= 2e-7 * max(1.0, sc)
+        assert np.abs(R - g[f"u_R{k}"]).max() <= 1e-6 and np.abs(t - g[f"u_t{k}"]).max() <= 1e-6
+        assert abs(np.linalg.det(R.astype(np.float64)) - 1.0) < 1e-5       # proper rotation even for the mirrored case
+
+
+def test_sim3_oracle_edge_cases():
+    from oracle import cref
+    rng = np.random.default_rng(3)
+    src = rng.random((40, 3)).astype(np.float32)
+    # no consistent transform: unrelated clouds -> best ratio stays below 0.1 -> the reference's None return
+    r = cref.sim3_ransac(src, rng.random((40, 3)).astype(np.float32) * 50, n_iter=16)
+    assert r["status"] in (0, 2)
+    # all draws identical (np.random can return five equal indices): zero variance -> no inliers for that iteration
+    si = np.zeros((16, 5), np.int32)
+    r = cref.sim3_ransac(src, src * 2 + 1, n_iter=16, sample_idx=si)
+    assert r["status"] == 2 and r["best_hyp"] == -1 and not r["hyp_counts"].any()
+    # counter RNG draws are in range and reproducible
+    a = cref.sim3_sample5(0x5EED, 3, 7, 40)
+    assert np.array_equal(a, cref.sim3_sample5(0x5EED, 3, 7, 40)) and a.min() >= 0 and a.max() < 40

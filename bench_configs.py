@@ -147,8 +147,45 @@ def c5(args, dev):
                       "data": "synthetic; 2048 distinct frames re-used for each of the chunks"}), flush=True)
 
 
+def f3(args, dev):
+    """B problems of n = 1000 correspondences, 128 iterations (lib/transform/umeyama.py defaults),
+    40 % outliers; beside it the C port of the same algorithm on one host core (bounded sample)."""
+    import time
+    from pose_estimation_b200 import ops_sim3
+    B, n = args.f3_problems, 1000
+    rng = np.random.default_rng(33)
+    src = ((rng.random((B, n, 3)) - 0.5) * 0.2).astype(np.float32)
+    dst = np.empty_like(src)
+    for b in range(B):
+        R = synth.random_rotation(np.random.default_rng(b))
+        d = src[b] @ R.T.astype(np.float32) + rng.normal(size=3).astype(np.float32) * 0.1
+        out = rng.random(n) < 0.4
+        d[out] = (rng.random((int(out.sum()), 3)) - 0.5).astype(np.float32)
+        dst[b] = d
+    sd, dd = torch.from_numpy(src).to(dev), torch.from_numpy(dst).to(dev)
+    cnt = torch.full((B,), n, dtype=torch.int32, device=dev)
+    ms = timed(lambda: ops_sim3.sim3_ransac(sd, dd, cnt), max(args.iters, 10))
+    r = ops_sim3.sim3_ransac(sd, dd, cnt)
+    ok = float((r.status == 0).float().mean())
+    out = {"config": "f3 sim3", "problems": B, "pairs": n, "n_iter": 128, "ms": ms, "problems_per_s": B / (ms * 1e-3),
+           "hyp_pairs_per_s": B * 128.0 * n / (ms * 1e-3), "status_ok_frac": ok}
+    try:
+        from oracle import cref
+        m = min(B, 64)
+        t0 = time.perf_counter()
+        for b in range(m):
+            cref.sim3_ransac(src[b], dst[b], prob=b)
+        dt = time.perf_counter() - t0
+        out["cpu_port"] = {"ms_per_problem": dt / m * 1e3, "problems_per_s_per_core": m / dt, "cores": 1,
+                           "sample": f"{m} problems, C restatement of the same algorithm (all 128 iterations scored)"}
+    except Exception as e:                                   # the oracle is optional here
+        out["cpu_port"] = {"unavailable": repr(e)[:100]}
+    print(json.dumps(out), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--f3-problems", type=int, default=1024)
     ap.add_argument("--c5-frames", type=int, default=65536)
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--c3-batch", type=int, default=4096)
@@ -164,6 +201,8 @@ def main():
         c4(args, dev)
     if args.only in ("", "c5"):
         c5(args, dev)
+    if args.only in ("", "f3"):
+        f3(args, dev)
 
 
 if __name__ == "__main__":

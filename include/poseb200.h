@@ -126,6 +126,15 @@ int pb_sim3_ransac(const float* src, const float* dst, const int32_t* count, int
 int pb_umeyama_fit(const float* src, const float* dst, const int32_t* count, int B, int cap, float* scale,
                    float* R, float* t, int32_t* status, void* stream);
 
+/* ---- farthest point sampling (tools/script/sample_model.py:33-63) ----------------------------------
+ * For each of B clouds pts [B,cap,3] (count[b] valid points, NULL -> cap): idx[b, 0] = 0, then
+ * repeatedly the point farthest from the chosen set; float32 sqrt((dx*dx+dy*dy)+dz*dz) distances
+ * and np.argmax's first-maximum rule, so the indices equal the reference's.  idx [B,n_samples]
+ * int32 (-1 rows for empty clouds).  ws only for cap > 57344 (pb_fps_workspace_bytes).           */
+size_t pb_fps_workspace_bytes(int B, int cap);
+int pb_fps(const float* pts, const int32_t* count, int B, int cap, int n_samples, int32_t* idx, void* ws,
+           size_t ws_bytes, void* stream);
+
 /* ---- K5: nearest neighbour / ADD-S -----------------------------------------------------------
  * pb_knn1 replaces the KeOps handle generic_argkmin('SqDist(x, y)','a = Vi(1)','x = Vi(3)',
  * 'y = Vj(3)') (train.py:126; used lib/network/loss.py:34, version/transparent/lib/utils.py:24):

@@ -195,3 +195,10 @@ def umeyama_fit(src, dst):
     scale = C.c_float(); R = np.zeros(9, np.float32); t = np.zeros(3, np.float32)
     st = lib().ref_umeyama_fit(_p(src), _p(dst), C.c_int(src.shape[0]), C.byref(scale), _p(R), _p(t))
     return int(st), float(scale.value), R.reshape(3, 3), t
+
+
+def fps(points, n_samples):
+    points = _f32(points)
+    out = np.zeros(n_samples, np.int32)
+    lib().ref_fps(_p(points), C.c_int(points.shape[0]), C.c_int(n_samples), _p(out))
+    return out

@@ -102,6 +102,7 @@ void ref_sim3_sample5(uint32_t seed_lo, uint32_t seed_hi, uint32_t prob, uint32_
 int ref_sim3_ransac(const float* src, const float* dst, int n, int H, float confidence, float min_ratio, uint32_t seed_lo,
                     uint32_t seed_hi, uint32_t prob, const int32_t* sample_idx, float* scale_out, float R_out[9],
                     float t_out[3], int32_t* n_inl, int32_t* best_hyp, int32_t* hyp_counts, uint32_t* bitmap);
+void ref_fps(const float* pts, int n, int n_samples, int32_t* out);
 int ref_umeyama_fit(const float* src, const float* dst, int n, float* scale_out, float R_out[9], float t_out[3]);
 
 #ifdef __cplusplus

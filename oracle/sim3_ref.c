@@ -10,6 +10,7 @@
  */
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 #include "pose_ref.h"
 
@@ -254,4 +255,29 @@ int ref_sim3_ransac(const float* src, const float* dst, int n, int H, float conf
 int ref_umeyama_fit(const float* src, const float* dst, int n, float* scale_out, float R_out[9], float t_out[3]) {
     int32_t n_inl, best;
     return ref_sim3_ransac(src, dst, n, 0, 0.99f, 0.0f, 0u, 0u, 0u, 0, scale_out, R_out, t_out, &n_inl, &best, 0, 0);
+}
+
+/* farthest point sampling, tools/script/sample_model.py:33-63: float32 sqrt((dx*dx+dy*dy)+dz*dz), start at
+ * index 0, np.argmax (first maximum) */
+void ref_fps(const float* pts, int n, int n_samples, int32_t* out) {
+    if (n <= 0) { for (int i = 0; i < n_samples; ++i) out[i] = -1; return; }
+    float* dist = (float*)malloc((size_t)n * sizeof(float));
+    for (int i = 0; i < n; ++i) dist[i] = INFINITY;
+    int cur = 0;
+    for (int it = 0; it < n_samples; ++it) {
+        out[it] = cur;
+        const float cx = pts[3 * (size_t)cur], cy = pts[3 * (size_t)cur + 1], cz = pts[3 * (size_t)cur + 2];
+        int best = 0;
+        float bv = -1.0f;
+        for (int i = 0; i < n; ++i) {
+            const float dx = pts[3 * (size_t)i] - cx, dy = pts[3 * (size_t)i + 1] - cy, dz = pts[3 * (size_t)i + 2] - cz;
+            const float a = dx * dx, b2 = dy * dy, c = dz * dz;
+            const float d = sqrtf((a + b2) + c);
+            const float m = dist[i] < d ? dist[i] : d;
+            dist[i] = m;
+            if (m > bv) { bv = m; best = i; }
+        }
+        cur = best;
+    }
+    free(dist);
 }

@@ -54,6 +54,8 @@ SIGNATURES = {
     "pb_sim3_ransac_workspace_bytes": (SZ, [I, P]),
     "pb_sim3_ransac": (I, [P, P, P, I, I, U32, P, P, P, P, P, P, P, P, P, P, P, SZ, P]),
     "pb_umeyama_fit": (I, [P, P, P, I, I, P, P, P, P, P]),
+    "pb_fps_workspace_bytes": (SZ, [I, I]),
+    "pb_fps": (I, [P, P, I, I, I, P, P, SZ, P]),
     "pb_probe_fma": (I, [I, I, I, P, P]),
     "pb_tc_selftest": (I, [P, P, P, P, P]),
     "pb_stage_timing": (I, [I]),

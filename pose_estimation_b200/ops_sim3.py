@@ -95,3 +95,21 @@ def umeyama_fit(src, dst, count=None):
     status = torch.empty((B,), dtype=torch.int32, device=dev)
     call("pb_umeyama_fit", _ptr(src), _ptr(dst), _ptr(count), B, cap, _ptr(scale), _ptr(R), _ptr(t), _ptr(status), _stream())
     return scale, R, t, status
+
+
+def farthest_point_sampling(points, n_samples, count=None):
+    """points [B,N,3] or [N,3] f32 CUDA -> int32 indices [B,n_samples] (or [n_samples]); same selection as
+    tools/script/sample_model.py:33-46 (start at index 0, float32 distances, first maximum on ties)."""
+    points = _chk(points, torch.float32, "points")
+    squeeze = points.dim() == 2
+    if squeeze:
+        points = points.unsqueeze(0)
+    if points.dim() != 3 or points.shape[-1] != 3:
+        raise ValueError("points must be [B,N,3] or [N,3]")
+    B, cap, _ = points.shape
+    count = _chk(count, torch.int32, "count", True)
+    out = torch.empty((B, n_samples), dtype=torch.int32, device=points.device)
+    nb = _lib.load().pb_fps_workspace_bytes(B, cap)
+    ws = torch.empty(nb, dtype=torch.uint8, device=points.device) if nb else None
+    call("pb_fps", _ptr(points), _ptr(count), B, cap, int(n_samples), _ptr(out), _ptr(ws), nb, _stream())
+    return out[0] if squeeze else out

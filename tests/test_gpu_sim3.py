@@ -110,3 +110,23 @@ def test_umeyama_fit_and_reference_shaped_api(dev):
     assert abs(S - float(g["scale0"])) < 2e-3 and np.abs(Rr - g["R0"]).max() < 2e-3      # other draws, same model
     none = pb.estimateSimilarityTransform(np.random.default_rng(1).random((50, 3)), np.random.default_rng(2).random((50, 3)) * 100)
     assert none == (None, None, None, None) or none[0] is not None
+
+
+def test_farthest_point_sampling_equals_reference_and_oracle(dev):
+    from oracle import cref
+    from pose_estimation_b200 import ops_sim3
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fps_ref.npz"))
+    for k in range(5):
+        pts, want = g[f"pts{k}"], g[f"idx{k}"]
+        got = ops_sim3.farthest_point_sampling(torch.from_numpy(pts).to(dev), want.shape[0]).cpu().numpy()
+        assert np.array_equal(got, want), k                                    # = the reference's selection
+    rng = np.random.default_rng(9)                                             # batched, ragged counts
+    B, cap = 4, 5000
+    pts = rng.random((B, cap, 3)).astype(np.float32)
+    cnt = np.array([5000, 1234, 0, 77], np.int32)
+    got = ops_sim3.farthest_point_sampling(torch.from_numpy(pts).to(dev), 128, torch.from_numpy(cnt).to(dev)).cpu().numpy()
+    for b in range(B):
+        if cnt[b] == 0:
+            assert (got[b] == -1).all()
+        else:
+            assert np.array_equal(got[b], cref.fps(pts[b, :cnt[b]], 128)), b

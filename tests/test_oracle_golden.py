@@ -196,3 +196,14 @@ def test_sim3_oracle_edge_cases():
     # counter RNG draws are in range and reproducible
     a = cref.sim3_sample5(0x5EED, 3, 7, 40)
     assert np.array_equal(a, cref.sim3_sample5(0x5EED, 3, 7, 40)) and a.min() >= 0 and a.max() < 40
+
+
+def test_fps_oracle_matches_reference_selection():
+    """tools/script/sample_model.py:33-46 run here (tests/golden/gen_golden_fps.py): identical index sequences,
+    including duplicated points and n_samples > N."""
+    import os
+    from oracle import cref
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fps_ref.npz"))
+    for k in range(5):
+        want = g[f"idx{k}"]
+        assert np.array_equal(cref.fps(g[f"pts{k}"], want.shape[0]), want), k

@@ -331,10 +331,10 @@ def ours_arm(args):
     dense_bytes = F * 480 * 640 * 12 + inp["n_px"] * 20
     sparse_bytes = F * 480 * 640 + inp["n_px"] * (3 * 32 + 20)
     score_flop = 27.0 * N_HYP * inp["n_px"]
-    roof_score = {"kernel": "ransac_score_kernel (K3: reprojection scoring of every masked pixel x 256 hypotheses)",
+    roof_score = {"kernel": "ransac_score_bal_kernel (K3: reprojection scoring of every masked pixel x 256 hypotheses; CTAs take equal ranges of the batch's point list)",
                   "bound": "fp32", "achieved": score_flop / (score_ms * 1e-3) / 1e12, "peak": fp32_peak,
                   "unit": "TFLOP/s", "frac": score_flop / (score_ms * 1e-3) / 1e12 / fp32_peak,
-                  "traffic": traffic.get("ransac_score_kernel"),
+                  "traffic": traffic.get("ransac_score_bal_kernel", traffic.get("ransac_score_kernel")),
                   "peak_source": "FFMA/FFMA2 probe kernel timed in this run (MEASURED_PEAKS.json has no FP32 entry); "
                                  "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4",
                   "algorithmic_flop_per_launch": score_flop, "flop_per_hyp_pt": 27, "launch_ms": score_ms,
@@ -415,11 +415,11 @@ def ours_arm(args):
                                             "api": "HostEvalSweep.run(zero_copy=False): whole maps copied H2D in "
                                                    "128-frame chunks overlapped with compute"}},
             "gpu_launches": args.steps * sw.launches_per_step,
-            "kernels_per_step": ["compact_sparse_kernel", "ransac_hypothesis_kernel", "ransac_score_kernel",
+            "kernels_per_step": ["compact_sparse_kernel", "ransac_hypothesis_kernel", "ransac_score_bal_kernel",
                                  "ransac_finalize_kernel", "pose_metrics_kernel", "accumulate_kernel"],
             "stage_ms": dict(zip(sw.STAGES, stage_ms)),
             "kernel_ms": {"compact_sparse_kernel": k0_ms, "ransac_hypothesis_kernel": hyp_ms,
-                          "ransac_score_kernel": score_ms, "ransac_finalize_kernel": final_ms,
+                          "ransac_score_bal_kernel": score_ms, "ransac_finalize_kernel": final_ms,
                           "pose_metrics_kernel": stage_ms[2], "accumulate_kernel": stage_ms[3]},
             "roofline": roof_score,                 # the dominant kernel of the step
             "roofline_all": [roof_score, roof_k0, roof_dense],

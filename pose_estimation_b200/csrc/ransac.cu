@@ -20,6 +20,7 @@ struct FinalArgs {
     const float* K4;
     const float* hypRt;
     const unsigned long long* slice_best;
+    const int32_t* cnt_all;          // balanced scoring: [F,H] counts, the arg-max is taken here
     float* R; float* t; int32_t* n_inl; int32_t* best_hyp; int32_t* n_inl_refined; int32_t* status;
     uint32_t* inl_bitmap; float* R0; float* t0;
     int cap, H, HS, gn_iters, lo_rounds, min_inliers;
@@ -170,11 +171,26 @@ __global__ void __launch_bounds__(32 * G) ransac_finalize_kernel(FinalArgs a) {
     const float* V = U + a.cap;
     const float fx = a.K4[4 * f], fy = a.K4[4 * f + 1], cx = a.K4[4 * f + 2], cy = a.K4[4 * f + 3];
 
-    // argmax over slices
-    unsigned long long key = a.slice_best[(size_t)f * a.HS];
-    for (int s = 1; s < a.HS; ++s) {
-        unsigned long long k = a.slice_best[(size_t)f * a.HS + s];
-        key = k > key ? k : key;
+    // argmax over slices (or, after balanced scoring, over the hypotheses' counts: every warp redundantly,
+    // max count, lowest hypothesis index on ties -- the same packed key the scoring kernel builds)
+    unsigned long long key = 0ull;
+    if (a.cnt_all) {
+        for (int h = lane; h < a.H; h += 32) {
+            const int cv = a.cnt_all[(size_t)f * a.H + h];
+            const unsigned long long k2 = ((unsigned long long)(uint32_t)(cv + 1) << 32) | (0xFFFFFFFFu - (uint32_t)h);
+            key = k2 > key ? k2 : key;
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+            const unsigned long long o = __shfl_xor_sync(0xffffffffu, key, off);
+            key = o > key ? o : key;
+        }
+    } else {
+        key = a.slice_best[(size_t)f * a.HS];
+        for (int s = 1; s < a.HS; ++s) {
+            unsigned long long k = a.slice_best[(size_t)f * a.HS + s];
+            key = k > key ? k : key;
+        }
     }
     const int bc = (int)(uint32_t)(key >> 32) - 1;
     const int bh = (int)(0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull));
@@ -385,12 +401,13 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     sa.hypRt = static_cast<float*>(ws);
     sa.hyp_counts = hyp_counts;
     sa.slice_best = reinterpret_cast<unsigned long long*>(static_cast<char*>(ws) + p.off_best);
+    sa.cnt_all = p.bal ? (hyp_counts ? hyp_counts : reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_cnt)) : nullptr;
     sa.cap = cap; sa.H = prm->n_hyp; sa.HS = p.HS; sa.Hs = p.Hs; sa.CH = p.CH; sa.PP = p.PP;
     sa.frame0 = frame0; sa.seed_lo = prm->seed_lo; sa.seed_hi = prm->seed_hi;
     sa.inv_thr = 1.0f / prm->thresh_px; sa.F = F;
     if (pb_launch_score(sa, p, F, st)) return -2;
     FinalArgs fa;
-    fa.pts = pts; fa.count = count; fa.K4 = K4; fa.hypRt = sa.hypRt; fa.slice_best = sa.slice_best;
+    fa.pts = pts; fa.count = count; fa.K4 = K4; fa.hypRt = sa.hypRt; fa.slice_best = sa.slice_best; fa.cnt_all = sa.cnt_all;
     fa.R = R; fa.t = t; fa.n_inl = n_inl; fa.best_hyp = best_hyp; fa.n_inl_refined = n_inl_refined;
     fa.status = status; fa.inl_bitmap = inl_bitmap; fa.R0 = R0; fa.t0 = t0;
     fa.cap = cap; fa.H = prm->n_hyp; fa.HS = p.HS; fa.gn_iters = prm->gn_iters; fa.lo_rounds = prm->lo_rounds;

@@ -10,6 +10,7 @@ struct ScoreArgs {
     float* hypRt;                    // [F,H,12] R|t of every hypothesis (t_z = NaN: no model)
     int32_t* hyp_counts;             // optional [F,H]
     unsigned long long* slice_best;  // [F,HS] packed (count+1, ~hyp)
+    int32_t* cnt_all;                // balanced mode: [F,H] inlier counts accumulated with atomics (-1 = no model)
     int cap, H, HS, Hs, CH, PP;      // Hs hypotheses per slice (power of two >= 32); PP point parts
     uint32_t frame0, seed_lo, seed_hi;
     float inv_thr;
@@ -19,11 +20,14 @@ struct ScoreArgs {
 struct Plan {
     int HS, Hs, CH, PP, NHL;
     size_t smem_score, smem_final, off_best, total;
+    int bal, bal_grid;               // balanced scoring (see ransac_score_bal_kernel): CTAs of equal point ranges
+    size_t smem_bal, off_cnt;
 };
 
 // Hypotheses of a frame are cut into HS slices of Hs (power of two) so that few-frame launches
 // still fill 148 SMs; a slice narrower than the CTA splits the points PP ways instead.
 #define PB_SCORE_THREADS 128     /* CTA size of the scoring kernel (ST in ransac_score.cu) */
+#define PB_BAL_CH 1024           /* points staged per chunk by the balanced scoring kernel */
 
 static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm) {
     Plan p;
@@ -46,6 +50,16 @@ static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm) {
     size_t hyp = (size_t)F * H * 12 * sizeof(float);
     p.off_best = (hyp + 255) / 256 * 256;
     p.total = p.off_best + (size_t)F * p.HS * sizeof(unsigned long long);
+    // A batch of about one wave of CTAs cannot be rebalanced by the hardware scheduler: frames carry different
+    // numbers of points and the launch lasts as long as the SM with the largest sum.  Then CTAs take equal
+    // ranges of the concatenated point list instead (H <= 256 hypotheses held by one CTA).
+    p.smem_bal = (size_t)PB_BAL_CH * 5 * 4 + (size_t)(F + 1) * 4;
+    int per_sm = (int)((220 * 1024) / (p.smem_bal + 1024));
+    if (per_sm > 6) per_sm = 6;                        // 80 registers x 128 threads: six CTAs per SM, one wave
+    p.bal = (p.HS == 1 && p.PP == 1 && F >= 296 && F <= 2368 && per_sm >= 4) ? 1 : 0;
+    p.bal_grid = 148 * per_sm;
+    p.off_cnt = (p.total + 255) / 256 * 256;
+    if (p.bal) p.total = p.off_cnt + (size_t)F * H * sizeof(int32_t);
     return p;
 }
 

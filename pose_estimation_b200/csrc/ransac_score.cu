@@ -68,6 +68,7 @@ __global__ void __launch_bounds__(HT) ransac_hypothesis_kernel(ScoreArgs a) {
     } else {
         o[11] = __int_as_float(0x7fffffff);  // t_z = NaN marks "no model"
     }
+    if (a.cnt_all) a.cnt_all[gid] = valid ? 0 : -1;   // balanced scoring accumulates into these
 }
 
 typedef unsigned long long f32x2;   // two packed binary32 values (lo = even point, hi = odd point)
@@ -261,6 +262,151 @@ __global__ void __launch_bounds__(ST) ransac_score_kernel(ScoreArgs a) {
     }
 }
 
+// Balanced scoring: gridDim.x CTAs, all resident, each takes an EQUAL range of the batch's concatenated point
+// list (a range usually touches two frames) -- for every frame segment it loads that frame's hypotheses, scores
+// the segment exactly like ransac_score_kernel and adds its counts to cnt_all[f][h].  Inlier counts are integer
+// sums, so the result does not depend on the cut.  The arg-max moves to the finalize kernel.
+template <int NHL>
+__global__ void __launch_bounds__(ST, 6) ransac_score_bal_kernel(ScoreArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int CH = PB_BAL_CH;
+    float4* sA = reinterpret_cast<float4*>(smem_raw);            // [CH/2]
+    float4* sB = sA + CH / 2;                                    // [CH/2]
+    float2* sC = reinterpret_cast<float2*>(sB + CH / 2);         // [CH/2]
+    int* prefix = reinterpret_cast<int*>(sC + CH / 2);           // [F+1] exclusive prefix of the frames' point counts
+    __shared__ int wsum[ST / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int F = a.F;
+    // ---- block scan of min(count, cap): thread t owns frames [t*per, (t+1)*per)
+    const int per = (F + ST - 1) / ST;
+    int mine = 0;
+    for (int k = 0; k < per; ++k) {
+        const int f = tid * per + k;
+        if (f < F) mine += min(a.count[f], a.cap);
+    }
+    int incl = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += v;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    int base = incl - mine;
+    for (int w = 0; w < warp; ++w) base += wsum[w];
+    for (int k = 0; k < per; ++k) {
+        const int f = tid * per + k;
+        if (f < F) { prefix[f] = base; base += min(a.count[f], a.cap); }
+    }
+    if (tid == ST - 1) prefix[F] = base;
+    __syncthreads();
+    const int T = prefix[F];
+    int U = (T + (int)gridDim.x - 1) / (int)gridDim.x;
+    U = (U + 7) & ~7;
+    const long long g0l = (long long)blockIdx.x * U;
+    if (g0l >= T) return;
+    const int g0 = (int)g0l, g1 = min(T, g0 + U);
+    int lo = 0, hi = F;                                          // last f with prefix[f] <= g0
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (prefix[mid] <= g0) lo = mid; else hi = mid;
+    }
+    const float ninf = __int_as_float(0xff800000);
+    float* sAf = reinterpret_cast<float*>(sA);
+    float* sBf = reinterpret_cast<float*>(sB);
+    float* sCf = reinterpret_cast<float*>(sC);
+    for (int f = lo; f < F && prefix[f] < g1; ++f) {
+        const int p0 = max(g0, prefix[f]) - prefix[f], p1 = min(g1, prefix[f + 1]) - prefix[f];
+        if (p1 <= p0) continue;
+        const float* X = a.pts + (size_t)f * 5 * a.cap;
+        const float* Y = X + a.cap;
+        const float* Z = Y + a.cap;
+        const float* Uu = Z + a.cap;
+        const float* V = Uu + a.cap;
+        const float fx = a.K4[4 * f], fy = a.K4[4 * f + 1], cx = a.K4[4 * f + 2], cy = a.K4[4 * f + 3];
+        f32x2 m[NHL][12];
+        int c[NHL];
+#pragma unroll
+        for (int j = 0; j < NHL; ++j) {
+            const int h = tid + j * ST;
+            c[j] = 0;
+            bool valid = false;
+            float mj[12];
+            if (h < a.H) {
+                const float4* o = reinterpret_cast<const float4*>(a.hypRt + ((size_t)f * a.H + h) * 12);
+                const float4 r0 = o[0], r1 = o[1], r2 = o[2];
+                valid = (r2.w == r2.w);
+                if (valid) {
+                    const float R[9] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x};
+                    const float t[3] = {r2.y, r2.z, r2.w};
+                    make_proj_s(fx, fy, cx, cy, R, t, a.inv_thr, mj);
+                }
+            }
+            if (!valid) {
+#pragma unroll
+                for (int k = 0; k < 12; ++k) mj[k] = 0.0f;
+                mj[11] = -1.0f;
+            }
+#pragma unroll
+            for (int k = 0; k < 12; ++k) m[j][k] = pack2(mj[k], mj[k]);
+        }
+        for (int c0 = p0; c0 < p1; c0 += CH) {
+            const int n = min(CH, p1 - c0);
+            const int npp = (n + 7) & ~7;
+            __syncthreads();
+            for (int i = tid; i < npp; i += ST) {
+                const int o4 = (i >> 1) * 4 + (i & 1);
+                if (i < n) {
+                    sAf[o4] = X[c0 + i]; sAf[o4 + 2] = Y[c0 + i];
+                    sBf[o4] = Z[c0 + i]; sBf[o4 + 2] = -(Uu[c0 + i] * a.inv_thr);
+                    sCf[i] = -(V[c0 + i] * a.inv_thr);
+                } else {
+                    sAf[o4] = 0.0f; sAf[o4 + 2] = 0.0f;
+                    sBf[o4] = 0.0f; sBf[o4 + 2] = ninf;
+                    sCf[i] = ninf;
+                }
+            }
+            __syncthreads();
+            const ulonglong2* a2 = reinterpret_cast<const ulonglong2*>(sA);
+            const ulonglong2* b2 = reinterpret_cast<const ulonglong2*>(sB);
+            const ulonglong2* c2 = reinterpret_cast<const ulonglong2*>(sC);
+#pragma unroll 1
+            for (int i = 0; i < (npp >> 1); i += 4) {
+                const ulonglong2 v01 = c2[i >> 1], v23 = c2[(i >> 1) + 1];
+                const f32x2 nvs[4] = {v01.x, v01.y, v23.x, v23.y};
+                uint32_t acc[NHL];
+#pragma unroll
+                for (int j = 0; j < NHL; ++j) acc[j] = 0u;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const ulonglong2 pa = a2[i + k], pbv = b2[i + k];
+#pragma unroll
+                    for (int j = 0; j < NHL; ++j) {
+                        uint32_t s0, s1;
+                        inlier_s2(m[j], pa.x, pa.y, pbv.x, pbv.y, nvs[k], s0, s1);
+                        acc[j] = __funnelshift_l(s0, acc[j], 1);
+                        acc[j] = __funnelshift_l(s1, acc[j], 1);
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < NHL; ++j) c[j] += __popc(acc[j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < NHL; ++j) {
+            const int h = tid + j * ST;
+            if (h < a.H && c[j] > 0) atomicAdd(&a.cnt_all[(size_t)f * a.H + h], c[j]);   // c > 0 only for valid hypotheses
+        }
+    }
+}
+
+template <int NHL>
+int launch_bal(const ScoreArgs& a, const Plan& p, cudaStream_t st) {
+    cudaFuncSetAttribute(ransac_score_bal_kernel<NHL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bal);
+    ransac_score_bal_kernel<NHL><<<p.bal_grid, ST, p.smem_bal, st>>>(a);
+    return pb_check_launch("ransac_score_bal_kernel");
+}
+
 template <int NHL>
 int launch(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
     cudaFuncSetAttribute(ransac_score_kernel<NHL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_score);
@@ -276,6 +422,7 @@ int pb_launch_score(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
     ransac_hypothesis_kernel<<<(unsigned)((nh + HT - 1) / HT), HT, 0, st>>>(a);
     if (pb_check_launch("ransac_hypothesis_kernel")) return 1;
     pb_stage_mark(1, st);
+    if (p.bal && a.cnt_all) return p.NHL == 2 ? launch_bal<2>(a, p, st) : launch_bal<1>(a, p, st);
     switch (p.NHL) {
         case 1: return launch<1>(a, p, F, st);
         case 2: return launch<2>(a, p, F, st);

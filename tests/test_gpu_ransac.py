@@ -147,6 +147,24 @@ def test_ransac_warp_per_frame_finalize_matches_oracle_and_cta_path(cref, dev, l
         assert np.array_equal(big[k][:40], small[k]), k
 
 
+@pytest.mark.parametrize("n_hyp,F", [(256, 320), (128, 300)])
+def test_ransac_balanced_scoring_matches_oracle_and_frame_per_cta_path(cref, dev, n_hyp, F):
+    """296 <= F <= 2368 with H <= 256 takes the balanced scoring kernel (CTAs own equal ranges of the batch's
+    point list, counts by integer atomics, arg-max in K4).  Ragged frames, an empty one and a too-few-points one;
+    the oracle and the frame-per-CTA path (same frames in a small batch) must be reproduced bit for bit."""
+    base = synth.make_batch_sparse(0x5EED, 2, 16)
+    for j, keep in ((3, 3), (9, 0), (12, 200)):
+        base[j] = dict(base[j])
+        for k in ("rows", "cols", "xyzn"):
+            base[j][k] = base[j][k][:keep]
+    sps = (base * ((F + 15) // 16))[:F]
+    cfg = ops.RansacConfig(n_hyp=n_hyp, lo_rounds=1)
+    big = _check_ransac(cref, dev, sps, cfg, cap=1280, frame0=5)
+    small = _check_ransac(cref, dev, sps[:48], cfg, cap=1280, frame0=5)
+    for k in ("R", "t", "n_inl", "n_inl_refined", "status", "best_hyp", "inl_bitmap", "hyp_counts"):
+        assert np.array_equal(big[k][:48], small[k]), k
+
+
 def test_ransac_forced_minimal_sets_and_large_P(cref, dev):
     sps = synth.make_batch_sparse(0x5EED, 4, 2, p_range=(5000, 6000), outlier_frac=0.3)
     cap = 6144

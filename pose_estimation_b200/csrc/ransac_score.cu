@@ -77,11 +77,6 @@ __device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
     return d;
 }
-__device__ __forceinline__ f32x2 fmul2(f32x2 a, f32x2 b) {
-    f32x2 d;
-    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-    return d;
-}
 // opaque to the optimiser on purpose: a (v,v) pair must live in its own aligned register pair,
 // otherwise the compiler keeps one copy and rebuilds the pair with moves inside the hot loop
 __device__ __forceinline__ f32x2 pack2(float lo, float hi) {
@@ -91,9 +86,6 @@ __device__ __forceinline__ f32x2 pack2(float lo, float hi) {
 }
 // inlier_s (common.cuh) for two points at once; nus/nvs are the NEGATED scaled pixel coordinates.
 // q = w*|w| enters as  w * (-|w|) = -q  (sign flips are exact), so every half has inlier_s' bits.
-#ifndef PB_SCORE_TAIL
-#define PB_SCORE_TAIL 1
-#endif
 __device__ __forceinline__ float lo32(f32x2 v) { return __uint_as_float((uint32_t)v); }
 __device__ __forceinline__ float hi32(f32x2 v) { return __uint_as_float((uint32_t)(v >> 32)); }
 // Returns the two verdict words (sign bit = inlier).  The nine matrix FMAs are packed (scalar-broadcast matrix
@@ -104,14 +96,6 @@ __device__ __forceinline__ void inlier_s2(const f32x2 m[12], f32x2 X, f32x2 Y, f
     const f32x2 x = ffma2(m[0], X, ffma2(m[1], Y, ffma2(m[2], Z, m[3])));
     const f32x2 y = ffma2(m[4], X, ffma2(m[5], Y, ffma2(m[6], Z, m[7])));
     const f32x2 w = ffma2(m[8], X, ffma2(m[9], Y, ffma2(m[10], Z, m[11])));
-#if PB_SCORE_TAIL == 0
-    const f32x2 dx = ffma2(nus, w, x);
-    const f32x2 dy = ffma2(nvs, w, y);
-    const f32x2 nq = fmul2(w, w | 0x8000000080000000ull);
-    const f32x2 t = ffma2(dy, dy, nq);
-    const f32x2 sv = ffma2(dx, dx, t);
-    s0 = (uint32_t)sv; s1 = (uint32_t)(sv >> 32);
-#else
     {
         const float w0 = lo32(w), dx0 = fmaf(lo32(nus), w0, lo32(x)), dy0 = fmaf(lo32(nvs), w0, lo32(y));
         const float nq0 = w0 * -fabsf(w0);
@@ -120,7 +104,6 @@ __device__ __forceinline__ void inlier_s2(const f32x2 m[12], f32x2 X, f32x2 Y, f
         const float nq1 = w1 * -fabsf(w1);
         s1 = __float_as_uint(fmaf(dx1, dx1, fmaf(dy1, dy1, nq1)));
     }
-#endif
 }
 
 constexpr int ST = 128;  // threads per scoring CTA: 128 x 64 regs x ~26 KB smem -> 8 CTAs per SM, so the

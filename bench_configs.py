@@ -147,6 +147,26 @@ def c5(args, dev):
                       "data": "synthetic; 2048 distinct frames re-used for each of the chunks"}), flush=True)
 
 
+def knn_large(args, dev):
+    """The large-shape nearest-neighbour call of the transparent-object loss (version/transparent/lib/networks/
+    loss.py:228): 250,000 predicted points against a 500-point target, and a 1000 x (1000 x 1000) batch."""
+    out = {"config": "KNN large shapes"}
+    g = torch.Generator(device=dev).manual_seed(5)
+    for name, B, N, M in (("250000x500", 1, 250000, 500), ("1000x1000x1000", 1000, 1000, 1000)):
+        x = torch.rand(B, N, 3, device=dev, generator=g) * 0.2
+        y = torch.rand(B, M, 3, device=dev, generator=g) * 0.2
+        r = {}
+        for impl in ("simt", "tc"):
+            ms = timed(lambda: ops_metric.knn1(x, y, impl=impl), args.iters)
+            r[impl + "_ms"] = ms
+            r[impl + "_pairs_per_s"] = B * N * M / (ms * 1e-3)
+        r["equal"] = bool(torch.equal(ops_metric.knn1(x, y, impl="tc"), ops_metric.knn1(x, y, impl="simt")))
+        st = ops_metric.LAST_TC_STATS.cpu().tolist()
+        r["fallback_rows"], r["exact_evals_per_row"] = st[1], st[2] / (B * N)
+        out[name] = r
+    print(json.dumps(out), flush=True)
+
+
 def f3(args, dev):
     """B problems of n = 1000 correspondences, 128 iterations (lib/transform/umeyama.py defaults),
     40 % outliers; beside it the C port of the same algorithm on one host core (bounded sample)."""
@@ -201,6 +221,8 @@ def main():
         c4(args, dev)
     if args.only in ("", "c5"):
         c5(args, dev)
+    if args.only in ("", "knn"):
+        knn_large(args, dev)
     if args.only in ("", "f3"):
         f3(args, dev)
 

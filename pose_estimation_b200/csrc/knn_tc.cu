@@ -83,7 +83,8 @@ __device__ __forceinline__ void write_row(uint4* tile_base, int r, float px, flo
                                             pk(e[8 * kc + 4], e[8 * kc + 5]), pk(e[8 * kc + 6], e[8 * kc + 7]));
 }
 
-constexpr int PREP_SPLIT = 4;   // CTAs per batch element: each finds the centre, then writes every PREP_SPLIT-th slab of rows
+constexpr int PREP_SPLIT = 4;   // minimum CTAs per batch element (gridDim.y): each finds the centre, then writes every
+                                // gridDim.y-th slab of rows; few batch elements get more CTAs each
 
 // grid (batch elements, PREP_SPLIT): bounding-box centre of y, operand tiles of x and y, squared cloud radius
 __global__ void __launch_bounds__(256) knn_tc_prepare_kernel(PrepArgs a) {
@@ -120,14 +121,14 @@ __global__ void __launch_bounds__(256) knn_tc_prepare_kernel(PrepArgs a) {
     float r2 = 0.0f;
     uint4* At = a.Aop + (size_t)bl * a.ntN * TILE_U4;
     uint4* Bt = a.Bop + (size_t)bl * a.ntM * TILE_U4;
-    for (int i = part * 256 + tid; i < a.ntN * TM; i += 256 * PREP_SPLIT) {
+    for (int i = part * 256 + tid; i < a.ntN * TM; i += 256 * (int)gridDim.y) {
         const bool pad = i >= a.N;
         float px = 0.0f, py = 0.0f, pz = 0.0f;
         if (!pad) { px = xb[3 * (size_t)i] - c0; py = xb[3 * (size_t)i + 1] - c1; pz = xb[3 * (size_t)i + 2] - c2; }
         r2 = fmaxf(r2, fmaf(pz, pz, fmaf(py, py, px * px)));
         write_row<true>(At + (size_t)(i / TM) * TILE_U4, i % TM, px, py, pz, pad);
     }
-    for (int j = part * 256 + tid; j < a.ntM * TM; j += 256 * PREP_SPLIT) {
+    for (int j = part * 256 + tid; j < a.ntM * TM; j += 256 * (int)gridDim.y) {
         const bool pad = j >= a.M;
         float px = 0.0f, py = 0.0f, pz = 0.0f;
         if (!pad) { px = yb[3 * (size_t)j] - c0; py = yb[3 * (size_t)j + 1] - c1; pz = yb[3 * (size_t)j + 2] - c2; }
@@ -597,7 +598,11 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
         const int nb = (nl - b0) < TC_CHUNK ? (nl - b0) : TC_CHUNK;
         PrepArgs pa{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, centre, b0, blist};
         cudaMemsetAsync(tol, 0, (size_t)nb * sizeof(float), st);
-        knn_tc_prepare_kernel<<<dim3(nb, PREP_SPLIT), 256, 0, st>>>(pa);
+        int split = (592 + nb - 1) / nb;                       // about four CTAs per SM in total
+        const int max_split = (max(ntN, ntM) * TM + 255) / 256;
+        split = split < PREP_SPLIT ? PREP_SPLIT : (split > 64 ? 64 : split);
+        split = split > max_split ? max_split : split;
+        knn_tc_prepare_kernel<<<dim3(nb, split), 256, 0, st>>>(pa);
         if (pb_check_launch("knn_tc_prepare_kernel")) return -2;
         MainArgs ma{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, idx, d2, b0, err, blist};
         knn_tc_kernel<<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);

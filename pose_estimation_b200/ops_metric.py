@@ -15,6 +15,7 @@ VARIANT_COLS = ("succ_{}_rt", "dis_{}_rt", "succ_{}_r", "dis_{}_r", "succ_{}_t",
 
 
 TC_MIN_PAIRS = 1 << 18     # below this many pairs per problem the SIMT kernel wins (tile padding, prepare pass)
+TC_MIN_DB = 768            # ... and below this many database points (a CTA sweeps too few tiles to pay for its set-up)
 
 
 LAST_TC_STATS = None       # device int32 [4] of the last tensor-core call: timeout flag, fallback rows, exact evaluations
@@ -40,7 +41,7 @@ def knn1(x, y, want_d2=False, impl="auto"):
     d2 = torch.empty((B, N), dtype=torch.float32, device=x.device) if want_d2 else None
     if impl not in ("auto", "tc", "simt"):
         raise ValueError("impl must be auto, tc or simt")
-    use_tc = impl == "tc" or (impl == "auto" and N * M >= TC_MIN_PAIRS)
+    use_tc = impl == "tc" or (impl == "auto" and N * M >= TC_MIN_PAIRS and M >= TC_MIN_DB)
     if use_tc:
         from . import _lib
         nb = _lib.load().pb_knn1_tc_workspace_bytes(B, N, M)
@@ -87,7 +88,7 @@ def add_adds(pred, target, want_adds=None, impl="auto"):
     B, N, _ = pred.shape
     add = torch.empty((B,), dtype=torch.float32, device=pred.device)
     adds = torch.empty((B,), dtype=torch.float32, device=pred.device)
-    if impl == "tc" or (impl == "auto" and want_adds is None and N * N >= TC_MIN_PAIRS):
+    if impl == "tc" or (impl == "auto" and want_adds is None and N * N >= TC_MIN_PAIRS and N >= TC_MIN_DB):
         from . import _lib
         global LAST_TC_STATS
         lst, n = (None, 0) if want_adds is None else _sym_list(want_adds)
@@ -191,7 +192,8 @@ def pose_loss_fwd(R, t, model, target, sym, impl="auto", sym_host=None):
     pred = torch.empty((B, N, 3), dtype=torch.float32, device=dev)
     nn_idx = torch.empty((B, N), dtype=torch.int64, device=dev)
     loss_b = torch.empty((B,), dtype=torch.float32, device=dev)
-    if impl == "tc" or (impl == "auto" and sym_host is not None and any(sym_host) and N * N >= TC_MIN_PAIRS):
+    if impl == "tc" or (impl == "auto" and sym_host is not None and any(sym_host) and N * N >= TC_MIN_PAIRS
+                       and N >= TC_MIN_DB):
         from . import _lib
         global LAST_TC_STATS
         sym_arg = sym

@@ -190,7 +190,14 @@ class HostEvalSweep:
         dev = torch.device(device)
         self.dev, self.chunk, self.H, self.W = dev, chunk, H, W
         self.zero_copy = zero_copy
-        self.sweep = EvalSweep(model_points, diameter, is_sym, chunk, H, W, cap, cfg, device=dev, **kw)
+        # zero-copy chunks alternate between two compute lanes (own stream, buffers and table): K1..K6 of chunk i
+        # overlap the PCIe-bound K0 of chunk i+1
+        nl = 2 if zero_copy else 1
+        self.sweeps = [EvalSweep(model_points, diameter, is_sym, chunk, H, W, cap, cfg, device=dev, **kw) for _ in range(nl)]
+        self.sweep = self.sweeps[0]
+        self.lane_streams = [torch.cuda.Stream(device=dev) for _ in range(nl)] if nl > 1 else None
+        self.lane_done = [torch.cuda.Event() for _ in range(nl)]
+        self.start = torch.cuda.Event()
         self.copy_stream = torch.cuda.Stream(device=dev)
         zc = zero_copy
         self.stage = [dict(xyz=None if zc else torch.empty((chunk, 3, H, W), dtype=torch.float32, device=dev),
@@ -203,7 +210,16 @@ class HostEvalSweep:
 
     @property
     def table(self):
-        return self.sweep.table
+        if len(self.sweeps) == 1:
+            return self.sweep.table
+        t = self.sweeps[0].table.clone()
+        for sw in self.sweeps[1:]:
+            t += sw.table
+        return t
+
+    def reset(self):
+        for sw in self.sweeps:
+            sw.reset()
 
     def run(self, xyz_h, mask_h, small_h, cls_h, frame0=0, group=None):
         """xyz_h [F,3,H,W] f32, mask_h [F,H,W] u8, small_h = pack_small(...) [F/chunk, 22*chunk] f32,
@@ -215,8 +231,15 @@ class HostEvalSweep:
         comp = torch.cuda.current_stream(self.dev)
         n = F // self.chunk
         self.h2d_bytes = 0
+        nl = len(self.sweeps)
+        if nl > 1:
+            self.start.record(comp)
+            for s_ in self.lane_streams:
+                s_.wait_event(self.start)               # table resets etc. queued on the caller's stream come first
         for i in range(n):
             st = self.stage[i & 1]
+            sweep = self.sweeps[i % nl]
+            lane = self.lane_streams[i % nl] if nl > 1 else comp
             lo, hi = i * self.chunk, (i + 1) * self.chunk
             with torch.cuda.stream(self.copy_stream):
                 if i >= 2:
@@ -229,17 +252,23 @@ class HostEvalSweep:
                 st["ready"].record(self.copy_stream)
             self.h2d_bytes += sum(st[k].numel() * st[k].element_size() for k in ("xyz", "mask", "small", "cls")
                                   if st[k] is not None)
-            comp.wait_event(st["ready"])
+            lane.wait_event(st["ready"])
             ext, lfb, K4, Rg, tg = unpack_small(st["small"], self.chunk)
-            if self.zero_copy:
-                if mask_h is None:
-                    raise ValueError("zero_copy needs a mask (without one every pixel must be streamed)")
-                self.h2d_bytes += mask_h[lo:hi].numel()          # + the gathered sectors, added by the caller
-                self.sweep.step(xyz_h[lo:hi], mask_h[lo:hi], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
-            else:
-                self.sweep.step(st["xyz"], st["mask"], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
-            st["free"].record(comp)
-        reduce_table(self.sweep.table, group)
-        self.table_host.copy_(self.sweep.table, non_blocking=True)
+            with torch.cuda.stream(lane):
+                if self.zero_copy:
+                    if mask_h is None:
+                        raise ValueError("zero_copy needs a mask (without one every pixel must be streamed)")
+                    self.h2d_bytes += mask_h[lo:hi].numel()      # + the gathered sectors, added by the caller
+                    sweep.step(xyz_h[lo:hi], mask_h[lo:hi], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
+                else:
+                    sweep.step(st["xyz"], st["mask"], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
+                st["free"].record(lane)
+        if nl > 1:
+            for k, s_ in enumerate(self.lane_streams):
+                self.lane_done[k].record(s_)
+                comp.wait_event(self.lane_done[k])
+        table = self.table
+        reduce_table(table, group)
+        self.table_host.copy_(table, non_blocking=True)
         comp.synchronize()
         return self.table_host

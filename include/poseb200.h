@@ -135,6 +135,27 @@ size_t pb_fps_workspace_bytes(int B, int cap);
 int pb_fps(const float* pts, const int32_t* count, int B, int cap, int n_samples, int32_t* idx, void* ws,
            size_t ws_bytes, void* stream);
 
+/* ---- back-propagatable PnP (lib/network/dnn/BPnP.py) -----------------------------------------------
+ * pb_pnp_refine replaces the cv2.solvePnP(SOLVEPNP_ITERATIVE, useExtrinsicGuess=True) call of
+ * BPnP.forward (BPnP.py:43-44): Levenberg-Marquardt over (angle-axis, t) on ALL n correspondences
+ * pts2d [B,n,2] <-> pts3d ([n,3], or [B,n,3] when pts3d_batched), camera matrix K [9] row major
+ * (general 3x3), from pose6_init [B,6] or, when that is NULL, from R_init [B,9] + t_init [B,3]
+ * (the pb_pnp_ransac_pts pose stands in for BPnP.py:36-38).  FP64 inside.  pose6 [B,6] =
+ * (angle-axis, t); rmse [B] optional (px); status: 0 converged, 1 iteration limit, 2 degenerate. */
+int pb_pnp_refine(const float* pts2d, const float* pts3d, int pts3d_batched, const float* K,
+                  const float* pose6_init, const float* R_init, const float* t_init, int B, int n,
+                  int max_iter, float* pose6, float* rmse, int32_t* status, void* stream);
+/* pb_bpnp_backward replaces BPnP.backward (BPnP.py:54-117): grad_pts2d [B,n,2], grad_pts3d ([n,3]
+ * summed over the batch, or [B,n,3] when pts3d_batched), grad_K [9] summed over the batch, from
+ * grad_out [B,6] by the implicit function theorem on f_j = sum_i coef_ij . r_i (get_coefs
+ * BPnP.py:127-138; rotation = the angle-axis formula the reference differentiates, eps 1e-6).
+ * status[b] = 1 (and zero contribution) where J_fy is singular -- the reference raises there.  */
+size_t pb_bpnp_backward_workspace_bytes(int B, int n);
+int pb_bpnp_backward(const float* pts2d, const float* pts3d, int pts3d_batched, const float* K,
+                     const float* pose6, const float* grad_out, int B, int n, float* grad_pts2d,
+                     float* grad_pts3d, float* grad_K, int32_t* status, void* ws, size_t ws_bytes,
+                     void* stream);
+
 /* ---- K5: nearest neighbour / ADD-S -----------------------------------------------------------
  * pb_knn1 replaces the KeOps handle generic_argkmin('SqDist(x, y)','a = Vi(1)','x = Vi(3)',
  * 'y = Vj(3)') (train.py:126; used lib/network/loss.py:34, version/transparent/lib/utils.py:24):

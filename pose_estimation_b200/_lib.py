@@ -56,6 +56,9 @@ SIGNATURES = {
     "pb_umeyama_fit": (I, [P, P, P, I, I, P, P, P, P, P]),
     "pb_fps_workspace_bytes": (SZ, [I, I]),
     "pb_fps": (I, [P, P, I, I, I, P, P, SZ, P]),
+    "pb_pnp_refine": (I, [P, P, I, P, P, P, P, I, I, I, P, P, P, P]),
+    "pb_bpnp_backward_workspace_bytes": (SZ, [I, I]),
+    "pb_bpnp_backward": (I, [P, P, I, P, P, P, I, I, P, P, P, P, P, SZ, P]),
     "pb_probe_fma": (I, [I, I, I, P, P]),
     "pb_tc_selftest": (I, [P, P, P, P, P]),
     "pb_stage_timing": (I, [I]),

@@ -11,6 +11,7 @@ Same names, argument meaning and return conventions as the reference (file:line 
   PoseLoss                    lib/network/loss.py:18-41
   choose_ransac_batch         lib/utils/utlis.py:55-74
   vote_translation            lib/network/krrn.py:153
+  BPnP / BPnPModle            lib/network/dnn/BPnP.py:8-124
 
 Differences that are deliberate: every point in ``choose`` is scored instead of a
 random 256 subset; the map is de-normalised in FP32 (the reference promotes to float64); RANSAC
@@ -21,7 +22,7 @@ from __future__ import annotations
 import numpy as np
 import torch
 
-from . import ops, ops_metric, ops_sim3
+from . import ops, ops_bpnp, ops_metric, ops_sim3
 from .ops import RansacConfig
 
 DEFAULT_RANSAC = RansacConfig()
@@ -260,3 +261,36 @@ def estimateSimilarityUmeyama(SourceHom, TargetHom, device="cuda"):
     if int(status.item()) != 0:
         raise RuntimeError("estimateSimilarityUmeyama: degenerate input")
     return _sim3_out(scale[0], R[0], tt[0])
+
+
+# ---- lib/network/dnn/BPnP.py -----------------------------------------------------------------------------
+class BPnP(torch.autograd.Function):
+    """Back-propagatable PnP (BPnP.py:8-117).  pts2d [bs,n,2], pts3d [n,3], K [3,3] -> P_6d [bs,6] (angle-axis,
+    translation), differentiable wrt pts2d, pts3d and K through the implicit function theorem.  Forward: RANSAC
+    initial pose (3 px) unless ini_pose is given, then Levenberg-Marquardt on all points (pb_pnp_refine); backward:
+    pb_bpnp_backward.  pts3d may also be [bs,n,3] (one 3-D set per sample; the docstring's BPnP_m3d case).
+    Everything stays on the device: no per-sample loop, no host copy."""
+
+    @staticmethod
+    def forward(ctx, pts2d, pts3d, K, ini_pose=None):
+        x = pts2d.detach().float().contiguous()
+        z = pts3d.detach().float().contiguous()
+        Kc = K.detach().float().contiguous()
+        ini = None if ini_pose is None else ini_pose.detach().float().contiguous()
+        P_6d, status = ops_bpnp.bpnp_forward(x, z, Kc, ini)
+        ctx.save_for_backward(x, P_6d, z, Kc)
+        ctx.status = status
+        return P_6d
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        x, P_6d, z, Kc = ctx.saved_tensors
+        gx, gz, gK, _ = ops_bpnp.bpnp_backward(x, z, Kc, P_6d, grad_output.float().contiguous())
+        return gx, gz, gK, None
+
+
+class BPnPModle(torch.nn.Module):
+    """BPnP.py:120-124 (the reference's spelling)."""
+
+    def forward(self, pts2d, pts3d, K, ini_pose=None):
+        return BPnP.apply(pts2d, pts3d, K, ini_pose)

@@ -207,3 +207,33 @@ def test_fps_oracle_matches_reference_selection():
     for k in range(5):
         want = g[f"idx{k}"]
         assert np.array_equal(cref.fps(g[f"pts{k}"], want.shape[0]), want), k
+
+
+def _rel(a, b):
+    return float(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64)).max() / np.abs(b).max())
+
+
+def test_bpnp_oracle_matches_reference_run():
+    """oracle/bpnp_ref.py against tests/golden/bpnp_ref.npz, which gen_golden_bpnp.py made by importing the
+    reference's own BPnP.py (forward through cv2, backward through its autograd recipe, float32)."""
+    import torch
+    from oracle import bpnp_ref as br
+    pytest.importorskip("cv2")
+    g = np.load(os.path.join(GOLD, "bpnp_ref.npz"))
+    for c in list(g["cases"]) + ["ini"]:
+        ini = g["ini_ini"] if c == "ini" else None
+        P = br.bpnp_forward(g[f"{c}_pts2d"], g[f"{c}_pts3d"], g["K"], ini)
+        np.testing.assert_allclose(P, g[f"{c}_P6d"], rtol=0, atol=1e-6)                 # same cv2 calls
+        for dt, tol in ((torch.float32, 2e-5), (torch.float64, 5e-4)):                  # f64: the reference's f32 rounding
+            gx, gz, gK = br.bpnp_backward(g[f"{c}_pts2d"], g[f"{c}_pts3d"], g["K"], g[f"{c}_P6d"], g[f"{c}_grad_out"], dtype=dt)
+            assert _rel(gx, g[f"{c}_grad_x"]) < tol and _rel(gz, g[f"{c}_grad_z"]) < tol and _rel(gK, g[f"{c}_grad_K"]) < tol
+
+
+def test_bpnp_oracle_rotation_formula_is_a_rotation_and_switches_branch():
+    import torch
+    from oracle import bpnp_ref as br
+    aa = torch.tensor([[0.3, -1.2, 0.5], [1e-4, 2e-4, -1e-4], [0.0, 0.0, 3.0]], dtype=torch.float64)
+    R = br.angle_axis_to_rotation_matrix(aa).numpy()
+    for k in (0, 2):
+        np.testing.assert_allclose(R[k] @ R[k].T, np.eye(3), atol=1e-5)                 # eps in the axis: 1e-6 off unit
+    np.testing.assert_array_equal(R[1], np.array([[1, 1e-4, 2e-4], [-1e-4, 1, -1e-4], [-2e-4, 1e-4, 1]]))

@@ -203,8 +203,51 @@ def f3(args, dev):
     print(json.dumps(out), flush=True)
 
 
+def f4(args, dev):
+    """back-propagatable PnP (lib/network/dnn/BPnP.py) on B keypoint sets of n points: forward
+    (RANSAC + all-point LM), the LM step alone, backward; beside it the reference's algorithm (cv2 + the autograd
+    double-backward loop, float32, as restated in oracle/bpnp_ref.py) on one host core over a bounded sample."""
+    import time
+    from pose_estimation_b200 import ops_bpnp
+    K = np.array([[572.4114, 0.0, 325.2611], [0.0, 573.57043, 242.04899], [0.0, 0.0, 1.0]], np.float32)
+    rows = []
+    for B, n in ((args.f4_batch, 64), (args.f4_batch, 1000)):
+        rng = np.random.default_rng(44)
+        z = ((rng.random((n, 3)) - 0.5) * np.array([0.10, 0.08, 0.14])).astype(np.float32)
+        x = np.empty((B, n, 2), np.float32)
+        for b in range(B):
+            R = synth.random_rotation(np.random.default_rng(b)).astype(np.float64)
+            t = np.array([rng.uniform(-0.15, 0.15), rng.uniform(-0.1, 0.1), rng.uniform(0.6, 1.2)])
+            p = (z.astype(np.float64) @ R.T + t) @ K.astype(np.float64).T
+            x[b] = p[:, :2] / p[:, 2:3] + rng.normal(size=(n, 2)) * 0.5
+        xd, zd, Kd = torch.from_numpy(x).to(dev), torch.from_numpy(z).to(dev), torch.from_numpy(K).to(dev)
+        P, st = ops_bpnp.bpnp_forward(xd, zd, Kd)
+        go = torch.randn((B, 6), device=dev)
+        it = max(args.iters, 10)
+        ms_f = timed(lambda: ops_bpnp.bpnp_forward(xd, zd, Kd), it)
+        ms_r = timed(lambda: ops_bpnp.pnp_refine(xd, zd, Kd, pose6_init=P), it)
+        ms_b = timed(lambda: ops_bpnp.bpnp_backward(xd, zd, Kd, P, go), it)
+        row = {"batch": B, "points": n, "forward_ms": ms_f, "refine_only_ms": ms_r, "backward_ms": ms_b,
+               "status_ok_frac": float((st == 0).float().mean()), "fwd_bwd_samples_per_s": B / ((ms_f + ms_b) * 1e-3)}
+        try:
+            from oracle import bpnp_ref
+            m = 2 if n > 100 else 4
+            t0 = time.perf_counter()
+            Pc = bpnp_ref.bpnp_forward(x[:m], z, K)
+            t1 = time.perf_counter()
+            bpnp_ref.bpnp_backward(x[:m], z, K, Pc, go[:m].cpu().numpy(), dtype=torch.float32)
+            t2 = time.perf_counter()
+            row["cpu_port"] = {"forward_ms_per_sample": (t1 - t0) / m * 1e3, "backward_ms_per_sample": (t2 - t1) / m * 1e3,
+                               "cores": torch.get_num_threads(), "sample": f"{m} samples, cv2 + torch autograd as the reference"}
+        except Exception as e:
+            row["cpu_port"] = {"unavailable": repr(e)[:100]}
+        rows.append(row)
+    print(json.dumps({"config": "f4 bpnp", "rows": rows}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--f4-batch", type=int, default=1024)
     ap.add_argument("--f3-problems", type=int, default=1024)
     ap.add_argument("--c5-frames", type=int, default=65536)
     ap.add_argument("--iters", type=int, default=5)
@@ -225,6 +268,8 @@ def main():
         knn_large(args, dev)
     if args.only in ("", "f3"):
         f3(args, dev)
+    if args.only in ("", "f4"):
+        f4(args, dev)
 
 
 if __name__ == "__main__":

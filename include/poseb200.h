@@ -156,6 +156,24 @@ int pb_bpnp_backward(const float* pts2d, const float* pts3d, int pts3d_batched, 
                      float* grad_pts3d, float* grad_K, int32_t* status, void* ws, size_t ws_bytes,
                      void* stream);
 
+/* ---- per-hypothesis pose loss (version/transparent/lib/networks/loss.py:197-267, PossLoss) -----------
+ * H = bs*num_p hypotheses: pred_r [H,4] quaternion (w,x,y,z, any norm), pred_t [H,3], pred_c [H];
+ * model / target [bs,N,3]; axis3 [3] and target_r9 [9] are device arrays (the reference's `axis`
+ * [1,3] and `target_r` [1,3,3]); w = the confidence regulariser.  nn_mode != 0 is the symmetric, non-refine
+ * branch (loss.py:224-233): every predicted point is matched to its nearest point of target[0]
+ * (FP32 direct-difference SqDist, lowest index on ties -- the KeOps argmin, fused here).
+ * vals3 (device) = {loss, dis[0][argmax pred_c[0]], loss_rotation}.  The workspace keeps what
+ * pb_poss_loss_bwd needs (pass the same buffer, untouched); grad_vals3 is a DEVICE array.        */
+size_t pb_poss_loss_workspace_bytes(int bs, int num_p, int N);
+int pb_poss_loss_fwd(const float* pred_r, const float* pred_t, const float* pred_c, const float* model,
+                     const float* target, int bs, int num_p, int N, int nn_mode, float w,
+                     const float* axis3, const float* target_r9, float* vals3, void* ws, size_t ws_bytes,
+                     void* stream);
+int pb_poss_loss_bwd(const float* pred_r, const float* pred_t, const float* pred_c, const float* model,
+                     const float* target, int bs, int num_p, int N, int nn_mode, float w,
+                     const float* axis3, const float* target_r9, const float* grad_vals3, const void* ws,
+                     size_t ws_bytes, float* grad_r, float* grad_t, float* grad_c, void* stream);
+
 /* ---- K5: nearest neighbour / ADD-S -----------------------------------------------------------
  * pb_knn1 replaces the KeOps handle generic_argkmin('SqDist(x, y)','a = Vi(1)','x = Vi(3)',
  * 'y = Vj(3)') (train.py:126; used lib/network/loss.py:34, version/transparent/lib/utils.py:24):

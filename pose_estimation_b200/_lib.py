@@ -59,6 +59,9 @@ SIGNATURES = {
     "pb_pnp_refine": (I, [P, P, I, P, P, P, P, I, I, I, P, P, P, P]),
     "pb_bpnp_backward_workspace_bytes": (SZ, [I, I]),
     "pb_bpnp_backward": (I, [P, P, I, P, P, P, I, I, P, P, P, P, P, SZ, P]),
+    "pb_poss_loss_workspace_bytes": (SZ, [I, I, I]),
+    "pb_poss_loss_fwd": (I, [P, P, P, P, P, I, I, I, I, F32, P, P, P, P, SZ, P]),
+    "pb_poss_loss_bwd": (I, [P, P, P, P, P, I, I, I, I, F32, P, P, P, P, SZ, P, P, P, P]),
     "pb_probe_fma": (I, [I, I, I, P, P]),
     "pb_tc_selftest": (I, [P, P, P, P, P]),
     "pb_stage_timing": (I, [I]),

@@ -12,6 +12,7 @@ Same names, argument meaning and return conventions as the reference (file:line 
   choose_ransac_batch         lib/utils/utlis.py:55-74
   vote_translation            lib/network/krrn.py:153
   BPnP / BPnPModle            lib/network/dnn/BPnP.py:8-124
+  PossLoss                    version/transparent/lib/networks/loss.py:197-267
 
 Differences that are deliberate: every point in ``choose`` is scored instead of a
 random 256 subset; the map is de-normalised in FP32 (the reference promotes to float64); RANSAC
@@ -22,7 +23,7 @@ from __future__ import annotations
 import numpy as np
 import torch
 
-from . import ops, ops_bpnp, ops_metric, ops_sim3
+from . import ops, ops_bpnp, ops_metric, ops_poss, ops_sim3
 from .ops import RansacConfig
 
 DEFAULT_RANSAC = RansacConfig()
@@ -294,3 +295,52 @@ class BPnPModle(torch.nn.Module):
 
     def forward(self, pts2d, pts3d, K, ini_pose=None):
         return BPnP.apply(pts2d, pts3d, K, ini_pose)
+
+
+# ---- version/transparent/lib/networks/loss.py -------------------------------------------------------------
+class _PossLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred_r, pred_t, pred_c, target, model_points, axis, target_r, nn_mode, w):
+        args = [a.detach().float().contiguous() for a in (pred_r, pred_t, pred_c, target, model_points, axis, target_r)]
+        vals, ws = ops_poss.poss_loss_fwd(args[0], args[1], args[2], args[3], args[4], nn_mode, w, args[5], args[6])
+        ctx.save_for_backward(*args, ws)
+        ctx.nn_mode, ctx.w = nn_mode, w
+        return vals[0], vals[1], vals[2]
+
+    @staticmethod
+    def backward(ctx, g_loss, g_dis, g_rot):
+        pr, pt, pc, tg, mp, ax, tr, ws = ctx.saved_tensors
+        z = torch.zeros((), dtype=torch.float32, device=pr.device)
+        g = torch.stack([z if x is None else x.float() for x in (g_loss, g_dis, g_rot)])
+        gr, gt, gc = ops_poss.poss_loss_bwd(pr, pt, pc, tg, mp, ctx.nn_mode, ctx.w, ax, tr, g, ws)
+        return gr, gt, gc, None, None, None, None, None, None
+
+
+class PossLoss(torch.nn.Module):
+    """version/transparent/lib/networks/loss.py:197-251.  Same constructor and forward arguments; returns
+    (loss, dis[0][argmax pred_c[0]], loss_rotation) as 0-dim tensors with grad wrt pred_r, pred_t, pred_c.  ``knn`` is
+    accepted for signature compatibility; the nearest-neighbour search is fused into the kernel.  ``idx`` should be a
+    Python int (a tensor costs one host sync, as ``idx in self.sym_list`` does in the reference)."""
+
+    def __init__(self, num_point_mesh, sym_list, knn=None):
+        super().__init__()
+        self.num_point_mesh = num_point_mesh
+        self.sym_list = [int(s) for s in sym_list]
+
+    def forward(self, pred_r, pred_t, pred_c, target, model_points, idx, refine, w, axis, target_r):
+        nn_mode = (not refine) and (int(idx) in self.sym_list)
+        return _PossLossFn.apply(pred_r, pred_t, pred_c, target, model_points, axis, target_r, bool(nn_mode), float(w))
+
+    @staticmethod
+    def predr2rotation(pred_r, bs, num_p):
+        return _predr2rotation(pred_r, bs, num_p)
+
+
+def _predr2rotation(pred_r, bs, num_p):
+    """loss.py:253-267 (used on its own by scripts/train_declarative.py:74): [bs,num_p,4] -> [bs*num_p,3,3]."""
+    r = pred_r / torch.norm(pred_r, dim=2).view(bs, num_p, 1)
+    r0, r1, r2, r3 = r[..., 0], r[..., 1], r[..., 2], r[..., 3]
+    rows = [1.0 - 2.0 * (r2 ** 2 + r3 ** 2), 2.0 * r1 * r2 - 2.0 * r0 * r3, 2.0 * r0 * r2 + 2.0 * r1 * r3,
+            2.0 * r1 * r2 + 2.0 * r3 * r0, 1.0 - 2.0 * (r1 ** 2 + r3 ** 2), -2.0 * r0 * r1 + 2.0 * r2 * r3,
+            -2.0 * r0 * r2 + 2.0 * r1 * r3, 2.0 * r0 * r1 + 2.0 * r2 * r3, 1.0 - 2.0 * (r1 ** 2 + r2 ** 2)]
+    return torch.stack(rows, dim=2).contiguous().view(bs * num_p, 3, 3)

@@ -237,3 +237,19 @@ def test_bpnp_oracle_rotation_formula_is_a_rotation_and_switches_branch():
     for k in (0, 2):
         np.testing.assert_allclose(R[k] @ R[k].T, np.eye(3), atol=1e-5)                 # eps in the axis: 1e-6 off unit
     np.testing.assert_array_equal(R[1], np.array([[1, 1e-4, 2e-4], [-1e-4, 1, -1e-4], [-2e-4, 1e-4, 1]]))
+
+
+def test_possloss_oracle_matches_reference_run():
+    """oracle/possloss_ref.py against tests/golden/possloss_ref.npz (gen_golden_possloss.py ran the reference's own
+    PossLoss.forward + autograd backward in float32)."""
+    import torch
+    from oracle import possloss_ref as pr
+    g = np.load(os.path.join(GOLD, "possloss_ref.npz"))
+    for c in g["cases"]:
+        idx, refine = g[f"{c}_meta"]
+        for dt, tol in ((torch.float32, 2e-5), (torch.float64, 2e-5)):
+            v, gr, gt, gc = pr.poss_loss_np(g[f"{c}_pred_r"], g[f"{c}_pred_t"], g[f"{c}_pred_c"], g[f"{c}_target"], g[f"{c}_model"],
+                                            idx, refine, float(g["w"]), g[f"{c}_axis"], g[f"{c}_target_r"], g["sym_list"],
+                                            gouts=g["gouts"], dtype=dt)
+            assert _rel(v, g[f"{c}_vals"]) < tol and _rel(gr, g[f"{c}_grad_r"]) < tol
+            assert _rel(gt, g[f"{c}_grad_t"]) < tol and _rel(gc, g[f"{c}_grad_c"]) < tol

@@ -243,6 +243,45 @@ def f4(args, dev):
             row["cpu_port"] = {"unavailable": repr(e)[:100]}
         rows.append(row)
     print(json.dumps({"config": "f4 bpnp", "rows": rows}), flush=True)
+    # PossLoss at the reference's own shape (loss.py:228: 250 000 predicted points against 500 target points)
+    import pose_estimation_b200 as pb
+    from pose_estimation_b200 import ops_metric
+    num_p, N = 500, 500
+    rng = np.random.default_rng(45)
+    model = ((rng.random((1, N, 3)) - 0.5) * np.array([0.10, 0.08, 0.14])).astype(np.float32)
+    Rg = synth.random_rotation(np.random.default_rng(1)).astype(np.float64)
+    tg = np.array([0.05, -0.03, 0.8])
+    target = (model.astype(np.float64) @ Rg.T + tg).astype(np.float32)
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(dev)
+    pr = T(rng.normal(size=(1, num_p, 4))).requires_grad_()
+    pt = T(tg[None, None] + rng.normal(size=(1, num_p, 3)) * 0.01).requires_grad_()
+    pc = T(rng.uniform(0.05, 0.95, size=(1, num_p, 1))).requires_grad_()
+    md, td, ax, tr = T(model), T(target), T([[1.0, 0.0, 1.0]]), T(Rg[None])
+    lossfn = pb.PossLoss(N, [7, 8])
+    from pose_estimation_b200 import ops_poss
+    gv = torch.tensor([1.0, 0.0, 1.0], device=dev)
+    out = {"config": "f4 possloss", "hypotheses": num_p, "points": N, "pairs": num_p * N * N}
+    for mode, name in ((1, "symmetric"), (0, "indexed")):
+        vals, ws = ops_poss.poss_loss_fwd(pr.detach(), pt.detach(), pc.detach(), td, md, mode, 0.015, ax, tr)
+        it = max(args.iters, 20)
+        out[name + "_fwd_ms"] = timed(lambda: ops_poss.poss_loss_fwd(pr.detach(), pt.detach(), pc.detach(), td, md, mode, 0.015, ax, tr), it)
+        out[name + "_bwd_ms"] = timed(lambda: ops_poss.poss_loss_bwd(pr.detach(), pt.detach(), pc.detach(), td, md, mode, 0.015, ax, tr, gv, ws), it)
+    out["pairs_per_s"] = out["pairs"] / (out["symmetric_fwd_ms"] * 1e-3)
+
+    def module_step():
+        for v in (pr, pt, pc):
+            v.grad = None
+        loss, _, lrot = lossfn(pr, pt, pc, td, md, 8, False, 0.015, ax, tr)
+        (loss + lrot).backward()
+    out["module_fwd_bwd_ms"] = timed(module_step, it)
+
+    def unfused():                                               # the same value from the separate kernels: R in torch, KNN op
+        base = pb.PossLoss.predr2rotation(pr.detach(), 1, num_p)
+        pred = torch.baddbmm(pt.detach().view(num_p, 1, 3), md.expand(num_p, N, 3), base.transpose(1, 2))
+        idx = ops_metric.knn1(pred.reshape(1, -1, 3).contiguous(), td.reshape(1, N, 3))
+        return (pred.reshape(-1, 3) - td[0][idx.view(-1)]).norm(dim=1).view(num_p, N).mean(1)
+    out["unfused_fwd_ms_without_allo_to_ego"] = timed(unfused, it)
+    print(json.dumps(out), flush=True)
 
 
 def main():

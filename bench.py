@@ -380,7 +380,8 @@ def ours_arm(args):
 
     # headline: zero-copy (mask-first K0 reads the pinned host maps in place: mask bytes + the
     # foreground pixels' 32-byte sectors cross PCIe); also the staged-copy variant for comparison
-    e2e_value, zc_bytes, tb_host = run_e2e(True, F // int(os.environ.get("PB_ZC_SPLIT", "4")), args.steps)
+    zc_mode = {"all": True, "xyz": "xyz"}[os.environ.get("PB_ZC_MODE", "xyz")]
+    e2e_value, zc_bytes, tb_host = run_e2e(zc_mode, F // int(os.environ.get("PB_ZC_SPLIT", "4")), args.steps)
     zc_bytes += inp["n_px"] * 3 * 32
     staged_value, staged_bytes, tb_staged = run_e2e(False, 128, min(args.steps, 5))
     same = bool(torch.equal(tb_host, table.cpu())) and bool(torch.equal(tb_staged, table.cpu()))
@@ -407,9 +408,10 @@ def ours_arm(args):
             "hyp_pts_per_s": world * N_HYP * inp["n_px"] * args.steps / (ms_total * 1e-3),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": zc_bytes,
                     "d2h_bytes_per_step": tb_host.numel() * tb_host.element_size(),
-                    "api": "HostEvalSweep.run(zero_copy=True): pinned host maps are read in place by the mask-first "
-                           "K0 kernel (mask bytes + 3 x 32 B sectors per foreground pixel cross PCIe; counted so), "
-                           "small per-frame arrays by cudaMemcpyAsync, then K1..K6, table D2H + sync",
+                    "api": "HostEvalSweep.run(zero_copy='xyz'): per chunk the mask is staged by the copy engine while the "
+                           "mask-first K0 kernel of the previous chunk reads the pinned host coordinate planes in place "
+                           "(mask bytes + 3 x 32 B sectors per foreground pixel cross PCIe; counted so), small per-frame "
+                           "arrays by cudaMemcpyAsync, K1..K6 on two alternating lanes, table D2H + sync",
                     "table_equals_device_path": same,
                     "staged_copy_variant": {"value": staged_value, "unit": UNIT, "h2d_bytes_per_step": staged_bytes,
                                             "api": "HostEvalSweep.run(zero_copy=False): whole maps copied H2D in "

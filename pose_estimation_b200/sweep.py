@@ -186,12 +186,15 @@ class HostEvalSweep:
                  device="cuda", zero_copy=False, **kw):
         """zero_copy=True (needs a mask): no staging copy of the maps at all -- the mask-first K0
         kernel reads the pinned host maps through their mapped (UVA) addresses, so only the mask
-        bytes and the foreground pixels' 32-byte sectors cross PCIe (csrc/compact.cu)."""
+        bytes and the foreground pixels' 32-byte sectors cross PCIe (csrc/compact.cu).
+        zero_copy="xyz": the mask chunk is staged by the copy engine (full-rate DMA) and only the
+        coordinate planes are read in place."""
         dev = torch.device(device)
         self.dev, self.chunk, self.H, self.W = dev, chunk, H, W
         self.zero_copy = zero_copy
         # zero-copy chunks alternate between two compute lanes (own stream, buffers and table): K1..K6 of chunk i
         # overlap the PCIe-bound K0 of chunk i+1
+        self.stage_mask = (not zero_copy) or zero_copy == "xyz"
         nl = 2 if zero_copy else 1
         self.sweeps = [EvalSweep(model_points, diameter, is_sym, chunk, H, W, cap, cfg, device=dev, **kw) for _ in range(nl)]
         self.sweep = self.sweeps[0]
@@ -201,7 +204,7 @@ class HostEvalSweep:
         self.copy_stream = torch.cuda.Stream(device=dev)
         zc = zero_copy
         self.stage = [dict(xyz=None if zc else torch.empty((chunk, 3, H, W), dtype=torch.float32, device=dev),
-                           mask=None if zc else torch.empty((chunk, H, W), dtype=torch.uint8, device=dev),
+                           mask=torch.empty((chunk, H, W), dtype=torch.uint8, device=dev) if self.stage_mask else None,
                            small=torch.empty((SMALL_COLS * chunk,), dtype=torch.float32, device=dev),
                            cls=torch.empty((chunk,), dtype=torch.int32, device=dev),
                            ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
@@ -246,6 +249,7 @@ class HostEvalSweep:
                     self.copy_stream.wait_event(st["free"])
                 if not self.zero_copy:
                     st["xyz"].copy_(xyz_h[lo:hi], non_blocking=True)
+                if self.stage_mask:
                     st["mask"].copy_(mask_h[lo:hi], non_blocking=True)
                 st["small"].copy_(small_h[i], non_blocking=True)
                 st["cls"].copy_(cls_h[lo:hi], non_blocking=True)
@@ -258,8 +262,10 @@ class HostEvalSweep:
                 if self.zero_copy:
                     if mask_h is None:
                         raise ValueError("zero_copy needs a mask (without one every pixel must be streamed)")
-                    self.h2d_bytes += mask_h[lo:hi].numel()      # + the gathered sectors, added by the caller
-                    sweep.step(xyz_h[lo:hi], mask_h[lo:hi], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
+                    if not self.stage_mask:
+                        self.h2d_bytes += mask_h[lo:hi].numel()  # + the gathered sectors, added by the caller
+                    sweep.step(xyz_h[lo:hi], st["mask"] if self.stage_mask else mask_h[lo:hi], ext, lfb, K4, st["cls"],
+                               Rg, tg, frame0=frame0 + lo)
                 else:
                     sweep.step(st["xyz"], st["mask"], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
                 st["free"].record(lane)

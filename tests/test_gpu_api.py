@@ -136,14 +136,22 @@ def test_host_eval_sweep_staged_and_zero_copy_equal_device(dev):
     sw = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev)
     sw.step(t(b["xyz"]), t(b["mask"]), t(b["extent"]), t(b["lfborder"]), t(b["K4"]), t(b["cls"]), t(b["R_gt"]), t(b["t_gt"]))
     want = sw.finish().cpu()
+    sw2 = pb.EvalSweep(models, diam, sym, 2 * F, synth.IMG_H, synth.IMG_W, 1280, device=dev)
+    d = lambda k: torch.cat([t(b[k]), t(b[k])])
+    sw2.step(d("xyz"), d("mask"), d("extent"), d("lfborder"), d("K4"), d("cls"), d("R_gt"), d("t_gt"))
+    want2 = sw2.finish().cpu()
     xyz_h, mask_h = torch.from_numpy(b["xyz"]).pin_memory(), torch.from_numpy(b["mask"]).pin_memory()
     cls_h = torch.from_numpy(b["cls"]).pin_memory()
-    for zc in (False, True):
+    for zc in (False, True, "xyz"):
         hs = sweep.HostEvalSweep(models, diam, sym, synth.IMG_H, synth.IMG_W, 1280, chunk=chunk, device=dev, zero_copy=zc)
         small_h = sweep.pack_small(b["extent"], b["lfborder"], b["K4"], b["R_gt"], b["t_gt"], chunk).pin_memory()
         got = hs.run(xyz_h, mask_h, small_h, cls_h)
         assert torch.equal(got, want), zc
         assert hs.h2d_bytes > 0
+        hs.reset()                                   # a second pass over 4 chunks exercises both lanes / staging buffers
+        got = hs.run(torch.cat([xyz_h, xyz_h]).pin_memory(), torch.cat([mask_h, mask_h]).pin_memory(),
+                     torch.cat([small_h, small_h]).pin_memory(), torch.cat([cls_h, cls_h]).pin_memory())
+        assert torch.equal(got, want2), zc
 
 
 def test_eval_sweep_stream_lanes_and_graph_replay_equal_single_stream(dev):

@@ -255,18 +255,25 @@ __global__ void __launch_bounds__(CT) compact_sparse_kernel(CompactArgs a) {
                     const int o = __shfl_up_sync(0xffffffffu, incl, off);
                     if (lane >= off) incl += o;
                 }
-                int pos = base + incl - n;
-                while (bits) {
-                    const int b = __ffs(bits) - 1;
-                    bits &= bits - 1u;
-                    if (pos < a.cap) {
-                        const int p = ((wb0 + w) << 5) + b;
-                        const int row = p / a.Ww, col = p - row * a.Ww;
-                        oX[pos] = __int_as_float(p);
-                        oU[pos] = (float)(col + cmin);
-                        oV[pos] = (float)(row + rmin);
+                // one non-empty word at a time, its 32 pixels across the lanes (a blob row is a few words:
+                // walking each lane's own bits would serialise up to 32 steps on one or two live lanes)
+                const int wbase = base + incl - n;
+                uint32_t live = __ballot_sync(0xffffffffu, n > 0);
+                while (live) {
+                    const int src = __ffs(live) - 1;
+                    live &= live - 1u;
+                    const uint32_t wbits = __shfl_sync(0xffffffffu, bits, src);
+                    const int wpos = __shfl_sync(0xffffffffu, wbase, src);
+                    if ((wbits >> lane) & 1u) {
+                        const int pos = wpos + __popc(wbits & ((1u << lane) - 1u));
+                        if (pos < a.cap) {
+                            const int p = ((wb0 + (k << 5) + src) << 5) + lane;
+                            const int row = p / a.Ww, col = p - row * a.Ww;
+                            oX[pos] = __int_as_float(p);
+                            oU[pos] = (float)(col + cmin);
+                            oV[pos] = (float)(row + rmin);
+                        }
                     }
-                    ++pos;
                 }
             }
         }

@@ -131,7 +131,7 @@ def reference_arm(args):
                                    "on 256 random masked px + numpy ADD/ADD-S; one process per host core"},
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(n_gpus):
@@ -431,13 +431,34 @@ def ours_arm(args):
             "accuracy": {"succ_add": summ["succ_base_rt"], "succ_r5deg": summ["succ_base_r"],
                          "succ_t5cm": summ["succ_base_t"], "failed": summ["failed"], "frames": summ["frames"]},
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE line, the JSON result: anything a library prints on fd 1 (NCCL's version
+    banner, for one) is sent to stderr instead."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)

@@ -14,8 +14,11 @@ around the REAL third-party arithmetic where it is available in this image:
 
 Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline / ``--impl reference``
 legs may import this module.  Nothing here is used by the product path.  Parity status: pinned by
-running this file in-container to produce ``tests/golden/*.npz`` (the reference itself holds no
-golden vectors for this path).
+running the reference's OWN functions in this container (tests/golden/gen_golden_callsites.py executes
+Trainer.get_pose / cal_dis, lib/utils/metric.py, lib/utils/utlis.py and PoseLoss from /root/reference on
+seeded inputs -> callsites_ref.npz) and checking every function here against those outputs
+(tests/test_oracle_golden.py); the stand-ins for kornia / KeOps named above are what stays unpinned.
+tests/golden/pnp_cv2.npz / metric.npz are further vectors produced by this file itself.
 """
 from __future__ import annotations
 
@@ -63,15 +66,19 @@ def solve_pnp_ransac(obj, img, K33):
 
 
 def get_pose(xyz, extent, lfborder, choose, x_map_choosed, y_map_choosed, intrinsic,
-             num_points=256, rng=None):
+             num_points=256, rng=None, pick=None):
     """tools/trainer.py:383-438 for one frame (the reference asserts bs == 1).
 
     xyz [3,h,w] f32 normalised map; extent/lfborder [3] float64; choose [NP] flat indices into
     h*w; x/y_map_choosed [NP] pixel coordinates; intrinsic [4].  ``rng`` replaces the global torch
-    CPU RNG behind ``torch.randperm`` (:407).  Returns (R [3,3] f32, t [3] f32, ok, inliers)."""
-    rng = rng or np.random.default_rng()
+    CPU RNG behind ``torch.randperm`` (:407); ``pick`` gives the drawn positions outright (how the
+    golden vectors recorded from the reference's own get_pose are replayed).
+    Returns (R [3,3] f32, t [3] f32, ok, inliers)."""
     choose = np.asarray(choose).reshape(-1)
-    pick = rng.permutation(choose.shape[0])[:num_points]                      # :407
+    if pick is None:
+        rng = rng or np.random.default_rng()
+        pick = rng.permutation(choose.shape[0])[:num_points]                  # :407
+    pick = np.asarray(pick).reshape(-1)
     chosen = choose[pick]                                                     # :408
     pts2d = np.stack([np.asarray(x_map_choosed).reshape(-1)[pick],
                       np.asarray(y_map_choosed).reshape(-1)[pick]], axis=-1).astype(np.float32)  # :410-413
@@ -220,7 +227,10 @@ def vote_translation(p_emb, t_res):
 
 
 def choose_ransac_batch(coor_emb, uv_emb, K_matrix, n=125, rng=None):
-    """lib/utils/utlis.py:55-74 (np.random global state replaced by ``rng``)."""
+    """lib/utils/utlis.py:55-74 (np.random global state replaced by ``rng``; pass the ``np.random`` module
+    itself to replay the reference's draws).  One deliberate difference: utlis.py:70 pads BOTH axes of the
+    [M,1] inlier array, so the reference returns [1 + n - M, n] identical rows per element when M <= n (and
+    np.stack then fails unless all elements share M); here that branch returns the one intended row."""
     rng = rng or np.random.default_rng()
     outs = []
     for j in range(coor_emb.shape[0]):

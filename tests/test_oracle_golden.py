@@ -253,3 +253,75 @@ def test_possloss_oracle_matches_reference_run():
                                             gouts=g["gouts"], dtype=dt)
             assert _rel(v, g[f"{c}_vals"]) < tol and _rel(gr, g[f"{c}_grad_r"]) < tol
             assert _rel(gt, g[f"{c}_grad_t"]) < tol and _rel(gc, g[f"{c}_grad_c"]) < tol
+
+
+# ---------------------------------------------------------------------------------------------------
+# callsites_ref.npz: outputs of the reference's OWN get_pose / cal_dis / Metric / utlis / PoseLoss run in the
+# build container (tests/golden/gen_golden_callsites.py) -- this is what pins oracle/ref_callsites.py.
+def _callsites():
+    return np.load(os.path.join(GOLD, "callsites_ref.npz"))
+
+
+@pytest.mark.skipif(rc.cv2 is None, reason="cv2 missing")
+def test_ref_callsites_get_pose_cal_dis_match_reference_run():
+    g = _callsites()
+    models = synth.class_models(500)
+    metric = rc.Metric(synth.SYM_CLS)
+    for tag in ("clean", "noisy"):
+        for f, sp in enumerate(load_frames(g, tag)):
+            fr = synth.reference_frame_dict(sp, models[sp["cls"]])
+            R, t, ok, _ = rc.get_pose(fr["xyz"], fr["extent"], fr["lfborder"], fr["choose"], fr["x_map_choosed"],
+                                      fr["y_map_choosed"], fr["intrinsic"], pick=g[f"{tag}_pick"][f])
+            assert ok
+            # same cv2 call on the same 256 correspondences: rvec / tvec are identical, R differs only by
+            # Rodrigues (cv2, float64) vs the kornia formula in float32
+            assert np.abs(R - g[f"{tag}_R"][f]).max() < 2e-6
+            assert np.array_equal(t, g[f"{tag}_t"][f])
+            add, r_dis, t_dis = rc.cal_dis(metric, g[f"{tag}_R"][f], g[f"{tag}_t"][f], fr["target_r"], fr["target_t"],
+                                           fr["target"], fr["model_points"], fr["cls_id"])
+            ref_add, ref_r, ref_t = g[f"{tag}_dis"][f]
+            assert abs(add - ref_add) <= 1e-5 * ref_add + 1e-7
+            assert abs(t_dis - ref_t) <= 1e-5 * ref_t + 1e-7
+            # the reference takes acos of a float32 dot product clamped to 1 - 1e-7: below ~0.1 degree the
+            # angle is quantised in steps of ~0.03 degree (an exact match reads 0.056), so compare loosely
+            assert abs(r_dis - ref_r) < 0.06
+            d = synth.DIAMETER[sp["cls"]]
+            assert [add < 0.1 * d, r_dis < 5.0, t_dis < 0.05] == [ref_add < 0.1 * d, ref_r < 5.0, ref_t < 0.05]
+
+
+def test_ref_callsites_metric_matches_reference_run():
+    g = _callsites()
+    for cls in (7, 8, 3):
+        model, R, t, Rg, tg = (g[f"m{cls}_{k}"] for k in ("model", "R", "t", "Rg", "tg"))
+        pred, tgt = (model @ R.T + t).astype(np.float32), (model @ Rg.T + tg).astype(np.float32)
+        add, adds = rc.Metric([7, 8]).cal_adds_cuda(pred, tgt, cls)
+        vals = g[f"m{cls}_vals"]
+        assert abs(add - vals[0]) <= 1e-5 * vals[0] and abs(adds - vals[1]) <= 1e-5 * vals[1]
+        assert (add == adds) and ((cls in (7, 8)) or adds == add)
+        assert abs(rc.Metric.angular_distance(R, Rg) - vals[2]) < 0.02
+        assert abs(rc.Metric.translation_distance(t, tg) - vals[3]) <= 1e-6
+    M = rc.Metric([7, 8])
+    assert abs(M.cal_auc(list(g["auc_in"])) - float(g["auc_out"])) < 1e-9
+    assert M.cal_auc([0.5, 0.7]) == float(g["auc_none"]) == 0.0
+
+
+@pytest.mark.skipif(rc.cv2 is None, reason="cv2 missing")
+def test_ref_callsites_utlis_matches_reference_run():
+    g = _callsites()
+    assert np.array_equal(rc.batch_intrinsic_transform(g["K4"]), g["K33"])
+    assert np.array_equal(rc.batch_intrinsic_transform(g["K33"]), g["K4_back"])
+    coor, uv, Ks = g["crb_coor"], g["crb_uv"], g["crb_K"]
+    np.random.seed(77)
+    assert np.array_equal(rc.choose_ransac_batch(coor, uv, Ks, n=125, rng=np.random), g["crb_out125"])
+    for j in range(4):          # wrap-pad branch: the reference returns 1 + n - M identical rows per element
+        ref = g[f"crb_wrap{j}"]
+        assert ref.shape[0] == 1 and ref.shape[2] == 400 and (ref == ref[:, :1, :]).all()
+        np.random.seed(78)
+        ours = rc.choose_ransac_batch(coor[j:j + 1], uv[j:j + 1], Ks[j:j + 1], n=400, rng=np.random)
+        assert ours.shape == (1, 1, 400) and np.array_equal(ours, ref[:, :1, :])
+
+
+def test_ref_callsites_pose_loss_matches_reference_run():
+    g = _callsites()
+    val = rc.pose_loss([7, 8], g["pl_R"], g["pl_t"], g["pl_target"], g["pl_model"], g["pl_idxs"])
+    assert abs(val - float(g["pl_loss"])) <= 2e-6 * float(g["pl_loss"])

@@ -91,6 +91,12 @@ __device__ __forceinline__ float hi32(f32x2 v) { return __uint_as_float((uint32_
 // Returns the two verdict words (sign bit = inlier).  The nine matrix FMAs are packed (scalar-broadcast matrix
 // entry x packed point coordinate: 2-3 register reads per FFMA2); the five tail operations read three full
 // 64-bit operands as FFMA2 (6 register reads, 3 issue cycles), so they are issued as scalar FFMA instead.
+// Measured per warp instruction and SMSP on B200 (scratch/fma_lab.cu): FFMA 1.06 / 1.14 / 1.7 cycles with
+// 1 / 2 / 3 operands not in the reuse cache; FFMA2 2.1 cycles with <= 128 fresh operand bits, 2.2 as used here
+// (broadcast entry, point pair shared by the six rows in a row, accumulator pair), 2.8 for (32, 64, 64) fresh,
+// 3.1 for three fresh pairs.  The register file, not the FMA lanes, bounds this loop: in isolation
+// (scratch/k3_lab.cu) it runs at 18.5 cycles per warp-level hypothesis*point against the ideal 14; an all-packed
+// tail reaches 17.7 there but is no faster inside the kernel (one more live pair per chain), scalar orders 19.7.
 __device__ __forceinline__ void inlier_s2(const f32x2 m[12], f32x2 X, f32x2 Y, f32x2 Z, f32x2 nus, f32x2 nvs,
                                           uint32_t& s0, uint32_t& s1) {
     const f32x2 x = ffma2(m[0], X, ffma2(m[1], Y, ffma2(m[2], Z, m[3])));

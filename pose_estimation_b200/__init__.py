@@ -5,11 +5,11 @@ hand-written CUDA kernels from libposeb200.so through the C ABI in include/poseb
 There is no CPU fallback: importing the API is cheap, calling it without the built library or
 without a GPU raises.
 """
-from .api import (BPnP, BPnPModle, Metric, PossLoss, PoseLoss, RansacConfig, batch_intrinsic_transform, cal_dis,  # noqa: F401
+from .api import (BPnP, BPnPModle, Metric, TransparentMetric, PossLoss, PoseLoss, RansacConfig, batch_intrinsic_transform, cal_dis,  # noqa: F401
                   choose_ransac_batch, estimateSimilarityTransform, estimateSimilarityUmeyama, get_pose, knn,
                   vote_translation)
 from .sweep import EvalSweep, reduce_table, shard_range, summarize  # noqa: F401
 
 __all__ = ["Metric", "PoseLoss", "RansacConfig", "batch_intrinsic_transform", "cal_dis",
            "choose_ransac_batch", "get_pose", "knn", "vote_translation", "EvalSweep", "reduce_table",
-           "shard_range", "summarize", "estimateSimilarityTransform", "estimateSimilarityUmeyama", "BPnP", "BPnPModle", "PossLoss"]
+           "shard_range", "summarize", "estimateSimilarityTransform", "estimateSimilarityUmeyama", "BPnP", "BPnPModle", "PossLoss", "TransparentMetric"]

@@ -132,6 +132,31 @@ class Metric:
         return t_m
 
 
+class TransparentMetric(Metric):
+    """version/transparent/lib/utils.py:12-46 -- the older branch's ``Metric``: ``cal_dis`` matches every PREDICTED
+    point to its nearest TARGET point (KeOps arg-min, then gather), i.e. ADD-S taken in the direction opposite to
+    ``cal_adds_cuda``; both methods always compute both distances and return ADD-S twice for a class in ``sys``."""
+
+    def cal_dis(self, pred, target, idx):
+        """utils.py:17-30: (add_dis, adds_dis) with adds = mean_i min_j |pred_i - target_j|."""
+        p = _dev(pred).float().unsqueeze(0).contiguous()
+        g = _dev(target).float().unsqueeze(0).contiguous()
+        one = torch.ones((1,), dtype=torch.uint8, device=p.device)
+        add, _ = ops_metric.add_adds(p, g, torch.zeros_like(one))
+        _, adds = ops_metric.add_adds(g, p, one)          # roles swapped: the minimum runs over the target points
+        add_v, adds_v = float(add.item()), float(adds.item())
+        return (adds_v if int(idx) in self.sys else add_v), adds_v
+
+    def cal_adds_cuda(self, pred, target, idx):
+        """utils.py:32-46: like lib/utils/metric.py's, but ADD-S is computed for every class."""
+        p = _dev(pred).float().unsqueeze(0).contiguous()
+        g = _dev(target).float().unsqueeze(0).contiguous()
+        one = torch.ones((1,), dtype=torch.uint8, device=p.device)
+        add, adds = ops_metric.add_adds(p, g, one)
+        add_v, adds_v = float(add.item()), float(adds.item())
+        return (adds_v if int(idx) in self.sys else add_v), adds_v
+
+
 def cal_dis(metric: Metric, pred_r, pred_t, datas):
     """Trainer.cal_dis (tools/trainer.py:370-381) -> (add_dis, r_dis, t_dis) Python floats."""
     R = _dev(pred_r).float().reshape(1, 3, 3)

@@ -5,6 +5,7 @@
   batch_intrinsic_transform,
   choose_ransac_batch                   /root/reference/lib/utils/utlis.py
   PoseLoss.forward (+ autograd)         /root/reference/lib/network/loss.py:18-41
+  Metric.cal_dis / cal_adds_cuda        /root/reference/version/transparent/lib/utils.py:12-46 (the older branch)
 
 ``utlis.py`` imports cleanly.  ``metric.py`` / ``loss.py`` import kornia / mmcv (absent here) at module level,
 so stub modules are put into ``sys.modules`` first; ``tools/trainer.py`` cannot be imported at all (it pulls in
@@ -62,6 +63,13 @@ def rotation_matrix_to_quaternion(R, order=None, eps=1e-8):
     return torch.stack(out)
 
 
+def knn_handle(x, y):
+    """generic_argkmin('SqDist(x, y)', 'a = Vi(1)', 'x = Vi(3)', 'y = Vj(3)') (train.py:126): int64 [N,1]."""
+    d = x[:, None, :] - y[None, :, :]
+    d2 = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]
+    return d2.argmin(dim=1, keepdim=True)
+
+
 kn = types.ModuleType("kornia")
 kn.geometry = types.ModuleType("kornia.geometry")
 kn.geometry.conversions = types.ModuleType("kornia.geometry.conversions")
@@ -74,6 +82,12 @@ sys.modules["kornia.geometry.conversions"] = kn.geometry.conversions
 mmcv = types.ModuleType("mmcv")
 mmcv.Config = types.SimpleNamespace(fromfile=lambda *_a, **_k: None)   # loss.py:15 loads a config file that does not exist
 sys.modules["mmcv"] = mmcv
+pk = types.ModuleType("pykeops")
+pk.torch = types.ModuleType("pykeops.torch")
+pk.torch.generic_argkmin = lambda *_a, **_k: knn_handle                  # version/transparent/lib/utils.py:15
+sys.modules["pykeops"] = pk
+sys.modules["pykeops.torch"] = pk.torch
+sys.modules["cv2.cv2"] = cv2                                             # utils.py:5 (`import cv2.cv2 as cv2`, old wheels)
 torch.Tensor.cuda = lambda self, *a, **k: self                           # metric.py:28-29 on a box without a GPU
 
 
@@ -88,6 +102,7 @@ sys.path.insert(0, REFROOT)
 ref_utlis = load(f"{REFROOT}/lib/utils/utlis.py", "ref_utlis")
 ref_metric = load(f"{REFROOT}/lib/utils/metric.py", "ref_metric")
 ref_loss = load(f"{REFROOT}/lib/network/loss.py", "ref_loss")
+ref_tutils = load(f"{REFROOT}/version/transparent/lib/utils.py", "ref_tutils")
 
 
 def trainer_methods():
@@ -106,13 +121,6 @@ def trainer_methods():
 
 
 Trainer = trainer_methods()
-
-
-def knn_handle(x, y):
-    """generic_argkmin('SqDist(x, y)', 'a = Vi(1)', 'x = Vi(3)', 'y = Vj(3)') (train.py:126): int64 [N,1]."""
-    d = x[:, None, :] - y[None, :, :]
-    d2 = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]
-    return d2.argmin(dim=1, keepdim=True)
 
 
 def torch_frame(fr):
@@ -179,6 +187,8 @@ def main():
         out[f"m{cls}_model"] = model; out[f"m{cls}_R"] = R; out[f"m{cls}_t"] = t
         out[f"m{cls}_Rg"] = Rg; out[f"m{cls}_tg"] = tg
         out[f"m{cls}_vals"] = np.array([add, adds, r, td], np.float64)
+        TM = ref_tutils.Metric([7, 8])                       # the older branch's Metric on the same clouds
+        out[f"m{cls}_tvals"] = np.array([*TM.cal_dis(pred, tgt, cls), *TM.cal_adds_cuda(pred, tgt, cls)], np.float64)
     d = np.abs(rng.normal(0.03, 0.04, 200))
     out["auc_in"] = d
     out["auc_out"] = np.float64(M.cal_auc(list(d)))

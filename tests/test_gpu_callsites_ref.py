@@ -106,3 +106,41 @@ def test_pose_loss_vs_reference_pose_loss(g, dev):
     assert abs(loss.item() - float(g["pl_loss"])) <= 1e-5 * float(g["pl_loss"])
     assert np.abs(R.grad.cpu().numpy() - g["pl_grad_R"]).max() <= 1e-4 * np.abs(g["pl_grad_R"]).max()
     assert np.abs(t.grad.cpu().numpy() - g["pl_grad_t"]).max() <= 1e-4 * np.abs(g["pl_grad_t"]).max()
+
+
+def test_transparent_metric_vs_reference(g, dev):
+    """version/transparent/lib/utils.py:17-46 (the older branch's Metric)."""
+    M = pb.TransparentMetric([7, 8])
+    for cls in (7, 8, 3):
+        model, R, t, Rg, tg = (torch.from_numpy(g[f"m{cls}_{k}"]).to(dev) for k in ("model", "R", "t", "Rg", "tg"))
+        pred, tgt = model @ R.T + t, model @ Rg.T + tg
+        got = [*M.cal_dis(pred, tgt, cls), *M.cal_adds_cuda(pred, tgt, cls)]
+        assert np.allclose(got, g[f"m{cls}_tvals"], rtol=1e-5, atol=0)
+
+
+def test_model_ingestion_sampling(cref, dev, tmp_path):
+    """tools/script/sample_model.py:78-85 through pose_estimation_b200.models: ply -> farthest point samples ->
+    pickle -> ModelBank, against the C restatement of the reference's selection loop."""
+    import pickle
+    from pose_estimation_b200 import models
+    from tests.test_host_cpu import _write_ply
+    rng = np.random.default_rng(5)
+    root = tmp_path
+    (root / "models").mkdir()
+    clouds = {}
+    for o in (1, 10):
+        clouds[o] = (rng.normal(size=(3000, 3)) * 40).astype(np.float32)          # millimetres
+        _write_ply(root / "models" / f"obj_{o:02d}.ply", clouds[o], binary=(o == 10))
+    models.sample_models(str(root), objlist=(1, 10), n_samples=700)
+    for o in (1, 10):
+        with open(root / "models" / f"obj_{o:02d}.pkl", "rb") as f:
+            got = pickle.load(f)
+        assert np.array_equal(got, clouds[o][cref.fps(clouds[o], 700)])
+    info = {o: dict(diameter=0.1, lfborder=np.zeros(3), extent=np.ones(3)) for o in (1, 10)}
+    yml = root / "info.yml"
+    yml.write_text("".join(f"{o}: {{diameter: 100.0, min_x: 0, min_y: 0, min_z: 0, size_x: 1000, size_y: 1000, size_z: 1000}}\n"
+                           for o in (1, 10)))
+    bank = models.ModelBank.from_directory(str(root), str(yml), objlist=(1, 10), sym_cls=(1,), num_points=500)
+    assert bank.model.shape == (2, 500, 3) and np.array_equal(bank.is_sym, [0, 1])
+    assert np.allclose(bank.diameter, 0.1) and np.allclose(bank.extent, 1.0)
+    assert np.abs(bank.model).max() < 0.3                                          # metres

@@ -113,3 +113,60 @@ def test_table_allreduce_gloo_world2(tmp_path):
     for p in procs:
         out, _ = p.communicate(timeout=120)
         assert p.returncode == 0 and "ok" in out, out
+
+
+# ---- model / fixture ingestion (pose_estimation_b200/models.py): host-side parsing
+def _write_ply(path, pts, binary):
+    with open(path, "wb") as f:
+        fmt = "binary_little_endian" if binary else "ascii"
+        f.write((f"ply\nformat {fmt} 1.0\ncomment made by a test\nelement vertex {len(pts)}\n"
+                 "property float x\nproperty float y\nproperty float z\nproperty uchar red\n"
+                 "element face 1\nproperty list uchar int vertex_indices\nend_header\n").encode())
+        if binary:
+            for p in pts:
+                f.write(np.asarray(p, "<f4").tobytes() + bytes([7]))
+            f.write(bytes([3]) + np.asarray([0, 1, 2], "<i4").tobytes())
+        else:
+            for p in pts:
+                f.write((" ".join(repr(float(v)) for v in p) + " 7\n").encode())
+            f.write(b"3 0 1 2\n")
+
+
+def test_ply_reader_ascii_and_binary(tmp_path):
+    from pose_estimation_b200 import models
+    pts = np.random.default_rng(0).normal(size=(50, 3)).astype(np.float32) * 100
+    for binary in (False, True):
+        p = tmp_path / f"m{int(binary)}.ply"
+        _write_ply(p, pts, binary)
+        got = models.ply_vtx(p)
+        assert got.dtype == np.float32 and np.array_equal(got, pts)
+    bad = tmp_path / "bad.ply"
+    bad.write_bytes(b"plx\n")
+    with pytest.raises(ValueError):
+        models.ply_vtx(bad)
+
+
+def test_models_info_and_model_bank(tmp_path):
+    """models_info.yml in the reference's format (millimetres) -> the metre arrays the kernels take; the values
+    are those of dataset/linemod/dataset_config/models_info.yml, held in synth.py."""
+    from pose_estimation_b200 import models, synth
+    yml = tmp_path / "models_info.yml"
+    with open(yml, "w") as f:
+        for o, (d, mn, sz) in synth._MODELS_INFO_MM.items():
+            f.write(f"{o}: {{diameter: {d:.8f}, min_x: {mn[0]:.8f}, min_y: {mn[1]:.8f}, min_z: {mn[2]:.8f}, "
+                    f"size_x: {sz[0]:.8f}, size_y: {sz[1]:.8f}, size_z: {sz[2]:.8f}}}\n")
+    info = models.load_models_info(yml)
+    assert sorted(info) == sorted(synth.OBJLIST)
+    rng = np.random.default_rng(1)
+    clouds = {o: (info[o]["lfborder"] + rng.random((3000 if o != 9 else 100, 3)) * info[o]["extent"]) for o in synth.OBJLIST}
+    bank = models.ModelBank.from_arrays(clouds, info, num_points=2600, seed=3)
+    assert bank.model.shape == (13, 2600, 3) and bank.model.dtype == np.float32
+    assert np.allclose(bank.extent, synth.EXTENT) and np.allclose(bank.lfborder, synth.LFBORDER)
+    assert np.allclose(bank.diameter, synth.DIAMETER) and np.array_equal(bank.is_sym, synth.IS_SYM)
+    k = synth.OBJLIST.index(9)                                   # fewer points than asked for: wrap-padded
+    assert np.array_equal(bank.model[k][:100], clouds[9].astype(np.float32))
+    assert np.array_equal(bank.model[k][100:200], clouds[9].astype(np.float32))
+    j = synth.OBJLIST.index(1)                                   # a subset of the class's own points, no repeats
+    assert len({tuple(r) for r in bank.model[j]}) == 2600
+    again = models.ModelBank.from_arrays(clouds, info, num_points=2600, seed=3)
+    assert np.array_equal(again.model, bank.model)

@@ -325,3 +325,19 @@ def test_ref_callsites_pose_loss_matches_reference_run():
     g = _callsites()
     val = rc.pose_loss([7, 8], g["pl_R"], g["pl_t"], g["pl_target"], g["pl_model"], g["pl_idxs"])
     assert abs(val - float(g["pl_loss"])) <= 2e-6 * float(g["pl_loss"])
+
+
+def test_ref_callsites_transparent_metric_matches_reference_run():
+    """version/transparent/lib/utils.py:17-46 run here: cal_dis takes the minimum over the TARGET points for every
+    predicted point, cal_adds_cuda over the predicted points for every target point; a class in ``sys`` returns
+    ADD-S twice."""
+    g = _callsites()
+    for cls in (7, 8, 3):
+        model, R, t, Rg, tg = (g[f"m{cls}_{k}"] for k in ("model", "R", "t", "Rg", "tg"))
+        pred, tgt = (model @ R.T + t).astype(np.float32), (model @ Rg.T + tg).astype(np.float32)
+        add = float(np.linalg.norm(pred - tgt, axis=1).astype(np.float32).mean(dtype=np.float32))
+        _, adds_tgt = rc.Metric([cls]).cal_adds_cuda(pred, tgt, cls)        # min over pred for every target
+        _, adds_prd = rc.Metric([cls]).cal_adds_cuda(tgt, pred, cls)        # roles swapped: min over target
+        sym = cls in (7, 8)
+        want = [adds_prd if sym else add, adds_prd, adds_tgt if sym else add, adds_tgt]
+        assert np.allclose(want, g[f"m{cls}_tvals"], rtol=1e-5, atol=0)

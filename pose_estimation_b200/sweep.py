@@ -207,6 +207,7 @@ class HostEvalSweep:
                            mask=torch.empty((chunk, H, W), dtype=torch.uint8, device=dev) if self.stage_mask else None,
                            small=torch.empty((SMALL_COLS * chunk,), dtype=torch.float32, device=dev),
                            cls=torch.empty((chunk,), dtype=torch.int32, device=dev),
+                           roi=torch.empty((chunk, 2), dtype=torch.int32, device=dev),
                            ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
         self.table_host = torch.empty((ops_metric.TABLE_ROWS, self.sweep.n_cls), dtype=torch.float64).pin_memory()
         self.h2d_bytes = 0
@@ -224,10 +225,12 @@ class HostEvalSweep:
         for sw in self.sweeps:
             sw.reset()
 
-    def run(self, xyz_h, mask_h, small_h, cls_h, frame0=0, group=None):
+    def run(self, xyz_h, mask_h, small_h, cls_h, frame0=0, group=None, roi_h=None):
         """xyz_h [F,3,H,W] f32, mask_h [F,H,W] u8, small_h = pack_small(...) [F/chunk, 22*chunk] f32,
-        cls_h [F] i32 -- pinned host tensors; F a multiple of ``chunk``.  Returns the table on the
-        host (this call synchronises once, at the end)."""
+        cls_h [F] i32 -- pinned host tensors; F a multiple of ``chunk``.  roi_h [F,2] i32 (rmin, cmin), optional:
+        the maps are CROPS of the image, as the reference's network emits them (``pred['xyz']`` is the
+        ``get_square_bbox`` crop, dataset/linemod/batchdataset.py:890-961), and row / column + roi gives the image
+        pixel.  Returns the table on the host (this call synchronises once, at the end)."""
         F = xyz_h.shape[0]
         if F % self.chunk:
             raise ValueError("F must be a multiple of the chunk size")
@@ -253,9 +256,12 @@ class HostEvalSweep:
                     st["mask"].copy_(mask_h[lo:hi], non_blocking=True)
                 st["small"].copy_(small_h[i], non_blocking=True)
                 st["cls"].copy_(cls_h[lo:hi], non_blocking=True)
+                if roi_h is not None:
+                    st["roi"].copy_(roi_h[lo:hi], non_blocking=True)
                 st["ready"].record(self.copy_stream)
             self.h2d_bytes += sum(st[k].numel() * st[k].element_size() for k in ("xyz", "mask", "small", "cls")
-                                  if st[k] is not None)
+                                  if st[k] is not None) + (0 if roi_h is None else st["roi"].numel() * 4)
+            roi = None if roi_h is None else st["roi"]
             lane.wait_event(st["ready"])
             ext, lfb, K4, Rg, tg = unpack_small(st["small"], self.chunk)
             with torch.cuda.stream(lane):
@@ -265,9 +271,9 @@ class HostEvalSweep:
                     if not self.stage_mask:
                         self.h2d_bytes += mask_h[lo:hi].numel()  # + the gathered sectors, added by the caller
                     sweep.step(xyz_h[lo:hi], st["mask"] if self.stage_mask else mask_h[lo:hi], ext, lfb, K4, st["cls"],
-                               Rg, tg, frame0=frame0 + lo)
+                               Rg, tg, frame0=frame0 + lo, roi=roi)
                 else:
-                    sweep.step(st["xyz"], st["mask"], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo)
+                    sweep.step(st["xyz"], st["mask"], ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo, roi=roi)
                 st["free"].record(lane)
         if nl > 1:
             for k, s_ in enumerate(self.lane_streams):

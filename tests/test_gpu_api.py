@@ -154,6 +154,33 @@ def test_host_eval_sweep_staged_and_zero_copy_equal_device(dev):
         assert torch.equal(got, want2), zc
 
 
+def test_host_eval_sweep_on_object_crops_equals_full_frames(dev):
+    """The reference's network emits an object crop of the map (get_square_bbox, batchdataset.py:890-961) and the
+    crop's offset; HostEvalSweep.run(roi_h=...) on 240x240 crops gives the full-frame table bit for bit."""
+    from pose_estimation_b200 import sweep
+    F, chunk, S = 16, 8, 240
+    sps = synth.make_batch_sparse(0x5EED, 2, F)
+    b = batch_arrays(sps)
+    models = torch.from_numpy(synth.class_models(500))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    t = lambda a: torch.from_numpy(a).to(dev)
+    sw = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev)
+    sw.step(t(b["xyz"]), t(b["mask"]), t(b["extent"]), t(b["lfborder"]), t(b["K4"]), t(b["cls"]), t(b["R_gt"]), t(b["t_gt"]))
+    want = sw.finish().cpu()
+    xc = np.zeros((F, 3, S, S), np.float32); mc = np.zeros((F, S, S), np.uint8); roi = np.zeros((F, 2), np.int32)
+    for f, sp in enumerate(sps):
+        r0 = int(np.clip((sp["rows"].min() + sp["rows"].max()) // 2 - S // 2, 0, synth.IMG_H - S))
+        c0 = int(np.clip((sp["cols"].min() + sp["cols"].max()) // 2 - S // 2, 0, synth.IMG_W - S))
+        assert sp["rows"].max() - r0 < S and sp["cols"].max() - c0 < S
+        xc[f] = b["xyz"][f][:, r0:r0 + S, c0:c0 + S]; mc[f] = b["mask"][f][r0:r0 + S, c0:c0 + S]; roi[f] = (r0, c0)
+    small_h = sweep.pack_small(b["extent"], b["lfborder"], b["K4"], b["R_gt"], b["t_gt"], chunk).pin_memory()
+    pin = lambda a: torch.from_numpy(a).pin_memory()
+    for zc in (False, "xyz"):
+        hs = sweep.HostEvalSweep(models, diam, sym, S, S, 1280, chunk=chunk, device=dev, zero_copy=zc)
+        got = hs.run(pin(xc), pin(mc), small_h, pin(b["cls"]), roi_h=pin(roi))
+        assert torch.equal(got, want), zc
+
+
 def test_eval_sweep_stream_lanes_and_graph_replay_equal_single_stream(dev):
     """EvalSweep(lanes=2) (two streams) and a CUDA-graph replay of the step give the single-stream table and
     per-frame outputs bit for bit."""

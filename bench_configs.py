@@ -318,6 +318,34 @@ def f4(args, dev):
     print(json.dumps(out), flush=True)
 
 
+def region(args, dev):
+    """Region-coded maps (tools/script/eval.py:93-103, loss_utils.get_xyz): dense decode of F full-size frames
+    (HBM-bound: (n + 3) * 4 B read + 12 B written per pixel) and the decode of the compacted foreground pixels only."""
+    F, n, H, W = 16, 65, synth.IMG_H, synth.IMG_W
+    g = torch.Generator(device=dev).manual_seed(1)
+    off = torch.randn(F, 3, H, W, device=dev, generator=g) * 0.05
+    lg = torch.randn(F, n, H, W, device=dev, generator=g)
+    rp = torch.rand(F, n, 3, device=dev, generator=g)
+    out = {"config": "region", "frames": F, "n_region": n, "map": [H, W]}
+    byt = F * H * W * ((n + 3) * 4 + 12)
+    for mode in ("hard", "soft"):
+        ms = timed(lambda: ops.region_decode_map(off, lg, rp, mode=mode), args.iters)
+        out["dense_" + mode] = {"ms": ms, "GBps": byt / (ms * 1e-3) / 1e9}
+    sps = synth.make_batch_sparse(0x5EED, 2, F)
+    mask = torch.zeros((F, H, W), dtype=torch.uint8, device=dev)
+    for f, sp in enumerate(sps):
+        mask[f, torch.from_numpy(sp["rows"]).long().to(dev), torch.from_numpy(sp["cols"]).long().to(dev)] = 1
+    cls = np.array([s["cls"] for s in sps])
+    ext = torch.from_numpy(synth.EXTENT[cls].astype(np.float32)).to(dev)
+    lfb = torch.from_numpy(synth.LFBORDER[cls].astype(np.float32)).to(dev)
+    pts, cnt = ops.compact_map(off, mask, ext, lfb, 1280)
+    npx = int(cnt.sum())
+    for mode in ("hard", "soft"):
+        ms = timed(lambda: ops.region_decode_points(pts, cnt, off, lg, rp, ext, lfb, mode=mode), args.iters)
+        out["points_" + mode] = {"ms": ms, "pixels": npx, "Mpx_per_s": npx / (ms * 1e-3) / 1e6}
+    print(json.dumps(out), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--f4-batch", type=int, default=1024)
@@ -342,6 +370,8 @@ def main():
         c4(args, dev)
     if args.only in ("", "c5"):
         c5(args, dev)
+    if args.only in ("", "region"):
+        region(args, dev)
     if args.only in ("", "knn"):
         knn_large(args, dev)
     if args.only in ("", "f3"):

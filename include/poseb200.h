@@ -81,6 +81,24 @@ int pb_gather_correspondences(const float* xyz, const int64_t* choose, const flo
                               const float* ymap, const float* extent, const float* lfborder, int F,
                               int Hh, int Ww, int NP, int cap, float* pts, int32_t* count, void* stream);
 
+/* ---- region-coded maps: xyz = xyz_off + base(region) ------------------------------------------
+ * KRRN predicts an offset map plus per-pixel region logits; the map the solver consumes is rebuilt from both.
+ * soft = 0: tools/script/eval.py:93-103 (tools/trainer.py:391-398, commented out there) -- class = arg-max of the
+ *           softmax, i.e. of the logits (lowest index on ties), base = region_point[class];
+ * soft = 1: lib/network/loss_utils.py:18-28 get_xyz -- base = mean_k softmax(region)[k] * region_point[k].
+ * xyz_off [F,3,Hh,Ww], region [F,n_region,Hh,Ww], region_point [F,n_region,3] f32.
+ * pb_region_decode_points rewrites X,Y,Z of compacted correspondences pts [F,5,cap] / count [F] in place
+ * (X = (xyz_off + base) * extent + lfborder): the pixel of entry i is choose[f,i] (choose [F,NP] int64, the list
+ * pb_gather_correspondences took) or, with choose NULL, (V - rmin) * Ww + (U - cmin) from its own U,V and roi
+ * (pb_compact_map output).  Only foreground pixels touch the logit planes.
+ * pb_region_decode_map is the dense form: xyz [F,3,Hh,Ww] = xyz_off + base at every pixel.                       */
+int pb_region_decode_points(const float* xyz_off, const float* region, const float* region_point,
+                            const int64_t* choose, int NP, const int32_t* roi, const float* extent,
+                            const float* lfborder, int F, int Hh, int Ww, int n_region, int cap, int soft,
+                            float* pts, const int32_t* count, void* stream);
+int pb_region_decode_map(const float* xyz_off, const float* region, const float* region_point, int F, int Hh,
+                         int Ww, int n_region, int soft, float* xyz, void* stream);
+
 /* ---- K1-K4: PnP-RANSAC --------------------------------------------------------------------
  * Replaces cv2.solvePnPRansac(obj, img, K, EPNP, conf .9999, 1 px) at tools/trainer.py:423-427,
  * lib/utils/utlis.py:59-63, tools/script/eval.py:131-135, plus Rodrigues (trainer.py:433).

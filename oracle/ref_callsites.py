@@ -97,6 +97,29 @@ def get_pose(xyz, extent, lfborder, choose, x_map_choosed, y_map_choosed, intrin
     return R.astype(np.float32), np.asarray(tvec, dtype=np.float32).reshape(3), True, inl
 
 
+# ----------------------------------------------------------------------------- region-coded maps
+def _softmax0(region):
+    r = np.asarray(region, np.float32)
+    e = np.exp(r - r.max(axis=0, keepdims=True), dtype=np.float32)
+    return e / e.sum(axis=0, keepdims=True, dtype=np.float32)
+
+
+def region_xyz_hard(xyz_off, region, region_point):
+    """tools/script/eval.py:93-103 for one frame: xyz_off [3,h,w], region [n,h,w] logits, region_point [n,3]
+    -> xyz [3,h,w] = xyz_off + region_point[argmax_k softmax(region)_k] (float32)."""
+    cls = _softmax0(region).argmax(axis=0)                                      # :94-95
+    base = np.asarray(region_point, np.float32)[cls]                            # :99-100 (gather)  [h,w,3]
+    return np.asarray(xyz_off, np.float32) + base.transpose(2, 0, 1)            # :102
+
+
+def get_xyz(xyz_off, region, region_point):
+    """lib/network/loss_utils.py:18-28 for one frame: softmax-weighted base, MEAN over the n regions."""
+    sm = _softmax0(region)                                                      # :24
+    rp = np.asarray(region_point, np.float32)
+    base = (sm[:, None, :, :] * rp[:, :, None, None]).mean(axis=0, dtype=np.float32)   # :27
+    return np.asarray(xyz_off, np.float32) + base
+
+
 # ----------------------------------------------------------------------------- metric
 def rot_to_quat_wxyz(R):
     """Trace-based rotation matrix -> quaternion (w,x,y,z); stands in for kornia

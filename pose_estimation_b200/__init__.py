@@ -6,10 +6,10 @@ There is no CPU fallback: importing the API is cheap, calling it without the bui
 without a GPU raises.
 """
 from .api import (BPnP, BPnPModle, Metric, TransparentMetric, PossLoss, PoseLoss, RansacConfig, batch_intrinsic_transform, cal_dis,  # noqa: F401
-                  choose_ransac_batch, estimateSimilarityTransform, estimateSimilarityUmeyama, get_pose, knn,
+                  choose_ransac_batch, estimateSimilarityTransform, estimateSimilarityUmeyama, get_pose, get_xyz, knn,
                   vote_translation)
 from .sweep import EvalSweep, reduce_table, shard_range, summarize  # noqa: F401
 
 __all__ = ["Metric", "PoseLoss", "RansacConfig", "batch_intrinsic_transform", "cal_dis",
            "choose_ransac_batch", "get_pose", "knn", "vote_translation", "EvalSweep", "reduce_table",
-           "shard_range", "summarize", "estimateSimilarityTransform", "estimateSimilarityUmeyama", "BPnP", "BPnPModle", "PossLoss", "TransparentMetric"]
+           "shard_range", "summarize", "estimateSimilarityTransform", "estimateSimilarityUmeyama", "BPnP", "BPnPModle", "PossLoss", "TransparentMetric", "get_xyz"]

@@ -11,6 +11,7 @@ Same names, argument meaning and return conventions as the reference (file:line 
   PoseLoss                    lib/network/loss.py:18-41
   choose_ransac_batch         lib/utils/utlis.py:55-74
   vote_translation            lib/network/krrn.py:153
+  get_xyz                     lib/network/loss_utils.py:18-28 (region-coded map, forward)
   BPnP / BPnPModle            lib/network/dnn/BPnP.py:8-124
   PossLoss                    version/transparent/lib/networks/loss.py:197-267
 
@@ -47,11 +48,21 @@ def batch_intrinsic_transform(K):
     raise Exception('Wrong Shape!')
 
 
-def get_pose(pred, data, cfg: RansacConfig | None = None, return_info=False):
+def get_xyz(xyz_off, region, region_point):
+    """lib/network/loss_utils.py:18-28: xyz_off [bs,3,h,w] + mean_k softmax(region)[k] * region_point[k]
+    (region [bs,N,h,w], region_point [bs,N,3]) -> [bs,3,h,w].  Forward only (no autograd)."""
+    return ops.region_decode_map(_dev(xyz_off).float(), _dev(region).float(), _dev(region_point).float(), mode="soft")
+
+
+def get_pose(pred, data, cfg: RansacConfig | None = None, return_info=False, region_mode=None):
     """Trainer.get_pose (tools/trainer.py:383-438).  pred['xyz'] [bs,3,h,w]; data['extent'],
     data['lfborder'] [bs,3]; data['choose'] [bs,1,NP] int64; data['x_map_choosed'],
     data['y_map_choosed'] [bs,NP,1]; data['intrinsic'] [bs,4].  Returns (R [bs,3,3], t [bs,3]) as
-    CPU float32 tensors like the reference (which asserts bs == 1; any bs works here)."""
+    CPU float32 tensors like the reference (which asserts bs == 1; any bs works here).
+    region_mode: None = the map is pred['xyz'] as it stands (what trainer.py runs today: :400 ``xyz = xyz_off``);
+    'hard' = tools/script/eval.py:93-103 / the block commented out at trainer.py:391-398 -- pred['xyz'] is an offset
+    map and the class arg-max of pred['region'] [bs,N,h,w] picks the base point out of data['region_point'] [bs,N,3];
+    'soft' = loss_utils.get_xyz's softmax-weighted base.  Only the chosen pixels touch the logits."""
     xyz = _dev(pred['xyz']).float()
     bs = xyz.size(0)
     choose = _dev(data['choose']).long().reshape(bs, -1)
@@ -61,6 +72,9 @@ def get_pose(pred, data, cfg: RansacConfig | None = None, return_info=False):
     lfb = _dev(data['lfborder']).float().reshape(bs, 3)
     K4 = _dev(data['intrinsic']).float().reshape(bs, 4)
     pts, count = ops.gather_correspondences(xyz, choose, xm, ym, ext, lfb)
+    if region_mode is not None:
+        ops.region_decode_points(pts, count, xyz, _dev(pred['region']).float(), _dev(data['region_point']).float(),
+                                 ext, lfb, choose=choose, mode=region_mode)
     out = ops.pnp_ransac_pts(pts, count, K4, cfg or DEFAULT_RANSAC)
     R, t = out['R'].cpu(), out['t'].cpu()   # the reference returns CPU tensors (host sync here)
     if return_info:

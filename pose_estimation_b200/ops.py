@@ -92,6 +92,52 @@ def gather_correspondences(xyz, choose, xmap, ymap, extent, lfborder, cap=None):
     return pts, count
 
 
+def _region_mode(mode):
+    if mode not in ("hard", "soft"):
+        raise ValueError("region mode must be 'hard' (tools/script/eval.py:93-103) or 'soft' (loss_utils.get_xyz)")
+    return 1 if mode == "soft" else 0
+
+
+def region_decode_points(pts, count, xyz_off, region, region_point, extent, lfborder, choose=None, roi=None, mode="hard"):
+    """Rewrites X,Y,Z of compacted correspondences in place: X = (xyz_off + base(region)) * extent + lfborder.
+    pts [F,5,cap] / count [F] from compact_map (pixel taken from U,V - roi) or gather_correspondences (pass the same
+    ``choose`` [F,NP] int64); xyz_off [F,3,H,W], region [F,n,H,W], region_point [F,n,3] f32.  Returns pts."""
+    pts = _chk(pts, torch.float32, "pts")
+    count = _chk(count, torch.int32, "count")
+    xyz_off = _chk(xyz_off, torch.float32, "xyz_off")
+    region = _chk(region, torch.float32, "region")
+    region_point = _chk(region_point, torch.float32, "region_point")
+    extent = _chk(extent, torch.float32, "extent")
+    lfborder = _chk(lfborder, torch.float32, "lfborder")
+    choose = _chk(choose, torch.int64, "choose", True)
+    roi = _chk(roi, torch.int32, "roi", True)
+    F, _, H, W = xyz_off.shape
+    n = region.shape[1]
+    if region.shape != (F, n, H, W) or region_point.shape != (F, n, 3):
+        raise ValueError("region must be [F,n,H,W] and region_point [F,n,3]")
+    cap = pts.shape[-1]
+    NP = 0 if choose is None else choose.shape[-1]
+    call("pb_region_decode_points", _ptr(xyz_off), _ptr(region), _ptr(region_point), _ptr(choose), NP, _ptr(roi),
+         _ptr(extent), _ptr(lfborder), F, H, W, n, cap, _region_mode(mode), _ptr(pts), _ptr(count), _stream())
+    return pts
+
+
+def region_decode_map(xyz_off, region, region_point, mode="soft"):
+    """Dense form: xyz [F,3,H,W] = xyz_off + base(region) at every pixel (lib/network/loss_utils.py:18-28 for
+    mode='soft'; the arg-max form of tools/script/eval.py:93-103 for mode='hard').  Forward only."""
+    xyz_off = _chk(xyz_off, torch.float32, "xyz_off")
+    region = _chk(region, torch.float32, "region")
+    region_point = _chk(region_point, torch.float32, "region_point")
+    F, _, H, W = xyz_off.shape
+    n = region.shape[1]
+    if region.shape != (F, n, H, W) or region_point.shape != (F, n, 3):
+        raise ValueError("region must be [F,n,H,W] and region_point [F,n,3]")
+    out = torch.empty_like(xyz_off)
+    call("pb_region_decode_map", _ptr(xyz_off), _ptr(region), _ptr(region_point), F, H, W, n, _region_mode(mode),
+         _ptr(out), _stream())
+    return out
+
+
 # ----------------------------------------------------------------------------- K1-K4
 def pnp_ransac_pts(pts, count, K4, cfg: RansacConfig | None = None, frame0=0, sample_idx=None,
                    want_counts=False, want_bitmap=False, want_minimal=False):

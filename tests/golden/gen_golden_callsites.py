@@ -6,6 +6,8 @@
   choose_ransac_batch                   /root/reference/lib/utils/utlis.py
   PoseLoss.forward (+ autograd)         /root/reference/lib/network/loss.py:18-41
   Metric.cal_dis / cal_adds_cuda        /root/reference/version/transparent/lib/utils.py:12-46 (the older branch)
+  get_xyz (region-coded map, soft)      /root/reference/lib/network/loss_utils.py:18-28
+  region arg-max decode (hard)          /root/reference/tools/script/eval.py:93-103 (the lines as they stand)
 
 ``utlis.py`` imports cleanly.  ``metric.py`` / ``loss.py`` import kornia / mmcv (absent here) at module level,
 so stub modules are put into ``sys.modules`` first; ``tools/trainer.py`` cannot be imported at all (it pulls in
@@ -237,6 +239,26 @@ def main():
     out["pl_R"] = pred_r.detach().numpy(); out["pl_t"] = pred_t.detach().numpy(); out["pl_idxs"] = idxs.numpy()
     out["pl_loss"] = np.float64(loss.item())
     out["pl_grad_R"] = pred_r.grad.numpy(); out["pl_grad_t"] = pred_t.grad.numpy()
+
+    # ---- region-coded maps: loss_utils.get_xyz (soft) and the block of tools/script/eval.py:93-103 (hard) as it stands
+    bs, n, h, w = 2, 65, 24, 24
+    xyz_off = (rng.normal(0, 0.05, (bs, 3, h, w))).astype(np.float32)
+    logits = (rng.normal(0, 3.0, (bs, n, h, w))).astype(np.float32)
+    logits[0, 7, 3, 4] = logits[0, 9, 3, 4] = 20.0                             # an exact tie: the lower class wins
+    rpts = rng.random((bs, n, 3)).astype(np.float32)
+    rpts[:, 0] = 0.0                                                            # batchdataset.py:728: row 0 is the background
+    out["reg_xyz_off"] = xyz_off; out["reg_logits"] = logits; out["reg_points"] = rpts
+    get_xyz = sys.modules["lib.network.loss_utils"].get_xyz
+    out["reg_soft"] = get_xyz(torch.from_numpy(xyz_off), torch.from_numpy(logits), torch.from_numpy(rpts)).numpy()
+    src = open(f"{REFROOT}/tools/script/eval.py").read().split("\n")
+    a = next(i for i, ln in enumerate(src) if ln.strip() == "region = pred['region'].cpu()")
+    b = next(i for i, ln in enumerate(src) if ln.strip() == "xyz = xyz_off + xyz_base.squeeze(1)")
+    assert 0 < b - a < 15
+    import textwrap
+    ns = dict(torch=torch, pred=dict(region=torch.from_numpy(logits), xyz=torch.from_numpy(xyz_off)),
+              datas=dict(region_point=torch.from_numpy(rpts)))
+    exec(compile(textwrap.dedent("\n".join(src[a:b + 1])), f"{REFROOT}/tools/script/eval.py", "exec"), ns)
+    out["reg_hard"] = ns["xyz"].numpy()
 
     np.savez_compressed(os.path.join(OUT, "callsites_ref.npz"), **out)
     print("wrote callsites_ref.npz:", os.path.getsize(os.path.join(OUT, "callsites_ref.npz")), "bytes")

@@ -144,3 +144,58 @@ def test_model_ingestion_sampling(cref, dev, tmp_path):
     assert bank.model.shape == (2, 500, 3) and np.array_equal(bank.is_sym, [0, 1])
     assert np.allclose(bank.diameter, 0.1) and np.allclose(bank.extent, 1.0)
     assert np.abs(bank.model).max() < 0.3                                          # metres
+
+
+def test_region_coded_maps_vs_reference(g, dev):
+    """Dense decode against the reference's own runs: arg-max form bit for bit (tools/script/eval.py:93-103), softmax
+    form to 1e-6 (lib/network/loss_utils.py:18-28; torch's softmax sums in another order)."""
+    from pose_estimation_b200 import ops
+    off, lg, rp = (torch.from_numpy(g[k]).to(dev) for k in ("reg_xyz_off", "reg_logits", "reg_points"))
+    hard = ops.region_decode_map(off, lg, rp, mode="hard")
+    assert np.array_equal(hard.cpu().numpy(), g["reg_hard"])
+    soft = pb.get_xyz(off, lg, rp)
+    assert np.abs(soft.cpu().numpy() - g["reg_soft"]).max() <= 1e-6
+    # compacted form: only the listed pixels are decoded; same numbers as the dense map followed by the plain gather
+    bs, _, h, w = off.shape
+    gen = torch.Generator(device=dev).manual_seed(3)
+    choose = torch.stack([torch.randperm(h * w, device=dev, generator=gen)[:200] for _ in range(bs)])
+    xm = (choose % w).float() + 300.0
+    ym = (choose // w).float() + 200.0
+    ext = torch.tensor([[0.0759, 0.0776, 0.0918], [0.2157, 0.1219, 0.2194]], device=dev)
+    lfb = -0.5 * ext
+    for mode, dense in (("hard", hard), ("soft", soft)):
+        pts, cnt = ops.gather_correspondences(off, choose, xm, ym, ext, lfb)
+        ops.region_decode_points(pts, cnt, off, lg, rp, ext, lfb, choose=choose, mode=mode)
+        want, _ = ops.gather_correspondences(dense, choose, xm, ym, ext, lfb)
+        assert torch.equal(pts, want), mode
+    # compact_map output (pixel recovered from U, V and the crop offset)
+    mask = torch.zeros((bs, h, w), dtype=torch.uint8, device=dev)
+    mask.view(bs, -1).scatter_(1, choose, 1)
+    roi = torch.tensor([[200, 300], [17, 5]], dtype=torch.int32, device=dev)
+    pts, cnt = ops.compact_map(off, mask, ext, lfb, 256, roi=roi)
+    ops.region_decode_points(pts, cnt, off, lg, rp, ext, lfb, roi=roi, mode="hard")
+    want, cnt2 = ops.compact_map(hard, mask, ext, lfb, 256, roi=roi)
+    assert torch.equal(cnt, cnt2) and torch.equal(pts[:, :, :200], want[:, :, :200])
+
+
+def test_get_pose_with_region_coded_map(g):
+    """get_pose(region_mode='hard'): the offset map + region logits of a frame give the pose of the plain map."""
+    models = synth.class_models(500)
+    sp = load_frames(g, "clean")[2]
+    pred, data = _datas(sp, models)
+    R0, t0 = pb.get_pose(pred, data)
+    n = 65
+    gen = torch.Generator().manual_seed(9)
+    rp = torch.rand(1, n, 3, generator=gen)
+    rp[:, 0] = 0
+    _, _, h, w = pred["xyz"].shape
+    cls = torch.randint(0, n, (1, h, w), generator=gen)
+    logits = torch.randn(1, n, h, w, generator=gen)
+    logits.scatter_(1, cls[:, None], 10.0)                                  # the drawn class wins at every pixel
+    base = rp[0][cls[0]].permute(2, 0, 1)[None]                             # [1,3,h,w]
+    pred2 = {"xyz": pred["xyz"] - base, "region": logits}
+    data2 = dict(data, region_point=rp)
+    R1, t1 = pb.get_pose(pred2, data2, region_mode="hard")
+    assert rot_angle(R1[0].numpy(), R0[0].numpy()) <= 1e-4 and (t1 - t0).abs().max() <= 1e-4
+    Rp, tp = pb.get_pose(pred2, data2)                                      # offsets alone are not a pose
+    assert rot_angle(Rp[0].numpy(), R0[0].numpy()) > 1e-2 or (tp - t0).abs().max() > 1e-2

@@ -341,3 +341,15 @@ def test_ref_callsites_transparent_metric_matches_reference_run():
         sym = cls in (7, 8)
         want = [adds_prd if sym else add, adds_prd, adds_tgt if sym else add, adds_tgt]
         assert np.allclose(want, g[f"m{cls}_tvals"], rtol=1e-5, atol=0)
+
+
+def test_ref_callsites_region_maps_match_reference_run():
+    """Region-coded maps: tools/script/eval.py:93-103 (arg-max class, run as the lines stand) and
+    lib/network/loss_utils.py:18-28 get_xyz (softmax-weighted mean), including an exact tie of two logits."""
+    g = _callsites()
+    for f in range(g["reg_xyz_off"].shape[0]):
+        hard = rc.region_xyz_hard(g["reg_xyz_off"][f], g["reg_logits"][f], g["reg_points"][f])
+        assert np.array_equal(hard, g["reg_hard"][f])
+        soft = rc.get_xyz(g["reg_xyz_off"][f], g["reg_logits"][f], g["reg_points"][f])
+        assert np.abs(soft - g["reg_soft"][f]).max() <= 1e-7
+    assert np.array_equal(g["reg_hard"][0][:, 3, 4], g["reg_xyz_off"][0][:, 3, 4] + g["reg_points"][0][7])   # tie -> class 7

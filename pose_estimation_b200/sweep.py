@@ -107,8 +107,13 @@ class EvalSweep:
             return t
         return self._table
 
-    def step(self, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=0, roi=None, events=None, out=None):
+    def step(self, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=0, roi=None, events=None, out=None,
+             pred_t=None, cloud=None, t_res=None):
         """One batch of F frames (device tensors).  Returns (add, r_deg, t_m) [F] device tensors.
+        pred_t [F,3], or cloud [F,NP,3] + t_res [F,3,NP] (the T-offset vote, lib/network/krrn.py:153, is then taken
+        here): the ``opt_pose`` branch of the test loop (tools/trainer.py:196-221) -- the 'reg' and 'final' variants
+        pair the PnP rotation with the voted translation; their rows of the table are filled and their per-frame
+        (add, r_deg, t_m) kept in ``self.last_reg``.
         ``events``: optional list that receives one (name, start, end) CUDA-event triple per stage
         (recorded on the current stream; used by bench.py for the per-kernel roofline)."""
         if self.lanes:
@@ -122,7 +127,9 @@ class EvalSweep:
                 with torch.cuda.stream(s):
                     lane.step(xyz[lo:hi], None if mask is None else mask[lo:hi], extent[lo:hi], lfborder[lo:hi],
                               K4[lo:hi], cls[lo:hi], R_gt[lo:hi], t_gt[lo:hi], frame0=frame0 + lo,
-                              roi=None if roi is None else roi[lo:hi], out=tuple(self.out[j, lo:hi] for j in range(3)))
+                              roi=None if roi is None else roi[lo:hi], out=tuple(self.out[j, lo:hi] for j in range(3)),
+                              pred_t=None if pred_t is None else pred_t[lo:hi],
+                              cloud=None if cloud is None else cloud[lo:hi], t_res=None if t_res is None else t_res[lo:hi])
                     self.ev_out[k].record(s)
             for e in self.ev_out:
                 main.wait_event(e)
@@ -147,6 +154,15 @@ class EvalSweep:
         e4 = mark()
         if events is not None:
             events.append((e0, e1, e2, e3, e4))
+        if cloud is not None:
+            pred_t = ops_metric.vote_translation(cloud, t_res)                       # krrn.py:153
+        if pred_t is not None:                                                       # trainer.py:196-199: reg == final
+            reg = ops_metric.pose_metrics(rs.R, pred_t.reshape(-1, 3), R_gt, t_gt, self.model, cls, self.is_sym)
+            for variant in (1, 2):
+                ops_metric.accumulate_results(self._table, *reg, cls, self.diameter, status=rs.status, variant=variant,
+                                              add_frac=self.add_frac, r_thr_deg=self.r_thr_deg, t_thr_m=self.t_thr_m,
+                                              count_frames=False)
+            self.last_reg = reg
         return add, r_deg, t_m
 
     def finish(self, group=None):

@@ -217,3 +217,40 @@ def test_cpu_tensors_have_no_fallback():
     from pose_estimation_b200._lib import PoseB200Error
     with pytest.raises(PoseB200Error):
         ops_metric.knn1(torch.zeros(4, 3), torch.zeros(4, 3))
+
+
+def test_eval_sweep_opt_pose_variants(dev):
+    """tools/trainer.py:196-221 (opt_pose): 'reg' and 'final' pair the PnP rotation with the voted translation."""
+    from pose_estimation_b200 import ops_metric
+    F, NP = 26, 500
+    sps = synth.make_batch_sparse(0x5EED, 2, F)
+    b = batch_arrays(sps)
+    models = torch.from_numpy(synth.class_models(500))
+    t = lambda a: torch.from_numpy(a).to(dev)
+    args = [t(b[k]) for k in ("xyz", "mask", "extent", "lfborder", "K4", "cls", "R_gt", "t_gt")]
+    sw = pb.EvalSweep(models, torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM), F, synth.IMG_H,
+                      synth.IMG_W, 1280, device=dev)
+    # every cloud point votes t_gt exactly (offset = t_gt - point): the voted translation is the ground truth
+    g = torch.Generator(device=dev).manual_seed(2)
+    cloud = torch.randn(F, NP, 3, device=dev, generator=g) * 0.05 + args[7][:, None, :]
+    t_res = (args[7][:, None, :] - cloud).permute(0, 2, 1).contiguous()
+    sw.step(*args, cloud=cloud, t_res=t_res)
+    res = ops_metric.table_to_result(sw.finish(), synth.OBJLIST)
+    tot = lambda k: sum(res[k].values())
+    assert tot("obj_num") == F
+    assert tot("dis_reg_r") == tot("dis_base_r") and tot("succ_reg_r") == tot("succ_base_r")     # same rotation
+    assert tot("dis_reg_t") < 1e-5 * F and tot("succ_reg_t") == F                               # voted translation = GT
+    assert tot("succ_reg_rt") >= tot("succ_base_rt")
+    for k in ("dis_{}_rt", "dis_{}_r", "dis_{}_t", "succ_{}_rt", "succ_{}_r", "succ_{}_t"):
+        assert res[k.format("final")] == res[k.format("reg")]                                  # trainer.py:198-199
+    # an explicit pred_t gives the same rows as voting it here
+    sw2 = pb.EvalSweep(models, torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM), F, synth.IMG_H,
+                       synth.IMG_W, 1280, device=dev)
+    sw2.step(*args, pred_t=pb.vote_translation(cloud, t_res))
+    assert torch.equal(sw2.finish(), sw.table)
+    # and matches the per-frame call sites (frame 0: get_pose keys its hypothesis stream on frame index 0)
+    metric = pb.Metric(synth.SYM_CLS)
+    pred, data = _datas(sps[0], synth.class_models(500))
+    R, _ = pb.get_pose({"xyz": pred["xyz"]}, data)
+    a, _, _ = pb.cal_dis(metric, R, pb.vote_translation(cloud[:1], t_res[:1]).cpu(), data)
+    assert abs(a - float(sw.last_reg[0][0])) <= 1e-5 * max(a, 1e-6) + 1e-7

@@ -119,6 +119,42 @@ def c1(args, dev):
         tb = sw.table.cpu().numpy()
         out[f"F{F}"] = {"ms_per_batch": ms, "frames_per_s": F / (ms * 1e-3), "P_mean": float(np.mean([len(s["rows"]) for s in sps])),
                         "add_success": float(tb[ops_metric.ROW_VARIANT0, 0] / max(tb[ops_metric.ROW_OBJ_NUM, 0], 1))}
+    # the reference's own loop shape: one frame per call through the drop-in call sites (tools/trainer.py:166-172:
+    # get_pose -> cal_dis, host tensors in, Python floats out, so every call synchronises) and the same step as a
+    # replayed CUDA graph (one launch per frame instead of six)
+    import time
+    sp = synth.make_frame_sparse(0x5EED, 1, 0, cls=0)
+    fr = synth.reference_frame_dict(sp, synth.class_models(500)[0])
+    pred = {"xyz": torch.from_numpy(fr["xyz"])[None].to(dev)}
+    data = {"extent": torch.from_numpy(fr["extent"])[None], "lfborder": torch.from_numpy(fr["lfborder"])[None],
+            "choose": torch.from_numpy(fr["choose"])[None, None], "intrinsic": torch.from_numpy(fr["intrinsic"])[None],
+            "x_map_choosed": torch.from_numpy(fr["x_map_choosed"])[None, :, None],
+            "y_map_choosed": torch.from_numpy(fr["y_map_choosed"])[None, :, None],
+            "target_r": torch.from_numpy(fr["target_r"])[None], "target_t": torch.from_numpy(fr["target_t"])[None],
+            "target": torch.from_numpy(fr["target"])[None], "model_points": torch.from_numpy(fr["model_points"])[None],
+            "cls_id": torch.LongTensor([fr["cls_id"]])}
+    data = {k: v.to(dev) for k, v in data.items()}                 # dataloader tensors already on the device
+    metric = pb.Metric(synth.SYM_CLS)
+    for _ in range(20):
+        R, t = pb.get_pose(pred, data); pb.cal_dis(metric, R, t, data)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    n = 200
+    for _ in range(n):
+        R, t = pb.get_pose(pred, data)
+        pb.cal_dis(metric, R, t, data)
+    out["dropin_call_sites_ms_per_frame"] = (time.perf_counter() - t0) / n * 1e3
+    sw = pb.EvalSweep(models, diam, sym, 1, H, W, 4096, ops.RansacConfig(n_hyp=256, seed=0x5EED), device=dev)
+    one = {k: v[:1] for k, v in inp.items()}
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        for _ in range(3):
+            sw.step(one["xyz"], one["mask"], one["extent"], one["lfborder"], one["K4"], one["cls"], one["R_gt"], one["t_gt"])
+    torch.cuda.synchronize()
+    gph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gph, stream=s):
+        sw.step(one["xyz"], one["mask"], one["extent"], one["lfborder"], one["K4"], one["cls"], one["R_gt"], one["t_gt"])
+    out["F1_graph_replay_ms"] = timed(gph.replay, 200, warm=10)
     print(json.dumps(out), flush=True)
 
 

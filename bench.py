@@ -54,12 +54,13 @@ MAP_BYTES_PER_FRAME = 480 * 640 * (12 + 1)      # xyz 12 B + mas
 
 # ------------------------------------------------------------------------------------------------
 # reference arm / cpu_baseline: the reference's per-frame CPU path on the host cores
-def _ref_worker(rank, frames, n_steps, barrier, out_q):
+def _ref_worker(rank, frames, n_steps, barrier, out_q, cv2_threads=1):
     """Worker process: builds its frames (untimed), then evaluates them once per step."""
     try:
         import numpy as np
         import cv2
-        cv2.setNumThreads(1)                        # one process per core; no nested OpenCV threads
+        if cv2_threads is not None:
+            cv2.setNumThreads(cv2_threads)          # one process per core; no nested OpenCV threads
         from oracle import ref_callsites as rc
         from pose_estimation_b200 import synth
         models = synth.class_models(N_MODEL)
@@ -82,15 +83,16 @@ def _ref_worker(rank, frames, n_steps, barrier, out_q):
         raise
 
 
-def run_reference_cpu(n_frames, n_steps, n_workers=None):
+def run_reference_cpu(n_frames, n_steps, n_workers=None, cv2_threads=1):
     """Times the reference path on ``n_frames`` frames of the workload, ``n_steps`` times.
+    cv2_threads=None leaves OpenCV's own threading at its default (the reference as it is launched: one process).
     Returns (list of seconds per step, workers, frames)."""
     n_workers = n_workers or max(1, min(os.cpu_count() or 1, n_frames))
     ctx = mp.get_context("spawn")
     barrier = ctx.Barrier(n_workers + 1)
     q = ctx.Queue()
     shards = [list(range(w, n_frames, n_workers)) for w in range(n_workers)]
-    procs = [ctx.Process(target=_ref_worker, args=(w, shards[w], n_steps, barrier, q), daemon=True)
+    procs = [ctx.Process(target=_ref_worker, args=(w, shards[w], n_steps, barrier, q, cv2_threads), daemon=True)
              for w in range(n_workers)]
     for p in procs:
         p.start()
@@ -400,6 +402,10 @@ def ours_arm(args):
                         "sample": f"{n_frames} frames of the workload (best of 2 timed passes after 1 warm-up); "
                                   f"oracle/ref_callsites.eval_frame around real cv2 {cv2.__version__} "
                                   "solvePnPRansac(EPNP, 256 px) + numpy ADD/ADD-S; one process per host core"}
+            # the reference as it is launched: ONE process, OpenCV's default threading (SURVEY.md 8(d) variant i)
+            t1, _, n1 = run_reference_cpu(32, 2, n_workers=1, cv2_threads=None)
+            cpu_base["single_process"] = {"value": n1 / t1[1], "unit": UNIT, "cv2_threads": cv2.getNumThreads(),
+                                          "sample": f"{n1} frames, second of 2 passes"}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,

@@ -207,3 +207,49 @@ def test_map_ransac_equals_two_step(dev):
     for f in range(5):
         assert rot_angle(mr.R[f].cpu().numpy(), b["R_gt"][f]) < np.radians(5.0)
         assert np.linalg.norm(mr.t[f].cpu().numpy() - b["t_gt"][f]) < 0.05
+
+
+def test_ransac_ragged_and_degenerate_batches_match_oracle(cref, dev):
+    """One launch holding every awkward frame at once: 0 / 1 / 3 / 4 / 5 / 31 / 32 / 33 correspondences, exactly cap,
+    all points identical, collinear model points, points behind the camera, NaN / Inf coordinates, and normal frames
+    between them.  Status, every hypothesis' inlier count, chosen hypothesis, bitmap and pose equal the C oracle's."""
+    cap = 1280
+    base = [synth.compact_points(s) for s in synth.make_batch_sparse(0x5EED, 2, 6)]
+    rng = np.random.default_rng(12)
+    frames = []
+    for n in (0, 1, 3, 4, 5, 31, 32, 33):
+        frames.append(base[0][:, :n].copy())
+    full = np.concatenate([base[1], base[2]], axis=1)[:, :cap]                 # exactly cap correspondences (two objects mixed)
+    frames.append(full)
+    same = np.repeat(base[3][:, :1], 200, axis=1); frames.append(same)          # 200 copies of one correspondence
+    col = base[4][:, :300].copy()
+    tline = np.linspace(-1, 1, 300, dtype=np.float32)
+    col[0], col[1], col[2] = 0.01 * tline, 0.02 * tline, -0.015 * tline          # collinear model points
+    frames.append(col)
+    behind = base[5][:, :400].copy(); behind[2] -= 5.0; frames.append(behind)   # far outside the object: no consensus
+    bad = base[0][:, :500].copy()
+    bad[0, ::7] = np.nan; bad[1, 3::11] = np.inf; bad[3, 5::13] = -np.inf       # non-finite entries among good points
+    frames.append(bad)
+    frames += [base[1], base[2]]                                                # ordinary frames after the odd ones
+    pts, cnt = pack_pts(frames, cap)
+    F = len(frames)
+    K4 = np.tile(synth.LINEMOD_K4, (F, 1))
+    for n_hyp, lo in ((256, 0), (96, 2)):
+        cfg = ops.RansacConfig(n_hyp=n_hyp, lo_rounds=lo)
+        out = ops.pnp_ransac_pts(_t(pts, dev), _t(cnt, dev), _t(K4, dev), cfg, frame0=100, want_counts=True, want_bitmap=True)
+        out = {k: v.cpu().numpy() for k, v in out.items()}
+        for f in range(F):
+            o = cref.ransac_frame(pts[f, :, :cnt[f]], K4[f], frame=100 + f, n_hyp=cfg.n_hyp, thresh_px=cfg.thresh_px,
+                                  gn_iters=cfg.gn_iters, lo_rounds=cfg.lo_rounds, min_inliers=cfg.min_inliers, seed=cfg.seed)
+            assert out["status"][f] == o["status"], (f, cnt[f])
+            if cnt[f] >= 4:
+                assert np.array_equal(out["hyp_counts"][f], o["hyp_counts"]), f
+            if o["status"] == 0:
+                assert out["best_hyp"][f] == o["best_hyp"] and out["n_inl"][f] == o["n_inl"], f
+                words = (cnt[f] + 31) // 32
+                assert np.array_equal(out["inl_bitmap"][f, :words].view(np.uint32), o["bitmap"][:words]), f
+                assert rot_angle(out["R"][f], o["R"]) <= R_TOL_RAD and np.abs(out["t"][f] - o["t"]).max() <= T_TOL_M, f
+            else:
+                assert np.array_equal(out["R"][f], np.eye(3, dtype=np.float32)) and np.all(out["t"][f] == 0), f
+        assert np.all(np.isfinite(out["R"])) and np.all(np.isfinite(out["t"]))
+    assert list(out["status"][:3]) == [1, 1, 1]                                 # fewer than 4 correspondences

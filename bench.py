@@ -9,7 +9,10 @@ hypotheses, ADD with 500-pt models, ADD-S for eggbox/glue).  The timed region is
 steps closed by the ONE all-reduce of the [24,13] accuracy table that the path has (NCCL when N > 1;
 weak scaling: every rank evaluates its own 1024-frame shard per step).
 
-  value     whole-job frames/s with the maps already resident in HBM (CUDA events, max over ranks)
+  value     whole-job frames/s with the maps already resident in HBM (CUDA events, max over ranks): K steps of
+            EvalSweep(lanes=2, free_running=True) -- each batch as two halves on two streams, joined once by
+            finish() -- with no events inside the region; `instrumented` is the same K steps on one stream with
+            events between the kernels, the pass the per-kernel times and the roofline come from
   e2e       the same pass through HostEvalSweep.run with PINNED HOST inputs, timed per step: the
             mask-first K0 kernel reads the pinned maps in place (zero-copy; the bytes that cross PCIe
             are counted in h2d_bytes_per_step), the table is all-reduced and read back every step;
@@ -286,12 +289,41 @@ def ours_arm(args):
     lib.pb_stage_timing_read(ms3, C.byref(ncalls))
     lib.pb_stage_timing(0)
     hyp_ms, score_ms, final_ms = float(ms3[0]), float(ms3[1]), float(ms3[2])
+    # ---- the same sweep as the product runs it: every batch cut in two halves that run on their own streams and
+    # are not joined between batches (EvalSweep(lanes=2, free_running=True)), so the HBM-bound K0 of one half overlaps
+    # the FP32-bound scoring / latency-bound refit of the other and no stream waits at a batch boundary; joined once
+    # by finish().  No events inside this region: `value` is this clean pass, the per-kernel times above come from
+    # the instrumented single-stream pass (same K steps, same inputs, same process).
+    sw2 = pb.EvalSweep(models, diam, sym, F, H, W, CAP, cfg, device=dev, lanes=2, free_running=True)
+
+    def lane_step():
+        sw2.step(inp["xyz"], inp["mask"], inp["extent"], inp["lfborder"], inp["K4"], inp["cls"], inp["R_gt"],
+                 inp["t_gt"], frame0=rank * F)
+    for _ in range(max(args.warmup, 3)):
+        lane_step()
+    sw2.reset()
+    lane_step()
+    same_lanes = bool(torch.equal(sw2.finish(), table))
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    sw2.reset()
+    c0.record()
+    for _ in range(args.steps):
+        lane_step()
+    sw2.finish()
+    c1.record()
+    barrier()
+    cmax = torch.tensor([c0.elapsed_time(c1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(cmax, op=dist.ReduceOp.MAX)
+    ms_clean = float(cmax.item())
     ms_total = e0.elapsed_time(e1)
     tmax = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     ms_total = float(tmax.item())
-    value = world * F * args.steps / (ms_total * 1e-3)
+    value_instr = world * F * args.steps / (ms_total * 1e-3)
+    value = world * F * args.steps / (ms_clean * 1e-3)
     stage_ms = [statistics.fmean(ev[i].elapsed_time(ev[i + 1]) for ev in evs) for i in range(4)]
     k0_ms = stage_ms[0]
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -408,10 +440,16 @@ def ours_arm(args):
                                           "sample": f"{n1} frames, second of 2 passes"}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_clean / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(world),
-            "hyp_pts_per_s": world * N_HYP * inp["n_px"] * args.steps / (ms_total * 1e-3),
+            "hyp_pts_per_s": world * N_HYP * inp["n_px"] * args.steps / (ms_clean * 1e-3),
+            "step_impl": "EvalSweep(lanes=2, free_running=True): each batch as two halves on two streams, joined once by "
+                         "finish() before the one table all-reduce; table identical to the single-stream step: "
+                         + str(same_lanes),
+            "instrumented": {"ms_per_step": ms_total / args.steps, "value": value_instr,
+                             "note": "the same K steps on one stream with CUDA events between the kernels (11 per step) -- "
+                                     "the pass kernel_ms / stage_ms / roofline.launch_ms are measured in"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": zc_bytes,
                     "d2h_bytes_per_step": tb_host.numel() * tb_host.element_size(),
                     "api": "HostEvalSweep.run(zero_copy='xyz'): per chunk the mask is staged by the copy engine while the "
@@ -422,7 +460,7 @@ def ours_arm(args):
                     "staged_copy_variant": {"value": staged_value, "unit": UNIT, "h2d_bytes_per_step": staged_bytes,
                                             "api": "HostEvalSweep.run(zero_copy=False): whole maps copied H2D in "
                                                    "128-frame chunks overlapped with compute"}},
-            "gpu_launches": args.steps * sw.launches_per_step,
+            "gpu_launches": args.steps * sw2.launches_per_step,
             "kernels_per_step": ["compact_sparse_kernel", "ransac_hypothesis_kernel", "ransac_score_bal_kernel",
                                  "ransac_finalize_kernel", "pose_metrics_kernel", "accumulate_kernel"],
             "stage_ms": dict(zip(sw.STAGES, stage_ms)),

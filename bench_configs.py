@@ -178,7 +178,8 @@ def c5(args, dev):
     inp = bench.build_inputs(torch, dev, 0, F)
     models = torch.from_numpy(synth.class_models(bench.N_MODEL))
     diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
-    sw = pb.EvalSweep(models, diam, sym, F, H, W, bench.CAP, ops.RansacConfig(n_hyp=bench.N_HYP, seed=bench.SEED), device=dev)
+    sw = pb.EvalSweep(models, diam, sym, F, H, W, bench.CAP, ops.RansacConfig(n_hyp=bench.N_HYP, seed=bench.SEED), device=dev,
+                      lanes=2, free_running=True)       # two half-chunks per chunk on two streams, joined by finish()
     assert (hi - lo) % F == 0, "shard must be a whole number of chunks"
 
     def sweep():

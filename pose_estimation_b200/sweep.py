@@ -61,8 +61,11 @@ class EvalSweep:
     STAGES = ("compact", "ransac", "metrics", "accumulate")
 
     def __init__(self, model_points, diameter, is_sym, F, H, W, cap, cfg: RansacConfig | None = None,
-                 device="cuda", add_frac=0.1, r_thr_deg=5.0, t_thr_m=0.05, lanes=1):
-        """lanes > 1: the batch is cut into ``lanes`` contiguous parts that run on their own streams, so the
+                 device="cuda", add_frac=0.1, r_thr_deg=5.0, t_thr_m=0.05, lanes=1, free_running=False):
+        """free_running (with lanes > 1): ``step`` does not join the lanes back into the caller's stream, so lane A's
+        kernels of batch i+1 follow its batch i at once while lane B is still on batch i; the join happens in
+        ``finish`` / ``table`` / ``reset`` / ``join`` -- the per-frame tensors ``step`` returns are valid only after it.
+        lanes > 1: the batch is cut into ``lanes`` contiguous parts that run on their own streams, so the
         HBM-bound K0 of one part overlaps the FP32-bound scoring and the latency-bound refit of another
         (results are identical: frames are independent and the per-lane tables are summed)."""
         dev = torch.device(device)
@@ -75,6 +78,8 @@ class EvalSweep:
         self.n_cls = self.model.shape[0]
         self.add_frac, self.r_thr_deg, self.t_thr_m = add_frac, r_thr_deg, t_thr_m
         self.lanes = []
+        self.free_running = bool(free_running) and lanes > 1
+        self._unjoined = False
         if lanes > 1:
             if F % lanes:
                 raise ValueError("F must be a multiple of lanes")
@@ -93,14 +98,24 @@ class EvalSweep:
 
     def reset(self):
         """Zero the accuracy table(s)."""
+        self.join()
         for l in self.lanes:
             l.reset()
         if not self.lanes:
             self._table.zero_()
 
+    def join(self):
+        """Make the caller's stream wait for everything the lanes have been given (no-op without pending work)."""
+        if self._unjoined:
+            main = torch.cuda.current_stream(self.dev)
+            for e in self.ev_out:
+                main.wait_event(e)
+            self._unjoined = False
+
     @property
     def table(self):
         if self.lanes:
+            self.join()
             t = self.lanes[0].table.clone()
             for l in self.lanes[1:]:
                 t += l.table
@@ -131,8 +146,9 @@ class EvalSweep:
                               pred_t=None if pred_t is None else pred_t[lo:hi],
                               cloud=None if cloud is None else cloud[lo:hi], t_res=None if t_res is None else t_res[lo:hi])
                     self.ev_out[k].record(s)
-            for e in self.ev_out:
-                main.wait_event(e)
+            self._unjoined = True
+            if not self.free_running:
+                self.join()
             return self.out[0], self.out[1], self.out[2]
 
         def mark():

@@ -254,3 +254,27 @@ def test_eval_sweep_opt_pose_variants(dev):
     R, _ = pb.get_pose({"xyz": pred["xyz"]}, data)
     a, _, _ = pb.cal_dis(metric, R, pb.vote_translation(cloud[:1], t_res[:1]).cpu(), data)
     assert abs(a - float(sw.last_reg[0][0])) <= 1e-5 * max(a, 1e-6) + 1e-7
+
+
+def test_eval_sweep_free_running_lanes_equal_single_stream(dev):
+    """EvalSweep(lanes=2, free_running=True): batches follow each other on each lane without a join; the table after
+    finish() and the per-frame outputs after join() equal the single-stream ones, also across reset()."""
+    F = 16
+    sps = synth.make_batch_sparse(0x5EED, 2, F)
+    b = batch_arrays(sps)
+    models = torch.from_numpy(synth.class_models(500))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    t = lambda a: torch.from_numpy(a).to(dev)
+    args = [t(b[k]) for k in ("xyz", "mask", "extent", "lfborder", "K4", "cls", "R_gt", "t_gt")]
+    sw1 = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev)
+    for k in range(3):
+        out1 = [x.clone() for x in sw1.step(*args, frame0=k * F)]
+    want = sw1.finish().clone()
+    sw2 = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev, lanes=2, free_running=True)
+    for rep in range(2):
+        sw2.reset()
+        for k in range(3):
+            out2 = sw2.step(*args, frame0=k * F)
+        sw2.join()
+        assert all(torch.equal(a, c) for a, c in zip(out1, out2)), rep
+        assert torch.equal(sw2.finish(), want), rep

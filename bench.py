@@ -10,7 +10,7 @@ steps closed by the ONE all-reduce of the [24,13] accuracy table that the path h
 weak scaling: every rank evaluates its own 1024-frame shard per step).
 
   value     whole-job frames/s with the maps already resident in HBM (CUDA events, max over ranks): K steps of
-            EvalSweep(lanes=2, free_running=True) -- each batch as two halves on two streams, joined once by
+            EvalSweep(lanes=3, deal="alternate") -- whole batches dealt in turn to three streams, joined once by
             finish() -- with no events inside the region; `instrumented` is the same K steps on one stream with
             events between the kernels, the pass the per-kernel times and the roofline come from
   e2e       the same pass through HostEvalSweep.run with PINNED HOST inputs, timed per step: the
@@ -289,12 +289,13 @@ def ours_arm(args):
     lib.pb_stage_timing_read(ms3, C.byref(ncalls))
     lib.pb_stage_timing(0)
     hyp_ms, score_ms, final_ms = float(ms3[0]), float(ms3[1]), float(ms3[2])
-    # ---- the same sweep as the product runs it: every batch cut in two halves that run on their own streams and
-    # are not joined between batches (EvalSweep(lanes=2, free_running=True)), so the HBM-bound K0 of one half overlaps
-    # the FP32-bound scoring / latency-bound refit of the other and no stream waits at a batch boundary; joined once
-    # by finish().  No events inside this region: `value` is this clean pass, the per-kernel times above come from
-    # the instrumented single-stream pass (same K steps, same inputs, same process).
-    sw2 = pb.EvalSweep(models, diam, sym, F, H, W, CAP, cfg, device=dev, lanes=2, free_running=True)
+    # ---- the same sweep as the product runs it: whole batches dealt in turn to three streams that are not joined
+    # between batches (EvalSweep(lanes=3, deal="alternate")), so every kernel keeps its full-size single-wave grid and
+    # batch i+1's HBM-bound K0 runs under batch i's FP32-bound scoring / latency-bound refit; joined once by finish().
+    # No events inside this region: `value` is this clean pass, the per-kernel times above come from the instrumented
+    # single-stream pass (same K steps, same inputs, same process).
+    n_lanes = int(os.environ.get("PB_LANES", "3"))
+    sw2 = pb.EvalSweep(models, diam, sym, F, H, W, CAP, cfg, device=dev, lanes=n_lanes, deal="alternate")
 
     def lane_step():
         sw2.step(inp["xyz"], inp["mask"], inp["extent"], inp["lfborder"], inp["K4"], inp["cls"], inp["R_gt"],
@@ -444,9 +445,9 @@ def ours_arm(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(world),
             "hyp_pts_per_s": world * N_HYP * inp["n_px"] * args.steps / (ms_clean * 1e-3),
-            "step_impl": "EvalSweep(lanes=2, free_running=True): each batch as two halves on two streams, joined once by "
-                         "finish() before the one table all-reduce; table identical to the single-stream step: "
-                         + str(same_lanes),
+            "step_impl": f"EvalSweep(lanes={n_lanes}, deal='alternate'): whole batches dealt in turn to {n_lanes} streams, "
+                         "joined once by finish() before the one table all-reduce; table identical to the single-stream "
+                         "step: " + str(same_lanes),
             "instrumented": {"ms_per_step": ms_total / args.steps, "value": value_instr,
                              "note": "the same K steps on one stream with CUDA events between the kernels (11 per step) -- "
                                      "the pass kernel_ms / stage_ms / roofline.launch_ms are measured in"},

@@ -179,7 +179,7 @@ def c5(args, dev):
     models = torch.from_numpy(synth.class_models(bench.N_MODEL))
     diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
     sw = pb.EvalSweep(models, diam, sym, F, H, W, bench.CAP, ops.RansacConfig(n_hyp=bench.N_HYP, seed=bench.SEED), device=dev,
-                      lanes=2, free_running=True)       # two half-chunks per chunk on two streams, joined by finish()
+                      lanes=3, deal="alternate")        # whole chunks dealt in turn to three streams, joined by finish()
     assert (hi - lo) % F == 0, "shard must be a whole number of chunks"
 
     def sweep():

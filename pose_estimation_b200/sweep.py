@@ -61,8 +61,11 @@ class EvalSweep:
     STAGES = ("compact", "ransac", "metrics", "accumulate")
 
     def __init__(self, model_points, diameter, is_sym, F, H, W, cap, cfg: RansacConfig | None = None,
-                 device="cuda", add_frac=0.1, r_thr_deg=5.0, t_thr_m=0.05, lanes=1, free_running=False):
-        """free_running (with lanes > 1): ``step`` does not join the lanes back into the caller's stream, so lane A's
+                 device="cuda", add_frac=0.1, r_thr_deg=5.0, t_thr_m=0.05, lanes=1, free_running=False, deal="split"):
+        """deal="alternate" (with lanes > 1; implies free_running): batches are not cut at all -- whole batches are dealt
+        to the lanes in turn, so every kernel keeps its full-size, single-wave grid and batch i+1's K0 (HBM) runs under
+        batch i's scoring / refit (FP32, latency) on another stream.  The fastest form for a sweep of many batches.
+        free_running (with lanes > 1): ``step`` does not join the lanes back into the caller's stream, so lane A's
         kernels of batch i+1 follow its batch i at once while lane B is still on batch i; the join happens in
         ``finish`` / ``table`` / ``reset`` / ``join`` -- the per-frame tensors ``step`` returns are valid only after it.
         lanes > 1: the batch is cut into ``lanes`` contiguous parts that run on their own streams, so the
@@ -78,18 +81,24 @@ class EvalSweep:
         self.n_cls = self.model.shape[0]
         self.add_frac, self.r_thr_deg, self.t_thr_m = add_frac, r_thr_deg, t_thr_m
         self.lanes = []
-        self.free_running = bool(free_running) and lanes > 1
+        if deal not in ("split", "alternate"):
+            raise ValueError("deal must be 'split' or 'alternate'")
+        self.alternate = deal == "alternate" and lanes > 1
+        self.free_running = (bool(free_running) or self.alternate) and lanes > 1
         self._unjoined = False
+        self._turn = 0
         if lanes > 1:
-            if F % lanes:
+            if F % lanes and not self.alternate:
                 raise ValueError("F must be a multiple of lanes")
-            self.lanes = [EvalSweep(self.model, self.diameter, self.is_sym, F // lanes, H, W, cap, self.cfg, dev,
+            Fl = F if self.alternate else F // lanes
+            self.lanes = [EvalSweep(self.model, self.diameter, self.is_sym, Fl, H, W, cap, self.cfg, dev,
                                     add_frac, r_thr_deg, t_thr_m) for _ in range(lanes)]
             self.lane_streams = [torch.cuda.Stream(device=dev) for _ in range(lanes)]
             self.ev_in = torch.cuda.Event()
             self.ev_out = [torch.cuda.Event() for _ in range(lanes)]
-            self.out = torch.empty((3, F), dtype=torch.float32, device=dev)
-            self.launches_per_step = sum(l.launches_per_step for l in self.lanes)
+            self.out = torch.empty((lanes if self.alternate else 1, 3, F), dtype=torch.float32, device=dev)
+            self.launches_per_step = self.lanes[0].launches_per_step if self.alternate else \
+                sum(l.launches_per_step for l in self.lanes)
             return
         self.compact = ops.MapCompactor(F, H, W, cap, device=dev)
         self.ransac = ops.PtsRansac(F, cap, self.cfg, device=dev)
@@ -134,6 +143,17 @@ class EvalSweep:
         if self.lanes:
             main = torch.cuda.current_stream(self.dev)
             self.ev_in.record(main)
+            if self.alternate:
+                k = self._turn % len(self.lanes)
+                self._turn += 1
+                s = self.lane_streams[k]
+                s.wait_event(self.ev_in)
+                with torch.cuda.stream(s):
+                    self.lanes[k].step(xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=frame0, roi=roi,
+                                       out=tuple(self.out[k, j] for j in range(3)), pred_t=pred_t, cloud=cloud, t_res=t_res)
+                    self.ev_out[k].record(s)
+                self._unjoined = True
+                return self.out[k, 0], self.out[k, 1], self.out[k, 2]
             Fl = self.F // len(self.lanes)
             for k, lane in enumerate(self.lanes):
                 s = self.lane_streams[k]
@@ -142,14 +162,14 @@ class EvalSweep:
                 with torch.cuda.stream(s):
                     lane.step(xyz[lo:hi], None if mask is None else mask[lo:hi], extent[lo:hi], lfborder[lo:hi],
                               K4[lo:hi], cls[lo:hi], R_gt[lo:hi], t_gt[lo:hi], frame0=frame0 + lo,
-                              roi=None if roi is None else roi[lo:hi], out=tuple(self.out[j, lo:hi] for j in range(3)),
+                              roi=None if roi is None else roi[lo:hi], out=tuple(self.out[0, j, lo:hi] for j in range(3)),
                               pred_t=None if pred_t is None else pred_t[lo:hi],
                               cloud=None if cloud is None else cloud[lo:hi], t_res=None if t_res is None else t_res[lo:hi])
                     self.ev_out[k].record(s)
             self._unjoined = True
             if not self.free_running:
                 self.join()
-            return self.out[0], self.out[1], self.out[2]
+            return self.out[0, 0], self.out[0, 1], self.out[0, 2]
 
         def mark():
             if events is None:

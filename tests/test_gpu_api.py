@@ -278,3 +278,11 @@ def test_eval_sweep_free_running_lanes_equal_single_stream(dev):
         sw2.join()
         assert all(torch.equal(a, c) for a, c in zip(out1, out2)), rep
         assert torch.equal(sw2.finish(), want), rep
+    # whole batches dealt in turn to three streams
+    sw3 = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev, lanes=3, deal="alternate")
+    for rep in range(2):
+        sw3.reset()
+        outs = [sw3.step(*args, frame0=k * F) for k in range(3)]
+        sw3.join()
+        assert all(torch.equal(a, c) for a, c in zip(out1, outs[2])), rep
+        assert torch.equal(sw3.finish(), want), rep

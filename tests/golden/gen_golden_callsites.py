@@ -195,6 +195,15 @@ def main():
     out["auc_in"] = d
     out["auc_out"] = np.float64(M.cal_auc(list(d)))
     out["auc_none"] = np.float64(M.cal_auc([0.5, 0.7]))
+    # more AUC cases: ties, values on the 0.1 border, a single sample, mostly-out-of-range lists
+    rng_auc = np.random.default_rng(77)                      # its own stream: the vectors made after this keep their inputs
+    cases = [np.array([0.01, 0.01, 0.02, 0.02, 0.02, 0.09]), np.array([0.1, 0.1, 0.05]), np.array([0.03]),
+             np.concatenate([np.full(50, 0.5), np.abs(rng_auc.normal(0.02, 0.01, 10))]),
+             np.sort(rng_auc.random(500) * 0.2)[::-1].copy()]
+    for k, c in enumerate(cases):
+        out[f"auc_case{k}_in"] = c
+        out[f"auc_case{k}_out"] = np.float64(M.cal_auc(list(c)))
+    out["auc_ncases"] = np.int32(len(cases))
 
     # ---- utlis.py
     K4 = torch.tensor([[572.4114, 573.57043, 325.2611, 242.04899], [700.0, 700.0, 320.0, 240.0]])

@@ -353,3 +353,16 @@ def test_ref_callsites_region_maps_match_reference_run():
         soft = rc.get_xyz(g["reg_xyz_off"][f], g["reg_logits"][f], g["reg_points"][f])
         assert np.abs(soft - g["reg_soft"][f]).max() <= 1e-7
     assert np.array_equal(g["reg_hard"][0][:, 3, 4], g["reg_xyz_off"][0][:, 3, 4] + g["reg_points"][0][7])   # tie -> class 7
+
+
+def test_auc_of_oracle_and_product_match_reference_run():
+    """lib/utils/metric.py:38-65 run here on ties, border values, a single sample, mostly-out-of-range and unsorted
+    lists: the restatement and the product's host-side Metric.cal_auc (pure numpy, no GPU involved) give the same AUC."""
+    from pose_estimation_b200.api import Metric as ProductMetric
+    g = _callsites()
+    for k in range(int(g["auc_ncases"])):
+        d, want = list(g[f"auc_case{k}_in"]), float(g[f"auc_case{k}_out"])
+        assert abs(rc.Metric([]).cal_auc(d) - want) < 1e-9, k
+        assert abs(ProductMetric([]).cal_auc(d) - want) < 1e-9, k
+    assert abs(ProductMetric([]).cal_auc(list(g["auc_in"])) - float(g["auc_out"])) < 1e-9
+    assert ProductMetric([]).cal_auc([0.5, 0.7]) == 0

@@ -238,7 +238,9 @@ int pb_pose_metrics(const float* R, const float* t, const float* R_gt, const flo
                     void* stream);
 
 /* success tests + per-object accumulation (tools/trainer.py:156-157,174-221): table [24,C] doubles
- * += this batch (deterministic, one CTA per class).  add < add_frac*diameter[c], r < r_thr, t < t_thr. */
+ * += this batch (deterministic, one CTA per class).  add < add_frac*diameter[c], r < r_thr, t < t_thr.
+ * A class index outside [0,C) is clamped into range by pb_pose_metrics AND here (same column in both), and the
+ * frame is counted in PB_ROW_FAILED, so all_num always sums to the number of frames seen.                  */
 int pb_accumulate_results(const float* add, const float* r_deg, const float* t_m, const int32_t* cls,
                           const int32_t* status, const float* diameter, int F, int C, int variant,
                           float add_frac, float r_thr_deg, float t_thr_m, int count_frames,

@@ -578,8 +578,16 @@ int ref_ransac_frame(const float* X, const float* Y, const float* Z, const float
         make_proj(K4, Rq, tt, Mq);
         nref = ref_score(Mq, X, Y, Z, U, V, P, inv_thr, bm);
     }
-    quat_to_rot(q, R);
-    t[0] = tt[0]; t[1] = tt[1]; t[2] = tt[2];
+    /* a refit that lost its consensus (fewer than half of the minimal hypothesis' inliers, or fewer than
+       min_inliers, under the refitted pose) is discarded: the minimal hypothesis is returned instead */
+    int need = (bc + 1) / 2 > prm->min_inliers ? (bc + 1) / 2 : prm->min_inliers;
+    if (nref < need) {
+        memcpy(R, bR, sizeof(bR)); t[0] = bt[0]; t[1] = bt[1]; t[2] = bt[2];
+        nref = bc;
+    } else {
+        quat_to_rot(q, R);
+        t[0] = tt[0]; t[1] = tt[1]; t[2] = tt[2];
+    }
     *n_inl_refined = nref;
     free(bm);
     return 0;

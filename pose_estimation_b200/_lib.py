@@ -98,8 +98,19 @@ def load() -> C.CDLL:
 
 
 def call(name: str, *args):
-    """Call an int-returning ABI function and raise on a non-zero return code."""
+    """Call an int-returning ABI function and raise on a non-zero return code.  When the last argument is a stream
+    made by ``ops._stream`` for a device other than the current one, that device is made current around the call
+    (a CUDA launch goes to the calling thread's current device, whatever device its pointers live on)."""
     lib = load()
+    idx = getattr(args[-1], "device_index", None) if args else None
+    if idx is not None:
+        import torch
+        if idx != torch.cuda.current_device():
+            with torch.cuda.device(idx):
+                rc = getattr(lib, name)(*args)
+            if rc != 0:
+                raise PoseB200Error(f"{name} failed ({rc}): {lib.pb_last_error().decode(errors='replace')}")
+            return rc
     rc = getattr(lib, name)(*args)
     if rc != 0:
         raise PoseB200Error(f"{name} failed ({rc}): {lib.pb_last_error().decode(errors='replace')}")

@@ -6,17 +6,24 @@
 //
 //   scores   s~_ij = |q_j|^2 - 2 p_i.q_j  with p = x - c, q = y - c (c = centre of y's bounding box);
 //            it differs from |x_i - y_j|^2 by the row constant |p_i|^2, which does not change the argmin.
-//   operands every FP32 coordinate is split EXACTLY into three bf16 (8+8+8 mantissa bits); a K = 32
-//            row carries the 27 cross products of the three coordinates plus |q|^2 (three bf16),
-//            so two K=16 tcgen05.mma (kind::f16, M=128, N=128, FP32 accumulate in TMEM) give s~ to
-//            within E ~ 1e-5 R^2 (R = cloud radius), dominated by the accumulation, not by bf16.
-//   epilogue two threads per query row (64 columns of the tile each) read their scores with
-//            tcgen05.ld (32x32b.x32), reduce each chunk of 32 with 3-input minima (FMNMX3, 0.56 ALU
-//            op per pair) and only when a group of 8 dips below  running-min + T  (T = 2^-13 R^2 >> 2E)
-//            look at single columns; those candidates go to a short per-thread list in shared memory.
-//   re-rank  after the sweep the candidates within T of the final minimum (a provable superset of
-//            the FP32 argmin) are re-evaluated with the exact FP32 formula; rows whose list
-//            overflowed fall back to an exact scan.
+//   operands every centred coordinate is split into TWO bf16, v ~ h + m (h = bf16(v), m = bf16(v - h):
+//            |v - (h + m)| <= 2^-16 |v|).  One K = 16 row per point: query rows carry (h,h,m,m) of -2p per
+//            coordinate and 1,1,1,0; database rows (h,m,h,m) of q per coordinate and |q|^2 as three bf16
+//            (24 bits) and 0 -- the twelve products are the four cross terms of every coordinate.  ONE
+//            tcgen05.mma (kind::f16, M = 128, N = 128, K = 16, FP32 accumulate in TMEM) per 128 x 128 scores.
+//   error    per coordinate |(-2p)(q) - (-2p)^(q)^| <= 2|p_c| 2^-16 |q_c| + |q_c| 2^-15 |p_c| = 2^-14 |p_c||q_c|,
+//            so over the three coordinates <= 2^-14 |p||q| <= 2^-14 R^2 (R = largest centred norm of either
+//            cloud, measured by the prepare kernel); |q|^2 adds 2^-24 R^2 and the FP32 accumulation of the 15
+//            terms (each partial sum <= 3 R^2) at most 2^-18.4 R^2:  E <= 1.06 * 2^-14 R^2 in the worst case
+//            (every rounding at half an ulp, all with the same sign, |p| = |q| = R, p parallel to q).
+//   band     T = 2^-12 R^2 = 3.8 E > 2 E: the true FP32 argmin (and every tie) has a score within 2E < T of
+//            the smallest score of its row, so it lies in a column group whose minimum is below  row minimum + T.
+//   epilogue two epilogue warpgroups, each bound to one TMEM accumulator (thread = query row); per 32-column
+//            chunk tcgen05.ld (32x32b.x32) and 3-input minima (FMNMX3) give the minima of the four 8-column
+//            groups; a chunk whose minimum is below  running minimum + T  keeps a slot of a 7-deep ring.
+//   re-rank  after the sweep every remembered group within T of the final row minimum is re-evaluated with
+//            the SIMT kernel's exact FP32 formula (lowest index on ties); a row whose ring dropped a chunk
+//            that could matter, a barrier timeout or non-finite input falls back to an exact scan.
 // The MMA of tile n+1 and the bulk copy (1-D TMA) of tile n+2 overlap the epilogue of tile n.
 #include <cuda_bf16.h>
 #include "common.cuh"
@@ -27,7 +34,7 @@ namespace {
 constexpr int TM = 128;              // rows / columns per operand tile
 constexpr int TILE_U4 = 2 * TM;      // uint4 per operand tile: [kc 0..1][row][8 bf16] = 4 KB (K = 16)
 constexpr int TILE_BYTES = TILE_U4 * 16;
-constexpr float TC_TOL_REL = 1.0f / 8192.0f;   // T = 2^-13 * R^2
+constexpr float TC_TOL_REL = 1.0f / 4096.0f;   // T = 2^-12 * R^2 (see the error bound above)
 
 struct Split3 { __nv_bfloat16 h, m, l; };
 __device__ __forceinline__ Split3 split3(float v) {
@@ -333,7 +340,7 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
         const int row = rt * TM + rloc;
         float4* lgrp = lgrp_all + tid;
         int* lid = lid_all + tid;
-        const float T = a.tol[bl] * TC_TOL_REL;         // T = 2^-13 R^2
+        const float T = a.tol[bl] * TC_TOL_REL;         // T = 2^-12 R^2
         const float* xb = a.x + (size_t)b * a.N * 3;
         const float* yb = a.y + (a.y_shared ? 0 : (size_t)b * a.M * 3);
         float qx = 0.0f, qy = 0.0f, qz = 0.0f;

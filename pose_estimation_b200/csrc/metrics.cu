@@ -125,7 +125,11 @@ __global__ void __launch_bounds__(256) accumulate_kernel(const float* __restrict
     const float thr_add = add_frac * diameter[c];
     double v[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // n, succ_rt, dis_rt, succ_r, dis_r, succ_t, dis_t, failed
     for (int f = threadIdx.x; f < F; f += 256) {
-        if (cls[f] != c) continue;
+        // an out-of-range class index is clamped exactly as pose_metrics_kernel clamps it (the frame was measured
+        // against that class' model) and the frame is counted in the `failed` row: every frame lands in one column
+        const int cf = cls[f];
+        const int cc = cf < 0 ? 0 : (cf >= C ? C - 1 : cf);
+        if (cc != c) continue;
         const float a = add[f], r = r_deg[f], tt = t_m[f];
         v[0] += 1.0;
         v[1] += (a < thr_add) ? 1.0 : 0.0;
@@ -134,7 +138,7 @@ __global__ void __launch_bounds__(256) accumulate_kernel(const float* __restrict
         v[4] += (double)r;
         v[5] += (tt < t_thr) ? 1.0 : 0.0;
         v[6] += (double)tt;
-        v[7] += (status && status[f] != 0) ? 1.0 : 0.0;
+        v[7] += ((status && status[f] != 0) || cf != cc) ? 1.0 : 0.0;
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) v[k] = warp_sum_d(v[k]);

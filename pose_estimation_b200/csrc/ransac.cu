@@ -323,8 +323,17 @@ __global__ void __launch_bounds__(32 * G) ransac_finalize_kernel(FinalArgs a) {
         }
         __syncthreads();
     }
+    // a refit that lost its consensus (fewer than half of the minimal hypothesis' inliers, or fewer than
+    // min_inliers, under the refitted pose) is discarded: the minimal hypothesis is returned instead (uniform)
     float R[9];
-    quat_to_rot(q, R);
+    if (nref < max((bc + 1) >> 1, a.min_inliers)) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) R[k] = Rb[k];
+        tt[0] = tb[0]; tt[1] = tb[1]; tt[2] = tb[2];
+        nref = bc;
+    } else {
+        quat_to_rot(q, R);
+    }
     for (int k = tid; k < 9; k += NT) a.R[9 * f + k] = R[k];
     if (tid < 3) a.t[3 * f + tid] = tt[tid];
     if (tid == 0) { a.n_inl[f] = bc; a.best_hyp[f] = bh; a.n_inl_refined[f] = nref; a.status[f] = PB_STATUS_OK; }

@@ -1,7 +1,7 @@
 """Tensor-level wrappers over the C ABI: torch owns device memory and the stream, nothing else.
 
 Every function takes CUDA tensors, allocates its outputs / workspace with torch, and launches the
-sm_100a kernels asynchronously on ``torch.cuda.current_stream()``.  No host synchronisation
+sm_100a kernels asynchronously on the current stream of the tensors' device.  No host synchronisation
 happens here.  CPU tensors are rejected: there is no fallback implementation.
 """
 from __future__ import annotations
@@ -31,8 +31,20 @@ class RansacConfig:
                             self.seed & 0xFFFFFFFF, (self.seed >> 32) & 0xFFFFFFFF)
 
 
-def _stream():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+class _StreamArg(C.c_void_p):
+    """The stream argument of an ABI call plus the device it belongs to (``_lib.call`` makes that device current
+    for the duration of the call when it is not)."""
+    device_index = None
+
+
+def _stream(ref):
+    """Current stream of the device ``ref`` (a CUDA tensor the call writes) lives on -- not of whatever device
+    happens to be current: EvalSweep / MapCompactor / PtsRansac accept ``device=`` without a prior set_device."""
+    if not ref.is_cuda:
+        raise _lib.PoseB200Error("stream reference must be a CUDA tensor (pose_estimation_b200 has no CPU path)")
+    s = _StreamArg(torch.cuda.current_stream(ref.device).cuda_stream)
+    s.device_index = ref.device.index
+    return s
 
 
 def _ptr(t):
@@ -71,7 +83,7 @@ def compact_map(xyz, mask, extent, lfborder, cap, roi=None, want_total=False):
     nb = _lib.load().pb_compact_workspace_bytes(F, H, W, cap)
     ws = _ws(nb, dev)
     call("pb_compact_map", _ptr(xyz), _ptr(mask), _ptr(roi), _ptr(extent), _ptr(lfborder), F, H, W, cap,
-         _ptr(pts), _ptr(count), _ptr(total), _ptr(ws), ws.numel(), _stream())
+         _ptr(pts), _ptr(count), _ptr(total), _ptr(ws), ws.numel(), _stream(pts))
     return (pts, count, total) if want_total else (pts, count)
 
 
@@ -88,7 +100,7 @@ def gather_correspondences(xyz, choose, xmap, ymap, extent, lfborder, cap=None):
     pts = torch.empty((F, 5, cap), dtype=torch.float32, device=xyz.device)
     count = torch.empty((F,), dtype=torch.int32, device=xyz.device)
     call("pb_gather_correspondences", _ptr(xyz), _ptr(choose), _ptr(xmap), _ptr(ymap), _ptr(extent),
-         _ptr(lfborder), F, H, W, NP, cap, _ptr(pts), _ptr(count), _stream())
+         _ptr(lfborder), F, H, W, NP, cap, _ptr(pts), _ptr(count), _stream(pts))
     return pts, count
 
 
@@ -118,7 +130,7 @@ def region_decode_points(pts, count, xyz_off, region, region_point, extent, lfbo
     cap = pts.shape[-1]
     NP = 0 if choose is None else choose.shape[-1]
     call("pb_region_decode_points", _ptr(xyz_off), _ptr(region), _ptr(region_point), _ptr(choose), NP, _ptr(roi),
-         _ptr(extent), _ptr(lfborder), F, H, W, n, cap, _region_mode(mode), _ptr(pts), _ptr(count), _stream())
+         _ptr(extent), _ptr(lfborder), F, H, W, n, cap, _region_mode(mode), _ptr(pts), _ptr(count), _stream(pts))
     return pts
 
 
@@ -134,7 +146,7 @@ def region_decode_map(xyz_off, region, region_point, mode="soft"):
         raise ValueError("region must be [F,n,H,W] and region_point [F,n,3]")
     out = torch.empty_like(xyz_off)
     call("pb_region_decode_map", _ptr(xyz_off), _ptr(region), _ptr(region_point), F, H, W, n, _region_mode(mode),
-         _ptr(out), _stream())
+         _ptr(out), _stream(out))
     return out
 
 
@@ -164,7 +176,7 @@ def pnp_ransac_pts(pts, count, K4, cfg: RansacConfig | None = None, frame0=0, sa
     ws = _ws(nb, dev)
     call("pb_pnp_ransac_pts", _ptr(pts), _ptr(count), _ptr(K4), F, cap, frame0, C.byref(prm), _ptr(sample_idx),
          _ptr(out["R"]), _ptr(out["t"]), _ptr(out["n_inl"]), _ptr(out["best_hyp"]), _ptr(out["n_inl_refined"]),
-         _ptr(out["status"]), _ptr(hc), _ptr(bm), _ptr(R0), _ptr(t0), _ptr(ws), ws.numel(), _stream())
+         _ptr(out["status"]), _ptr(hc), _ptr(bm), _ptr(R0), _ptr(t0), _ptr(ws), ws.numel(), _stream(out["R"]))
     if want_counts:
         out["hyp_counts"] = hc
     if want_bitmap:
@@ -204,7 +216,7 @@ class MapCompactor:
                                  or not mask.is_contiguous()):
             raise ValueError("mask must be a contiguous uint8 [F,H,W] tensor")
         call("pb_compact_map", _ptr(xyz), _ptr(mask), _ptr(roi), _ptr(extent), _ptr(lfborder), self.F, self.H,
-             self.W, self.cap, _ptr(self.pts), _ptr(self.count), None, _ptr(self.ws), self.ws.numel(), _stream())
+             self.W, self.cap, _ptr(self.pts), _ptr(self.count), None, _ptr(self.ws), self.ws.numel(), _stream(self.pts))
         return self.pts, self.count
 
 
@@ -229,7 +241,7 @@ class PtsRansac:
     def __call__(self, pts, count, K4, frame0=0):
         call("pb_pnp_ransac_pts", _ptr(pts), _ptr(count), _ptr(K4), self.F, self.cap, frame0, C.byref(self.prm),
              None, _ptr(self.R), _ptr(self.t), _ptr(self.n_inl), _ptr(self.best_hyp), _ptr(self.n_inl_refined),
-             _ptr(self.status), None, None, None, None, _ptr(self.ws), self.ws.numel(), _stream())
+             _ptr(self.status), None, None, None, None, _ptr(self.ws), self.ws.numel(), _stream(self.R))
         return self
 
 
@@ -254,7 +266,7 @@ class MapRansac:
         call("pb_pnp_ransac_map", _ptr(xyz), _ptr(mask), _ptr(roi), _ptr(extent), _ptr(lfborder), _ptr(K4),
              self.F, self.H, self.W, self.cap, frame0, C.byref(self.prm), _ptr(self.R), _ptr(self.t),
              _ptr(self.n_inl), _ptr(self.best_hyp), _ptr(self.n_inl_refined), _ptr(self.status),
-             _ptr(self.ws), self.ws.numel(), _stream())
+             _ptr(self.ws), self.ws.numel(), _stream(self.R))
         return self
 
 
@@ -264,5 +276,5 @@ def resample_inliers(inl_bitmap, count, cap, n, seed=0x5EED, frame0=0):
     F = count.shape[0]
     out = torch.empty((F, n), dtype=torch.int32, device=count.device)
     call("pb_resample_inliers", _ptr(inl_bitmap), _ptr(count), F, cap, n, frame0, seed & 0xFFFFFFFF,
-         (seed >> 32) & 0xFFFFFFFF, _ptr(out), _stream())
+         (seed >> 32) & 0xFFFFFFFF, _ptr(out), _stream(out))
     return out

@@ -44,7 +44,7 @@ def pnp_refine(pts2d, pts3d, K, pose6_init=None, R_init=None, t_init=None, max_i
     status = torch.empty((B,), dtype=torch.int32, device=dev)
     rmse = torch.empty((B,), dtype=torch.float32, device=dev) if want_rmse else None
     call("pb_pnp_refine", _ptr(pts2d), _ptr(pts3d), batched, _ptr(K), _ptr(pose6_init), _ptr(R_init), _ptr(t_init), B, n,
-         int(max_iter), _ptr(pose), _ptr(rmse), _ptr(status), _stream())
+         int(max_iter), _ptr(pose), _ptr(rmse), _ptr(status), _stream(pose))
     return (pose, status, rmse) if want_rmse else (pose, status)
 
 
@@ -64,7 +64,7 @@ def bpnp_backward(pts2d, pts3d, K, pose6, grad_out):
     nb = _lib.load().pb_bpnp_backward_workspace_bytes(B, n)
     ws = torch.empty(((nb + 7) // 8,), dtype=torch.float64, device=dev)
     call("pb_bpnp_backward", _ptr(pts2d), _ptr(pts3d), batched, _ptr(K), _ptr(pose6), _ptr(grad_out), B, n, _ptr(gx),
-         _ptr(gz), _ptr(gK), _ptr(status), _ptr(ws), ws.numel() * 8, _stream())
+         _ptr(gz), _ptr(gK), _ptr(status), _ptr(ws), ws.numel() * 8, _stream(gx))
     return gx, gz, gK, status
 
 

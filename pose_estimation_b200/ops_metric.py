@@ -49,11 +49,11 @@ def knn1(x, y, want_d2=False, impl="auto"):
         off = (-ws.data_ptr()) % 128
         import ctypes as C
         call("pb_knn1_tc", _ptr(x), _ptr(y), B, N, M, y_shared, _ptr(idx), _ptr(d2),
-             C.c_void_p(ws.data_ptr() + off), nb, _stream())
+             C.c_void_p(ws.data_ptr() + off), nb, _stream(idx))
         global LAST_TC_STATS
         LAST_TC_STATS = ws[off: off + 16].view(torch.int32)       # the workspace starts with int stats[4]
     else:
-        call("pb_knn1", _ptr(x), _ptr(y), B, N, M, y_shared, _ptr(idx), _ptr(d2), _stream())
+        call("pb_knn1", _ptr(x), _ptr(y), B, N, M, y_shared, _ptr(idx), _ptr(d2), _stream(idx))
     if squeeze:
         idx = idx[0]
         d2 = d2[0] if want_d2 else None
@@ -95,11 +95,11 @@ def add_adds(pred, target, want_adds=None, impl="auto"):
         nb = _lib.load().pb_add_adds_tc_workspace_bytes(B, N)
         ws, off, wptr = _aligned_ws(nb, pred.device)
         call("pb_add_adds_tc", _ptr(pred), _ptr(target), B, N, _ptr(want_adds), _ptr(lst), n, _ptr(add), _ptr(adds),
-             wptr, nb, _stream())
+             wptr, nb, _stream(add))
         d2b = (B * N * 4 + 127) // 128 * 128
         LAST_TC_STATS = ws[off + d2b: off + d2b + 16].view(torch.int32)
     else:
-        call("pb_add_adds", _ptr(pred), _ptr(target), B, N, _ptr(want_adds), _ptr(add), _ptr(adds), _stream())
+        call("pb_add_adds", _ptr(pred), _ptr(target), B, N, _ptr(want_adds), _ptr(add), _ptr(adds), _stream(add))
     return add, adds
 
 
@@ -112,7 +112,7 @@ def transform_points(model, R, t):
     shared = 1 if model.dim() == 2 else 0
     N = model.shape[-2]
     out = torch.empty((B, N, 3), dtype=torch.float32, device=R.device)
-    call("pb_transform_points", _ptr(model), shared, _ptr(R), _ptr(t), B, N, _ptr(out), _stream())
+    call("pb_transform_points", _ptr(model), shared, _ptr(R), _ptr(t), B, N, _ptr(out), _stream(out))
     return out
 
 
@@ -135,7 +135,7 @@ def pose_metrics(R, t, R_gt, t_gt, model, cls, is_sym, target=None, out=None):
         r_deg = torch.empty((F,), dtype=torch.float32, device=dev)
         t_m = torch.empty((F,), dtype=torch.float32, device=dev)
     call("pb_pose_metrics", _ptr(R), _ptr(t), _ptr(R_gt), _ptr(t_gt), _ptr(model), _ptr(target), _ptr(cls),
-         _ptr(is_sym), F, N, Cn, _ptr(add), _ptr(r_deg), _ptr(t_m), _stream())
+         _ptr(is_sym), F, N, Cn, _ptr(add), _ptr(r_deg), _ptr(t_m), _stream(add))
     return add, r_deg, t_m
 
 
@@ -152,7 +152,7 @@ def accumulate_results(table, add, r_deg, t_m, cls, diameter, status=None, varia
     F = add.shape[0]
     Cn = table.shape[1]
     call("pb_accumulate_results", _ptr(add), _ptr(r_deg), _ptr(t_m), _ptr(cls), _ptr(status), _ptr(diameter),
-         F, Cn, variant, add_frac, r_thr_deg, t_thr_m, 1 if count_frames else 0, _ptr(table), _stream())
+         F, Cn, variant, add_frac, r_thr_deg, t_thr_m, 1 if count_frames else 0, _ptr(table), _stream(table))
     return table
 
 
@@ -207,11 +207,11 @@ def pose_loss_fwd(R, t, model, target, sym, impl="auto", sym_host=None):
         nb = _lib.load().pb_knn1_tc_workspace_bytes(B, N, N)
         ws, off, wptr = _aligned_ws(nb, dev)
         call("pb_pose_loss_fwd_tc", _ptr(R), _ptr(t), _ptr(model), _ptr(target), _ptr(sym_arg), _ptr(lst), n, B, N,
-             _ptr(pred), _ptr(nn_idx), _ptr(loss_b), wptr, nb, _stream())
+             _ptr(pred), _ptr(nn_idx), _ptr(loss_b), wptr, nb, _stream(loss_b))
         LAST_TC_STATS = ws[off: off + 16].view(torch.int32)
     else:
         call("pb_pose_loss_fwd", _ptr(R), _ptr(t), _ptr(model), _ptr(target), _ptr(sym), B, N, _ptr(pred),
-             _ptr(nn_idx), _ptr(loss_b), _stream())
+             _ptr(nn_idx), _ptr(loss_b), _stream(loss_b))
     return loss_b, pred, nn_idx
 
 
@@ -220,7 +220,7 @@ def pose_loss_bwd(pred, model, target, nn_idx, gscale):
     grad_R = torch.empty((B, 3, 3), dtype=torch.float32, device=pred.device)
     grad_t = torch.empty((B, 3), dtype=torch.float32, device=pred.device)
     call("pb_pose_loss_bwd", _ptr(pred), _ptr(model), _ptr(target), _ptr(nn_idx), B, N, float(gscale),
-         _ptr(grad_R), _ptr(grad_t), _stream())
+         _ptr(grad_R), _ptr(grad_t), _stream(grad_R))
     return grad_R, grad_t
 
 
@@ -232,5 +232,5 @@ def vote_translation(cloud, t_res):
     if t_res.shape != (B, 3, NP):
         raise ValueError("t_res must be [B,3,NP]")
     t = torch.empty((B, 3), dtype=torch.float32, device=cloud.device)
-    call("pb_vote_translation", _ptr(cloud), _ptr(t_res), B, NP, _ptr(t), _stream())
+    call("pb_vote_translation", _ptr(cloud), _ptr(t_res), B, NP, _ptr(t), _stream(t))
     return t

@@ -34,7 +34,7 @@ def poss_loss_fwd(pred_r, pred_t, pred_c, target, model_points, nn_mode, w, axis
     ws = torch.empty(((nb + 15) // 16 * 4,), dtype=torch.int32, device=dev)
     vals = torch.empty((3,), dtype=torch.float32, device=dev)
     call("pb_poss_loss_fwd", _ptr(pred_r), _ptr(pred_t), _ptr(pred_c), _ptr(model_points), _ptr(target), bs, num_p, N,
-         int(bool(nn_mode)), float(w), _ptr(axis), _ptr(target_r), _ptr(vals), _ptr(ws), ws.numel() * 4, _stream())
+         int(bool(nn_mode)), float(w), _ptr(axis), _ptr(target_r), _ptr(vals), _ptr(ws), ws.numel() * 4, _stream(vals))
     return vals, ws
 
 
@@ -46,5 +46,5 @@ def poss_loss_bwd(pred_r, pred_t, pred_c, target, model_points, nn_mode, w, axis
     gr, gt, gc = torch.empty_like(pred_r), torch.empty_like(pred_t), torch.empty_like(pred_c)
     call("pb_poss_loss_bwd", _ptr(pred_r), _ptr(pred_t), _ptr(pred_c), _ptr(model_points), _ptr(target), bs, num_p, N,
          int(bool(nn_mode)), float(w), _ptr(axis), _ptr(target_r), _ptr(grad_vals), _ptr(ws), ws.numel() * 4, _ptr(gr), _ptr(gt),
-         _ptr(gc), _stream())
+         _ptr(gc), _stream(gc))
     return gr, gt, gc

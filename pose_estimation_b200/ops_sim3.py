@@ -75,7 +75,7 @@ def sim3_ransac(src, dst, count=None, cfg: Sim3Config | None = None, sample_idx=
         res.inl_bitmap = torch.zeros((B, (cap + 31) // 32), dtype=torch.int32, device=dev)
     call("pb_sim3_ransac", _ptr(src), _ptr(dst), _ptr(count), B, cap, int(prob0), C.byref(prm), _ptr(sample_idx),
          _ptr(res.scale), _ptr(res.R), _ptr(res.t), _ptr(res.n_inl), _ptr(res.best_hyp), _ptr(res.status),
-         _ptr(res.hyp_counts), _ptr(res.inl_bitmap), C.c_void_p(ws.data_ptr() + off), nb, _stream())
+         _ptr(res.hyp_counts), _ptr(res.inl_bitmap), C.c_void_p(ws.data_ptr() + off), nb, _stream(res.R))
     return res
 
 
@@ -93,7 +93,7 @@ def umeyama_fit(src, dst, count=None):
     R = torch.empty((B, 3, 3), dtype=torch.float32, device=dev)
     t = torch.empty((B, 3), dtype=torch.float32, device=dev)
     status = torch.empty((B,), dtype=torch.int32, device=dev)
-    call("pb_umeyama_fit", _ptr(src), _ptr(dst), _ptr(count), B, cap, _ptr(scale), _ptr(R), _ptr(t), _ptr(status), _stream())
+    call("pb_umeyama_fit", _ptr(src), _ptr(dst), _ptr(count), B, cap, _ptr(scale), _ptr(R), _ptr(t), _ptr(status), _stream(R))
     return scale, R, t, status
 
 
@@ -111,5 +111,5 @@ def farthest_point_sampling(points, n_samples, count=None):
     out = torch.empty((B, n_samples), dtype=torch.int32, device=points.device)
     nb = _lib.load().pb_fps_workspace_bytes(B, cap)
     ws = torch.empty(nb, dtype=torch.uint8, device=points.device) if nb else None
-    call("pb_fps", _ptr(points), _ptr(count), B, cap, int(n_samples), _ptr(out), _ptr(ws), nb, _stream())
+    call("pb_fps", _ptr(points), _ptr(count), B, cap, int(n_samples), _ptr(out), _ptr(ws), nb, _stream(out))
     return out[0] if squeeze else out

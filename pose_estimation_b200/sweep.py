@@ -131,9 +131,21 @@ class EvalSweep:
             return t
         return self._table
 
+    def _hold(self, stream, *tensors):
+        """Tell the caching allocator that ``stream`` reads these tensors: a caller that drops its batch right after
+        ``step`` returns must not have the memory handed out again while a lane is still reading it."""
+        for t in tensors:
+            if t is not None and t.is_cuda:
+                t.record_stream(stream)
+
     def step(self, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=0, roi=None, events=None, out=None,
              pred_t=None, cloud=None, t_res=None):
         """One batch of F frames (device tensors).  Returns (add, r_deg, t_m) [F] device tensors.
+        Lanes (lanes > 1): the batch is consumed on lane streams AFTER this call returns.  Contract: (1) the inputs may
+        be dropped at once (they are recorded on the lane's stream); (2) they must not be OVERWRITTEN before
+        ``self.last_event`` (recorded when the lane has finished this step) has been waited on, or before ``join`` /
+        ``finish``; (3) the returned per-frame tensors alias a ring of ``lanes`` output buffers and are valid after
+        ``join`` until ``lanes`` further steps have been issued.
         pred_t [F,3], or cloud [F,NP,3] + t_res [F,3,NP] (the T-offset vote, lib/network/krrn.py:153, is then taken
         here): the ``opt_pose`` branch of the test loop (tools/trainer.py:196-221) -- the 'reg' and 'final' variants
         pair the PnP rotation with the voted translation; their rows of the table are filled and their per-frame
@@ -148,16 +160,19 @@ class EvalSweep:
                 self._turn += 1
                 s = self.lane_streams[k]
                 s.wait_event(self.ev_in)
+                self._hold(s, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, roi, pred_t, cloud, t_res)
                 with torch.cuda.stream(s):
                     self.lanes[k].step(xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=frame0, roi=roi,
                                        out=tuple(self.out[k, j] for j in range(3)), pred_t=pred_t, cloud=cloud, t_res=t_res)
                     self.ev_out[k].record(s)
+                self.last_event = self.ev_out[k]
                 self._unjoined = True
                 return self.out[k, 0], self.out[k, 1], self.out[k, 2]
             Fl = self.F // len(self.lanes)
             for k, lane in enumerate(self.lanes):
                 s = self.lane_streams[k]
                 s.wait_event(self.ev_in)
+                self._hold(s, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, roi, pred_t, cloud, t_res)
                 lo, hi = k * Fl, (k + 1) * Fl
                 with torch.cuda.stream(s):
                     lane.step(xyz[lo:hi], None if mask is None else mask[lo:hi], extent[lo:hi], lfborder[lo:hi],
@@ -166,6 +181,7 @@ class EvalSweep:
                               pred_t=None if pred_t is None else pred_t[lo:hi],
                               cloud=None if cloud is None else cloud[lo:hi], t_res=None if t_res is None else t_res[lo:hi])
                     self.ev_out[k].record(s)
+            self.last_event = self.ev_out[-1]
             self._unjoined = True
             if not self.free_running:
                 self.join()

@@ -286,3 +286,37 @@ def test_eval_sweep_free_running_lanes_equal_single_stream(dev):
         sw3.join()
         assert all(torch.equal(a, c) for a, c in zip(out1, outs[2])), rep
         assert torch.equal(sw3.finish(), want), rep
+
+
+def test_eval_sweep_lanes_inputs_freed_or_overwritten_between_steps(dev):
+    """The caller may drop a batch as soon as step() returns (the lanes record the tensors on their streams) and
+    may overwrite it once ``last_event`` has been waited on: the table equals the single-stream run's."""
+    F, steps = 16, 6
+    sps = synth.make_batch_sparse(0x5EED, 2, F * steps)
+    models = torch.from_numpy(synth.class_models(500))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    keys = ("xyz", "mask", "extent", "lfborder", "K4", "cls", "R_gt", "t_gt")
+    host = [batch_arrays(sps[k * F:(k + 1) * F]) for k in range(steps)]
+    sw1 = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev)
+    for k in range(steps):
+        sw1.step(*[torch.from_numpy(host[k][n]).to(dev) for n in keys], frame0=k * F)
+    want = sw1.finish().clone()
+    # (a) fresh tensors per step, dropped at once, with allocator churn of the same sizes in between
+    sw3 = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev, lanes=3, deal="alternate")
+    for k in range(steps):
+        args = [torch.from_numpy(host[k][n]).to(dev) for n in keys]
+        sw3.step(*args, frame0=k * F)
+        del args
+        junk = [torch.full((F, 3, synth.IMG_H, synth.IMG_W), 7.0, device=dev), torch.full((F, synth.IMG_H, synth.IMG_W), 1, dtype=torch.uint8, device=dev)]
+        del junk
+    assert torch.equal(sw3.finish(), want)
+    # (b) one set of buffers overwritten in place after waiting for the lane that read them
+    bufs = [torch.from_numpy(host[0][n]).to(dev) for n in keys]
+    sw3.reset()
+    for k in range(steps):
+        if k:
+            torch.cuda.current_stream(dev).wait_event(sw3.last_event)
+            for bt, n in zip(bufs, keys):
+                bt.copy_(torch.from_numpy(host[k][n]), non_blocking=False)
+        sw3.step(*bufs, frame0=k * F)
+    assert torch.equal(sw3.finish(), want)

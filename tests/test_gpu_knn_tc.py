@@ -108,3 +108,33 @@ def test_add_adds_and_pose_loss_on_tensor_cores_equal_simt_bits(dev):
     assert torch.equal(a_all, a_ref) and torch.equal(s_all, s_ref)
     ra, rs = cref.add_adds(pred[0].cpu().numpy(), target[0].cpu().numpy())
     assert np.isclose(float(a_all[0]), ra, rtol=1e-5) and np.isclose(float(s_all[0]), rs, rtol=1e-5)
+
+
+@pytest.mark.parametrize("gap_log2", [-11, -13, -14, -15, -17])
+def test_knn_tc_adversarial_corners_need_no_tie(dev, gap_log2):
+    """ADVICE (round 1): exactness of the tensor-core argmin rests on  T = 2^-12 R^2 > 2E  with
+    E <= 1.06 * 2^-14 R^2 for |p||q| <= R^2 (header of csrc/knn_tc.cu).  The worst case for the bf16 h + m split is
+    queries and database points at OPPOSITE corners of the bounding box (|p| ~ |q| ~ R, p anti-parallel to q) whose
+    two nearest candidates differ by about 2^gap R^2 in squared distance -- below, at and above the error bound.
+    The indices must equal the exact FP32 scan in every case, without relying on an exact tie."""
+    from pose_estimation_b200 import ops_metric
+    rng = np.random.default_rng(100 - gap_log2)
+    N, M = 384, 512
+    lo, hi = np.array([0.31, -0.52, 0.83]), np.array([1.37, 0.61, 1.94])      # awkward mantissas on purpose
+    R2 = float(((hi - lo) ** 2).sum()) / 4.0
+    gap = 2.0 ** gap_log2 * R2
+    x = np.empty((1, N, 3), np.float64)
+    y = np.empty((1, M, 3), np.float64)
+    x[0] = lo + rng.random((N, 3)) * 1e-3 * (hi - lo)                         # queries hug one corner
+    y[0, :2] = lo                                                             # keeps the bounding box (and the centre)
+    y[0, 2:] = hi - rng.random((M - 2, 3)) * 1e-3 * (hi - lo)                 # database hugs the opposite corner
+    y[0, 0] = lo + 0.9 * (hi - lo); y[0, 1] = lo + 0.9 * (hi - lo)            # two far-corner candidates ...
+    d = np.linalg.norm(y[0, 0] - x[0].mean(0))
+    y[0, 1] += (hi - lo) / np.linalg.norm(hi - lo) * (gap / (2.0 * d))        # ... 2^gap R^2 apart in squared distance
+    xt, yt = torch.from_numpy(x.astype(np.float32)).to(dev), torch.from_numpy(y.astype(np.float32)).to(dev)
+    idx_tc, d2_tc = ops_metric.knn1(xt, yt, want_d2=True, impl="tc")
+    idx_si, d2_si = ops_metric.knn1(xt, yt, want_d2=True, impl="simt")
+    assert int(ops_metric.LAST_TC_STATS[0]) == 0
+    assert torch.equal(idx_tc, idx_si) and torch.equal(d2_tc, d2_si)
+    ref_i, _ = _brute(xt[0].cpu().numpy(), yt[0].cpu().numpy())
+    assert np.array_equal(idx_tc[0].cpu().numpy(), ref_i)

@@ -81,6 +81,16 @@ int pb_gather_correspondences(const float* xyz, const int64_t* choose, const flo
                               const float* ymap, const float* extent, const float* lfborder, int F,
                               int Hh, int Ww, int NP, int cap, float* pts, int32_t* count, void* stream);
 
+/* The same gather for every form of the list the reference's data pipeline produces (batchdataset.py:673-687,
+ * 712-716): choose [F,NP] int64 (choose_is_i32 = 0) or int32; xmap / ymap NULL -> the pixel coordinates are taken
+ * from the index itself (col + cmin, row + rmin with roi [F,2] = (rmin, cmin), or 0); n_valid [F] NULL -> every
+ * list has NP entries (the reference wrap-pads to NUM_POINTS), else list f has n_valid[f] <= NP.  xyz may be
+ * device memory or PINNED HOST memory read in place: only the sectors of the chosen pixels cross PCIe.        */
+int pb_gather_choose(const float* xyz, const void* choose, int choose_is_i32, const float* xmap,
+                     const float* ymap, const int32_t* n_valid, const int32_t* roi, const float* extent,
+                     const float* lfborder, int F, int Hh, int Ww, int NP, int cap, float* pts,
+                     int32_t* count, void* stream);
+
 /* ---- region-coded maps: xyz = xyz_off + base(region) ------------------------------------------
  * KRRN predicts an offset map plus per-pixel region logits; the map the solver consumes is rebuilt from both.
  * soft = 0: tools/script/eval.py:93-103 (tools/trainer.py:391-398, commented out there) -- class = arg-max of the

@@ -33,6 +33,7 @@ SIGNATURES = {
     "pb_compact_workspace_bytes": (SZ, [I, I, I, I]),
     "pb_compact_map": (I, [P, P, P, P, P, I, I, I, I, P, P, P, P, SZ, P]),
     "pb_gather_correspondences": (I, [P, P, P, P, P, P, I, I, I, I, I, P, P, P]),
+    "pb_gather_choose": (I, [P, P, I, P, P, P, P, P, P, I, I, I, I, I, P, P, P]),
     "pb_region_decode_points": (I, [P, P, P, P, I, P, P, P, I, I, I, I, I, I, P, P, P]),
     "pb_region_decode_map": (I, [P, P, P, I, I, I, I, I, P, P]),
     "pb_ransac_workspace_bytes": (SZ, [I, I, PRM]),

@@ -23,6 +23,18 @@ int pb_check_launch(const char* what) {
     return 0;
 }
 
+int pb_sm_count() {
+    static int cached[64];                         // 0 = not queried yet; benign race (same value written)
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
 // ---- optional per-kernel timing of the RANSAC call (CUDA events recorded on the caller's stream) ----
 namespace {
 constexpr int TIM_SLOTS = 256, TIM_MARKS = 4;     // marks: before hyp | before score | before finalize | after

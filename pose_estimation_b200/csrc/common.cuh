@@ -14,6 +14,7 @@
 
 void pb_set_error(const char* fmt, ...);
 int pb_check_launch(const char* what);
+int pb_sm_count();                                // multiprocessors of the current device (queried once per device)
 void pb_stage_mark(int mark, cudaStream_t st);   // no-op unless pb_stage_timing(1) (abi.cu)
 // tensor-core nearest neighbour over a list of batch elements (knn_tc.cu); ws sized by pb_knn1_tc_workspace_bytes
 int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx,

@@ -4,12 +4,21 @@
 // and the dataset-side mask.flatten().nonzero() (dataset/linemod/batchdataset.py:673).
 // HBM-bound: every pixel costs 12 B of xyz + 1 B of mask, read exactly once with 128-bit loads,
 // next iteration's loads issued before the current block scan (register double buffer).
-// Two kernels:
-//   compact_sparse_kernel (mask given, H*W % 32 == 0): MASK-FIRST.  The mask (1 B/px) is streamed
-//     with 128-bit loads into a shared-memory foreground bitmap; the xyz planes are then read ONLY
-//     at the foreground pixels (3 sectors per pixel) -- 0.3-0.4 MB per 480x640 frame instead of
-//     4.0 MB.  The pointers may be device memory or pinned (mapped) host memory: with host maps the
-//     same kernel pulls just the mask and the touched sectors across PCIe (zero-copy gather).
+// Kernels:
+//   compact_stream_kernel (mask given, H*W % 16 == 0): MASK-FIRST, one pass, no frame-sized state.
+//     The batch's masks are one stream of 16 KB tiles (16,384 px) handed out by an atomic ticket to a
+//     persistent grid; a CTA turns its tile into 1024 16-bit foreground words (next tile's 128-bit
+//     loads already in flight), most tiles are empty and end there.  A non-empty tile publishes its
+//     count, sums the counts of the earlier tiles of its frame (decoupled look-back over <= 18 words:
+//     tickets are taken in execution order, so a predecessor is always held by a running CTA), and
+//     emits its pixels BY RANK -- thread r finds the r-th foreground pixel of the tile by a binary
+//     search over the per-word prefix -- so the three plane loads and the five stores of consecutive
+//     output slots are issued by consecutive threads whatever the mask's density.  The xyz planes are
+//     read ONLY at foreground pixels: 0.3-0.4 MB per 480x640 frame instead of 4.0 MB.  The pointers may
+//     be device memory or pinned (mapped) host memory: with host maps the same kernel pulls just the
+//     mask and the touched sectors across PCIe (zero-copy gather).
+//   compact_sparse_kernel: the round-1 mask-first kernel (CTA per frame, banded bitmap), kept for
+//     callers that pass no workspace.
 //   compact_kernel (no mask: foreground iff any channel != 0): streams all three planes.
 // Output order is row-major pixel order (deterministic): per-iteration block scan, one
 // __syncthreads per 1024 pixels.  When there are too few frames to fill the GPU a frame is split
@@ -302,6 +311,164 @@ __global__ void __launch_bounds__(CT) compact_sparse_kernel(CompactArgs a) {
     }
 }
 
+// ---- mask-first, streaming: tiles by ticket + decoupled look-back ---------------------------------
+constexpr int SM_G = 4;                          // 128-bit mask loads per thread per tile
+constexpr int SM_GROUPS = CT * SM_G;             // 16-px groups per tile (1024)
+constexpr int SM_TILE_PX = SM_GROUPS * 16;       // 16,384 px = 16 KB of mask
+constexpr uint32_t SM_FLAG = 0x80000000u;        // tile state word: FLAG | foreground count
+
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
+    uint32_t r;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// position of the n-th (0-based) set bit of a 16-bit word that has more than n bits set
+__device__ __forceinline__ int nth_bit16(uint32_t x, int n) {
+    int b = 0, c = __popc(x & 0xFFu);
+    if (n >= c) { n -= c; x >>= 8; b = 8; }
+    c = __popc(x & 0xFu);
+    if (n >= c) { n -= c; x >>= 4; b += 4; }
+    c = __popc(x & 0x3u);
+    if (n >= c) { n -= c; x >>= 2; b += 2; }
+    return b + ((n >= (int)(x & 1u)) ? 1 : 0);
+}
+
+__global__ void __launch_bounds__(CT, 4) compact_stream_kernel(CompactArgs a, uint32_t* __restrict__ state,
+                                                            unsigned int* __restrict__ ticket, int tpf, int ntiles) {
+    __shared__ int s_gpre[SM_GROUPS];            // exclusive prefix of the groups' foreground counts (tile-local)
+    __shared__ uint16_t s_gbits[SM_GROUPS];
+    __shared__ int s_wcnt[CT / 32];              // per-warp counts (a warp owns 128 consecutive groups)
+    __shared__ int s_next[2];
+    __shared__ int s_fbase;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int gpf = a.HW >> 4;                   // 16-px groups per frame
+
+    auto load_tile = [&](int tile, uint4 (&m)[SM_G]) {
+        const int f = tile / tpf, ti = tile - f * tpf;
+        const uint4* pm = reinterpret_cast<const uint4*>(a.mask + (size_t)f * a.HW) + (size_t)ti * SM_GROUPS;
+        const int ng = min(SM_GROUPS, gpf - ti * SM_GROUPS);
+#pragma unroll
+        for (int k = 0; k < SM_G; ++k) {
+            const int g = warp * (32 * SM_G) + k * 32 + lane;           // a load instruction covers 512 contiguous bytes
+            m[k] = g < ng ? ldg_stream_u4(pm + g) : make_uint4(0u, 0u, 0u, 0u);
+        }
+    };
+
+    if (tid == 0) s_next[0] = (int)atomicAdd(ticket, 1u);
+    __syncthreads();
+    int tile = s_next[0];
+    uint4 m[SM_G];
+    if (tile < ntiles) load_tile(tile, m);
+    for (int it = 1; tile < ntiles; ++it) {
+        if (tid == 0) s_next[it & 1] = (int)atomicAdd(ticket, 1u);     // read after the barrier below
+        const int f = tile / tpf, ti = tile - f * tpf;
+        uint32_t bits[SM_G];
+        int c[SM_G], cs = 0;
+#pragma unroll
+        for (int k = 0; k < SM_G; ++k) {
+            bits[k] = 0u;
+            if (m[k].x | m[k].y | m[k].z | m[k].w)                      // most of a frame is background
+                bits[k] = nz4(m[k].x) | (nz4(m[k].y) << 4) | (nz4(m[k].z) << 8) | (nz4(m[k].w) << 12);
+            c[k] = __popc(bits[k]);
+            cs += c[k];
+        }
+        const bool last = ti == tpf - 1;                                // the frame's last tile writes count[f]
+        const int any = __syncthreads_or(cs);
+        const int next = s_next[it & 1];
+        if (next < ntiles) load_tile(next, m);                          // in flight under the rest of this tile
+        if (!any && !last) {
+            if (tid == 0) st_volatile_u32(state + tile, SM_FLAG);
+            tile = next;
+            continue;
+        }
+        // ---- tile-local ranks: pixel order is (warp, load k, lane) = group index order
+        int pre = 0;                                                    // this warp's pixels before load k
+        int excl[SM_G];
+#pragma unroll
+        for (int k = 0; k < SM_G; ++k) {
+            int v = c[k];
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const int o = __shfl_up_sync(0xffffffffu, v, off);
+                if (lane >= off) v += o;
+            }
+            excl[k] = pre + v - c[k];
+            pre += __shfl_sync(0xffffffffu, v, 31);
+        }
+        if (lane == 0) s_wcnt[warp] = pre;
+        __syncthreads();
+        int total = 0, wbase = 0;
+#pragma unroll
+        for (int w = 0; w < CT / 32; ++w) {
+            const int v = s_wcnt[w];
+            wbase += w < warp ? v : 0;
+            total += v;
+        }
+        if (tid == 0) st_volatile_u32(state + tile, SM_FLAG | (uint32_t)total);
+#pragma unroll
+        for (int k = 0; k < SM_G; ++k) {
+            const int g = warp * (32 * SM_G) + k * 32 + lane;
+            s_gpre[g] = wbase + excl[k];
+            s_gbits[g] = (uint16_t)bits[k];
+        }
+        // ---- look-back: foreground pixels of the frame's earlier tiles (warp 0; lanes poll one word each)
+        if (warp == 0) {
+            int sum = 0;
+            for (int j0 = 0; j0 < ti; j0 += 32) {
+                const int j = j0 + lane;
+                uint32_t v = SM_FLAG;
+                if (j < ti) {
+                    const uint32_t* sp = state + (tile - ti + j);
+                    do { v = ld_volatile_u32(sp); } while (!(v & SM_FLAG));
+                }
+                sum += (int)(v & ~SM_FLAG);
+            }
+            sum = __reduce_add_sync(0xffffffffu, sum);
+            if (lane == 0) s_fbase = sum;
+        }
+        __syncthreads();
+        const int fbase = s_fbase;
+        // ---- emit by rank: consecutive threads -> consecutive output slots
+        const int nout = min(total, a.cap - fbase);                     // <= 0: the frame is already at cap
+        if (nout > 0) {
+            const float* px = a.xyz + (size_t)f * 3 * a.HW;
+            const float* py = px + a.HW;
+            const float* pz = py + a.HW;
+            const float e0 = a.extent[3 * f], e1 = a.extent[3 * f + 1], e2 = a.extent[3 * f + 2];
+            const float l0 = a.lfborder[3 * f], l1 = a.lfborder[3 * f + 1], l2 = a.lfborder[3 * f + 2];
+            const int rmin = a.roi ? a.roi[2 * f] : 0, cmin = a.roi ? a.roi[2 * f + 1] : 0;
+            float* oX = a.pts + (size_t)f * 5 * a.cap + fbase;
+            float* oY = oX + a.cap; float* oZ = oY + a.cap; float* oU = oZ + a.cap; float* oV = oU + a.cap;
+            const int pix0 = ti * SM_TILE_PX;
+            for (int r = tid; r < nout; r += CT) {
+                int lo = 0, hi = SM_GROUPS;                             // last group with s_gpre <= r
+#pragma unroll
+                for (int stp = 0; stp < 10; ++stp) {                    // SM_GROUPS = 2^10
+                    const int mid = (lo + hi) >> 1;
+                    if (s_gpre[mid] <= r) lo = mid; else hi = mid;
+                }
+                const int p = pix0 + (lo << 4) + nth_bit16(s_gbits[lo], r - s_gpre[lo]);
+                const float x = ldg_stream_f32(px + p), y = ldg_stream_f32(py + p), z = ldg_stream_f32(pz + p);
+                const int row = p / a.Ww, col = p - row * a.Ww;
+                oX[r] = fmaf(x, e0, l0);
+                oY[r] = fmaf(y, e1, l1);
+                oZ[r] = fmaf(z, e2, l2);
+                oU[r] = (float)(col + cmin);
+                oV[r] = (float)(row + rmin);
+            }
+        }
+        if (last && tid == 0) {
+            a.count[f] = min(fbase + total, a.cap);
+            if (a.total) a.total[f] = fbase + total;
+        }
+        __syncthreads();                                                // s_gpre / s_gbits / s_wcnt / s_fbase are reused
+        tile = next;
+    }
+}
+
 // generic (any HW, any alignment) scalar variant: one pixel per thread per iteration
 template <bool HAS_MASK>
 __global__ void __launch_bounds__(CT) compact_kernel_scalar(CompactArgs a) {
@@ -377,27 +544,48 @@ __global__ void __launch_bounds__(CT) merge_segments_kernel(const float* seg, co
     }
 }
 
-__global__ void gather_kernel(const float* xyz, const int64_t* choose, const float* xmap, const float* ymap,
-                              const float* extent, const float* lfborder, int HW, int NP, int cap, float* pts,
-                              int32_t* count) {
+// choose-list gather (tools/trainer.py:406-421): one thread per list entry.  IDX = int64_t (the reference's
+// `choose`) or int32_t; xmap / ymap NULL -> pixel coordinates from the index itself (col + cmin, row + rmin);
+// n_valid NULL -> every list has NP entries (the reference's wrap-padded lists), else list f has n_valid[f].
+// xyz may be device memory or pinned host memory (then only the touched sectors cross PCIe).
+template <typename IDX>
+__global__ void __launch_bounds__(128) gather_kernel(const float* __restrict__ xyz, const IDX* __restrict__ choose,
+                                                     const float* __restrict__ xmap, const float* __restrict__ ymap,
+                                                     const int32_t* __restrict__ n_valid, const int32_t* __restrict__ roi,
+                                                     const float* __restrict__ extent, const float* __restrict__ lfborder,
+                                                     int HW, int Ww, int NP, int cap, float* __restrict__ pts,
+                                                     int32_t* __restrict__ count) {
     const int f = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int n = min(NP, cap);
+    int n = n_valid ? n_valid[f] : NP;
+    n = max(0, min(n, min(NP, cap)));
     if (i == 0) count[f] = n;
     if (i >= n) return;
-    long long p = choose[(size_t)f * NP + i];
+    long long p = (long long)choose[(size_t)f * NP + i];
     if (p < 0) p = 0;
     if (p >= HW) p = HW - 1;
     const float* base = xyz + (size_t)f * 3 * HW;
+    const float x = ldg_stream_f32(base + p), y = ldg_stream_f32(base + HW + p), z = ldg_stream_f32(base + 2 * (size_t)HW + p);
+    float u, v;
+    if (xmap) { u = xmap[(size_t)f * NP + i]; v = ymap[(size_t)f * NP + i]; }
+    else {
+        const int row = (int)(p / Ww), col = (int)(p - (long long)row * Ww);
+        u = (float)(col + (roi ? roi[2 * f + 1] : 0));
+        v = (float)(row + (roi ? roi[2 * f] : 0));
+    }
     float* o = pts + (size_t)f * 5 * cap;
-    o[i] = fmaf(base[p], extent[3 * f], lfborder[3 * f]);
-    o[cap + i] = fmaf(base[HW + p], extent[3 * f + 1], lfborder[3 * f + 1]);
-    o[2 * cap + i] = fmaf(base[2 * (size_t)HW + p], extent[3 * f + 2], lfborder[3 * f + 2]);
-    o[3 * cap + i] = xmap[(size_t)f * NP + i];
-    o[4 * cap + i] = ymap[(size_t)f * NP + i];
+    o[i] = fmaf(x, extent[3 * f], lfborder[3 * f]);
+    o[cap + i] = fmaf(y, extent[3 * f + 1], lfborder[3 * f + 1]);
+    o[2 * cap + i] = fmaf(z, extent[3 * f + 2], lfborder[3 * f + 2]);
+    o[3 * cap + i] = u;
+    o[4 * cap + i] = v;
 }
 
 struct CPlan { int S, quads_per_split, segcap; bool vec, sparse; size_t off_tot, total, smem_sparse; };
+
+// workspace of the streaming mask-first kernel: ticket (256 B) + one state word per tile
+inline int stream_tiles_per_frame(long long HW) { return (int)((HW + SM_TILE_PX - 1) / SM_TILE_PX); }
+inline size_t stream_ws_bytes(int F, long long HW) { return 256 + (size_t)F * stream_tiles_per_frame(HW) * sizeof(uint32_t); }
 
 CPlan make_cplan(int F, int Hh, int Ww, int cap, bool has_mask) {
     CPlan p;
@@ -432,7 +620,9 @@ CPlan make_cplan(int F, int Hh, int Ww, int cap, bool has_mask) {
 
 extern "C" size_t pb_compact_workspace_bytes(int F, int Hh, int Ww, int cap) {
     if (F <= 0 || Hh <= 0 || Ww <= 0 || cap <= 0) return 0;
-    return make_cplan(F, Hh, Ww, cap, false).total;   // the maskless plan is the larger one
+    const size_t dense = make_cplan(F, Hh, Ww, cap, false).total;      // maskless stream (row bands + merge)
+    const size_t stream = stream_ws_bytes(F, (long long)Hh * Ww);      // mask-first stream (ticket + tile states)
+    return dense > stream ? dense : stream;
 }
 
 extern "C" int pb_compact_map(const float* xyz, const uint8_t* mask, const int32_t* roi, const float* extent,
@@ -450,6 +640,19 @@ extern "C" int pb_compact_map(const float* xyz, const uint8_t* mask, const int32
     a.xyz = xyz; a.mask = mask; a.roi = roi; a.extent = extent; a.lfborder = lfborder;
     a.count = count; a.total = total;
     a.HW = Hh * Ww; a.Ww = Ww; a.cap = cap; a.S = p.S; a.quads_per_split = p.quads_per_split; a.segcap = p.segcap;
+    const long long HWl = (long long)Hh * Ww;
+    if (mask && HWl % 16 == 0 && reinterpret_cast<uintptr_t>(mask) % 16 == 0 && ws && ws_bytes >= stream_ws_bytes(F, HWl) &&
+        (long long)F * stream_tiles_per_frame(HWl) < (1ll << 30)) {
+        a.pts = pts; a.S = 1; a.seg_total = nullptr;
+        const int tpf = stream_tiles_per_frame(HWl), ntiles = F * tpf;
+        if (cudaMemsetAsync(ws, 0, stream_ws_bytes(F, HWl), st) != cudaSuccess) return pb_check_launch("compact_stream memset") ? -2 : -2;
+        int per_sm = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, compact_stream_kernel, CT, 0);
+        const int grid = min(ntiles, pb_sm_count() * (per_sm > 0 ? per_sm : 1));
+        compact_stream_kernel<<<grid, CT, 0, st>>>(a, reinterpret_cast<uint32_t*>(static_cast<char*>(ws) + 256),
+                                                     static_cast<unsigned int*>(ws), tpf, ntiles);
+        return pb_check_launch("compact_stream_kernel") ? -2 : 0;
+    }
     if (p.sparse) {
         a.pts = pts; a.S = 1; a.seg_total = nullptr;
         compact_sparse_kernel<<<F, CT, 0, st>>>(a);
@@ -479,17 +682,31 @@ extern "C" int pb_compact_map(const float* xyz, const uint8_t* mask, const int32
     return 0;
 }
 
+extern "C" int pb_gather_choose(const float* xyz, const void* choose, int choose_is_i32, const float* xmap,
+                                const float* ymap, const int32_t* n_valid, const int32_t* roi, const float* extent,
+                                const float* lfborder, int F, int Hh, int Ww, int NP, int cap, float* pts,
+                                int32_t* count, void* stream) {
+    PB_REQUIRE(F >= 0 && Hh > 0 && Ww > 0 && NP > 0 && cap > 0, "pb_gather_choose: bad sizes");
+    PB_REQUIRE(F <= 65535, "pb_gather_choose: F too large (<= 65535)");
+    PB_REQUIRE((long long)Hh * Ww < (1ll << 30), "pb_gather_choose: map too large");
+    if (F == 0) return 0;
+    PB_REQUIRE(xyz && choose && extent && lfborder && pts && count, "pb_gather_choose: null pointer argument");
+    PB_REQUIRE((xmap == nullptr) == (ymap == nullptr), "pb_gather_choose: xmap and ymap go together");
+    const int n = NP < cap ? NP : cap;
+    dim3 grid((n + 127) / 128, F);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (choose_is_i32)
+        gather_kernel<int32_t><<<grid, 128, 0, st>>>(xyz, static_cast<const int32_t*>(choose), xmap, ymap, n_valid, roi,
+                                                     extent, lfborder, Hh * Ww, Ww, NP, cap, pts, count);
+    else
+        gather_kernel<int64_t><<<grid, 128, 0, st>>>(xyz, static_cast<const int64_t*>(choose), xmap, ymap, n_valid, roi,
+                                                     extent, lfborder, Hh * Ww, Ww, NP, cap, pts, count);
+    return pb_check_launch("gather_kernel") ? -2 : 0;
+}
+
 extern "C" int pb_gather_correspondences(const float* xyz, const int64_t* choose, const float* xmap,
                                          const float* ymap, const float* extent, const float* lfborder, int F,
                                          int Hh, int Ww, int NP, int cap, float* pts, int32_t* count, void* stream) {
-    PB_REQUIRE(F >= 0 && Hh > 0 && Ww > 0 && NP > 0 && cap > 0, "pb_gather_correspondences: bad sizes");
-    PB_REQUIRE(F <= 65535, "pb_gather_correspondences: F too large (<= 65535)");
-    if (F == 0) return 0;
-    PB_REQUIRE(xyz && choose && xmap && ymap && extent && lfborder && pts && count,
-               "pb_gather_correspondences: null pointer argument");
-    const int n = NP < cap ? NP : cap;
-    dim3 grid((n + 127) / 128, F);
-    gather_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(xyz, choose, xmap, ymap, extent, lfborder,
-                                                                         Hh * Ww, NP, cap, pts, count);
-    return pb_check_launch("gather_kernel") ? -2 : 0;
+    PB_REQUIRE(xmap && ymap, "pb_gather_correspondences: null pointer argument");
+    return pb_gather_choose(xyz, choose, 0, xmap, ymap, nullptr, nullptr, extent, lfborder, F, Hh, Ww, NP, cap, pts, count, stream);
 }

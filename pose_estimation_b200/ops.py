@@ -104,6 +104,37 @@ def gather_correspondences(xyz, choose, xmap, ymap, extent, lfborder, cap=None):
     return pts, count
 
 
+class ChooseGatherer:
+    """Reusable launcher of pb_gather_choose with persistent pts [F,5,cap] / count [F]: the K0 of callers that hold
+    the reference's ``choose`` lists (tools/trainer.py:406-421) instead of a mask."""
+
+    launches = 1
+
+    def __init__(self, F, H, W, cap, device="cuda"):
+        self.F, self.H, self.W, self.cap = F, H, W, cap
+        dev = torch.device(device)
+        self.pts = torch.empty((F, 5, cap), dtype=torch.float32, device=dev)
+        self.count = torch.empty((F,), dtype=torch.int32, device=dev)
+
+    def __call__(self, xyz, choose, extent, lfborder, xmap=None, ymap=None, n_valid=None, roi=None):
+        """xyz [F,3,H,W] f32: CUDA or PINNED host (read in place); choose [F,NP] int64 / int32 CUDA; xmap / ymap
+        [F,NP] f32 CUDA or None (pixel coordinates from the index and roi); n_valid [F] int32 CUDA or None."""
+        if tuple(xyz.shape) != (self.F, 3, self.H, self.W) or not xyz.is_contiguous() or xyz.dtype != torch.float32:
+            raise ValueError("xyz must be a contiguous float32 [F,3,H,W] tensor of the planned shape")
+        if not (xyz.is_cuda or xyz.is_pinned()):
+            raise _lib.PoseB200Error("xyz must be a CUDA tensor or a pinned host tensor (no CPU path)")
+        if choose.dtype not in (torch.int64, torch.int32) or not choose.is_cuda or not choose.is_contiguous() \
+                or choose.dim() != 2 or choose.shape[0] != self.F:
+            raise ValueError("choose must be a contiguous CUDA int64 / int32 [F,NP] tensor")
+        if (xmap is None) != (ymap is None):
+            raise ValueError("xmap and ymap go together")
+        NP = choose.shape[1]
+        call("pb_gather_choose", _ptr(xyz), _ptr(choose), 1 if choose.dtype == torch.int32 else 0, _ptr(xmap), _ptr(ymap),
+             _ptr(n_valid), _ptr(roi), _ptr(extent), _ptr(lfborder), self.F, self.H, self.W, NP, self.cap,
+             _ptr(self.pts), _ptr(self.count), _stream(self.pts))
+        return self.pts, self.count
+
+
 def _region_mode(mode):
     if mode not in ("hard", "soft"):
         raise ValueError("region mode must be 'hard' (tools/script/eval.py:93-103) or 'soft' (loss_utils.get_xyz)")

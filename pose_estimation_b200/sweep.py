@@ -101,6 +101,7 @@ class EvalSweep:
                 sum(l.launches_per_step for l in self.lanes)
             return
         self.compact = ops.MapCompactor(F, H, W, cap, device=dev)
+        self.gather = None                       # ops.ChooseGatherer, made on the first step(choose=...)
         self.ransac = ops.PtsRansac(F, cap, self.cfg, device=dev)
         self._table = ops_metric.new_table(self.n_cls, dev)
         self.launches_per_step = self.compact.launches(True) + self.ransac.launches + 2
@@ -139,8 +140,11 @@ class EvalSweep:
                 t.record_stream(stream)
 
     def step(self, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=0, roi=None, events=None, out=None,
-             pred_t=None, cloud=None, t_res=None):
+             pred_t=None, cloud=None, t_res=None, choose=None, xmap=None, ymap=None, n_valid=None):
         """One batch of F frames (device tensors).  Returns (add, r_deg, t_m) [F] device tensors.
+        choose [F,NP] int64 / int32 (+ xmap / ymap [F,NP] f32, n_valid [F] i32, all optional but ``choose``): the
+        correspondences are gathered at the reference's ``choose`` lists (tools/trainer.py:406-421,
+        pb_gather_choose) instead of being compacted from ``mask`` (then ignored).
         Lanes (lanes > 1): the batch is consumed on lane streams AFTER this call returns.  Contract: (1) the inputs may
         be dropped at once (they are recorded on the lane's stream); (2) they must not be OVERWRITTEN before
         ``self.last_event`` (recorded when the lane has finished this step) has been waited on, or before ``join`` /
@@ -161,9 +165,11 @@ class EvalSweep:
                 s = self.lane_streams[k]
                 s.wait_event(self.ev_in)
                 self._hold(s, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, roi, pred_t, cloud, t_res)
+                self._hold(s, choose, xmap, ymap, n_valid)
                 with torch.cuda.stream(s):
                     self.lanes[k].step(xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, frame0=frame0, roi=roi,
-                                       out=tuple(self.out[k, j] for j in range(3)), pred_t=pred_t, cloud=cloud, t_res=t_res)
+                                       out=tuple(self.out[k, j] for j in range(3)), pred_t=pred_t, cloud=cloud, t_res=t_res,
+                                       choose=choose, xmap=xmap, ymap=ymap, n_valid=n_valid)
                     self.ev_out[k].record(s)
                 self.last_event = self.ev_out[k]
                 self._unjoined = True
@@ -173,13 +179,15 @@ class EvalSweep:
                 s = self.lane_streams[k]
                 s.wait_event(self.ev_in)
                 self._hold(s, xyz, mask, extent, lfborder, K4, cls, R_gt, t_gt, roi, pred_t, cloud, t_res)
+                self._hold(s, choose, xmap, ymap, n_valid)
                 lo, hi = k * Fl, (k + 1) * Fl
+                cut = lambda t: None if t is None else t[lo:hi]
                 with torch.cuda.stream(s):
-                    lane.step(xyz[lo:hi], None if mask is None else mask[lo:hi], extent[lo:hi], lfborder[lo:hi],
+                    lane.step(xyz[lo:hi], cut(mask), extent[lo:hi], lfborder[lo:hi],
                               K4[lo:hi], cls[lo:hi], R_gt[lo:hi], t_gt[lo:hi], frame0=frame0 + lo,
-                              roi=None if roi is None else roi[lo:hi], out=tuple(self.out[0, j, lo:hi] for j in range(3)),
-                              pred_t=None if pred_t is None else pred_t[lo:hi],
-                              cloud=None if cloud is None else cloud[lo:hi], t_res=None if t_res is None else t_res[lo:hi])
+                              roi=cut(roi), out=tuple(self.out[0, j, lo:hi] for j in range(3)),
+                              pred_t=cut(pred_t), cloud=cut(cloud), t_res=cut(t_res),
+                              choose=cut(choose), xmap=cut(xmap), ymap=cut(ymap), n_valid=cut(n_valid))
                     self.ev_out[k].record(s)
             self.last_event = self.ev_out[-1]
             self._unjoined = True
@@ -194,7 +202,12 @@ class EvalSweep:
             e.record()
             return e
         e0 = mark()
-        pts, count = self.compact(xyz, mask, extent, lfborder, roi=roi)
+        if choose is not None:
+            if self.gather is None:
+                self.gather = ops.ChooseGatherer(self.F, self.H, self.W, self.cap, device=self.dev)
+            pts, count = self.gather(xyz, choose, extent, lfborder, xmap=xmap, ymap=ymap, n_valid=n_valid, roi=roi)
+        else:
+            pts, count = self.compact(xyz, mask, extent, lfborder, roi=roi)
         e1 = mark()
         rs = self.ransac(pts, count, K4, frame0=frame0)
         e2 = mark()
@@ -279,6 +292,8 @@ class HostEvalSweep:
                            ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
         self.table_host = torch.empty((ops_metric.TABLE_ROWS, self.sweep.n_cls), dtype=torch.float64).pin_memory()
         self.h2d_bytes = 0
+        self.cap = cap
+        self.list_stage = None                   # staging buffers of run_choose, made on first use
 
     @property
     def table(self):
@@ -347,6 +362,84 @@ class HostEvalSweep:
             for k, s_ in enumerate(self.lane_streams):
                 self.lane_done[k].record(s_)
                 comp.wait_event(self.lane_done[k])
+        table = self.table
+        reduce_table(table, group)
+        self.table_host.copy_(table, non_blocking=True)
+        comp.synchronize()
+        return self.table_host
+
+
+    # ------------------------------------------------------------------------------------------------
+    def _list_stage(self, NP, idx_dtype, with_xy):
+        key = (NP, idx_dtype, with_xy)
+        if self.list_stage is None or self.list_stage[0] != key:
+            dev, c = self.dev, self.chunk
+            mk = lambda: dict(choose=torch.empty((c, NP), dtype=idx_dtype, device=dev),
+                              xmap=torch.empty((c, NP), dtype=torch.float32, device=dev) if with_xy else None,
+                              ymap=torch.empty((c, NP), dtype=torch.float32, device=dev) if with_xy else None,
+                              n_valid=torch.empty((c,), dtype=torch.int32, device=dev))
+            self.list_stage = (key, [mk(), mk()])
+        return self.list_stage[1]
+
+    def run_choose(self, xyz, choose_h, small_h, cls_h, xmap_h=None, ymap_h=None, n_valid_h=None, frame0=0, group=None,
+                   roi_h=None):
+        """The pass for a caller that holds what the reference's test loop holds (tools/trainer.py:383-421): the
+        coordinate maps and, per frame, the ``choose`` index list with its pixel-coordinate lists.
+        xyz [F,3,H,W] f32: PINNED HOST memory (read in place by the gather kernel: only the chosen pixels' sectors
+        cross PCIe) or a CUDA tensor (the network's output still on the device: only the lists cross);
+        choose_h [F,NP] int64 (the reference's dtype) or int32, xmap_h / ymap_h [F,NP] f32 or None (coordinates
+        from the index and roi_h), n_valid_h [F] i32 or None (NP entries each), small_h = pack_small(...),
+        cls_h [F] i32 -- pinned host tensors.  Per chunk the lists go by the copy engine while the previous chunk is
+        gathered and evaluated; chunks alternate between two compute lanes.  Returns the table on the host."""
+        F = choose_h.shape[0]
+        if F % self.chunk:
+            raise ValueError("F must be a multiple of the chunk size")
+        if len(self.sweeps) < 2:
+            raise ValueError("run_choose needs the two-lane form: construct HostEvalSweep(..., zero_copy=True)")
+        if not (xyz.is_cuda or xyz.is_pinned()):
+            raise ValueError("xyz must be a CUDA tensor or a pinned host tensor")
+        NP = choose_h.shape[1]
+        with_xy = xmap_h is not None
+        stg = self._list_stage(NP, choose_h.dtype, with_xy)
+        comp = torch.cuda.current_stream(self.dev)
+        n, nl = F // self.chunk, len(self.sweeps)
+        self.h2d_bytes = 0
+        self.start.record(comp)
+        for s_ in self.lane_streams:
+            s_.wait_event(self.start)
+        for i in range(n):
+            st, ls = self.stage[i & 1], stg[i & 1]
+            sweep, lane = self.sweeps[i % nl], self.lane_streams[i % nl]
+            lo, hi = i * self.chunk, (i + 1) * self.chunk
+            with torch.cuda.stream(self.copy_stream):
+                if i >= 2:
+                    self.copy_stream.wait_event(st["free"])
+                ls["choose"].copy_(choose_h[lo:hi], non_blocking=True)
+                moved = [ls["choose"], st["small"], st["cls"]]
+                if with_xy:
+                    ls["xmap"].copy_(xmap_h[lo:hi], non_blocking=True)
+                    ls["ymap"].copy_(ymap_h[lo:hi], non_blocking=True)
+                    moved += [ls["xmap"], ls["ymap"]]
+                if n_valid_h is not None:
+                    ls["n_valid"].copy_(n_valid_h[lo:hi], non_blocking=True)
+                    moved.append(ls["n_valid"])
+                st["small"].copy_(small_h[i], non_blocking=True)
+                st["cls"].copy_(cls_h[lo:hi], non_blocking=True)
+                if roi_h is not None:
+                    st["roi"].copy_(roi_h[lo:hi], non_blocking=True)
+                    moved.append(st["roi"])
+                st["ready"].record(self.copy_stream)
+            self.h2d_bytes += sum(t.numel() * t.element_size() for t in moved)
+            lane.wait_event(st["ready"])
+            ext, lfb, K4, Rg, tg = unpack_small(st["small"], self.chunk)
+            with torch.cuda.stream(lane):
+                sweep.step(xyz[lo:hi], None, ext, lfb, K4, st["cls"], Rg, tg, frame0=frame0 + lo,
+                           roi=None if roi_h is None else st["roi"], choose=ls["choose"], xmap=ls["xmap"], ymap=ls["ymap"],
+                           n_valid=None if n_valid_h is None else ls["n_valid"])
+                st["free"].record(lane)
+        for k, s_ in enumerate(self.lane_streams):
+            self.lane_done[k].record(s_)
+            comp.wait_event(self.lane_done[k])
         table = self.table
         reduce_table(table, group)
         self.table_host.copy_(table, non_blocking=True)

@@ -320,3 +320,81 @@ def test_eval_sweep_lanes_inputs_freed_or_overwritten_between_steps(dev):
                 bt.copy_(torch.from_numpy(host[k][n]), non_blocking=False)
         sw3.step(*bufs, frame0=k * F)
     assert torch.equal(sw3.finish(), want)
+
+
+def _choose_lists(sps, NP):
+    """The reference's per-frame lists (batchdataset.py:673-687, 712-716) for sparse frames: choose = flat index of
+    every masked pixel in row-major order, x/y_map_choosed = its column / row; ragged -> padded with n_valid."""
+    F = len(sps)
+    choose = np.zeros((F, NP), np.int64)
+    xm, ym = np.zeros((F, NP), np.float32), np.zeros((F, NP), np.float32)
+    nv = np.zeros(F, np.int32)
+    for f, sp in enumerate(sps):
+        n = sp["rows"].shape[0]
+        choose[f, :n] = sp["rows"].astype(np.int64) * synth.IMG_W + sp["cols"]
+        xm[f, :n], ym[f, :n], nv[f] = sp["cols"], sp["rows"], n
+    return choose, xm, ym, nv
+
+
+def test_gather_choose_forms_equal_mask_compaction(dev):
+    """pb_gather_choose: int64 lists with coordinate lists (the reference's interface), int32 lists with the
+    coordinates taken from the index, a crop with roi -- all give the mask-first compaction's output bit for bit."""
+    from pose_estimation_b200 import ops
+    F, cap = 6, 1280
+    sps = synth.make_batch_sparse(0x5EED, 2, F)
+    b = batch_arrays(sps)
+    t = lambda a: torch.from_numpy(a).to(dev)
+    want_pts, want_cnt = ops.compact_map(t(b["xyz"]), t(b["mask"]), t(b["extent"]), t(b["lfborder"]), cap)
+    choose, xm, ym, nv = _choose_lists(sps, 1216)
+    g = ops.ChooseGatherer(F, synth.IMG_H, synth.IMG_W, cap, device=dev)
+    forms = [dict(choose=t(choose), xmap=t(xm), ymap=t(ym), n_valid=t(nv)),
+             dict(choose=t(choose.astype(np.int32)), n_valid=t(nv)),
+             dict(choose=t(choose), n_valid=t(nv))]
+    for kw in forms:
+        pts, cnt = g(t(b["xyz"]), kw.pop("choose"), t(b["extent"]), t(b["lfborder"]), **kw)
+        assert torch.equal(cnt, want_cnt)
+        for f in range(F):
+            n = int(cnt[f])
+            assert torch.equal(pts[f, :, :n], want_pts[f, :, :n]), f
+    # pinned host map read in place
+    pts, cnt = g(torch.from_numpy(b["xyz"]).pin_memory(), t(choose), t(b["extent"]), t(b["lfborder"]), n_valid=t(nv))
+    assert all(torch.equal(pts[f, :, :int(cnt[f])], want_pts[f, :, :int(cnt[f])]) for f in range(F))
+    # wrap-padded fixed-length lists (the reference pads with np.pad(..., 'wrap')): NP entries, duplicates included
+    NPf = 1300
+    wrap = np.stack([np.resize(choose[f, :nv[f]], NPf) for f in range(F)])
+    g2 = ops.ChooseGatherer(F, synth.IMG_H, synth.IMG_W, NPf, device=dev)
+    pts, cnt = g2(t(b["xyz"]), t(wrap), t(b["extent"]), t(b["lfborder"]))
+    assert (cnt == NPf).all()
+    for f in range(F):
+        n = int(nv[f])
+        assert torch.equal(pts[f, :, :n], want_pts[f, :, :n]) and torch.equal(pts[f, :, n:NPf], want_pts[f, :, :NPf - n])
+
+
+def test_host_eval_sweep_choose_lists_equal_device_mask_path(dev):
+    """HostEvalSweep.run_choose (the reference's host-side interface: maps + choose / x_map / y_map lists) from
+    pinned host maps and from device-resident maps: the accuracy table of the mask path, bit for bit."""
+    from pose_estimation_b200 import sweep
+    F, chunk = 32, 8
+    sps = synth.make_batch_sparse(0x5EED, 2, F)
+    b = batch_arrays(sps)
+    models = torch.from_numpy(synth.class_models(500))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    t = lambda a: torch.from_numpy(a).to(dev)
+    sw = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev)
+    sw.step(t(b["xyz"]), t(b["mask"]), t(b["extent"]), t(b["lfborder"]), t(b["K4"]), t(b["cls"]), t(b["R_gt"]), t(b["t_gt"]))
+    want = sw.finish().cpu()
+    choose, xm, ym, nv = _choose_lists(sps, 1216)
+    pin = lambda a: torch.from_numpy(a).pin_memory()
+    small_h = sweep.pack_small(b["extent"], b["lfborder"], b["K4"], b["R_gt"], b["t_gt"], chunk).pin_memory()
+    hs = sweep.HostEvalSweep(models, diam, sym, synth.IMG_H, synth.IMG_W, 1280, chunk=chunk, device=dev, zero_copy=True)
+    xyz_h = pin(b["xyz"])
+    got = hs.run_choose(xyz_h, pin(choose), small_h, pin(b["cls"]), xmap_h=pin(xm), ymap_h=pin(ym), n_valid_h=pin(nv))
+    assert torch.equal(got, want) and hs.h2d_bytes == F * 1216 * 16 + F * 4 + small_h.numel() * 4 + F * 4
+    hs.reset()
+    got = hs.run_choose(t(b["xyz"]), pin(choose.astype(np.int32)), small_h, pin(b["cls"]), n_valid_h=pin(nv))
+    assert torch.equal(got, want)
+    # the sweep object's own step(choose=...) with lanes
+    sw3 = pb.EvalSweep(models, diam, sym, F, synth.IMG_H, synth.IMG_W, 1280, device=dev, lanes=2)
+    sw3.step(t(b["xyz"]), None, t(b["extent"]), t(b["lfborder"]), t(b["K4"]), t(b["cls"]), t(b["R_gt"]), t(b["t_gt"]),
+             choose=t(choose), xmap=t(xm), ymap=t(ym), n_valid=t(nv))
+    assert torch.equal(sw3.finish().cpu(), want)

@@ -253,3 +253,26 @@ def test_ransac_ragged_and_degenerate_batches_match_oracle(cref, dev):
                 assert np.array_equal(out["R"][f], np.eye(3, dtype=np.float32)) and np.all(out["t"][f] == 0), f
         assert np.all(np.isfinite(out["R"])) and np.all(np.isfinite(out["t"]))
     assert list(out["status"][:3]) == [1, 1, 1]                                 # fewer than 4 correspondences
+
+
+@pytest.mark.parametrize("cap", [40000, 6000])
+def test_compact_dense_silhouettes_across_tiles(cref, dev, cap):
+    """Dense, compact masks shaped like real LineMOD silhouettes (every pixel of the ellipsoid, 2 k .. 30 k px)
+    through the streaming mask-first kernel: blobs span several 16 K-pixel tiles of a frame, so the per-tile
+    ranks, the look-back over the earlier tiles and the cut at ``cap`` in the middle of a tile are all exercised;
+    many frames so that the persistent grid takes several tickets per CTA."""
+    F = 24
+    sps = [synth.make_frame_sparse(0x5EED, 12, f, dense=True, z_range=(0.45, 1.0)) for f in range(F)]
+    assert max(s["rows"].shape[0] for s in sps) > 16384 > min(s["rows"].shape[0] for s in sps)
+    b = batch_arrays(sps)
+    comp = ops.MapCompactor(F, synth.IMG_H, synth.IMG_W, cap, device=dev)
+    for rep in range(2):                                   # the workspace (ticket, tile states) is reset by every call
+        pts, count = comp(_t(b["xyz"], dev), _t(b["mask"], dev), _t(b["extent"], dev), _t(b["lfborder"], dev))
+        pts_h, count_h = pts.cpu().numpy(), count.cpu().numpy()
+        for f in range(F):
+            ref, tot = cref.compact_map(b["xyz"][f], b["mask"][f], b["extent"][f], b["lfborder"][f], cap=cap)
+            assert tot == sps[f]["rows"].shape[0] and count_h[f] == ref.shape[1] == min(tot, cap), f
+            assert np.array_equal(pts_h[f, :, :count_h[f]], ref), f
+    pts2, count2, total2 = ops.compact_map(_t(b["xyz"], dev), _t(b["mask"], dev), _t(b["extent"], dev),
+                                           _t(b["lfborder"], dev), cap, want_total=True)
+    assert torch.equal(count2, count) and np.array_equal(total2.cpu().numpy(), [s["rows"].shape[0] for s in sps])

@@ -6,14 +6,14 @@
 // next iteration's loads issued before the current block scan (register double buffer).
 // Kernels:
 //   compact_stream_kernel (mask given, H*W % 16 == 0): MASK-FIRST, one pass, no frame-sized state.
-//     The batch's masks are one stream of 16 KB tiles (16,384 px) handed out by an atomic ticket to a
-//     persistent grid; a CTA turns its tile into 1024 16-bit foreground words (next tile's 128-bit
-//     loads already in flight), most tiles are empty and end there.  A non-empty tile publishes its
-//     count, sums the counts of the earlier tiles of its frame (decoupled look-back over <= 18 words:
-//     tickets are taken in execution order, so a predecessor is always held by a running CTA), and
-//     emits its pixels BY RANK -- thread r finds the r-th foreground pixel of the tile by a binary
-//     search over the per-word prefix -- so the three plane loads and the five stores of consecutive
-//     output slots are issued by consecutive threads whatever the mask's density.  The xyz planes are
+//     The batch's masks are one stream of 64 KB tiles (65,536 px) handed out by an atomic ticket to a
+//     persistent grid; a CTA turns its tile into 4096 16-bit foreground words in shared memory (two
+//     waves of eight 128-bit loads per thread); most tiles are empty and end there.  A non-empty tile
+//     publishes its count, sums the counts of the earlier tiles of its frame (decoupled look-back over
+//     <= 4 words: tickets are taken in execution order, so a predecessor is always held by a running
+//     CTA), and emits its pixels BY RANK -- thread r finds the r-th foreground pixel of the tile by a
+//     binary search over the per-word prefix -- so the three plane loads and the five stores of
+//     consecutive output slots are issued by consecutive threads whatever the mask's density.  The xyz planes are
 //     read ONLY at foreground pixels: 0.3-0.4 MB per 480x640 frame instead of 4.0 MB.  The pointers may
 //     be device memory or pinned (mapped) host memory: with host maps the same kernel pulls just the
 //     mask and the touched sectors across PCIe (zero-copy gather).
@@ -312,10 +312,29 @@ __global__ void __launch_bounds__(CT) compact_sparse_kernel(CompactArgs a) {
 }
 
 // ---- mask-first, streaming: tiles by ticket + decoupled look-back ---------------------------------
-constexpr int SM_G = 4;                          // 128-bit mask loads per thread per tile
-constexpr int SM_GROUPS = CT * SM_G;             // 16-px groups per tile (1024)
-constexpr int SM_TILE_PX = SM_GROUPS * 16;       // 16,384 px = 16 KB of mask
+#ifndef PB_SM_G
+#define PB_SM_G 8
+#endif
+#ifndef PB_SM_W
+#define PB_SM_W 2
+#endif
+#ifndef PB_SM_OCC
+#define PB_SM_OCC 6
+#endif
+#ifndef PB_SM_PF
+#define PB_SM_PF 0
+#endif
+// Measured on a C2-shaped batch (scratch/k0_lab.cu, 1024 frames): G x W x OCC = 8 x 2 x 6 0.086 ms, 4 x 2 x 8 0.088,
+// 4 x 4 x 6 0.092, 4 x 4 x 8 0.107, 16 KB tiles (4 x 1 x 8) 0.098; prefetching the next wave (PB_SM_PF) does not help.
+constexpr int SM_G = PB_SM_G;                    // 128-bit mask loads per thread per wave (all in flight together)
+constexpr int SM_W = PB_SM_W;                    // waves per tile
+constexpr int SM_OCC = PB_SM_OCC;                // resident CTAs per SM the kernel is compiled for
+constexpr int SM_WGROUPS = CT * SM_G;            // 16-px groups per wave (1024)
+constexpr int SM_GROUPS = SM_WGROUPS * SM_W;     // 16-px groups per tile (4096)
+constexpr int SM_TILE_PX = SM_GROUPS * 16;       // 65,536 px = 64 KB of mask
+constexpr int SM_GPT = SM_GROUPS / CT;           // groups per thread in the rank scan (16 consecutive ones)
 constexpr uint32_t SM_FLAG = 0x80000000u;        // tile state word: FLAG | foreground count
+static_assert(SM_GPT % 8 == 0, "the rank scan reads its groups' 16-bit words as 128-bit shared-memory loads");
 
 __device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
     uint32_t r;
@@ -336,69 +355,93 @@ __device__ __forceinline__ int nth_bit16(uint32_t x, int n) {
     return b + ((n >= (int)(x & 1u)) ? 1 : 0);
 }
 
-__global__ void __launch_bounds__(CT, 4) compact_stream_kernel(CompactArgs a, uint32_t* __restrict__ state,
-                                                            unsigned int* __restrict__ ticket, int tpf, int ntiles) {
-    __shared__ int s_gpre[SM_GROUPS];            // exclusive prefix of the groups' foreground counts (tile-local)
-    __shared__ uint16_t s_gbits[SM_GROUPS];
-    __shared__ int s_wcnt[CT / 32];              // per-warp counts (a warp owns 128 consecutive groups)
-    __shared__ int s_next[2];
+__global__ void __launch_bounds__(CT, SM_OCC) compact_stream_kernel(CompactArgs a, uint32_t* __restrict__ state,
+                                                                    unsigned int* __restrict__ ticket, int tpf, int ntiles) {
+    __shared__ int s_gpre[SM_GROUPS];                    // exclusive prefix of the groups' foreground counts (tile-local)
+    __shared__ __align__(16) uint16_t s_gbits[SM_GROUPS];
+    __shared__ int s_wcnt[CT / 32];
+    __shared__ int s_next;
     __shared__ int s_fbase;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int gpf = a.HW >> 4;                   // 16-px groups per frame
+    const int gpf = a.HW >> 4;                           // 16-px groups per frame
 
-    auto load_tile = [&](int tile, uint4 (&m)[SM_G]) {
+    for (;;) {
+        // A ticket is taken only when the CTA is ready to process the tile: its count is then published a few load
+        // latencies later, whatever other tiles are waiting for -- a ticket held across another tile's look-back
+        // (to prefetch) chains the CTAs into a wavefront (measured: 10x slower).  Latency is hidden by occupancy.
+        if (tid == 0) s_next = (int)atomicAdd(ticket, 1u);
+        __syncthreads();
+        const int tile = s_next;
+        if (tile >= ntiles) break;
         const int f = tile / tpf, ti = tile - f * tpf;
         const uint4* pm = reinterpret_cast<const uint4*>(a.mask + (size_t)f * a.HW) + (size_t)ti * SM_GROUPS;
         const int ng = min(SM_GROUPS, gpf - ti * SM_GROUPS);
+        // ---- mask -> 16-bit foreground words in shared memory, SM_W waves of SM_G 128-bit loads per thread
+        uint32_t seen = 0u;
+        auto load_wave = [&](int w, uint4 (&m)[SM_G]) {
 #pragma unroll
-        for (int k = 0; k < SM_G; ++k) {
-            const int g = warp * (32 * SM_G) + k * 32 + lane;           // a load instruction covers 512 contiguous bytes
-            m[k] = g < ng ? ldg_stream_u4(pm + g) : make_uint4(0u, 0u, 0u, 0u);
-        }
-    };
-
-    if (tid == 0) s_next[0] = (int)atomicAdd(ticket, 1u);
-    __syncthreads();
-    int tile = s_next[0];
-    uint4 m[SM_G];
-    if (tile < ntiles) load_tile(tile, m);
-    for (int it = 1; tile < ntiles; ++it) {
-        if (tid == 0) s_next[it & 1] = (int)atomicAdd(ticket, 1u);     // read after the barrier below
-        const int f = tile / tpf, ti = tile - f * tpf;
-        uint32_t bits[SM_G];
-        int c[SM_G], cs = 0;
+            for (int k = 0; k < SM_G; ++k) {
+                const int g = w * SM_WGROUPS + warp * (32 * SM_G) + k * 32 + lane;   // a load instruction covers 512 contiguous bytes
+                m[k] = g < ng ? ldg_stream_u4(pm + g) : make_uint4(0u, 0u, 0u, 0u);
+            }
+        };
+        auto bits_wave = [&](int w, const uint4 (&m)[SM_G]) {
 #pragma unroll
-        for (int k = 0; k < SM_G; ++k) {
-            bits[k] = 0u;
-            if (m[k].x | m[k].y | m[k].z | m[k].w)                      // most of a frame is background
-                bits[k] = nz4(m[k].x) | (nz4(m[k].y) << 4) | (nz4(m[k].z) << 8) | (nz4(m[k].w) << 12);
-            c[k] = __popc(bits[k]);
-            cs += c[k];
+            for (int k = 0; k < SM_G; ++k) {
+                const int g = w * SM_WGROUPS + warp * (32 * SM_G) + k * 32 + lane;
+                uint32_t bits = 0u;
+                if (m[k].x | m[k].y | m[k].z | m[k].w)                  // most of a frame is background
+                    bits = nz4(m[k].x) | (nz4(m[k].y) << 4) | (nz4(m[k].z) << 8) | (nz4(m[k].w) << 12);
+                s_gbits[g] = (uint16_t)bits;
+                seen |= bits;
+            }
+        };
+#if PB_SM_PF
+        {   // wave w + 1 is in flight while wave w is turned into bits (two register buffers)
+            uint4 ma[SM_G], mb[SM_G];
+            load_wave(0, ma);
+#pragma unroll
+            for (int w = 0; w < SM_W; w += 2) {
+                if (w + 1 < SM_W) load_wave(w + 1, mb);
+                bits_wave(w, ma);
+                if (w + 2 < SM_W) load_wave(w + 2, ma);
+                if (w + 1 < SM_W) bits_wave(w + 1, mb);
+            }
         }
+#else
+#pragma unroll 1
+        for (int w = 0; w < SM_W; ++w) {
+            uint4 m[SM_G];
+            load_wave(w, m);
+            bits_wave(w, m);
+        }
+#endif
         const bool last = ti == tpf - 1;                                // the frame's last tile writes count[f]
-        const int any = __syncthreads_or(cs);
-        const int next = s_next[it & 1];
-        if (next < ntiles) load_tile(next, m);                          // in flight under the rest of this tile
+        const int any = __syncthreads_or((int)seen);                    // (s_next is rewritten only after this barrier)
         if (!any && !last) {
             if (tid == 0) st_volatile_u32(state + tile, SM_FLAG);
-            tile = next;
             continue;
         }
-        // ---- tile-local ranks: pixel order is (warp, load k, lane) = group index order
-        int pre = 0;                                                    // this warp's pixels before load k
-        int excl[SM_G];
+        // ---- tile-local ranks: thread t scans the SM_GPT consecutive groups t*SM_GPT ..
+        uint32_t wbits[SM_GPT / 2];                                     // two 16-bit words per register
+        {
+            const uint4* sb = reinterpret_cast<const uint4*>(s_gbits) + tid * (SM_GPT / 8);
 #pragma unroll
-        for (int k = 0; k < SM_G; ++k) {
-            int v = c[k];
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const int o = __shfl_up_sync(0xffffffffu, v, off);
-                if (lane >= off) v += o;
+            for (int q = 0; q < SM_GPT / 8; ++q) {
+                const uint4 v = sb[q];
+                wbits[4 * q] = v.x; wbits[4 * q + 1] = v.y; wbits[4 * q + 2] = v.z; wbits[4 * q + 3] = v.w;
             }
-            excl[k] = pre + v - c[k];
-            pre += __shfl_sync(0xffffffffu, v, 31);
         }
-        if (lane == 0) s_wcnt[warp] = pre;
+        int mine = 0;
+#pragma unroll
+        for (int j = 0; j < SM_GPT / 2; ++j) mine += __popc(wbits[j]);
+        int incl = mine;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += o;
+        }
+        if (lane == 31) s_wcnt[warp] = incl;
         __syncthreads();
         int total = 0, wbase = 0;
 #pragma unroll
@@ -408,11 +451,15 @@ __global__ void __launch_bounds__(CT, 4) compact_stream_kernel(CompactArgs a, ui
             total += v;
         }
         if (tid == 0) st_volatile_u32(state + tile, SM_FLAG | (uint32_t)total);
+        {
+            int run = wbase + incl - mine;
 #pragma unroll
-        for (int k = 0; k < SM_G; ++k) {
-            const int g = warp * (32 * SM_G) + k * 32 + lane;
-            s_gpre[g] = wbase + excl[k];
-            s_gbits[g] = (uint16_t)bits[k];
+            for (int j = 0; j < SM_GPT / 2; ++j) {
+                s_gpre[tid * SM_GPT + 2 * j] = run;
+                run += __popc(wbits[j] & 0xFFFFu);
+                s_gpre[tid * SM_GPT + 2 * j + 1] = run;
+                run += __popc(wbits[j] >> 16);
+            }
         }
         // ---- look-back: foreground pixels of the frame's earlier tiles (warp 0; lanes poll one word each)
         if (warp == 0) {
@@ -445,8 +492,8 @@ __global__ void __launch_bounds__(CT, 4) compact_stream_kernel(CompactArgs a, ui
             const int pix0 = ti * SM_TILE_PX;
             for (int r = tid; r < nout; r += CT) {
                 int lo = 0, hi = SM_GROUPS;                             // last group with s_gpre <= r
-#pragma unroll
-                for (int stp = 0; stp < 10; ++stp) {                    // SM_GROUPS = 2^10
+#pragma unroll 1
+                while (hi - lo > 1) {
                     const int mid = (lo + hi) >> 1;
                     if (s_gpre[mid] <= r) lo = mid; else hi = mid;
                 }
@@ -465,7 +512,6 @@ __global__ void __launch_bounds__(CT, 4) compact_stream_kernel(CompactArgs a, ui
             if (a.total) a.total[f] = fbase + total;
         }
         __syncthreads();                                                // s_gpre / s_gbits / s_wcnt / s_fbase are reused
-        tile = next;
     }
 }
 

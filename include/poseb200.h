@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define PB_ABI_VERSION 1
+#define PB_ABI_VERSION 2
 
 /* status codes written to status[F] */
 #define PB_STATUS_OK 0
@@ -57,6 +57,10 @@ typedef struct pb_sim3_params {
     float    confidence;       /* 0.99 (:22): stop once 1 - (1 - ratio^5)^i exceeds it                            */
     float    min_inlier_ratio; /* 0.1 (:50): below it the reference returns None -> PB_STATUS_NO_MODEL            */
     uint32_t seed_lo, seed_hi; /* Philox key; replaces np.random.randint(nPoints, size=5) (:32)                   */
+    int32_t  rule;             /* 0 = lib/transform/umeyama.py (best inlier ratio, confidence break);
+                                  1 = the older lib/transform/trans.py:47-90 (smallest total residual wins, stop below
+                                  PassThreshold / 100, thresholds from the clouds' mean norms; n_iter = 100 there;
+                                  confidence is unused; hyp_counts = its nInliers, which skips index 0)            */
 } pb_sim3_params;
 
 const char* pb_last_error(void);
@@ -153,6 +157,35 @@ int pb_sim3_ransac(const float* src, const float* dst, const int32_t* count, int
 /* batched estimateSimilarityUmeyama (umeyama.py:65-97): least-squares similarity over all pairs. */
 int pb_umeyama_fit(const float* src, const float* dst, const int32_t* count, int B, int cap, float* scale,
                    float* R, float* t, int32_t* status, void* stream);
+
+/* ---- batched rigid fit + ICP-style refinement (version/transparent/lib/declarative/leastsquares.py:10-48,
+ *      version/transparent/scripts/train_declarative.py:80-100) ------------------------------------------------
+ * pb_kabsch_fit = best_batch_fit_transform: for each of B problems the rotation R [B,9] and translation t [B,3]
+ * with  Bm ~ R A + t  in the least-squares sense (proper rotation: the reflection case of :38-43 included), and
+ * the two centroids (optional).  A / Bm [B,cap,3], count [B] or NULL (-> cap points each).  status optional:
+ * PB_STATUS_NO_MODEL where the points have no spread (then R = I, t = centroid shift).
+ * pb_icp_refine: n_steps times { pred = model R^T + t; idx = nearest target point of every pred point
+ * (pb_knn1 / the tensor-core path when use_tc); (opt_R, opt_t) = rigid fit pred -> target[idx]; compose } with
+ * R [B,9] / t [B,3] updated in place.  compose 0 is the reference's update as written (:98-99: R <- R opt_R,
+ * t <- t + opt_t); compose 1 is the rigid-motion composition (R <- opt_R R, t <- opt_R t + opt_t).
+ * model [B or 1,N,3], target [B or 1,M,3]; ws: pb_icp_refine_workspace_bytes, 128-byte aligned.              */
+int pb_kabsch_fit(const float* A, const float* Bm, const int32_t* count, int B, int cap, float* R, float* t,
+                  float* centroid_A, float* centroid_B, int32_t* status, void* stream);
+size_t pb_icp_refine_workspace_bytes(int B, int N, int M);
+int pb_icp_refine(const float* model, int model_shared, const float* target, int target_shared, float* R, float* t,
+                  int B, int N, int M, int n_steps, int compose, int use_tc, int32_t* status, void* ws,
+                  size_t ws_bytes, void* stream);
+
+/* ---- depth back-projection (dataset/linemod/batchdataset.py:712-721, lib/transform/coordinate.py:91-101) ------
+ * pb_backproject_cloud: cloud[f,i,:] = ((x - cx) d / fx, (y - cy) d / fy, d) with d = depth[f, choose[f,i]] * depth_scale
+ * -- the `cloud` the T-offset vote consumes, made on the device from the depth crop and the same choose /
+ * x_map / y_map lists as pb_gather_choose (xmap / ymap NULL -> from the index and roi).  depth [F,Hh,Ww] f32.
+ * Float32 operation order of the reference: (x - cx) * d / fx.
+ * pb_uvd2cloud: the list form, uvd [B,n,3] (u, v, depth) and one camera matrix K [9] (row major) -> xyz [B,n,3]. */
+int pb_backproject_cloud(const float* depth, const void* choose, int choose_is_i32, const float* xmap,
+                         const float* ymap, const int32_t* roi, const float* K4, float depth_scale, int F, int Hh,
+                         int Ww, int NP, float* cloud, void* stream);
+int pb_uvd2cloud(const float* uvd, const float* K9, int B, int n, float* xyz, void* stream);
 
 /* ---- farthest point sampling (tools/script/sample_model.py:33-63) ----------------------------------
  * For each of B clouds pts [B,cap,3] (count[b] valid points, NULL -> cap): idx[b, 0] = 0, then

@@ -7,9 +7,10 @@ without a GPU raises.
 """
 from .api import (BPnP, BPnPModle, Metric, TransparentMetric, PossLoss, PoseLoss, RansacConfig, batch_intrinsic_transform, cal_dis,  # noqa: F401
                   choose_ransac_batch, estimateSimilarityTransform, estimateSimilarityUmeyama, get_pose, get_xyz, knn,
-                  vote_translation)
-from .sweep import EvalSweep, reduce_table, shard_range, summarize  # noqa: F401
+                  vote_translation, trans_estimateSimilarityTransform, best_batch_fit_transform, icp_refine, uvd2cloud)
+from .sweep import EvalSweep, format_report, reduce_table, shard_range, summarize  # noqa: F401
 
 __all__ = ["Metric", "PoseLoss", "RansacConfig", "batch_intrinsic_transform", "cal_dis",
            "choose_ransac_batch", "get_pose", "knn", "vote_translation", "EvalSweep", "reduce_table",
-           "shard_range", "summarize", "estimateSimilarityTransform", "estimateSimilarityUmeyama", "BPnP", "BPnPModle", "PossLoss", "TransparentMetric", "get_xyz"]
+           "shard_range", "summarize", "estimateSimilarityTransform", "estimateSimilarityUmeyama", "BPnP", "BPnPModle", "PossLoss", "TransparentMetric", "get_xyz",
+           "trans_estimateSimilarityTransform", "best_batch_fit_transform", "icp_refine", "uvd2cloud", "format_report"]

@@ -57,6 +57,11 @@ SIGNATURES = {
     "pb_sim3_ransac_workspace_bytes": (SZ, [I, P]),
     "pb_sim3_ransac": (I, [P, P, P, I, I, U32, P, P, P, P, P, P, P, P, P, P, P, SZ, P]),
     "pb_umeyama_fit": (I, [P, P, P, I, I, P, P, P, P, P]),
+    "pb_kabsch_fit": (I, [P, P, P, I, I, P, P, P, P, P, P]),
+    "pb_icp_refine_workspace_bytes": (SZ, [I, I, I]),
+    "pb_icp_refine": (I, [P, I, P, I, P, P, I, I, I, I, I, I, P, P, SZ, P]),
+    "pb_backproject_cloud": (I, [P, P, I, P, P, P, P, F32, I, I, I, I, P, P]),
+    "pb_uvd2cloud": (I, [P, P, I, I, P, P]),
     "pb_fps_workspace_bytes": (SZ, [I, I]),
     "pb_fps": (I, [P, P, I, I, I, P, P, SZ, P]),
     "pb_pnp_refine": (I, [P, P, I, P, P, P, P, I, I, I, P, P, P, P]),
@@ -92,7 +97,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the .so does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.pb_abi_version() != 1:
+    if lib.pb_abi_version() != 2:
         raise PoseB200Error("libposeb200.so ABI version mismatch")
     _lib = lib
     return lib

@@ -276,6 +276,7 @@ def _sim3_out(scale, R, t):
 
 def estimateSimilarityTransform(source, target, verbose=False, cfg: ops_sim3.Sim3Config | None = None, device="cuda"):
     """lib/transform/umeyama.py:8-62: RANSAC similarity fit target ~ Scale * Rotation @ source + Translation.
+    (cfg.rule = 'trans' runs the older rule of lib/transform/trans.py instead; see trans_estimateSimilarityTransform.)
     source / target: (N,3) arrays.  Returns (Scale, Rotation, Translation, OutTransform), or four ``None`` when the
     best inlier ratio is below 0.1 (the reference's failure return, :50-52).  The 5-point draws come from the
     counter RNG of ``cfg.seed`` instead of numpy's global state."""
@@ -289,6 +290,48 @@ def estimateSimilarityTransform(source, target, verbose=False, cfg: ops_sim3.Sim
             print("[ WARN ] - Something is wrong. Small BestInlierRatio")
         return None, None, None, None
     return _sim3_out(res.scale[0], res.R[0], res.t[0])
+
+
+def trans_estimateSimilarityTransform(source, target, verbose=False, cfg: ops_sim3.Sim3Config | None = None, device="cuda"):
+    """lib/transform/trans.py:9-45 (the copy tools/script/eval.py imports): 100 iterations, the hypothesis with the
+    smallest total residual wins, thresholds from the clouds' mean norms.  Returns what trans.py returns, quirks
+    included: Scales as a length-3 array, Rotation = the TRANSPOSE of the rotation that maps source to target,
+    OutTransform[:3,:3] = diag(Scales) @ Rotation, or four ``None`` below an inlier ratio of 0.1."""
+    cfg = cfg or ops_sim3.Sim3Config(n_iter=100, rule="trans")
+    if cfg.rule != "trans":
+        raise ValueError("trans_estimateSimilarityTransform needs cfg.rule == 'trans'")
+    src = torch.as_tensor(np.asarray(source), dtype=torch.float32, device=device).reshape(1, -1, 3).contiguous()
+    dst = torch.as_tensor(np.asarray(target), dtype=torch.float32, device=device).reshape(1, -1, 3).contiguous()
+    res = ops_sim3.sim3_ransac(src, dst, cfg=cfg)
+    if int(res.status.item()) != 0:
+        if verbose:
+            print("[ WARN ] - Something is wrong. Small BestInlierRatio")
+        return None, None, None, None
+    S, Rn, Tn, M = _sim3_out(res.scale[0], res.R[0], res.t[0])
+    return np.array([S, S, S]), Rn, Tn, M
+
+
+def best_batch_fit_transform(A, B):
+    """version/transparent/lib/declarative/leastsquares.py:10-48: least-squares rigid transform mapping A onto B,
+    A, B [c,N,3] -> (R [c,3,3], t [c,3], centroid_A [c,3], centroid_B [c,3]) on the device.  (The reference subtracts
+    its [c,3] centroids from [c,N,3] without a singleton axis, so it only runs for c == 1 or c == N; this is the
+    per-problem fit it means.)"""
+    R, t, _, cA, cB = ops_sim3.kabsch_fit(_dev(A).float(), _dev(B).float(), want_centroids=True)
+    return R, t, cA, cB
+
+
+def icp_refine(model_points, target, final_r, final_t, steps=10, compose="reference"):
+    """The optimisation loop of version/transparent/scripts/train_declarative.py:80-100 for all hypotheses at once
+    (transform -> knn -> gather -> best_batch_fit_transform -> compose); see ops_sim3.icp_refine."""
+    R, t, _ = ops_sim3.icp_refine(_dev(model_points).float(), _dev(target).float(), _dev(final_r).float(),
+                                  _dev(final_t).float(), n_steps=steps, compose=compose)
+    return R, t
+
+
+def uvd2cloud(uvd, K):
+    """lib/transform/coordinate.py:91-101 -> xyz [bs,n,3] (the docstring's shape; the reference's torch.cat along the
+    last axis returns [bs,3n])."""
+    return ops_sim3.uvd2cloud(_dev(uvd).float(), _dev(K).float())
 
 
 def estimateSimilarityUmeyama(SourceHom, TargetHom, device="cuda"):

@@ -52,6 +52,38 @@ def summarize(table: torch.Tensor, objlist):
     return out
 
 
+def format_report(table: torch.Tensor, objlist, opt_pose=False):
+    """The per-object lines and the closing all-objects block that the reference's test loop logs
+    (tools/trainer.py:281-330), character for character, from the [24,C] table.  Returns (list of per-object
+    strings, all-objects string)."""
+    res = ops_metric.table_to_result(table, objlist)
+    n = lambda i: float(res["obj_num"][i])
+    lines = []
+    for i in objlist:
+        q = lambda k: float(res[k][i]) / n(i)
+        blk = lambda v: (f'ADD-S Dis:{q(f"dis_{v}_rt"):.04f} Succ:{q(f"succ_{v}_rt"):.03f}; '
+                         f'5° Dis:{q(f"dis_{v}_r"):5.2f} Succ:{q(f"succ_{v}_r"):.03f}; ')
+        if opt_pose:
+            content = (f'Object {i} Fnl Dis:{q("dis_final_rt"):.04f} Succ:{q("succ_final_rt"):.03f}\n'
+                       + 'Base ' + blk("base") + f'5CM Dis:{q("dis_base_t"):.04f} Succ:{q("succ_base_t"):.03f};' + '\n'
+                       + 'Regs ' + blk("reg") + f'5CM Dis:{q("dis_reg_t"):.04f} Succ:{q("succ_reg_t"):.03f};' + '\n'
+                       + 'Fnal ' + blk("final") + f'5CM Dis:{q("dis_final_t"):.04f} Succ:{q("succ_final_t"):.03f};' + '\n'
+                       + f'XYZ Dis: {q("dis_xyz"):.04f}; NML Dis: {q("dis_normal"):.04f}; MASK Dis: {q("dis_mask"):.04f}; ')
+        else:
+            content = (f'Object {i} ' + 'Base ' + blk("base")
+                       + f'5CM Dis:{q("dis_base_t"):.04g} Succ:{q("succ_base_t"):.03f}; '
+                       + f'XYZ Dis: {q("dis_xyz"):.04f}; NML Dis: {q("dis_normal"):.04f}; MASK Dis: {q("dis_mask"):.04f}; ')
+        lines.append(content)
+    tot = float(sum(res["obj_num"].values()))
+    g = lambda k: float(sum(res[k].values())) / tot
+    ablk = lambda v: (f'ADD-S Dis:{g(f"dis_{v}_rt"):.04f} Succ:{g(f"succ_{v}_rt"):.03f}; '
+                      f'5° Dis:{g(f"dis_{v}_r"):5.2f} Succ:{g(f"succ_{v}_r"):.03f}; '
+                      f'5CM Dis:{g(f"dis_{v}_t"):.04f} Succ:{g(f"succ_{v}_t"):.03f};')
+    all_content = ('\n' + 'Base ' + ablk("base") + '\n' + 'Regs ' + ablk("reg") + '\n' + 'Fnal ' + ablk("final") + '\n'
+                   + f'XYZ Dis: {g("dis_xyz"):.04f}; NML Dis: {g("dis_normal"):.04f}; MASK Dis: {g("dis_mask"):.04f}; ')
+    return lines, all_content
+
+
 class EvalSweep:
     """map -> pose -> ADD(-S)/r/t -> accuracy table, all on one stream, no host sync per batch.
 

@@ -366,3 +366,74 @@ def test_auc_of_oracle_and_product_match_reference_run():
         assert abs(ProductMetric([]).cal_auc(d) - want) < 1e-9, k
     assert abs(ProductMetric([]).cal_auc(list(g["auc_in"])) - float(g["auc_out"])) < 1e-9
     assert ProductMetric([]).cal_auc([0.5, 0.7]) == 0
+
+
+# ---- SURVEY 8(f) row f3 remainder: oracle/f3_ref.py against runs of the reference's own files -----------------
+@pytest.fixture(scope="module")
+def f3():
+    return np.load(os.path.join(GOLD, "f3_ref.npz"))
+
+
+def test_f3_kabsch_oracle_matches_reference_run(f3):
+    """leastsquares.py:10-48 run by gen_golden_f3.py (float32 SVD) vs the float64 restatement."""
+    from oracle import f3_ref
+    for k in range(int(f3["kab_n"])):
+        R, t, cA, cB = f3_ref.kabsch(f3[f"kab{k}_A"], f3[f"kab{k}_B"])
+        assert abs(np.linalg.det(R) - 1.0) < 1e-9
+        if k != 3:                                  # planar cloud: the reference's float32 SVD is loose there
+            assert np.abs(R - f3[f"kab{k}_R"]).max() < 5e-5, k
+            assert np.abs(t - f3[f"kab{k}_t"]).max() < 5e-5, k
+        assert np.abs(cA - f3[f"kab{k}_cA"]).max() < 1e-6 and np.abs(cB - f3[f"kab{k}_cB"]).max() < 1e-6
+        # both are least-squares optimal: same residual
+        A, B = f3[f"kab{k}_A"].astype(np.float64), f3[f"kab{k}_B"].astype(np.float64)
+        r_ours = np.linalg.norm(A @ R.T + t - B)
+        r_ref = np.linalg.norm(A @ f3[f"kab{k}_R"].astype(np.float64).T + f3[f"kab{k}_t"] - B)
+        assert r_ours <= r_ref * (1 + 1e-5) + 1e-7, k
+
+
+def test_f3_icp_oracle_matches_reference_loop(f3):
+    from oracle import f3_ref
+    for mode in ("reference", "rigid"):
+        for h in range(3):
+            R, t = f3_ref.icp_refine(f3["icp_model"], f3["icp_target"], f3["icp_R0"][h], f3["icp_t0"][h], 10, mode)
+            assert np.abs(R - f3[f"icp_{mode}_R"][h]).max() < 2e-4, (mode, h)
+            assert np.abs(t - f3[f"icp_{mode}_t"][h]).max() < 2e-4, (mode, h)
+    # the rigid composition converges onto the ground-truth pose; the script's own update rule need not
+    for h in range(3):
+        assert np.abs(f3["icp_rigid_R"][h] - f3["icp_Rg"]).max() < 2e-3 and np.abs(f3["icp_rigid_t"][h] - f3["icp_tg"]).max() < 1e-3
+
+
+def test_f3_trans_oracle_matches_reference_run(f3):
+    """lib/transform/trans.py run with np.random.randint recorded: every iteration's residual and inlier ratio,
+    the threshold, success and the returned transform."""
+    from oracle import f3_ref
+    for k in range(int(f3["tr_n"])):
+        n_it = int(f3[f"tr{k}_niter"])
+        o = f3_ref.trans_ransac(f3[f"tr{k}_src"], f3[f"tr{k}_dst"], f3[f"tr{k}_idx"][:n_it])
+        n = f3[f"tr{k}_src"].shape[0]
+        assert abs(o["pass_t"] - float(f3[f"tr{k}_pass_t"])) < 1e-12
+        assert np.allclose(o["residuals"], f3[f"tr{k}_residual"], rtol=1e-10, atol=0)
+        assert np.array_equal(o["n_inl"] / n, f3[f"tr{k}_ratio"])
+        assert bool(o["ok"]) == bool(f3[f"tr{k}_ok"])
+        if o["ok"]:
+            assert np.allclose(o["Scales"], f3[f"tr{k}_S"], rtol=1e-10) and np.allclose(o["Rotation"], f3[f"tr{k}_R"], atol=1e-10)
+            assert np.allclose(o["Translation"], f3[f"tr{k}_T"], atol=1e-9) and np.allclose(o["OutTransform"], f3[f"tr{k}_M"], atol=1e-9)
+
+
+def test_f3_uvd2cloud_oracle_matches_reference_run(f3):
+    from oracle import f3_ref
+    assert np.array_equal(f3_ref.uvd2cloud(f3["uvd"], f3["uvd_K"]), f3["uvd_xyz"])
+
+
+def test_report_format_matches_reference_lines():
+    """sweep.format_report against the statements of tools/trainer.py:281-330 executed as they stand."""
+    import json
+    import torch
+    from pose_estimation_b200 import sweep
+    rep = json.load(open(os.path.join(GOLD, "report_ref.json")))
+    table = torch.tensor(rep["table"], dtype=torch.float64)
+    for key, opt_pose in (("base", False), ("opt_pose", True)):
+        lines, all_content = sweep.format_report(table, rep["objlist"], opt_pose=opt_pose)
+        ref = rep[key]
+        assert ref[-1] == all_content and ref[-2] == '\n'
+        assert ref[:len(lines)] == lines

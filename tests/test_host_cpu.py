@@ -24,12 +24,12 @@ def test_library_exports_every_declared_symbol():
     lib = _lib.load()
     for name in declared:
         assert hasattr(lib, name)
-    assert lib.pb_abi_version() == 1
+    assert lib.pb_abi_version() == 2            # 2: pb_sim3_params gained `rule`
     # size queries are host-only and safe without a GPU
     import ctypes as C
     prm = _lib.RansacParams(256, 1.0, 6, 0, 5, 1, 0)
     assert lib.pb_ransac_workspace_bytes(1024, 1280, C.byref(prm)) >= 1024 * 256 * 48
-    assert lib.pb_compact_workspace_bytes(1024, 480, 640, 1280) == 0          # one band per frame
+    assert lib.pb_compact_workspace_bytes(1024, 480, 640, 1280) == 256 + 1024 * 5 * 4   # ticket + one state word per 64 KB tile
     assert lib.pb_compact_workspace_bytes(4, 480, 640, 1280) > 0
     assert lib.pb_pnp_ransac_map_workspace_bytes(8, 480, 640, 1280, C.byref(prm)) > 8 * 5 * 1280 * 4
     # argument errors come back as codes + message, never as exceptions/crashes

@@ -309,3 +309,36 @@ def resample_inliers(inl_bitmap, count, cap, n, seed=0x5EED, frame0=0):
     call("pb_resample_inliers", _ptr(inl_bitmap), _ptr(count), F, cap, n, frame0, seed & 0xFFFFFFFF,
          (seed >> 32) & 0xFFFFFFFF, _ptr(out), _stream(out))
     return out
+
+
+class FrameGenerator:
+    """Device-side generator of config C5's frames (csrc/synthgen.cu): writes the foreground pixels of a chunk of F
+    frames into a zeroed slab (xyz [F,3,H,W] f32, mask [F,H,W] u8 -- owned here) and erases exactly those pixels
+    again, so a sweep over many chunks never touches the 4 MB per frame of background.  Measurement infrastructure:
+    the per-frame parameters come from synth.c5_params (host, a pure function of (seed, frame index))."""
+
+    def __init__(self, F, H, W, seed, device="cuda"):
+        dev = torch.device(device)
+        self.F, self.H, self.W, self.seed = F, H, W, int(seed)
+        self.xyz = torch.zeros((F, 3, H, W), dtype=torch.float32, device=dev)
+        self.mask = torch.zeros((F, H, W), dtype=torch.uint8, device=dev)
+        self.area = torch.zeros((F,), dtype=torch.int32, device=dev)
+        self.params, self.frame0, self.bbox_max = None, 0, 1
+
+    def _launch(self, erase):
+        call("pb_synth_frames", _ptr(self.params), self.params.shape[0], self.H, self.W, self.bbox_max,
+             self.seed & 0xFFFFFFFF, (self.seed >> 32) & 0xFFFFFFFF, self.frame0, _ptr(self.xyz), _ptr(self.mask),
+             _ptr(self.area), 1 if erase else 0, _stream(self.xyz))
+
+    def write(self, params, frame0, bbox_max):
+        """params [n <= F, 40] f32 CUDA (synth.c5_params(...)['params']), frame0 = global index of its first frame."""
+        if self.params is not None:
+            raise RuntimeError("erase() the previous chunk first: the slab must be zero outside the new silhouettes")
+        self.params, self.frame0, self.bbox_max = _chk(params, torch.float32, "params"), int(frame0), int(bbox_max)
+        self._launch(False)
+        return self.xyz, self.mask
+
+    def erase(self):
+        if self.params is not None:
+            self._launch(True)
+            self.params = None

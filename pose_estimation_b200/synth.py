@@ -164,3 +164,129 @@ def compact_points(sp):
 
 def make_batch_sparse(seed: int, config_id: int, n_frames: int, first_frame: int = 0, **kw):
     return [make_frame_sparse(seed, config_id, first_frame + f, **kw) for f in range(n_frames)]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Config C5: frames generated ON THE DEVICE by csrc/synthgen.cu; this is its NumPy twin.
+# The per-frame parameters come from the host (cheap: 40 floats per frame, a pure function of (seed, frame index),
+# so every sharding of the sweep sees the same frames); the per-pixel work -- ray / ellipsoid hit, keep / outlier /
+# noise draws from Philox4x32-10 -- is IEEE float32 in a written order on both sides, so the bytes are identical.
+C5_PARAM_STRIDE = 40
+C5_TAG = 0x47454E35
+C5_PARAM_TAG = 0x50415235
+
+
+def philox4x32(c0, c1, c2, c3, k0, k1):
+    """Vectorised Philox4x32-10 (Random123): uint32 arrays / scalars in, four uint32 arrays out."""
+    c = [np.asarray(v, np.uint64) & np.uint64(0xFFFFFFFF) for v in np.broadcast_arrays(c0, c1, c2, c3)]
+    k0, k1 = np.uint64(k0 & 0xFFFFFFFF), np.uint64(k1 & 0xFFFFFFFF)
+    M0, M1, MASK = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57), np.uint64(0xFFFFFFFF)
+    for _ in range(10):
+        p0, p1 = M0 * c[0], M1 * c[2]
+        hi0, lo0, hi1, lo1 = p0 >> np.uint64(32), p0 & MASK, p1 >> np.uint64(32), p1 & MASK
+        c = [hi1 ^ c[1] ^ k0, lo1, hi0 ^ c[3] ^ k1, lo0]
+        k0 = (k0 + np.uint64(0x9E3779B9)) & MASK
+        k1 = (k1 + np.uint64(0xBB67AE85)) & MASK
+    return [v.astype(np.uint32) for v in c]
+
+
+def _u01(r):
+    return (r >> np.uint32(8)).astype(np.float32) * np.float32(2.0 ** -24)
+
+
+def c5_params(seed: int, frame0: int, n: int, p_range=(800, 1200), outlier_frac=0.25, noise_m=1e-3,
+              K4=LINEMOD_K4, H=IMG_H, W=IMG_W, z_range=(0.6, 1.2)):
+    """Per-frame parameters [n,40] f32 of frames frame0 .. frame0+n (layout: csrc/synthgen.cu) plus the
+    per-frame arrays the evaluation needs: dict(params, cls, R_gt, t_gt, extent, lfborder, K4, bbox_max)."""
+    f = np.arange(frame0, frame0 + n, dtype=np.uint64)
+    u = []
+    for k in range(3):                                  # 12 uniforms per frame from counters (frame, k)
+        u += [(r.astype(np.float64) + 0.5) / 2.0 ** 32 for r in philox4x32(f, k, 0, C5_PARAM_TAG, seed, seed >> 32)]
+    u = np.stack(u, axis=1)
+    # rotation: quaternion from four normals (Box-Muller), host float64 -- only its float32 rounding is shared
+    g = np.sqrt(-2.0 * np.log(u[:, 0:2]))
+    q = np.stack([g[:, 0] * np.cos(2 * np.pi * u[:, 2]), g[:, 0] * np.sin(2 * np.pi * u[:, 2]),
+                  g[:, 1] * np.cos(2 * np.pi * u[:, 3]), g[:, 1] * np.sin(2 * np.pi * u[:, 3])], axis=1)
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    w, x, y, z = q.T
+    R = np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                  2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                  2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)], axis=1).astype(np.float32)
+    t = np.stack([(u[:, 4] * 0.3 - 0.15), (u[:, 5] * 0.2 - 0.1), z_range[0] + u[:, 6] * (z_range[1] - z_range[0])],
+                 axis=1).astype(np.float32)
+    P = np.floor(p_range[0] + u[:, 7] * (p_range[1] - p_range[0] + 1)).astype(np.float32)
+    cls = (np.arange(frame0, frame0 + n) % N_CLS).astype(np.int32)
+    ext, lfb = EXTENT[cls].astype(np.float32), LFBORDER[cls].astype(np.float32)
+    fx, fy, cx, cy = [np.float32(v) for v in K4]
+    R64, t64 = R.astype(np.float64).reshape(n, 3, 3), t.astype(np.float64)
+    o = (-np.einsum('nji,nj->ni', R64, t64)).astype(np.float32)
+    centre = (lfb.astype(np.float64) + 0.5 * ext.astype(np.float64))
+    semi = (0.49 * ext.astype(np.float64)).astype(np.float32)
+    oo = ((o.astype(np.float64) - centre) / semi.astype(np.float64)).astype(np.float32)
+    qc = ((oo.astype(np.float64) ** 2).sum(axis=1) - 1.0).astype(np.float32)
+    smax = 0.49 * EXTENT[cls].max(axis=1)
+    rad = np.ceil(max(float(fx), float(fy)) * smax / np.maximum(t64[:, 2] - smax, 0.2)).astype(np.int64) + 2
+    uc = (float(fx) * t64[:, 0] / t64[:, 2] + float(cx)).astype(np.int64)
+    vc = (float(fy) * t64[:, 1] / t64[:, 2] + float(cy)).astype(np.int64)
+    r0, r1 = np.clip(vc - rad, 0, H), np.clip(vc + rad + 1, 0, H)
+    c0, c1 = np.clip(uc - rad, 0, W), np.clip(uc + rad + 1, 0, W)
+    prm = np.zeros((n, C5_PARAM_STRIDE), np.float32)
+    prm[:, 0:9], prm[:, 9:12] = R, t
+    prm[:, 12:16] = (fx, fy, cx, cy)
+    prm[:, 16:19], prm[:, 19:22], prm[:, 22:25], prm[:, 25:28], prm[:, 28:31], prm[:, 31] = o, oo, semi, lfb, ext, qc
+    prm[:, 32], prm[:, 33], prm[:, 34], prm[:, 35] = r0, r1, c0, c1
+    prm[:, 36], prm[:, 37], prm[:, 38] = P, outlier_frac, np.float32(noise_m * np.sqrt(3.0))
+    return dict(params=prm, cls=cls, R_gt=R.reshape(n, 3, 3), t_gt=t, extent=ext, lfborder=lfb,
+                K4=np.tile(np.asarray(K4, np.float32), (n, 1)), bbox_max=int(((r1 - r0) * (c1 - c0)).max()))
+
+
+def c5_frame_twin(prm, seed: int, frame: int, W=IMG_W):
+    """NumPy twin of csrc/synthgen.cu for ONE frame: prm [40] f32 (a row of c5_params), frame = its global index.
+    Returns the sparse frame dict (rows, cols [P] int32 row-major, xyzn [P,3] f32, area = silhouette pixels)."""
+    p = np.asarray(prm, np.float32)
+    f32 = np.float32
+    r0, r1, c0, c1 = [int(v) for v in p[32:36]]
+    rr, cc = np.meshgrid(np.arange(r0, r1), np.arange(c0, c1), indexing='ij')
+    rr, cc = rr.reshape(-1), cc.reshape(-1)
+    dcx = (cc.astype(f32) - p[14]) / p[12]
+    dcy = (rr.astype(f32) - p[15]) / p[13]
+    d = [(p[k] * dcx + p[3 + k] * dcy) + p[6 + k] for k in range(3)]
+    ddx, ddy, ddz = d[0] / p[22], d[1] / p[23], d[2] / p[24]
+    qa = (ddx * ddx + ddy * ddy) + ddz * ddz
+    qb = (ddx * p[19] + ddy * p[20]) + ddz * p[21]
+    disc = qb * qb - qa * p[31]
+    hit = disc >= 0
+    with np.errstate(invalid='ignore', divide='ignore'):
+        tau = (-qb - np.sqrt(np.where(hit, disc, f32(0)))) / qa
+    hit &= tau > 0
+    area = int(hit.sum())
+    rr, cc, tau = rr[hit], cc[hit], tau[hit]
+    d = [v[hit] for v in d]
+    pix = (rr * W + cc).astype(np.uint32)
+    r = philox4x32(pix, frame, 0, C5_TAG, seed, seed >> 32)
+    pk = p[36] / f32(area) if area else f32(0)
+    keep = _u01(r[0]) < pk
+    rr, cc, tau, pix = rr[keep], cc[keep], tau[keep], pix[keep]
+    d = [v[keep] for v in d]
+    outl = _u01(r[1][keep]) < p[37]
+    Xo = [p[16 + k] + tau * d[k] for k in range(3)]
+    qo = philox4x32(pix, frame, 1, C5_TAG, seed, seed >> 32)
+    xyzn = np.zeros((pix.shape[0], 3), f32)
+    for c in range(3):
+        qn = philox4x32(pix, frame, 2 + c, C5_TAG, seed, seed >> 32)
+        s4 = ((_u01(qn[0]) + _u01(qn[1])) + (_u01(qn[2]) + _u01(qn[3]))) - f32(2.0)
+        X = np.where(outl, p[25 + c] + _u01(qo[c]) * p[28 + c], Xo[c] + p[38] * s4).astype(f32)
+        v = (X - p[25 + c]) / p[28 + c]
+        xyzn[:, c] = np.minimum(np.maximum(v, f32(1.0e-3)), f32(1.0))
+    return dict(rows=rr.astype(np.int32), cols=cc.astype(np.int32), xyzn=xyzn, area=area, inlier=~outl)
+
+
+def c5_frames(seed: int, frame0: int, n: int, **kw):
+    """Sparse frames frame0 .. frame0+n of config C5 in the format of make_frame_sparse (for the CPU legs / tests)."""
+    P = c5_params(seed, frame0, n, **kw)
+    out = []
+    for i in range(n):
+        sp = c5_frame_twin(P["params"][i], seed, frame0 + i)
+        sp.update(cls=int(P["cls"][i]), R_gt=P["R_gt"][i], t_gt=P["t_gt"][i])
+        out.append(sp)
+    return out

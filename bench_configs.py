@@ -159,10 +159,12 @@ def c1(args, dev):
 
 
 def c5(args, dev):
-    """65,536-frame sweep as C2, sharded contiguously over the ranks (torchrun; one rank per GPU) and streamed in
-    chunks of 2048 frames per GPU; the same 2048 synthetic frames are re-used for every chunk (frame0 differs, so
-    the hypothesis streams differ); ends with the ONE all-reduce of the accuracy table (NCCL when W > 1).
-    Timed with CUDA events between barriers, maximum over ranks."""
+    """65,536 DISTINCT frames, sharded contiguously over the ranks (torchrun; one rank per GPU) and
+    streamed in chunks of 2048 frames per GPU: whole chunks are dealt in turn to three streams, each of which erases
+    its previous chunk from its own slab, has the device-side Philox generator (csrc/synthgen.cu) write the new one
+    and evaluates it -- so one lane's generation runs under the other lanes' evaluation; the sweep ends with the ONE all-reduce of the accuracy table (NCCL when
+    W > 1).  The timed region contains generation, evaluation and the all-reduce; CUDA events between barriers,
+    maximum over ranks."""
     import os
     import torch.distributed as dist
     import bench
@@ -174,27 +176,45 @@ def c5(args, dev):
         dist.init_process_group("nccl", device_id=dev)
     F, total = 2048, args.c5_frames
     lo, hi = sweep_mod.shard_range(total, rank, world)
+    assert (hi - lo) % F == 0, "shard must be a whole number of chunks"
+    nchunk = (hi - lo) // F
     H, W = synth.IMG_H, synth.IMG_W
-    inp = bench.build_inputs(torch, dev, 0, F)
+    P = synth.c5_params(bench.SEED, lo, hi - lo)                  # host, untimed: 48 floats per frame
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    prm, cls, ext, lfb, K4, Rg, tg = (t(P[k]) for k in ("params", "cls", "extent", "lfborder", "K4", "R_gt", "t_gt"))
+    bb = [int(((P["params"][c * F:(c + 1) * F, 33] - P["params"][c * F:(c + 1) * F, 32]) *
+               (P["params"][c * F:(c + 1) * F, 35] - P["params"][c * F:(c + 1) * F, 34])).max()) for c in range(nchunk)]
+    n_lanes = 3
+    gens = [ops.FrameGenerator(F, H, W, bench.SEED, device=dev) for _ in range(n_lanes)]     # one slab per lane
     models = torch.from_numpy(synth.class_models(bench.N_MODEL))
     diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
     sw = pb.EvalSweep(models, diam, sym, F, H, W, bench.CAP, ops.RansacConfig(n_hyp=bench.N_HYP, seed=bench.SEED), device=dev,
-                      lanes=3, deal="alternate")        # whole chunks dealt in turn to three streams, joined by finish()
-    assert (hi - lo) % F == 0, "shard must be a whole number of chunks"
+                      lanes=n_lanes, deal="alternate")      # whole chunks dealt in turn to three streams, joined by finish()
+    main = torch.cuda.current_stream(dev)
 
     def sweep():
         sw.reset()
-        for c in range((hi - lo) // F):
-            sw.step(inp["xyz"], inp["mask"], inp["extent"], inp["lfborder"], inp["K4"], inp["cls"], inp["R_gt"], inp["t_gt"],
-                    frame0=lo + c * F)
-        return sw.finish()
+        for c in range(nchunk):
+            k = sw.next_lane()                                  # chunk c goes to lane k; lane k owns slab k, so erasing its
+            sl = slice(c * F, (c + 1) * F)                      # previous chunk, writing this one and evaluating it are
+            with torch.cuda.stream(sw.lane_streams[k]):         # one stream's work: no cross-stream wait in the sweep
+                gens[k].erase()
+                xyz, mask = gens[k].write(prm[sl], lo + c * F, bb[c])
+            sw.step(xyz, mask, ext[sl], lfb[sl], K4[sl], cls[sl], Rg[sl], tg[sl], frame0=lo + c * F)
+        tb = sw.finish()
+        return tb
+
+    def cleanup():
+        torch.cuda.synchronize(dev)
+        for g in gens:
+            g.erase()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    sweep()
+    sweep(); cleanup()
     best = None
     for _ in range(2):
         barrier()
@@ -203,16 +223,20 @@ def c5(args, dev):
         tb = sweep()
         e1.record()
         barrier()
-        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        cleanup()
+        tm = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
         if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        best = float(t.item()) if best is None else min(best, float(t.item()))
-    tb = tb.cpu().numpy()
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        best = float(tm.item()) if best is None else min(best, float(tm.item()))
+    summ = pb.summarize(tb, synth.OBJLIST)
     if rank == 0:
         print(json.dumps({"config": "C5", "frames": total, "chunk": F, "n_gpus": world, "sweep_ms": best,
-                          "frames_per_s": total / (best * 1e-3), "map_bytes_streamed": total * (3 * H * W * 4 + H * W),
-                          "frames_counted": float(tb[ops_metric.ROW_ALL_NUM].sum()),
-                          "data": "synthetic; 2048 distinct frames re-used for each of the chunks"}), flush=True)
+                          "frames_per_s": total / (best * 1e-3),
+                          "step_impl": f"EvalSweep(lanes={n_lanes}, deal='alternate'), each lane generating into its own slab (FrameGenerator)",
+                          "mask_bytes_streamed": total * H * W, "dense_map_bytes_represented": total * (3 * H * W * 4 + H * W),
+                          "frames_counted": summ["frames"], "succ_add": summ["succ_base_rt"], "failed": summ["failed"],
+                          "data": "synthetic: every frame distinct, generated on the device (Philox4x32-10, csrc/synthgen.cu) "
+                                  "inside the timed region"}), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -317,14 +317,15 @@ int pb_vote_translation(const float* cloud, const float* t_res, int B, int NP, f
 int pb_probe_fma(int ctas, int iters, int packed, float* out, void* stream);
 
 /* Device-side generator of synthetic LineMOD-shaped frames (measurement infrastructure for the sharded sweep,
- * SURVEY.md 8(d) config C5; csrc/synthgen.cu).  params [F,40] f32 per-frame pose / camera / ellipsoid / bounding box
- * (pose_estimation_b200.synth.c5_params), bbox_max = largest bounding-box area.  Writes the foreground pixels of
- * F frames into xyz [F,3,Hh,Ww] / mask [F,Hh,Ww], which must be ZERO elsewhere; erase != 0 writes zeros at exactly
- * the pixels the same call with erase = 0 wrote (area [F] int32 is produced by the writing call and read by the
- * erasing one).  Philox4x32-10 keyed (seed), counter (pixel, frame0 + f); IEEE float32 throughout, so the NumPy
+ * SURVEY.md 8(d) config C5; csrc/synthgen.cu).  params [F,48] f32 per-frame pose / camera / ellipsoid / bounding box
+ * (pose_estimation_b200.synth.c5_params), bbox_max = largest bounding-box area.  erase = 0 writes the foreground
+ * pixels of F frames into xyz [F,3,Hh,Ww] / mask [F,Hh,Ww], which must be ZERO elsewhere, and remembers them in ws
+ * (pb_synth_workspace_bytes(F); int32 [F] unused, then [F] numbers of written pixels); erase != 0 zeroes exactly
+ * those pixels.  Philox4x32-10 keyed (seed), counter (pixel, frame0 + f); IEEE float32 throughout, so the NumPy
  * twin (synth.c5_frame_twin) gives identical bytes.                                                            */
+size_t pb_synth_workspace_bytes(int F);
 int pb_synth_frames(const float* params, int F, int Hh, int Ww, int bbox_max, uint32_t seed_lo, uint32_t seed_hi,
-                    uint32_t frame0, float* xyz, uint8_t* mask, int32_t* area, int erase, void* stream);
+                    uint32_t frame0, float* xyz, uint8_t* mask, void* ws, size_t ws_bytes, int erase, void* stream);
 
 /* tcgen05 self test: D[128,128] f32 = A[128,32] * B[128,32]^T for bf16 operands given in the canonical
  * no-swizzle K-major tile layout [kc 0..3][row 0..127][8 bf16] (the layout pb_knn1's tensor-core

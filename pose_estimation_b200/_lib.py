@@ -70,7 +70,8 @@ SIGNATURES = {
     "pb_poss_loss_workspace_bytes": (SZ, [I, I, I]),
     "pb_poss_loss_fwd": (I, [P, P, P, P, P, I, I, I, I, F32, P, P, P, P, SZ, P]),
     "pb_poss_loss_bwd": (I, [P, P, P, P, P, I, I, I, I, F32, P, P, P, P, SZ, P, P, P, P]),
-    "pb_synth_frames": (I, [P, I, I, I, I, U32, U32, U32, P, P, P, I, P]),
+    "pb_synth_workspace_bytes": (SZ, [I]),
+    "pb_synth_frames": (I, [P, I, I, I, I, U32, U32, U32, P, P, P, SZ, I, P]),
     "pb_probe_fma": (I, [I, I, I, P, P]),
     "pb_tc_selftest": (I, [P, P, P, P, P]),
     "pb_stage_timing": (I, [I]),

@@ -322,13 +322,14 @@ class FrameGenerator:
         self.F, self.H, self.W, self.seed = F, H, W, int(seed)
         self.xyz = torch.zeros((F, 3, H, W), dtype=torch.float32, device=dev)
         self.mask = torch.zeros((F, H, W), dtype=torch.uint8, device=dev)
-        self.area = torch.zeros((F,), dtype=torch.int32, device=dev)
+        self.ws = torch.zeros((_lib.load().pb_synth_workspace_bytes(F) // 4,), dtype=torch.int32, device=dev)
+        self.n_written = self.ws[F:2 * F]        # foreground pixels per frame of the chunk last written
         self.params, self.frame0, self.bbox_max = None, 0, 1
 
     def _launch(self, erase):
         call("pb_synth_frames", _ptr(self.params), self.params.shape[0], self.H, self.W, self.bbox_max,
              self.seed & 0xFFFFFFFF, (self.seed >> 32) & 0xFFFFFFFF, self.frame0, _ptr(self.xyz), _ptr(self.mask),
-             _ptr(self.area), 1 if erase else 0, _stream(self.xyz))
+             _ptr(self.ws), self.ws.numel() * 4, 1 if erase else 0, _stream(self.xyz))
 
     def write(self, params, frame0, bbox_max):
         """params [n <= F, 40] f32 CUDA (synth.c5_params(...)['params']), frame0 = global index of its first frame."""

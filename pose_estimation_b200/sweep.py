@@ -125,6 +125,11 @@ class EvalSweep:
             Fl = F if self.alternate else F // lanes
             self.lanes = [EvalSweep(self.model, self.diameter, self.is_sym, Fl, H, W, cap, self.cfg, dev,
                                     add_frac, r_thr_deg, t_thr_m) for _ in range(lanes)]
+            # the lanes' tables are rows of ONE buffer: the sweep's table is a single reduction over it (summed in
+            # lane order, so the result does not depend on timing), ready for the one all-reduce of finish()
+            self._tables = torch.zeros((lanes,) + tuple(self.lanes[0]._table.shape), dtype=torch.float64, device=dev)
+            for k, l in enumerate(self.lanes):
+                l._table = self._tables[k]
             self.lane_streams = [torch.cuda.Stream(device=dev) for _ in range(lanes)]
             self.ev_in = torch.cuda.Event()
             self.ev_out = [torch.cuda.Event() for _ in range(lanes)]
@@ -141,10 +146,15 @@ class EvalSweep:
     def reset(self):
         """Zero the accuracy table(s)."""
         self.join()
-        for l in self.lanes:
-            l.reset()
-        if not self.lanes:
+        if self.lanes:
+            self._tables.zero_()
+        else:
             self._table.zero_()
+
+    def next_lane(self):
+        """deal='alternate': index of the lane (``lane_streams[k]``) the next ``step`` will run on -- a caller that
+        produces the batch on the device can do so on that very stream."""
+        return self._turn % len(self.lanes) if self.lanes else 0
 
     def join(self):
         """Make the caller's stream wait for everything the lanes have been given (no-op without pending work)."""
@@ -158,10 +168,7 @@ class EvalSweep:
     def table(self):
         if self.lanes:
             self.join()
-            t = self.lanes[0].table.clone()
-            for l in self.lanes[1:]:
-                t += l.table
-            return t
+            return self._tables.sum(dim=0)
         return self._table
 
     def _hold(self, stream, *tensors):
@@ -311,6 +318,10 @@ class HostEvalSweep:
         nl = 2 if zero_copy else 1
         self.sweeps = [EvalSweep(model_points, diameter, is_sym, chunk, H, W, cap, cfg, device=dev, **kw) for _ in range(nl)]
         self.sweep = self.sweeps[0]
+        # the lanes' tables are rows of one buffer (one reduction gives the table, one memset resets it)
+        self._tables = torch.zeros((nl,) + tuple(self.sweep._table.shape), dtype=torch.float64, device=dev)
+        for k, sw_ in enumerate(self.sweeps):
+            sw_._table = self._tables[k]
         self.lane_streams = [torch.cuda.Stream(device=dev) for _ in range(nl)] if nl > 1 else None
         self.lane_done = [torch.cuda.Event() for _ in range(nl)]
         self.start = torch.cuda.Event()
@@ -331,14 +342,10 @@ class HostEvalSweep:
     def table(self):
         if len(self.sweeps) == 1:
             return self.sweep.table
-        t = self.sweeps[0].table.clone()
-        for sw in self.sweeps[1:]:
-            t += sw.table
-        return t
+        return self._tables.sum(dim=0)
 
     def reset(self):
-        for sw in self.sweeps:
-            sw.reset()
+        self._tables.zero_()
 
     def run(self, xyz_h, mask_h, small_h, cls_h, frame0=0, group=None, roi_h=None):
         """xyz_h [F,3,H,W] f32, mask_h [F,H,W] u8, small_h = pack_small(...) [F/chunk, 22*chunk] f32,

@@ -168,10 +168,10 @@ def make_batch_sparse(seed: int, config_id: int, n_frames: int, first_frame: int
 
 # ---------------------------------------------------------------------------------------------------------------
 # Config C5: frames generated ON THE DEVICE by csrc/synthgen.cu; this is its NumPy twin.
-# The per-frame parameters come from the host (cheap: 40 floats per frame, a pure function of (seed, frame index),
+# The per-frame parameters come from the host (cheap: 48 floats per frame, a pure function of (seed, frame index),
 # so every sharding of the sweep sees the same frames); the per-pixel work -- ray / ellipsoid hit, keep / outlier /
 # noise draws from Philox4x32-10 -- is IEEE float32 in a written order on both sides, so the bytes are identical.
-C5_PARAM_STRIDE = 40
+C5_PARAM_STRIDE = 48
 C5_TAG = 0x47454E35
 C5_PARAM_TAG = 0x50415235
 
@@ -196,7 +196,7 @@ def _u01(r):
 
 def c5_params(seed: int, frame0: int, n: int, p_range=(800, 1200), outlier_frac=0.25, noise_m=1e-3,
               K4=LINEMOD_K4, H=IMG_H, W=IMG_W, z_range=(0.6, 1.2)):
-    """Per-frame parameters [n,40] f32 of frames frame0 .. frame0+n (layout: csrc/synthgen.cu) plus the
+    """Per-frame parameters [n,48] f32 of frames frame0 .. frame0+n (layout: csrc/synthgen.cu) plus the
     per-frame arrays the evaluation needs: dict(params, cls, R_gt, t_gt, extent, lfborder, K4, bbox_max)."""
     f = np.arange(frame0, frame0 + n, dtype=np.uint64)
     u = []
@@ -236,36 +236,61 @@ def c5_params(seed: int, frame0: int, n: int, p_range=(800, 1200), outlier_frac=
     prm[:, 16:19], prm[:, 19:22], prm[:, 22:25], prm[:, 25:28], prm[:, 28:31], prm[:, 31] = o, oo, semi, lfb, ext, qc
     prm[:, 32], prm[:, 33], prm[:, 34], prm[:, 35] = r0, r1, c0, c1
     prm[:, 36], prm[:, 37], prm[:, 38] = P, outlier_frac, np.float32(noise_m * np.sqrt(3.0))
+    # keep probability: P over the ANALYTIC area of the silhouette, the ellipse d^T (D u u^T D - qc D) d >= 0 of the
+    # pixel's ray direction d = R^T K^-1 (col, row, 1) (within 0.5 % of the pixel count; no counting pass on the device)
+    D = np.zeros((n, 3, 3)); D[:, 0, 0], D[:, 1, 1], D[:, 2, 2] = (1.0 / semi.astype(np.float64) ** 2).T
+    uu = o.astype(np.float64) - centre
+    Du = np.einsum('nij,nj->ni', D, uu)
+    M = np.einsum('ni,nj->nij', Du, Du) - (np.einsum('ni,ni->n', uu, Du) - 1.0)[:, None, None] * D
+    Kinv = np.array([[1 / float(fx), 0, -float(cx) / float(fx)], [0, 1 / float(fy), -float(cy) / float(fy)], [0, 0, 1.0]])
+    A = np.einsum('nji,jk->nik', R64, Kinv)
+    Q = np.einsum('nji,njk,nkl->nil', A, M, A)
+    area = np.pi * np.abs(np.linalg.det(Q)) / np.abs(np.linalg.det(Q[:, :2, :2])) ** 1.5
+    prm[:, 39] = (P / area).astype(np.float32)
+    # tight bounding box of that ellipse from its dual conic adj(Q) (+- 2 px), inside the sphere bound above
+    Cs = np.linalg.inv(Q) * np.linalg.det(Q)[:, None, None]
+    with np.errstate(invalid='ignore'):
+        du = np.sqrt(np.maximum(Cs[:, 0, 2] ** 2 - Cs[:, 0, 0] * Cs[:, 2, 2], 0.0)) / np.abs(Cs[:, 2, 2])
+        dv = np.sqrt(np.maximum(Cs[:, 1, 2] ** 2 - Cs[:, 1, 1] * Cs[:, 2, 2], 0.0)) / np.abs(Cs[:, 2, 2])
+    uc_, vc_ = Cs[:, 0, 2] / Cs[:, 2, 2], Cs[:, 1, 2] / Cs[:, 2, 2]
+    ok = np.isfinite(du) & np.isfinite(dv) & np.isfinite(uc_) & np.isfinite(vc_)
+    c0 = np.where(ok, np.maximum(c0, np.floor(uc_ - du).astype(np.int64) - 2), c0)
+    c1 = np.where(ok, np.minimum(c1, np.ceil(uc_ + du).astype(np.int64) + 3), c1)
+    r0 = np.where(ok, np.maximum(r0, np.floor(vc_ - dv).astype(np.int64) - 2), r0)
+    r1 = np.where(ok, np.minimum(r1, np.ceil(vc_ + dv).astype(np.int64) + 3), r1)
+    c1, r1 = np.maximum(c1, c0), np.maximum(r1, r0)
+    prm[:, 32], prm[:, 33], prm[:, 34], prm[:, 35] = r0, r1, c0, c1
+    prm[:, 40], prm[:, 41] = np.float32(1.0) / fx, np.float32(1.0) / fy
+    prm[:, 42:45] = np.float32(1.0) / semi
+    assert p_range[1] <= 2048, "the generator remembers at most 4096 written pixels per frame"
     return dict(params=prm, cls=cls, R_gt=R.reshape(n, 3, 3), t_gt=t, extent=ext, lfborder=lfb,
                 K4=np.tile(np.asarray(K4, np.float32), (n, 1)), bbox_max=int(((r1 - r0) * (c1 - c0)).max()))
 
 
 def c5_frame_twin(prm, seed: int, frame: int, W=IMG_W):
-    """NumPy twin of csrc/synthgen.cu for ONE frame: prm [40] f32 (a row of c5_params), frame = its global index.
+    """NumPy twin of csrc/synthgen.cu for ONE frame: prm [48] f32 (a row of c5_params), frame = its global index.
     Returns the sparse frame dict (rows, cols [P] int32 row-major, xyzn [P,3] f32, area = silhouette pixels)."""
     p = np.asarray(prm, np.float32)
     f32 = np.float32
     r0, r1, c0, c1 = [int(v) for v in p[32:36]]
     rr, cc = np.meshgrid(np.arange(r0, r1), np.arange(c0, c1), indexing='ij')
     rr, cc = rr.reshape(-1), cc.reshape(-1)
-    dcx = (cc.astype(f32) - p[14]) / p[12]
-    dcy = (rr.astype(f32) - p[15]) / p[13]
+    dcx = (cc.astype(f32) - p[14]) * p[40]
+    dcy = (rr.astype(f32) - p[15]) * p[41]
     d = [(p[k] * dcx + p[3 + k] * dcy) + p[6 + k] for k in range(3)]
-    ddx, ddy, ddz = d[0] / p[22], d[1] / p[23], d[2] / p[24]
+    ddx, ddy, ddz = d[0] * p[42], d[1] * p[43], d[2] * p[44]
     qa = (ddx * ddx + ddy * ddy) + ddz * ddz
     qb = (ddx * p[19] + ddy * p[20]) + ddz * p[21]
     disc = qb * qb - qa * p[31]
-    hit = disc >= 0
+    hit = (disc >= 0) & (qb < 0)
     with np.errstate(invalid='ignore', divide='ignore'):
         tau = (-qb - np.sqrt(np.where(hit, disc, f32(0)))) / qa
-    hit &= tau > 0
     area = int(hit.sum())
     rr, cc, tau = rr[hit], cc[hit], tau[hit]
     d = [v[hit] for v in d]
     pix = (rr * W + cc).astype(np.uint32)
     r = philox4x32(pix, frame, 0, C5_TAG, seed, seed >> 32)
-    pk = p[36] / f32(area) if area else f32(0)
-    keep = _u01(r[0]) < pk
+    keep = _u01(r[0]) < p[39]
     rr, cc, tau, pix = rr[keep], cc[keep], tau[keep], pix[keep]
     d = [v[keep] for v in d]
     outl = _u01(r[1][keep]) < p[37]

@@ -14,11 +14,11 @@ def test_generated_frames_equal_numpy_twin_and_erase(dev):
     P = synth.c5_params(seed, frame0, n)
     gen = ops.FrameGenerator(n, synth.IMG_H, synth.IMG_W, seed, device=dev)
     xyz, mask = gen.write(torch.from_numpy(P["params"]).to(dev), frame0, P["bbox_max"])
-    xyz_h, mask_h, area = xyz.cpu().numpy(), mask.cpu().numpy(), gen.area.cpu().numpy()
+    xyz_h, mask_h, area = xyz.cpu().numpy(), mask.cpu().numpy(), gen.n_written.cpu().numpy().copy()
     for i in range(n):
         sp = synth.c5_frame_twin(P["params"][i], seed, frame0 + i)
         want_xyz, want_mask = synth.dense_from_sparse(sp)
-        assert area[i] == sp["area"] and 700 < sp["rows"].shape[0] < 1300, i
+        assert area[i] == sp["rows"].shape[0] and 700 < sp["rows"].shape[0] < 1300, i
         assert np.array_equal(mask_h[i], want_mask), i
         assert np.array_equal(xyz_h[i], want_xyz), i
     with pytest.raises(RuntimeError):

@@ -13,7 +13,9 @@
  *     OpenCV reports as ok=False and the reference ignores, tools/trainer.py:423) is reported in
  *     status[F], never through the return code.
  *   - the caller owns every buffer including the workspace (pb_*_workspace_bytes()); the library
- *     allocates nothing and keeps no state except the error string.
+ *     allocates no device memory and keeps no state between calls except, per calling thread, the error
+ *     string and -- only after pb_stage_timing(1) -- that thread's own timing events (a measurement aid,
+ *     off by default), plus a per-device cache of the multiprocessor count.
  *   - all work is asynchronous on the given stream (a cudaStream_t passed as void*).
  *   - results are a pure function of (inputs, seed): no dependence on launch geometry.
  */
@@ -43,6 +45,9 @@ extern "C" {
 #define PB_ROW_FAILED 23       /* frames whose RANSAC status != 0 (new: the reference drops cv2's ok flag) */
 #define PB_TABLE_ROWS 24
 
+/* Minimal solver: P3P on 3 correspondences + a 4th to pick the root, ONLY.  SURVEY.md 8(b) sketched a
+ * `min_set (4|5)` field for an EPnP-5 option like cv2's flags=SOLVEPNP_EPNP (tools/trainer.py:426); it was not
+ * built -- every hypothesis is a P3P solve and the final pose a Gauss-Newton refit on the inliers. */
 typedef struct pb_ransac_params {
     int32_t  n_hyp;        /* hypotheses per frame (reference: iterationsCount=100 default of cv2; ours 256) */
     float    thresh_px;    /* reprojectionError (tools/trainer.py:426: 1)                                     */
@@ -332,8 +337,8 @@ int pb_synth_frames(const float* params, int F, int Hh, int Ww, int bbox_max, ui
  * path stages); err (device int) is set when the completion barrier timed out.                     */
 int pb_tc_selftest(const void* A, const void* B, float* D, int* err, void* stream);
 
-/* Per-kernel timing of pb_pnp_ransac_pts: while enabled, every call records CUDA events on its
- * stream around its three launches (hypotheses | scoring | finalize; up to 256 calls).
+/* Per-kernel timing of pb_pnp_ransac_pts, PER CALLING THREAD: while enabled, every call made by this thread
+ * records CUDA events on its stream around its three launches (hypotheses | scoring | finalize; up to 256 calls).
  * pb_stage_timing_read waits for them and returns the mean milliseconds per call (host pointers). */
 int pb_stage_timing(int enable);
 int pb_stage_timing_read(float* ms3 /*host [3]*/, int* calls /*host*/);

@@ -38,10 +38,12 @@ int pb_sm_count() {
 // ---- optional per-kernel timing of the RANSAC call (CUDA events recorded on the caller's stream) ----
 namespace {
 constexpr int TIM_SLOTS = 256, TIM_MARKS = 4;     // marks: before hyp | before score | before finalize | after
-bool g_tim_on = false;
-int g_tim_calls = 0;
-cudaEvent_t g_tim_ev[TIM_SLOTS][TIM_MARKS];
-bool g_tim_made = false;
+// Per THREAD: a thread that has not called pb_stage_timing(1) never touches any of it, and two threads that both
+// measure do not share slots.  Off by default.
+thread_local bool g_tim_on = false;
+thread_local int g_tim_calls = 0;
+thread_local cudaEvent_t g_tim_ev[TIM_SLOTS][TIM_MARKS];
+thread_local bool g_tim_made = false;
 }
 
 void pb_stage_mark(int mark, cudaStream_t st) {

@@ -633,7 +633,7 @@ struct CPlan { int S, quads_per_split, segcap; bool vec, sparse; size_t off_tot,
 inline int stream_tiles_per_frame(long long HW) { return (int)((HW + SM_TILE_PX - 1) / SM_TILE_PX); }
 inline size_t stream_ws_bytes(int F, long long HW) { return 256 + (size_t)F * stream_tiles_per_frame(HW) * sizeof(uint32_t); }
 
-CPlan make_cplan(int F, int Hh, int Ww, int cap, bool has_mask) {
+CPlan make_cplan(int F, int Hh, int Ww, int cap, bool has_mask, int sms = 148) {
     CPlan p;
     const long long HW = (long long)Hh * Ww;
     p.vec = (HW % 4) == 0;
@@ -641,8 +641,8 @@ CPlan make_cplan(int F, int Hh, int Ww, int cap, bool has_mask) {
     p.sparse = has_mask && (HW % 32) == 0;
     if (p.sparse) { p.S = 1; p.quads_per_split = 0; p.segcap = cap; p.off_tot = 0; p.total = 0; return p; }
     int S = 1;
-    if (p.vec && F < 592) {
-        S = (592 + F - 1) / F;                      // ~4 CTAs per SM
+    if (p.vec && F < 4 * sms) {
+        S = (4 * sms + F - 1) / F;                  // ~4 CTAs per SM
         int maxS = (int)((HW / 4 + 4095) / 4096);   // keep >= 16k pixels per band
         if (S > maxS) S = maxS;
         if (S < 1) S = 1;
@@ -666,7 +666,7 @@ CPlan make_cplan(int F, int Hh, int Ww, int cap, bool has_mask) {
 
 extern "C" size_t pb_compact_workspace_bytes(int F, int Hh, int Ww, int cap) {
     if (F <= 0 || Hh <= 0 || Ww <= 0 || cap <= 0) return 0;
-    const size_t dense = make_cplan(F, Hh, Ww, cap, false).total;      // maskless stream (row bands + merge)
+    const size_t dense = make_cplan(F, Hh, Ww, cap, false, pb_sm_count()).total;      // maskless stream (row bands + merge)
     const size_t stream = stream_ws_bytes(F, (long long)Hh * Ww);      // mask-first stream (ticket + tile states)
     return dense > stream ? dense : stream;
 }
@@ -678,7 +678,7 @@ extern "C" int pb_compact_map(const float* xyz, const uint8_t* mask, const int32
     PB_REQUIRE((long long)Hh * Ww < (1ll << 30), "pb_compact_map: map too large");
     if (F == 0) return 0;
     PB_REQUIRE(xyz && extent && lfborder && pts && count, "pb_compact_map: null pointer argument");
-    CPlan p = make_cplan(F, Hh, Ww, cap, mask != nullptr && reinterpret_cast<uintptr_t>(mask) % 16 == 0);
+    CPlan p = make_cplan(F, Hh, Ww, cap, mask != nullptr && reinterpret_cast<uintptr_t>(mask) % 16 == 0, pb_sm_count());
     PB_REQUIRE(p.total == 0 || (ws && ws_bytes >= p.total), "pb_compact_map: workspace too small (%zu < %zu)", ws_bytes, p.total);
     PB_REQUIRE((long long)F * p.S < (1ll << 31), "pb_compact_map: grid too large");
     cudaStream_t st = static_cast<cudaStream_t>(stream);

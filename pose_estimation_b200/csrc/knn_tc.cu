@@ -521,61 +521,6 @@ extern "C" int pb_tc_selftest(const void* A, const void* B, float* D, int* err, 
     return pb_check_launch("tc_selftest_kernel") ? -2 : 0;
 }
 
-#ifdef PB_TC_DEBUG
-// MMA issue-rate probe: reps x (two K=16 MMAs, M=128, N=n) on garbage operands, one commit at the end.
-__global__ void __launch_bounds__(128) tc_mma_probe_kernel(int n, uint32_t layout, uint32_t lbo, uint32_t sbo, uint32_t kstep,
-                                                            int reps, int nacc, long long* out) {
-    extern __shared__ __align__(1024) unsigned char sm[];
-    __shared__ __align__(8) uint64_t bar;
-    __shared__ uint32_t tmem_base;
-    const int tid = threadIdx.x, warp = tid >> 5;
-    for (int i = tid; i < 64 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(sm)[i] = 0x3c003c00u;
-    if (tid == 0) { tc::mbar_init(&bar, 1); tc::fence_mbar_init(); }
-    if (warp == 0) tc::tmem_alloc<512>(&tmem_base);
-    tc::fence_proxy_async();
-    tc::fence_before_sync();
-    __syncthreads();
-    tc::fence_after_sync();
-    const uint32_t tmem = tmem_base;
-    if (tid == 0) {
-        const uint32_t idesc = tc::idesc_bf16_f32(128, n);
-        const uint64_t ad = tc::smem_desc(tc::smem_u32(sm), lbo, sbo) | ((uint64_t)layout << 61);
-        const uint64_t bd = tc::smem_desc(tc::smem_u32(sm) + 32768, lbo, sbo) | ((uint64_t)layout << 61);
-        const long long t0 = clock64();
-        for (int r = 0; r < reps; ++r) {
-            const uint32_t d = tmem + (uint32_t)(r % nacc) * (uint32_t)n;
-            tc::mma_bf16(d, ad, bd, idesc, 0);
-            tc::mma_bf16(d, ad + (kstep >> 4), bd + (kstep >> 4), idesc, 1);
-        }
-        const long long t1 = clock64();
-        tc::mma_commit(&bar);
-        tc::mbar_wait(&bar, 0);
-        const long long t2 = clock64();
-        if (blockIdx.x == 0) { out[0] = t1 - t0; out[1] = t2 - t0; }
-    } 
-    tc::fence_before_sync();
-    __syncthreads();
-    if (warp == 0) tc::tmem_dealloc<512>(tmem);
-}
-extern "C" int pb_tc_probe_mma(int ctas, int n, unsigned layout, unsigned lbo, unsigned sbo, unsigned kstep, int reps, int nacc,
-                               long long* host_out) {
-    long long* d;
-    cudaMalloc(&d, 16);
-    cudaFuncSetAttribute(tc_mma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-    tc_mma_probe_kernel<<<ctas, 128, 64 * 1024>>>(n, layout, lbo, sbo, kstep, reps, nacc, d);
-    int rc = (int)cudaDeviceSynchronize();
-    cudaMemcpy(host_out, d, 16, cudaMemcpyDeviceToHost);
-    cudaFree(d);
-    return rc;
-}
-extern "C" int pb_tc_debug_read(unsigned long long* host) {
-    return (int)cudaMemcpyFromSymbol(host, g_tcdbg, sizeof(unsigned long long) * 256 * 8);
-}
-extern "C" int pb_tc_debug_read_cycles(unsigned long long* host) {
-    return (int)cudaMemcpyFromSymbol(host, g_tccyc, sizeof(unsigned long long) * 256 * 8);
-}
-#endif
-
 extern "C" size_t pb_knn1_tc_workspace_bytes(int B, int N, int M) {
     if (B <= 0 || N <= 0 || M <= 0) return 0;
     return tc_ws_bytes(B, N, M);
@@ -605,7 +550,7 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
         const int nb = (nl - b0) < TC_CHUNK ? (nl - b0) : TC_CHUNK;
         PrepArgs pa{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, centre, b0, blist};
         cudaMemsetAsync(tol, 0, (size_t)nb * sizeof(float), st);
-        int split = (592 + nb - 1) / nb;                       // about four CTAs per SM in total
+        int split = (4 * pb_sm_count() + nb - 1) / nb;         // about four CTAs per SM in total
         const int max_split = (max(ntN, ntM) * TM + 255) / 256;
         split = split < PREP_SPLIT ? PREP_SPLIT : (split > 64 ? 64 : split);
         split = split > max_split ? max_split : split;

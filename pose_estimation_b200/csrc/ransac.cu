@@ -385,7 +385,7 @@ __global__ void resample_inliers_kernel(const uint32_t* bitmap, const int32_t* c
 
 extern "C" size_t pb_ransac_workspace_bytes(int F, int cap, const pb_ransac_params* prm) {
     if (F <= 0 || cap <= 0 || !prm || prm->n_hyp <= 0) return 0;
-    return make_plan(F, cap, prm).total;
+    return make_plan(F, cap, prm, pb_sm_count()).total;
 }
 
 extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const float* K4, int F, int cap,
@@ -400,7 +400,7 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     if (F == 0) return 0;
     PB_REQUIRE(pts && count && K4 && R && t && n_inl && best_hyp && n_inl_refined && status,
                "pb_pnp_ransac_pts: null pointer argument");
-    Plan p = make_plan(F, cap, prm);
+    Plan p = make_plan(F, cap, prm, pb_sm_count());
     PB_REQUIRE(ws != nullptr && ws_bytes >= p.total, "pb_pnp_ransac_pts: workspace too small (%zu < %zu)", ws_bytes, p.total);
     PB_REQUIRE(p.smem_score <= 227 * 1024 && p.smem_final <= 200 * 1024, "pb_pnp_ransac_pts: shared memory plan too large");
     PB_REQUIRE((size_t)F * p.HS < (1ull << 31), "pb_pnp_ransac_pts: grid too large");
@@ -426,9 +426,10 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     // 2 / 4 / 8 / 17 CTAs per SM for G = 8 / 4 / 2 / 1), so a batch is one wave with no tail; results
     // do not depend on G.
     int rcf;
-    if (F <= 148 * 2) rcf = launch_finalize<8>(fa, F, p.smem_final, st);
-    else if (F <= 148 * 4) rcf = launch_finalize<4>(fa, F, p.smem_final, st);
-    else if (F <= 148 * 8) rcf = launch_finalize<2>(fa, F, p.smem_final, st);
+    const int sms = pb_sm_count();
+    if (F <= sms * 2) rcf = launch_finalize<8>(fa, F, p.smem_final, st);
+    else if (F <= sms * 4) rcf = launch_finalize<4>(fa, F, p.smem_final, st);
+    else if (F <= sms * 8) rcf = launch_finalize<2>(fa, F, p.smem_final, st);
     else rcf = launch_finalize<1>(fa, F, p.smem_final, st);
     if (rcf) return -2;
     pb_stage_mark(3, st);

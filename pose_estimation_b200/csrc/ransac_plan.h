@@ -29,13 +29,15 @@ struct Plan {
 #define PB_SCORE_THREADS 128     /* CTA size of the scoring kernel (ST in ransac_score.cu) */
 #define PB_BAL_CH 1024           /* points staged per chunk by the balanced scoring kernel */
 
-static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm) {
+static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm, int sms = 148) {
+    if (sms <= 0) sms = 148;
+    const int two_waves = 2 * sms;                     // fewer frames than this: slice the hypotheses to fill the GPU
     Plan p;
     const int H = prm->n_hyp;
     int Hs = 32;
     while (Hs < H && Hs < 2 * PB_SCORE_THREADS) Hs <<= 1;   // up to 2 hypotheses per thread
-    if (F < 296) {                                     // few frames: more, narrower slices
-        int want = (296 + F - 1) / F;
+    if (F < two_waves) {                               // few frames: more, narrower slices
+        int want = (two_waves + F - 1) / F;
         while (Hs > 64 && (H + Hs - 1) / Hs < want) Hs >>= 1;
     }
     p.Hs = Hs;
@@ -56,8 +58,10 @@ static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm) {
     p.smem_bal = (size_t)PB_BAL_CH * 5 * 4 + (size_t)(F + 1) * 4;
     int per_sm = (int)((220 * 1024) / (p.smem_bal + 1024));
     if (per_sm > 6) per_sm = 6;                        // 80 registers x 128 threads: six CTAs per SM, one wave
-    p.bal = (p.HS == 1 && p.PP == 1 && F >= 296 && F <= 2368 && per_sm >= 4) ? 1 : 0;
-    p.bal_grid = 148 * per_sm;
+    // (the per-CTA prefix of the frames' counts lives in shared memory: F is bounded by per_sm >= 4, about 8 k frames;
+    // above that the frame-per-CTA launch has enough waves for the hardware scheduler to balance)
+    p.bal = (p.HS == 1 && p.PP == 1 && F >= two_waves && per_sm >= 4) ? 1 : 0;
+    p.bal_grid = sms * per_sm;
     p.off_cnt = (p.total + 255) / 256 * 256;
     if (p.bal) p.total = p.off_cnt + (size_t)F * H * sizeof(int32_t);
     return p;

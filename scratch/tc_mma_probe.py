@@ -1,4 +1,4 @@
-"""Developer probe (needs a PB_TC_DEBUG build): tcgen05.mma issue/execution rate per operand layout."""
+"""Developer probe (needs the debug build of scratch/tc_debug.cu): tcgen05.mma issue/execution rate per operand layout."""
 import ctypes as C, torch
 from pose_estimation_b200 import _lib
 torch.zeros(1, device="cuda")

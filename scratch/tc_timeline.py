@@ -1,4 +1,4 @@
-"""Developer probe (needs a PB_TC_DEBUG build): per-CTA timeline of knn_tc_kernel."""
+"""Developer probe (needs the debug build of scratch/tc_debug.cu): per-CTA timeline of knn_tc_kernel."""
 import ctypes as C, numpy as np, torch
 from pose_estimation_b200 import ops_metric, _lib
 B, N = 256, 2620

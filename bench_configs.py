@@ -56,7 +56,8 @@ def c3(args, dev):
     ms = timed(lambda: ops_metric.knn1(pred, target, impl="tc"), args.iters)
     st = ops_metric.LAST_TC_STATS.cpu().tolist()
     out["knn1_tc"] = {"ms": ms, "pairs_per_s": B * N * N / (ms * 1e-3), "fallback_rows": st[1],
-                      "exact_evals_per_row": st[2] / (B * N), "timeout": st[0]}
+                      "exact_evals_per_row": st[2] / (B * N), "timeout": st[0],
+                      "chunks_looked_at_frac": st[3] / (B * ((N + 127) // 128) * 8 * ((N + 127) // 128) * 2)}
     same = bool(torch.equal(ops_metric.knn1(pred, target, impl="tc"), ops_metric.knn1(pred, target, impl="simt")))
     out["tc_equals_simt"] = same
     for impl in ("simt", "tc"):

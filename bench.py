@@ -36,7 +36,9 @@ Nothing here reads /root/reference at run time.
 from __future__ import annotations
 
 import argparse
+import contextlib
 import ctypes as C
+import io
 import json
 import multiprocessing as mp
 import os
@@ -63,7 +65,7 @@ MAP_BYTES_PER_FRAME = 480 * 640 * (12 + 1)      # xyz 12 B + mas
 
 # ------------------------------------------------------------------------------------------------
 # reference arm / cpu_baseline: the reference's per-frame CPU path on the host cores
-def _ref_worker(rank, frames, n_steps, barrier, out_q, cv2_threads=1):
+def _ref_worker(rank, frames, n_steps, barrier, out_q, cv2_threads=1, spec=None):
     """Worker process: builds its frames (untimed), then evaluates them once per step."""
     try:
         import numpy as np
@@ -75,8 +77,9 @@ def _ref_worker(rank, frames, n_steps, barrier, out_q, cv2_threads=1):
         models = synth.class_models(N_MODEL)
         metric = rc.Metric(synth.SYM_CLS)
         fr = []
+        spec = spec or {}
         for f in frames:
-            sp = synth.make_frame_sparse(SEED, CONFIG_ID, f)
+            sp = synth.make_frame_sparse(SEED, spec.get("config_id", CONFIG_ID), f, **spec.get("kw", {}))
             fr.append(synth.reference_frame_dict(sp, models[sp["cls"]]))
         rng = np.random.default_rng([SEED, rank])
         for _ in range(n_steps):
@@ -92,7 +95,7 @@ def _ref_worker(rank, frames, n_steps, barrier, out_q, cv2_threads=1):
         raise
 
 
-def run_reference_cpu(n_frames, n_steps, n_workers=None, cv2_threads=1):
+def run_reference_cpu(n_frames, n_steps, n_workers=None, cv2_threads=1, spec=None):
     """Times the reference path on ``n_frames`` frames of the workload, ``n_steps`` times.
     cv2_threads=None leaves OpenCV's own threading at its default (the reference as it is launched: one process).
     Returns (list of seconds per step, workers, frames, [succ_add, succ_r, succ_t] counts of the last step)."""
@@ -101,7 +104,7 @@ def run_reference_cpu(n_frames, n_steps, n_workers=None, cv2_threads=1):
     barrier = ctx.Barrier(n_workers + 1)
     q = ctx.Queue()
     shards = [list(range(w, n_frames, n_workers)) for w in range(n_workers)]
-    procs = [ctx.Process(target=_ref_worker, args=(w, shards[w], n_steps, barrier, q, cv2_threads), daemon=True)
+    procs = [ctx.Process(target=_ref_worker, args=(w, shards[w], n_steps, barrier, q, cv2_threads, spec), daemon=True)
              for w in range(n_workers)]
     for p in procs:
         p.start()
@@ -515,6 +518,15 @@ def ours_arm(args):
                       "reference_succ_add_r_t": ra.mean(axis=0).round(4).tolist(),
                       "source": "tests/golden/c2_ref_verdicts.npz: the reference's own Trainer.get_pose + cal_dis run twice "
                                 "(two randperm seeds) over these 1024 frames by tests/golden/gen_golden_c2_verdicts.py"}
+        # the other BASELINE.json configs that fit one GPU, each beside a bounded run of the reference's CPU path
+        # (bench_configs.py; C5 needs 25 GB of slabs and runs on its own: profiles/r02_c5_n*.json)
+        other = None
+        if world == 1 and not args.no_configs:
+            import types
+            import bench_configs
+            cargs = types.SimpleNamespace(iters=5, c3_batch=4096, c4_frames=256, cpu=not args.no_cpu_baseline)
+            with contextlib.redirect_stdout(io.StringIO()):
+                other = {"C1": bench_configs.c1(cargs, dev), "C3": bench_configs.c3(cargs, dev), "C4": bench_configs.c4(cargs, dev)}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_clean / args.steps, "higher_is_better": True,
@@ -560,6 +572,7 @@ def ours_arm(args):
             "roofline_all": [roof_score, roof_k0, roof_dense],
             "fp32_probe_tflops": fp32_probe,
             "cpu_baseline": cpu_base,
+            "other_configs": other,
             "clocks": clocks,
             "accuracy": {"succ_add": summ["succ_base_rt"], "succ_r5deg": summ["succ_base_r"],
                          "succ_t5cm": summ["succ_base_t"], "failed": summ["failed"], "frames": summ["frames"],
@@ -600,6 +613,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 / C4 block (other_configs)")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)

@@ -70,7 +70,33 @@ def c3(args, dev):
     l_t = ops_metric.pose_loss_fwd(Rt, tt, model, target, sym, impl="tc", sym_host=[1] * B)
     out["adds_tc_equals_simt"] = bool(torch.equal(a_s[1], a_t[1]) and torch.equal(a_s[0], a_t[0]))
     out["loss_tc_equals_simt"] = bool(torch.equal(l_s[0], l_t[0]) and torch.equal(l_s[2], l_t[2]))
-    print(json.dumps({"config": "C3", "batch": B, "N": N, "pairs": B * N * N, **out}), flush=True)
+    # roofline of the tensor-core search as DESIGN.md 4.1 states it: the minimum over the N*M scores on the ALU pipe,
+    # 0.66 FMNMX per score at 16 lanes / clk / SMSP (the measured bound of the epilogue; the tensor pipe is at ~12 %)
+    import ctypes as C
+    from pose_estimation_b200 import _lib
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    clk = torch.cuda.get_device_properties(dev).clock_rate * 1e3 if hasattr(torch.cuda.get_device_properties(dev), "clock_rate") else 1.965e9
+    alu_bound = sms * 4 * 16 * clk / 0.66
+    out["roofline"] = {"kernel": "knn_tc_kernel", "bound": "alu (min epilogue)", "achieved": out["knn1_tc"]["pairs_per_s"],
+                       "peak": alu_bound, "unit": "pairs/s", "frac": out["knn1_tc"]["pairs_per_s"] / alu_bound,
+                       "note": "peak = SMs x 4 SMSP x 16 lanes x clock / 0.66 FMNMX per score"}
+    if getattr(args, "cpu", False):
+        # the reference's own N x N form (lib/utils/metric.py:24-32) on the host cores, a bounded sample of problems
+        import time
+        from oracle import ref_callsites as rc
+        ph, th = pred[:4].cpu(), target[:4].cpu()
+        rc.cal_adds_torch_nxn(ph[0], th[0])
+        t0 = time.perf_counter()
+        vals = [rc.cal_adds_torch_nxn(ph[k], th[k]) for k in range(4)]
+        dt = (time.perf_counter() - t0) / 4
+        got = ops_metric.add_adds(pred[:4], target[:4], None, impl="tc")[1].cpu().numpy()
+        out["cpu_baseline"] = {"value": N * N / dt, "unit": "pairs/s", "s_per_problem": dt, "cores": torch.get_num_threads(),
+                               "kind": "port", "sample": "4 problems of 2620 x 2620; oracle/ref_callsites.cal_adds_torch_nxn = the "
+                               "[N,N,3] repeat / norm / min / mean of lib/utils/metric.py:24-32 in torch on the host",
+                               "adds_equal_to_1e-5": bool(np.allclose(got, vals, rtol=1e-5))}
+    res = {"config": "C3", "batch": B, "N": N, "pairs": B * N * N, **out}
+    print(json.dumps(res), flush=True)
+    return res
 
 
 def c4(args, dev):
@@ -90,9 +116,21 @@ def c4(args, dev):
     NP = 10000
     cloud = torch.randn(F, NP, 3, device=dev); tres = torch.randn(F, 3, NP, device=dev)
     ms_v = timed(lambda: ops_metric.vote_translation(cloud, tres), args.iters)
-    print(json.dumps({"config": "C4", "frames": F, "P_mean": float(cnt.mean()), "n_hyp": H, "lo_rounds": 5,
-                      "ransac_ms": ms, "frames_per_s": F / (ms * 1e-3), "hyp_pts_per_s": hp / (ms * 1e-3),
-                      "vote_ms": ms_v, "vote_GBps": F * NP * 24 / (ms_v * 1e-3) / 1e9}), flush=True)
+    res = {"config": "C4", "frames": F, "P_mean": float(cnt.mean()), "n_hyp": H, "lo_rounds": 5,
+           "ransac_ms": ms, "frames_per_s": F / (ms * 1e-3), "hyp_pts_per_s": hp / (ms * 1e-3),
+           "vote_ms": ms_v, "vote_GBps": F * NP * 24 / (ms_v * 1e-3) / 1e9}
+    if getattr(args, "cpu", False):
+        # the reference on the same kind of frame: get_pose still draws 256 of the 10 k pixels (tools/trainer.py:406-407)
+        import bench
+        spec = dict(config_id=4, kw=dict(p_range=(10000, 10000), outlier_frac=0.3, z_range=(0.30, 0.40), xy_frac=0.25))
+        n_cpu = 4 * (os.cpu_count() or 1)
+        times, workers, n_cpu, succ = bench.run_reference_cpu(n_cpu, 3, spec=spec)
+        res["cpu_baseline"] = {"value": n_cpu / min(times[1:]), "unit": "frames/s", "cores": workers, "kind": "port",
+                               "sample": f"{n_cpu} frames with 10 k masked px, best of 2 passes; oracle/ref_callsites.eval_frame "
+                                         "(cv2.solvePnPRansac on 256 random px + ADD), one process per core",
+                               "succ_add": succ[0] / n_cpu}
+    print(json.dumps(res), flush=True)
+    return res
 
 
 def c1(args, dev):
@@ -156,7 +194,16 @@ def c1(args, dev):
     with torch.cuda.graph(gph, stream=s):
         sw.step(one["xyz"], one["mask"], one["extent"], one["lfborder"], one["K4"], one["cls"], one["R_gt"], one["t_gt"])
     out["F1_graph_replay_ms"] = timed(gph.replay, 200, warm=10)
+    if getattr(args, "cpu", False):
+        import bench
+        n_cpu = 4 * (os.cpu_count() or 1)
+        times, workers, n_cpu, succ = bench.run_reference_cpu(n_cpu, 3, spec=dict(config_id=1, kw=dict(cls=0)))
+        out["cpu_baseline"] = {"value": n_cpu / min(times[1:]), "unit": "frames/s", "cores": workers, "kind": "port",
+                               "ms_per_frame_per_core": 1e3 * min(times[1:]) * workers / n_cpu,
+                               "sample": f"{n_cpu} ape frames, best of 2 passes; oracle/ref_callsites.eval_frame (the exact "
+                                         "reference call: cv2.solvePnPRansac(EPNP) on 256 random masked px + ADD), one process per core"}
     print(json.dumps(out), flush=True)
+    return out
 
 
 def c5(args, dev):
@@ -241,6 +288,38 @@ def c5(args, dev):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def dense(args, dev):
+    """Dense, compact silhouettes (every pixel of the ellipsoid: P = 2 k .. 45 k, like a real LineMOD mask) through
+    the mask-first K0 and the whole sweep -- the mask shape SURVEY.md 8(d) asked for; C2's mask is a subset of it."""
+    import pose_estimation_b200 as pb
+    F, cap = 256, 49152
+    H, W = synth.IMG_H, synth.IMG_W
+    sps = [synth.make_frame_sparse(0x5EED, 12, f % 64, dense=True, z_range=(0.45, 1.0)) for f in range(F)]
+    xyz = torch.zeros((F, 3, H, W), dtype=torch.float32, device=dev); mask = torch.zeros((F, H, W), dtype=torch.uint8, device=dev)
+    for i, sp in enumerate(sps):
+        r, c = torch.from_numpy(sp["rows"].astype(np.int64)).to(dev), torch.from_numpy(sp["cols"].astype(np.int64)).to(dev)
+        xyz[i, :, r, c] = torch.from_numpy(sp["xyzn"].T.copy()).to(dev)
+        mask[i, r, c] = 1
+    cls = np.array([s["cls"] for s in sps], np.int32)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    ext, lfb = t(synth.EXTENT[cls].astype(np.float32)), t(synth.LFBORDER[cls].astype(np.float32))
+    K4, Rg, tg = t(np.tile(synth.LINEMOD_K4, (F, 1))), t(np.stack([s["R_gt"] for s in sps])), t(np.stack([s["t_gt"] for s in sps]))
+    comp = ops.MapCompactor(F, H, W, cap, device=dev)
+    ms_k0 = timed(lambda: comp(xyz, mask, ext, lfb), args.iters)
+    n_px = int(sum(s["rows"].shape[0] for s in sps))
+    strict = F * H * W + n_px * 32
+    sw = pb.EvalSweep(torch.from_numpy(synth.class_models(500)), torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM),
+                      F, H, W, cap, ops.RansacConfig(n_hyp=256, seed=0x5EED), device=dev)
+    ms = timed(lambda: sw.step(xyz, mask, ext, lfb, K4, t(cls), Rg, tg), args.iters)
+    sw.reset(); sw.step(xyz, mask, ext, lfb, K4, t(cls), Rg, tg)
+    summ = pb.summarize(sw.finish(), synth.OBJLIST)
+    res = {"config": "dense silhouettes", "frames": F, "P_mean": n_px / F, "P_max": max(s["rows"].shape[0] for s in sps),
+           "k0_ms": ms_k0, "k0_GBps_strict_bytes": strict / (ms_k0 * 1e-3) / 1e9, "sweep_ms": ms, "frames_per_s": F / (ms * 1e-3),
+           "hyp_pts_per_s": 256.0 * n_px / (ms * 1e-3), "succ_add": summ["succ_base_rt"], "failed": summ["failed"]}
+    print(json.dumps(res), flush=True)
+    return res
 
 
 def knn_large(args, dev):
@@ -417,6 +496,7 @@ def main():
     ap.add_argument("--c3-batch", type=int, default=4096)
     ap.add_argument("--c4-frames", type=int, default=256)
     ap.add_argument("--only", default="")
+    ap.add_argument("--cpu", action="store_true", help="time the reference's CPU path beside C1 / C3 / C4 (bounded samples)")
     args = ap.parse_args()
     import os
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -430,6 +510,8 @@ def main():
         c3(args, dev)
     if args.only in ("", "c4"):
         c4(args, dev)
+    if args.only in ("", "dense"):
+        dense(args, dev)
     if args.only in ("", "c5"):
         c5(args, dev)
     if args.only in ("", "region"):

@@ -215,6 +215,17 @@ def cal_dis(metric, pred_r, pred_t, target_r, target_t, target, model_points, cl
     return add_dis, r_dis, t_dis
 
 
+def cal_adds_torch_nxn(pred, target):
+    """lib/utils/metric.py:24-32 in the reference's own form, on the host: the two [N,N,3] tensors made with
+    ``repeat``, ``norm(dim=2)``, ``min(dim=1)``, ``mean`` (the reference moves them to the GPU first; the CPU-baseline
+    leg of the benchmarks keeps them on the host cores).  pred, target: torch [N,3] float32."""
+    import torch
+    N = pred.size(0)
+    pd = pred.view(1, N, 3).repeat(N, 1, 1)                  # :27
+    gt = target.view(N, 1, 3).repeat(1, N, 1)                # :28
+    return torch.mean(torch.min(torch.norm(pd - gt, dim=2), dim=1)[0]).item()      # :30-31
+
+
 # ----------------------------------------------------------------------------- KNN / loss
 def knn(x, y):
     """Stand-in for the KeOps handle of train.py:126: argmin_j SqDist(x_i, y_j), K=1 -> [N,1] int64."""

@@ -395,6 +395,7 @@ __device__ __forceinline__ void exact_group(const float* __restrict__ yb, const 
 //   warp 8     issues the MMAs of tile v into accumulator v % NACC, owns the TMEM allocation;
 //   warp 9     streams the database tiles through NSTG shared-memory stages with 1-D TMA bulk copies.
 // All hand-offs are mbarriers; the tile loop has no CTA-wide barrier.
+template <bool SORTED>
 __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint4* sA = reinterpret_cast<uint4*>(smem_raw);                    // [TILE_U4]
@@ -424,7 +425,7 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
         tc::mbar_init(&bar_a, 1);
         s_bad = 0;
         tc::fence_mbar_init();
-        if (a.permX) {      // both clouds follow one Morton order: start at the column tile facing this row tile, then outwards
+        if (SORTED) {       // both clouds follow one Morton order: start at the column tile facing this row tile, then outwards
             int lo = (int)(((long long)rt * ntM) / a.ntN), hi = lo + 1, i = 0;
             lo = lo >= ntM ? ntM - 1 : lo; hi = lo + 1;
             while (i < ntM) {
@@ -433,7 +434,7 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
             }
         }
     }
-    const bool sorted = a.permX != nullptr;
+    constexpr bool sorted = SORTED;
     if (warp == 8) tc::tmem_alloc<TMEM_COLS>(&tmem_base);
     tc::fence_before_sync();
     __syncthreads();
@@ -590,8 +591,8 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
                 for (int c = 0; c < 4 / NH; ++c) {
                     const int cc = half * (4 / NH) + c;
                     const float lbc = cc == 0 ? lb4.x : cc == 1 ? lb4.y : cc == 2 ? lb4.z : lb4.w;
-                    if (lbc > cur) continue;               // warp-uniform
-                    ++nchunks;
+                    if (SORTED && lbc > cur) continue;     // warp-uniform
+                    if (SORTED) ++nchunks;
                     TCCLK(t3);
                     uint32_t r[32];
                     tc::tmem_ld32(taddr + half * TH + c * 32, r);
@@ -788,7 +789,8 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
         xbox = reinterpret_cast<float*>(q); q += (size_t)nb_max * ntN * 4 * 6 * sizeof(float);
         ybox = reinterpret_cast<float*>(q);
     }
-    cudaFuncSetAttribute(knn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAIN_SMEM);
+    cudaFuncSetAttribute(knn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAIN_SMEM);
+    cudaFuncSetAttribute(knn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAIN_SMEM);
     cudaMemsetAsync(err, 0, 4 * sizeof(int), st);   // [0] barrier timeout, [1] fallback rows, [2] exact evaluations
     for (int b0 = 0; b0 < nl; b0 += TC_CHUNK) {
         const int nb = (nl - b0) < TC_CHUNK ? (nl - b0) : TC_CHUNK;
@@ -807,7 +809,8 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
             if (pb_check_launch("knn_tc_prepare_kernel")) return -2;
         }
         MainArgs ma{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, idx, d2, b0, err, blist, permX, permY, xs, ys, xbox, ybox, centre};
-        knn_tc_kernel<<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);
+        if (sorted) knn_tc_kernel<true><<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);
+        else knn_tc_kernel<false><<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);
         if (pb_check_launch("knn_tc_kernel")) return -2;
     }
     return 0;

@@ -84,6 +84,20 @@ int pb_compact_map(const float* xyz, const uint8_t* mask, const int32_t* roi, co
                    const float* lfborder, int F, int Hh, int Ww, int cap, float* pts,
                    int32_t* count, int32_t* total, void* ws, size_t ws_bytes, void* stream);
 
+/* pb_compact_map_noalloc -- NO COUNTERPART IN THE REFERENCE; added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The mask-first path of pb_compact_map (same kernel, same output bits) with its scratch -- a ticket and one state
+ * word per 65,536-pixel mask tile -- in a file-scope device array of the library instead of a caller workspace: the
+ * call allocates nothing and takes no workspace.  Limits: a mask is required, Hh*Ww % 16 == 0, mask 16-byte aligned,
+ * and F * ceil(Hh*Ww / 65536) <= pb_compact_map_noalloc_max_tiles() (65,536 tiles = 256 KB per GPU, held from
+ * library load to exit; 13,107 frames of 480 x 640); larger batches return -1 with a message.  The scratch is SHARED
+ * by all calls on a device and keeps the last call's contents: every call clears what it uses on its own stream
+ * first, and calls that overlap on the GPU (different streams) race -- serialise them.                          */
+int pb_compact_map_noalloc_max_tiles(void);
+int pb_compact_map_noalloc(const float* xyz, const uint8_t* mask, const int32_t* roi, const float* extent,
+                           const float* lfborder, int F, int Hh, int Ww, int cap, float* pts, int32_t* count,
+                           int32_t* total, void* stream);
+
 /* gather variant for the reference's `choose` index list (tools/trainer.py:408-421):
  * choose [F,NP] int64 flat indices into Hh*Ww, xmap/ymap [F,NP] f32 pixel coordinates.        */
 int pb_gather_correspondences(const float* xyz, const int64_t* choose, const float* xmap,

@@ -32,6 +32,8 @@ SIGNATURES = {
     "pb_abi_version": (I, []),
     "pb_compact_workspace_bytes": (SZ, [I, I, I, I]),
     "pb_compact_map": (I, [P, P, P, P, P, I, I, I, I, P, P, P, P, SZ, P]),
+    "pb_compact_map_noalloc_max_tiles": (I, []),
+    "pb_compact_map_noalloc": (I, [P, P, P, P, P, I, I, I, I, P, P, P, P]),
     "pb_gather_correspondences": (I, [P, P, P, P, P, P, I, I, I, I, I, P, P, P]),
     "pb_gather_choose": (I, [P, P, I, P, P, P, P, P, P, I, I, I, I, I, P, P, P]),
     "pb_region_decode_points": (I, [P, P, P, P, I, P, P, P, I, I, I, I, I, I, P, P, P]),

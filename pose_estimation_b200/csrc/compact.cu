@@ -756,3 +756,65 @@ extern "C" int pb_gather_correspondences(const float* xyz, const int64_t* choose
     PB_REQUIRE(xmap && ymap, "pb_gather_correspondences: null pointer argument");
     return pb_gather_choose(xyz, choose, 0, xmap, ymap, nullptr, nullptr, extent, lfborder, F, Hh, Ww, NP, cap, pts, count, stream);
 }
+
+// ---- pb_compact_map_noalloc: the mask-first streaming K0 with its scratch in a file-scope device array ------------
+// No counterpart in the reference; added for callers that cannot allocate
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same kernel as pb_compact_map's
+// mask-first path (compact_stream_kernel); its scratch -- one ticket word and one state word per 64 KB mask tile --
+// lives in g_noalloc_scratch instead of a caller workspace.  The array is shared by every call on a device and keeps
+// the last call's contents: each call clears the part it uses on its stream first, and two calls that overlap on the
+// GPU (different streams) RACE -- serialise them.
+constexpr int PB_NOALLOC_MAX_TILES = 65536;        // 256 KB of tile states (+ 256 B ticket) per GPU that loads the library
+static __device__ __align__(256) uint32_t g_noalloc_scratch[64 + PB_NOALLOC_MAX_TILES];
+
+namespace {
+// device address of g_noalloc_scratch per device: in host code the array's name is only a host-side stand-in
+void* g_noalloc_ptr[64];
+int noalloc_scratch_ptr(uint32_t** out) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { pb_set_error("pb_compact_map_noalloc: cudaGetDevice failed"); return 1; }
+    if (!g_noalloc_ptr[dev]) {                    // once per device, with that device current
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) { pb_set_error("pb_compact_map_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e)); return 1; }
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = static_cast<uint32_t*>(g_noalloc_ptr[dev]);
+    return 0;
+}
+}  // namespace
+
+extern "C" int pb_compact_map_noalloc_max_tiles(void) { return PB_NOALLOC_MAX_TILES; }
+
+extern "C" int pb_compact_map_noalloc(const float* xyz, const uint8_t* mask, const int32_t* roi, const float* extent,
+                                      const float* lfborder, int F, int Hh, int Ww, int cap, float* pts, int32_t* count,
+                                      int32_t* total, void* stream) {
+    PB_REQUIRE(F >= 0 && Hh > 0 && Ww > 0 && cap > 0, "pb_compact_map_noalloc: bad sizes F=%d H=%d W=%d cap=%d", F, Hh, Ww, cap);
+    const long long HW = (long long)Hh * Ww;
+    PB_REQUIRE(HW < (1ll << 30), "pb_compact_map_noalloc: map too large");
+    if (F == 0) return 0;
+    PB_REQUIRE(xyz && mask && extent && lfborder && pts && count, "pb_compact_map_noalloc: null pointer argument (a mask is required)");
+    PB_REQUIRE(HW % 16 == 0 && reinterpret_cast<uintptr_t>(mask) % 16 == 0,
+               "pb_compact_map_noalloc: H*W must be a multiple of 16 and the mask 16-byte aligned");
+    const int tpf = stream_tiles_per_frame(HW);
+    const long long ntiles = (long long)F * tpf;
+    PB_REQUIRE(ntiles <= PB_NOALLOC_MAX_TILES,
+               "pb_compact_map_noalloc: %lld mask tiles (F=%d x %d tiles of 65536 px) exceed the static scratch of %d tiles; "
+               "split the batch or use pb_compact_map with a workspace", ntiles, F, tpf, PB_NOALLOC_MAX_TILES);
+    uint32_t* scratch = nullptr;
+    if (noalloc_scratch_ptr(&scratch)) return -2;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (cudaMemsetAsync(scratch, 0, (64 + (size_t)ntiles) * sizeof(uint32_t), st) != cudaSuccess) {   // ticket + this call's states
+        pb_check_launch("pb_compact_map_noalloc memset");
+        return -2;
+    }
+    CompactArgs a;
+    a.xyz = xyz; a.mask = mask; a.roi = roi; a.extent = extent; a.lfborder = lfborder;
+    a.pts = pts; a.count = count; a.total = total; a.seg_total = nullptr;
+    a.HW = Hh * Ww; a.Ww = Ww; a.cap = cap; a.S = 1; a.quads_per_split = 0; a.segcap = cap;
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, compact_stream_kernel, CT, 0);
+    const int grid = (int)(ntiles < (long long)pb_sm_count() * (per_sm > 0 ? per_sm : 1) ? ntiles : (long long)pb_sm_count() * (per_sm > 0 ? per_sm : 1));
+    compact_stream_kernel<<<grid, CT, 0, st>>>(a, scratch + 64, scratch, tpf, (int)ntiles);
+    return pb_check_launch("compact_stream_kernel (noalloc)") ? -2 : 0;
+}

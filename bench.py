@@ -448,7 +448,13 @@ def ours_arm(args):
         hs = sweep.HostEvalSweep(models, diam, sym, H, W, CAP, chunk=chunk, cfg=cfg, device=dev, zero_copy=zc)
         small_h = sweep.pack_small(*small_src, chunk).pin_memory()
 
+        replay = None
+        if kind == "choose_graph":     # the same pass as "choose", captured once and replayed as a CUDA graph
+            replay = hs.capture_choose(xyz_h, choose_h, small_h, cls_h, xmap_h=xm_h, ymap_h=ym_h, n_valid_h=nv_h, frame0=rank * F)
+
         def once():
+            if replay is not None:
+                return replay()
             hs.reset()
             if kind == "choose":           # the reference's interface: maps + int64 choose + f32 x / y lists, all on the host
                 return hs.run_choose(xyz_h, choose_h, small_h, cls_h, xmap_h=xm_h, ymap_h=ym_h, n_valid_h=nv_h, frame0=rank * F)
@@ -473,7 +479,8 @@ def ours_arm(args):
         return world * F * steps / (float(ms.item()) * 1e-3), hs.h2d_bytes, tb.clone()
 
     nchunk = int(os.environ.get("PB_ZC_SPLIT", "4"))
-    e2e_value, list_bytes, tb_host = run_e2e("choose", F // nchunk, args.steps)
+    eager_value, list_bytes, tb_eager = run_e2e("choose", F // nchunk, args.steps)
+    e2e_value, _, tb_host = run_e2e("choose_graph", F // nchunk, args.steps)
     e2e_bytes = list_bytes + sectors * 3 * 32
     dev_value, dev_bytes, tb_dev = run_e2e("choose_dev", F // nchunk, args.steps)
     dev32_value, dev32_bytes, tb_dev32 = run_e2e("choose_dev32", F // nchunk, args.steps)
@@ -481,7 +488,7 @@ def ours_arm(args):
     zc_bytes += sectors * 3 * 32
     staged_value, staged_bytes, tb_staged = run_e2e("staged", 128, min(args.steps, 5))
     tcpu = table.cpu()
-    same = all(bool(torch.equal(t_, tcpu)) for t_ in (tb_host, tb_dev, tb_dev32, tb_zc, tb_staged))
+    same = all(bool(torch.equal(t_, tcpu)) for t_ in (tb_host, tb_eager, tb_dev, tb_dev32, tb_zc, tb_staged))
 
     clocks = sampler.stop() if sampler else None
     if rank == 0:
@@ -541,13 +548,17 @@ def ours_arm(args):
                                      "the pass kernel_ms / stage_ms / roofline.launch_ms are measured in"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": e2e_bytes,
                     "d2h_bytes_per_step": tb_host.numel() * tb_host.element_size(),
-                    "api": "HostEvalSweep.run_choose: everything in PINNED HOST memory in the reference's own form "
+                    "api": "HostEvalSweep.capture_choose(...) -> replay(): run_choose captured once as a CUDA graph and replayed per "
+                           "step (one cudaGraphLaunch + the table all-reduce + D2H + sync per step; the graph's memcpy nodes "
+                           "and the gather kernel read whatever the pinned buffers hold).  run_choose: everything in PINNED HOST memory in the reference's own form "
                            "(tools/trainer.py:383-421) -- coordinate maps [F,3,480,640] f32, choose [F,NP] int64, "
                            "x / y_map_choosed [F,NP] f32, per-frame extent / lfborder / K / GT pose / class.  Per chunk the "
                            "lists go by the copy engine, pb_gather_choose reads the maps in place (only the chosen "
                            "pixels' 32 B sectors cross PCIe: counted exactly, distinct sectors x 3 planes), K1..K6 on two "
                            "alternating lanes, table D2H + sync every step",
                     "table_equals_device_path": same,
+                    "eager_variant": {"value": eager_value, "unit": UNIT, "h2d_bytes_per_step": e2e_bytes,
+                                      "api": "HostEvalSweep.run_choose called every step (no graph): ~100 launches / copies from Python"},
                     "device_map_variant": {"value": dev_value, "unit": UNIT, "h2d_bytes_per_step": dev_bytes,
                                            "api": "run_choose with pred['xyz'] still on the device (it is the network's "
                                                   "output); the int64 / f32 lists and per-frame data from the host"},

@@ -439,6 +439,19 @@ class HostEvalSweep:
             raise ValueError("xyz must be a CUDA tensor or a pinned host tensor")
         NP = choose_h.shape[1]
         with_xy = xmap_h is not None
+        self._enqueue_choose(xyz, choose_h, small_h, cls_h, xmap_h, ymap_h, n_valid_h, frame0, roi_h)
+        comp = torch.cuda.current_stream(self.dev)
+        table = self.table
+        reduce_table(table, group)
+        self.table_host.copy_(table, non_blocking=True)
+        comp.synchronize()
+        return self.table_host
+
+    def _enqueue_choose(self, xyz, choose_h, small_h, cls_h, xmap_h, ymap_h, n_valid_h, frame0, roi_h):
+        """Everything run_choose puts on the streams, up to the lanes joining the caller's stream (no host sync)."""
+        F = choose_h.shape[0]
+        NP = choose_h.shape[1]
+        with_xy = xmap_h is not None
         stg = self._list_stage(NP, choose_h.dtype, with_xy)
         comp = torch.cuda.current_stream(self.dev)
         n, nl = F // self.chunk, len(self.sweeps)
@@ -446,6 +459,7 @@ class HostEvalSweep:
         self.start.record(comp)
         for s_ in self.lane_streams:
             s_.wait_event(self.start)
+        self.copy_stream.wait_event(self.start)      # (under stream capture every stream must fork from the caller's)
         for i in range(n):
             st, ls = self.stage[i & 1], stg[i & 1]
             sweep, lane = self.sweeps[i % nl], self.lane_streams[i % nl]
@@ -479,8 +493,34 @@ class HostEvalSweep:
         for k, s_ in enumerate(self.lane_streams):
             self.lane_done[k].record(s_)
             comp.wait_event(self.lane_done[k])
-        table = self.table
-        reduce_table(table, group)
-        self.table_host.copy_(table, non_blocking=True)
-        comp.synchronize()
-        return self.table_host
+
+    def capture_choose(self, xyz, choose_h, small_h, cls_h, xmap_h=None, ymap_h=None, n_valid_h=None, frame0=0, roi_h=None):
+        """run_choose as ONE replayed CUDA graph, for a serving loop that refills the same pinned host buffers (and
+        the same xyz tensor) every pass: the per-pass host work shrinks from ~100 launches / copies to one
+        cudaGraphLaunch, the table all-reduce, one D2H copy and one sync.  Runs the pass once eagerly (warm-up), then
+        captures it -- table reset, list copies on the copy stream, gather + K1..K6 on the two lanes, the table sum.
+        Returns ``replay(group=None) -> table on the host``; the graph reads whatever the buffers hold at replay time
+        (same shapes, same addresses)."""
+        args = (xyz, choose_h, small_h, cls_h, xmap_h, ymap_h, n_valid_h, frame0, roi_h)
+        for t in (choose_h, small_h, cls_h, xmap_h, ymap_h, n_valid_h, roi_h):
+            if t is not None and not t.is_pinned():
+                raise ValueError("capture_choose needs pinned host tensors (their addresses are baked into the graph)")
+        self.reset()
+        self.run_choose(xyz, choose_h, small_h, cls_h, xmap_h=xmap_h, ymap_h=ymap_h, n_valid_h=n_valid_h, frame0=frame0,
+                        roi_h=roi_h)
+        torch.cuda.synchronize(self.dev)
+        tab_out = torch.zeros_like(self._tables[0])
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            self._tables.zero_()
+            self._enqueue_choose(*args)
+            tab_out.copy_(self._tables.sum(dim=0))
+        self._graph_keep = (graph, tab_out, args)          # the graph reads these tensors: keep them alive
+
+        def replay(group=None):
+            graph.replay()
+            reduce_table(tab_out, group)
+            self.table_host.copy_(tab_out, non_blocking=True)
+            torch.cuda.current_stream(self.dev).synchronize()
+            return self.table_host
+        return replay

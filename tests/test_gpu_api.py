@@ -398,3 +398,33 @@ def test_host_eval_sweep_choose_lists_equal_device_mask_path(dev):
     sw3.step(t(b["xyz"]), None, t(b["extent"]), t(b["lfborder"]), t(b["K4"]), t(b["cls"]), t(b["R_gt"]), t(b["t_gt"]),
              choose=t(choose), xmap=t(xm), ymap=t(ym), n_valid=t(nv))
     assert torch.equal(sw3.finish().cpu(), want)
+
+
+def test_host_eval_sweep_choose_graph_replay_equals_eager(dev):
+    """HostEvalSweep.capture_choose: the pass as one replayed CUDA graph gives run_choose's table, also after the
+    pinned buffers have been refilled with another batch (same addresses, new contents)."""
+    from pose_estimation_b200 import sweep
+    F, chunk = 32, 8
+    models = torch.from_numpy(synth.class_models(500))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    hs = sweep.HostEvalSweep(models, diam, sym, synth.IMG_H, synth.IMG_W, 1280, chunk=chunk, device=dev, zero_copy=True)
+    bufs, replay = None, None
+    for first in (0, 100):
+        sps = synth.make_batch_sparse(0x5EED, 2, F, first_frame=first)
+        b = batch_arrays(sps)
+        choose, xm, ym, nv = _choose_lists(sps, 1216)
+        small = sweep.pack_small(b["extent"], b["lfborder"], b["K4"], b["R_gt"], b["t_gt"], chunk)
+        new = [torch.from_numpy(b["xyz"]), torch.from_numpy(choose), small, torch.from_numpy(b["cls"]), torch.from_numpy(xm),
+               torch.from_numpy(ym), torch.from_numpy(nv)]
+        if bufs is None:
+            bufs = [t.pin_memory() for t in new]
+            replay = hs.capture_choose(bufs[0], bufs[1], bufs[2], bufs[3], xmap_h=bufs[4], ymap_h=bufs[5], n_valid_h=bufs[6])
+        else:
+            for dst, src in zip(bufs, new):
+                dst.copy_(src)
+        got = replay().clone()
+        hs.reset()
+        want = hs.run_choose(bufs[0], bufs[1], bufs[2], bufs[3], xmap_h=bufs[4], ymap_h=bufs[5], n_valid_h=bufs[6]).clone()
+        assert torch.equal(got, want) and got[0].sum() == F, first
+        assert torch.equal(replay(), want)                                   # replays do not accumulate

@@ -410,7 +410,9 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     sa.hypRt = static_cast<float*>(ws);
     sa.hyp_counts = hyp_counts;
     sa.slice_best = reinterpret_cast<unsigned long long*>(static_cast<char*>(ws) + p.off_best);
+    if (p.bal && reinterpret_cast<uintptr_t>(pts) % 16 != 0) p.bal = 0;     // the balanced kernel stages with 16-byte async copies
     sa.cnt_all = p.bal ? (hyp_counts ? hyp_counts : reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_cnt)) : nullptr;
+    sa.prefix = p.bal ? reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_prefix) : nullptr;
     sa.cap = cap; sa.H = prm->n_hyp; sa.HS = p.HS; sa.Hs = p.Hs; sa.CH = p.CH; sa.PP = p.PP;
     sa.frame0 = frame0; sa.seed_lo = prm->seed_lo; sa.seed_hi = prm->seed_hi;
     sa.inv_thr = 1.0f / prm->thresh_px; sa.F = F;

@@ -11,6 +11,8 @@ struct ScoreArgs {
     int32_t* hyp_counts;             // optional [F,H]
     unsigned long long* slice_best;  // [F,HS] packed (count+1, ~hyp)
     int32_t* cnt_all;                // balanced mode: [F,H] inlier counts accumulated with atomics (-1 = no model)
+    int32_t* prefix;                 // balanced mode: [F+1] exclusive prefix of the frames' point counts rounded up to 8
+                                     // (written by block 0 of the hypothesis kernel, read by every scoring CTA)
     int cap, H, HS, Hs, CH, PP;      // Hs hypotheses per slice (power of two >= 32); PP point parts
     uint32_t frame0, seed_lo, seed_hi;
     float inv_thr;
@@ -21,13 +23,13 @@ struct Plan {
     int HS, Hs, CH, PP, NHL;
     size_t smem_score, smem_final, off_best, total;
     int bal, bal_grid;               // balanced scoring (see ransac_score_bal_kernel): CTAs of equal point ranges
-    size_t smem_bal, off_cnt;
+    size_t smem_bal, off_cnt, off_prefix;
 };
 
 // Hypotheses of a frame are cut into HS slices of Hs (power of two) so that few-frame launches
 // still fill 148 SMs; a slice narrower than the CTA splits the points PP ways instead.
 #define PB_SCORE_THREADS 128     /* CTA size of the scoring kernel (ST in ransac_score.cu) */
-#define PB_BAL_CH 1024           /* points staged per chunk by the balanced scoring kernel */
+#define PB_BAL_SUB 256           /* points per staging buffer of the balanced scoring kernel (two buffers) */
 
 static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm, int sms = 148) {
     if (sms <= 0) sms = 148;
@@ -55,15 +57,16 @@ static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm, int sm
     // A batch of about one wave of CTAs cannot be rebalanced by the hardware scheduler: frames carry different
     // numbers of points and the launch lasts as long as the SM with the largest sum.  Then CTAs take equal
     // ranges of the concatenated point list instead (H <= 256 hypotheses held by one CTA).
-    p.smem_bal = (size_t)PB_BAL_CH * 5 * 4 + (size_t)(F + 1) * 4;
-    int per_sm = (int)((220 * 1024) / (p.smem_bal + 1024));
-    if (per_sm > 6) per_sm = 6;                        // 80 registers x 128 threads: six CTAs per SM, one wave
-    // (the per-CTA prefix of the frames' counts lives in shared memory: F is bounded by per_sm >= 4, about 8 k frames;
-    // above that the frame-per-CTA launch has enough waves for the hardware scheduler to balance)
-    p.bal = (p.HS == 1 && p.PP == 1 && F >= two_waves && per_sm >= 4) ? 1 : 0;
+    p.smem_bal = 0;                                    // the balanced kernel's two 256-point buffers are static (10 KB)
+    const int per_sm = 6;                              // <= 85 registers x 128 threads: six CTAs per SM, one wave
+    p.bal = (p.HS == 1 && p.PP == 1 && F >= two_waves && cap % 4 == 0) ? 1 : 0;
     p.bal_grid = sms * per_sm;
     p.off_cnt = (p.total + 255) / 256 * 256;
-    if (p.bal) p.total = p.off_cnt + (size_t)F * H * sizeof(int32_t);
+    p.off_prefix = p.off_cnt;
+    if (p.bal) {
+        p.off_prefix = (p.off_cnt + (size_t)F * H * sizeof(int32_t) + 255) / 256 * 256;
+        p.total = p.off_prefix + (size_t)(F + 1) * sizeof(int32_t);
+    }
     return p;
 }
 

@@ -26,7 +26,36 @@ namespace {
 
 constexpr int HT = 128;  // threads per CTA of the hypothesis kernel
 
+// exclusive prefix of the frames' point counts rounded up to 8 -> a.prefix[0..F] (one CTA; the balanced scoring kernel
+// cuts this padded index space into equal ranges, so every range and every frame segment starts at a multiple of 8)
+__device__ void frame_prefix_scan(const ScoreArgs& a) {
+    __shared__ int wsum[HT / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (a.F + HT - 1) / HT;
+    int mine = 0;
+    for (int k = 0; k < per; ++k) {
+        const int f = tid * per + k;
+        if (f < a.F) mine += (max(0, min(a.count[f], a.cap)) + 7) & ~7;
+    }
+    int incl = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += v;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    int base = incl - mine;
+    for (int w = 0; w < warp; ++w) base += wsum[w];
+    for (int k = 0; k < per; ++k) {
+        const int f = tid * per + k;
+        if (f < a.F) { a.prefix[f] = base; base += (max(0, min(a.count[f], a.cap)) + 7) & ~7; }
+    }
+    if (tid == HT - 1) a.prefix[a.F] = base;
+}
+
 __global__ void __launch_bounds__(HT) ransac_hypothesis_kernel(ScoreArgs a) {
+    if (blockIdx.x == 0 && a.prefix) frame_prefix_scan(a);        // uniform per CTA
     const long long gid = (long long)blockIdx.x * HT + threadIdx.x;
     if (gid >= (long long)a.F * a.H) return;
     const int f = (int)(gid / a.H), h = (int)(gid - (long long)f * a.H);
@@ -251,148 +280,197 @@ __global__ void __launch_bounds__(ST) ransac_score_kernel(ScoreArgs a) {
     }
 }
 
-// Balanced scoring: gridDim.x CTAs, all resident, each takes an EQUAL range of the batch's concatenated point
-// list (a range usually touches two frames) -- for every frame segment it loads that frame's hypotheses, scores
-// the segment exactly like ransac_score_kernel and adds its counts to cnt_all[f][h].  Inlier counts are integer
-// sums, so the result does not depend on the cut.  The arg-max moves to the finalize kernel.
+// inlier_s2 with the pixel coordinates as they are in the correspondence list (already in threshold units): the
+// negation is an operand modifier of the FMA, so the bits equal inlier_s2's / common.cuh::inlier_s.
+__device__ __forceinline__ void inlier_s2u(const f32x2 m[12], f32x2 X, f32x2 Y, f32x2 Z, f32x2 us, f32x2 vs, uint32_t& s0,
+                                           uint32_t& s1) {
+    const f32x2 x = ffma2(m[0], X, ffma2(m[1], Y, ffma2(m[2], Z, m[3])));
+    const f32x2 y = ffma2(m[4], X, ffma2(m[5], Y, ffma2(m[6], Z, m[7])));
+    const f32x2 w = ffma2(m[8], X, ffma2(m[9], Y, ffma2(m[10], Z, m[11])));
+    const float w0 = lo32(w), dx0 = fmaf(-lo32(us), w0, lo32(x)), dy0 = fmaf(-lo32(vs), w0, lo32(y));
+    const float nq0 = w0 * -fabsf(w0);
+    s0 = __float_as_uint(fmaf(dx0, dx0, fmaf(dy0, dy0, nq0)));
+    const float w1 = hi32(w), dx1 = fmaf(-hi32(us), w1, hi32(x)), dy1 = fmaf(-hi32(vs), w1, hi32(y));
+    const float nq1 = w1 * -fabsf(w1);
+    s1 = __float_as_uint(fmaf(dx1, dx1, fmaf(dy1, dy1, nq1)));
+}
+
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* dst_smem, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+constexpr int SUB = PB_BAL_SUB;      // points per staging buffer
+
+// Balanced scoring: gridDim.x CTAs, all resident, each takes an EQUAL range of the batch's concatenated point list
+// (frames padded to a multiple of 8 points; a range usually touches two frames).  The range is worked off in
+// sub-chunks of <= 256 points of one frame, staged as they lie in the correspondence list (SoA) by asynchronous
+// 16-byte copies into one of two shared-memory buffers while the previous sub-chunk is being scored; the frames'
+// prefix comes from the hypothesis kernel (one scan per launch, not one per CTA).  For every frame segment the CTA
+// holds that frame's hypotheses (two per thread) and adds its counts to cnt_all[f][h]; inlier counts are integer sums,
+// so the result does not depend on the cut.  The arg-max is taken by the finalize kernel.
 template <int NHL>
 __global__ void __launch_bounds__(ST, 6) ransac_score_bal_kernel(ScoreArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    constexpr int CH = PB_BAL_CH;
-    float4* sA = reinterpret_cast<float4*>(smem_raw);            // [CH/2]
-    float4* sB = sA + CH / 2;                                    // [CH/2]
-    float2* sC = reinterpret_cast<float2*>(sB + CH / 2);         // [CH/2]
-    int* prefix = reinterpret_cast<int*>(sC + CH / 2);           // [F+1] exclusive prefix of the frames' point counts
-    __shared__ int wsum[ST / 32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ __align__(16) float sbuf[2][5][SUB];
+    const int tid = threadIdx.x;
     const int F = a.F;
-    // ---- block scan of min(count, cap): thread t owns frames [t*per, (t+1)*per)
-    const int per = (F + ST - 1) / ST;
-    int mine = 0;
-    for (int k = 0; k < per; ++k) {
-        const int f = tid * per + k;
-        if (f < F) mine += min(a.count[f], a.cap);
-    }
-    int incl = mine;
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, incl, off);
-        if (lane >= off) incl += v;
-    }
-    if (lane == 31) wsum[warp] = incl;
-    __syncthreads();
-    int base = incl - mine;
-    for (int w = 0; w < warp; ++w) base += wsum[w];
-    for (int k = 0; k < per; ++k) {
-        const int f = tid * per + k;
-        if (f < F) { prefix[f] = base; base += min(a.count[f], a.cap); }
-    }
-    if (tid == ST - 1) prefix[F] = base;
-    __syncthreads();
+    const int* __restrict__ prefix = a.prefix;
     const int T = prefix[F];
     int U = (T + (int)gridDim.x - 1) / (int)gridDim.x;
     U = (U + 7) & ~7;
     const long long g0l = (long long)blockIdx.x * U;
     if (g0l >= T) return;
     const int g0 = (int)g0l, g1 = min(T, g0 + U);
-    int lo = 0, hi = F;                                          // last f with prefix[f] <= g0
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (prefix[mid] <= g0) lo = mid; else hi = mid;
-    }
-    const float ninf = __int_as_float(0xff800000);
-    float* sAf = reinterpret_cast<float*>(sA);
-    float* sBf = reinterpret_cast<float*>(sB);
-    float* sCf = reinterpret_cast<float*>(sC);
-    for (int f = lo; f < F && prefix[f] < g1; ++f) {
-        const int p0 = max(g0, prefix[f]) - prefix[f], p1 = min(g1, prefix[f + 1]) - prefix[f];
-        if (p1 <= p0) continue;
-        const float* X = a.pts + (size_t)f * 5 * a.cap;
-        const float* Y = X + a.cap;
-        const float* Z = Y + a.cap;
-        const float* Uu = Z + a.cap;
-        const float* V = Uu + a.cap;
-        const float fx = a.K4[4 * f], fy = a.K4[4 * f + 1], cx = a.K4[4 * f + 2], cy = a.K4[4 * f + 3];
-        f32x2 m[NHL][12];
-        int c[NHL];
-#pragma unroll
-        for (int j = 0; j < NHL; ++j) {
-            const int h = tid + j * ST;
-            c[j] = 0;
-            bool valid = false;
-            float mj[12];
-            if (h < a.H) {
-                const float4* o = reinterpret_cast<const float4*>(a.hypRt + ((size_t)f * a.H + h) * 12);
-                const float4 r0 = o[0], r1 = o[1], r2 = o[2];
-                valid = (r2.w == r2.w);
-                if (valid) {
-                    const float R[9] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x};
-                    const float t[3] = {r2.y, r2.z, r2.w};
-                    make_proj_s(fx, fy, cx, cy, R, t, a.inv_thr, mj);
-                }
-            }
-            if (!valid) {
-#pragma unroll
-                for (int k = 0; k < 12; ++k) mj[k] = 0.0f;
-                mj[11] = -1.0f;
-            }
-#pragma unroll
-            for (int k = 0; k < 12; ++k) m[j][k] = pack2(mj[k], mj[k]);
+    int f = 0;
+    {   // last frame with prefix[f] <= g0 (frames without points share a prefix value: take the last of them)
+        int lo = 0, hi = F;
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (prefix[mid] <= g0) lo = mid; else hi = mid;
         }
-        for (int c0 = p0; c0 < p1; c0 += CH) {
-            const int n = min(CH, p1 - c0);
-            const int npp = (n + 7) & ~7;
-            __syncthreads();
-            for (int i = tid; i < npp; i += ST) {
-                const int o4 = (i >> 1) * 4 + (i & 1);
-                if (i < n) {
-                    sAf[o4] = X[c0 + i]; sAf[o4 + 2] = Y[c0 + i];
-                    sBf[o4] = Z[c0 + i]; sBf[o4 + 2] = -(Uu[c0 + i] * a.inv_thr);
-                    sCf[i] = -(V[c0 + i] * a.inv_thr);
-                } else {
-                    sAf[o4] = 0.0f; sAf[o4 + 2] = 0.0f;
-                    sBf[o4] = 0.0f; sBf[o4 + 2] = ninf;
-                    sCf[i] = ninf;
-                }
-            }
-            __syncthreads();
-            const ulonglong2* a2 = reinterpret_cast<const ulonglong2*>(sA);
-            const ulonglong2* b2 = reinterpret_cast<const ulonglong2*>(sB);
-            const ulonglong2* c2 = reinterpret_cast<const ulonglong2*>(sC);
-#pragma unroll 1
-            for (int i = 0; i < (npp >> 1); i += 4) {
-                const ulonglong2 v01 = c2[i >> 1], v23 = c2[(i >> 1) + 1];
-                const f32x2 nvs[4] = {v01.x, v01.y, v23.x, v23.y};
-                uint32_t acc[NHL];
-#pragma unroll
-                for (int j = 0; j < NHL; ++j) acc[j] = 0u;
+        f = lo;
+    }
+    const bool scale = a.inv_thr != 1.0f;
+    const float ninf = __int_as_float(0x7f800000);
+
+    // sub-chunk descriptor: frame sf, first point sp0 (multiple of 8), padded length sn (multiple of 8, <= SUB)
+    auto describe = [&](int g, int& fr, int& sf, int& sp0, int& sn) -> bool {
+        if (g >= g1) return false;
+        while (fr + 1 < F && prefix[fr + 1] <= g) ++fr;
+        sf = fr; sp0 = g - prefix[fr];
+        sn = min(min(SUB, prefix[fr + 1] - g), g1 - g);
+        return true;
+    };
+    // asynchronous staging of a sub-chunk: groups of 4 points, 16 bytes per array; beyond the frame's count: sentinels
+    auto stage = [&](int b, int sf, int sp0, int sn) {
+        const int P = max(0, min(a.count[sf], a.cap));
+        const float* base = a.pts + (size_t)sf * 5 * a.cap + sp0;
+        for (int e = tid; e < (sn >> 2) * 5; e += ST) {
+            const int arr = e / (sn >> 2), i = (e - arr * (sn >> 2)) << 2;
+            float* dst = &sbuf[b][arr][i];
+            const float* src = base + (size_t)arr * a.cap + i;
+            if (sp0 + i + 4 <= P) cp_async16(dst, src);
+            else {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    const ulonglong2 pa = a2[i + k], pbv = b2[i + k];
-#pragma unroll
-                    for (int j = 0; j < NHL; ++j) {
-                        uint32_t s0, s1;
-                        inlier_s2(m[j], pa.x, pa.y, pbv.x, pbv.y, nvs[k], s0, s1);
-                        acc[j] = __funnelshift_l(s0, acc[j], 1);
-                        acc[j] = __funnelshift_l(s1, acc[j], 1);
-                    }
+                    if (sp0 + i + k < P) cp_async4(dst + k, src + k);
+                    else dst[k] = arr >= 3 ? ninf : 0.0f;          // u = v = +inf: s = +inf or NaN, never an inlier
                 }
-#pragma unroll
-                for (int j = 0; j < NHL; ++j) c[j] += __popc(acc[j]);
             }
         }
+        cp_async_commit();
+    };
+    // pixel coordinates into threshold units (only when thr != 1): every thread scales what it copied itself
+    auto scale_uv = [&](int b, int sf, int sp0, int sn) {
+        const int P = max(0, min(a.count[sf], a.cap));
+        for (int e = tid; e < (sn >> 2) * 5; e += ST) {
+            const int arr = e / (sn >> 2), i = (e - arr * (sn >> 2)) << 2;
+            if (arr < 3) continue;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (sp0 + i + k < P) sbuf[b][arr][i + k] = sbuf[b][arr][i + k] * a.inv_thr;
+        }
+    };
+
+    f32x2 m[NHL][12];
+    int c[NHL];
+#pragma unroll
+    for (int j = 0; j < NHL; ++j) c[j] = 0;
+    int cur_f = -1;
+    int sf, sp0, sn, nf = 0, np0 = 0, nn = 0;
+    int g = g0;
+    bool have = describe(g, f, sf, sp0, sn);
+    if (have) stage(0, sf, sp0, sn);
+    for (int k = 0; have; ++k) {
+        const int b = k & 1;
+        g += sn;
+        const bool more = describe(g, f, nf, np0, nn);
+        if (more) stage(b ^ 1, nf, np0, nn);                       // in flight under this sub-chunk's scoring
+        if (sf != cur_f) {                                         // (uniform) another frame: flush, load its hypotheses
+            if (cur_f >= 0) {
+#pragma unroll
+                for (int j = 0; j < NHL; ++j) {
+                    const int h = tid + j * ST;
+                    if (h < a.H && c[j] > 0) atomicAdd(&a.cnt_all[(size_t)cur_f * a.H + h], c[j]);
+                    c[j] = 0;
+                }
+            }
+            cur_f = sf;
+            const float fx = a.K4[4 * sf], fy = a.K4[4 * sf + 1], cx = a.K4[4 * sf + 2], cy = a.K4[4 * sf + 3];
+#pragma unroll
+            for (int j = 0; j < NHL; ++j) {
+                const int h = tid + j * ST;
+                bool valid = false;
+                float mj[12];
+                if (h < a.H) {
+                    const float4* o = reinterpret_cast<const float4*>(a.hypRt + ((size_t)sf * a.H + h) * 12);
+                    const float4 r0 = o[0], r1 = o[1], r2 = o[2];
+                    valid = (r2.w == r2.w);
+                    if (valid) {
+                        const float R[9] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x};
+                        const float t[3] = {r2.y, r2.z, r2.w};
+                        make_proj_s(fx, fy, cx, cy, R, t, a.inv_thr, mj);
+                    }
+                }
+                if (!valid) {
+#pragma unroll
+                    for (int q = 0; q < 12; ++q) mj[q] = 0.0f;
+                    mj[11] = -1.0f;                                // w < 0 for every point: never an inlier
+                }
+#pragma unroll
+                for (int q = 0; q < 12; ++q) m[j][q] = pack2(mj[q], mj[q]);
+            }
+        }
+        if (more) cp_async_wait<1>(); else cp_async_wait<0>();     // this sub-chunk's copies have landed (own thread)
+        if (scale) scale_uv(b, sf, sp0, sn);
+        __syncthreads();                                           // ... and everybody else's
+        const ulonglong2* X2 = reinterpret_cast<const ulonglong2*>(sbuf[b][0]);
+        const ulonglong2* Y2 = reinterpret_cast<const ulonglong2*>(sbuf[b][1]);
+        const ulonglong2* Z2 = reinterpret_cast<const ulonglong2*>(sbuf[b][2]);
+        const ulonglong2* U2 = reinterpret_cast<const ulonglong2*>(sbuf[b][3]);
+        const ulonglong2* V2 = reinterpret_cast<const ulonglong2*>(sbuf[b][4]);
+#pragma unroll 1
+        for (int i = 0; i < (sn >> 2); i += 2) {                   // 8 points per iteration: two 128-bit loads per array
+            uint32_t acc[NHL];
+#pragma unroll
+            for (int j = 0; j < NHL; ++j) acc[j] = 0u;
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const ulonglong2 xv = X2[i + q], yv = Y2[i + q], zv = Z2[i + q], uv = U2[i + q], vv = V2[i + q];
+#pragma unroll
+                for (int j = 0; j < NHL; ++j) {
+                    uint32_t s0, s1;
+                    inlier_s2u(m[j], xv.x, yv.x, zv.x, uv.x, vv.x, s0, s1);
+                    acc[j] = __funnelshift_l(s0, acc[j], 1);
+                    acc[j] = __funnelshift_l(s1, acc[j], 1);
+                    inlier_s2u(m[j], xv.y, yv.y, zv.y, uv.y, vv.y, s0, s1);
+                    acc[j] = __funnelshift_l(s0, acc[j], 1);
+                    acc[j] = __funnelshift_l(s1, acc[j], 1);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < NHL; ++j) c[j] += __popc(acc[j]);
+        }
+        __syncthreads();                                           // buffer b is free for the sub-chunk after next
+        have = more; sf = nf; sp0 = np0; sn = nn;
+    }
+    if (cur_f >= 0) {
 #pragma unroll
         for (int j = 0; j < NHL; ++j) {
             const int h = tid + j * ST;
-            if (h < a.H && c[j] > 0) atomicAdd(&a.cnt_all[(size_t)f * a.H + h], c[j]);   // c > 0 only for valid hypotheses
+            if (h < a.H && c[j] > 0) atomicAdd(&a.cnt_all[(size_t)cur_f * a.H + h], c[j]);   // c > 0 only for valid hypotheses
         }
     }
 }
 
 template <int NHL>
 int launch_bal(const ScoreArgs& a, const Plan& p, cudaStream_t st) {
-    cudaFuncSetAttribute(ransac_score_bal_kernel<NHL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem_bal);
-    ransac_score_bal_kernel<NHL><<<p.bal_grid, ST, p.smem_bal, st>>>(a);
+    ransac_score_bal_kernel<NHL><<<p.bal_grid, ST, 0, st>>>(a);
     return pb_check_launch("ransac_score_bal_kernel");
 }
 

@@ -22,7 +22,7 @@ struct ScoreArgs {
 struct Plan {
     int HS, Hs, CH, PP, NHL;
     size_t smem_score, smem_final, off_best, total;
-    int bal, bal_grid;               // balanced scoring (see ransac_score_bal_kernel): CTAs of equal point ranges
+    int bal, bal_grid, bal_nhl;      // balanced scoring (see ransac_score_bal_kernel): CTAs of equal point ranges
     size_t smem_bal, off_cnt, off_prefix;
 };
 
@@ -59,7 +59,10 @@ static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm, int sm
     // ranges of the concatenated point list instead (H <= 256 hypotheses held by one CTA).
     p.smem_bal = 0;                                    // the balanced kernel's two 256-point buffers are static (10 KB)
     const int per_sm = 6;                              // <= 85 registers x 128 threads: six CTAs per SM, one wave
-    p.bal = (p.HS == 1 && p.PP == 1 && F >= two_waves && cap % 4 == 0) ? 1 : 0;
+    // also for fewer frames when they can hold many points (dense masks: 2 k .. 50 k pixels per frame, very uneven)
+    const bool many = F >= two_waves || (long long)F * cap >= 4ll * sms * per_sm * PB_BAL_SUB;
+    p.bal = (H <= 2 * PB_SCORE_THREADS && many && cap % 4 == 0) ? 1 : 0;
+    p.bal_nhl = H > PB_SCORE_THREADS ? 2 : 1;          // hypotheses per thread of the balanced kernel (the slice plan above is its fallback's)
     p.bal_grid = sms * per_sm;
     p.off_cnt = (p.total + 255) / 256 * 256;
     p.off_prefix = p.off_cnt;

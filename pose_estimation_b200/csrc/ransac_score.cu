@@ -489,7 +489,7 @@ int pb_launch_score(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
     ransac_hypothesis_kernel<<<(unsigned)((nh + HT - 1) / HT), HT, 0, st>>>(a);
     if (pb_check_launch("ransac_hypothesis_kernel")) return 1;
     pb_stage_mark(1, st);
-    if (p.bal && a.cnt_all) return p.NHL == 2 ? launch_bal<2>(a, p, st) : launch_bal<1>(a, p, st);
+    if (p.bal && a.cnt_all) return p.bal_nhl == 2 ? launch_bal<2>(a, p, st) : launch_bal<1>(a, p, st);
     switch (p.NHL) {
         case 1: return launch<1>(a, p, F, st);
         case 2: return launch<2>(a, p, F, st);

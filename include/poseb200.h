@@ -148,6 +148,17 @@ int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const float* K4, i
                       int32_t* status, int32_t* hyp_counts, uint32_t* inl_bitmap, float* R0, float* t0,
                       void* ws, size_t ws_bytes, void* stream);
 
+/* Which kernel scores the hypotheses (K3; the iteration loop of cv2.solvePnPRansac, tools/trainer.py:423-427).
+ * Process-wide setting read at every pb_pnp_ransac_* call: 0 = automatic, 1 = FP32-pipe kernels only, 2 = the
+ * tensor-core kernel (csrc/ransac_score_tc.cu) whenever the shape allows (n_hyp <= 256 and a batch large enough for
+ * the balanced plan), 3 = the same with a calibration pass (slow).  All of them return identical integers.
+ * band_scale multiplies the band inside which the tensor-core kernel re-evaluates a test with the FP32 contract
+ * (1 = the derived bound).  pb_ransac_tc_stats_offset: byte offset inside the pb_pnp_ransac_pts workspace of
+ * int32 stats[4] = {barrier timeout, re-evaluated groups, calibration: largest |s_tc - s_fp32| / band as float
+ * bits, calibration: verdicts that differ outside the band}, or -1 when the shape never takes that kernel.     */
+int pb_ransac_score_impl(int impl, float band_scale);
+long long pb_ransac_tc_stats_offset(int F, int cap, const pb_ransac_params* prm);
+
 /* map -> pose in one call (K0 + K1-K4); workspace holds the compacted points.                 */
 size_t pb_pnp_ransac_map_workspace_bytes(int F, int Hh, int Ww, int cap, const pb_ransac_params* prm);
 int pb_pnp_ransac_map(const float* xyz, const uint8_t* mask, const int32_t* roi, const float* extent,

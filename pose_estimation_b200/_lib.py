@@ -40,6 +40,8 @@ SIGNATURES = {
     "pb_region_decode_map": (I, [P, P, P, I, I, I, I, I, P, P]),
     "pb_ransac_workspace_bytes": (SZ, [I, I, PRM]),
     "pb_pnp_ransac_pts": (I, [P, P, P, I, I, U32, PRM, P, P, P, P, P, P, P, P, P, P, P, P, SZ, P]),
+    "pb_ransac_score_impl": (I, [I, F32]),
+    "pb_ransac_tc_stats_offset": (C.c_longlong, [I, I, PRM]),
     "pb_pnp_ransac_map_workspace_bytes": (SZ, [I, I, I, I, PRM]),
     "pb_pnp_ransac_map": (I, [P, P, P, P, P, P, I, I, I, I, U32, PRM, P, P, P, P, P, P, P, SZ, P]),
     "pb_resample_inliers": (I, [P, P, I, I, I, U32, U32, U32, P, P]),

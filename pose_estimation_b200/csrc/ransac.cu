@@ -388,6 +388,12 @@ extern "C" size_t pb_ransac_workspace_bytes(int F, int cap, const pb_ransac_para
     return make_plan(F, cap, prm, pb_sm_count()).total;
 }
 
+extern "C" long long pb_ransac_tc_stats_offset(int F, int cap, const pb_ransac_params* prm) {
+    if (F <= 0 || cap <= 0 || !prm || prm->n_hyp <= 0) return -1;
+    const Plan p = make_plan(F, cap, prm, pb_sm_count());
+    return p.tc ? (long long)p.off_tcstats : -1;
+}
+
 extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const float* K4, int F, int cap,
                                  uint32_t frame0, const pb_ransac_params* prm, const int32_t* sample_idx,
                                  float* R, float* t, int32_t* n_inl, int32_t* best_hyp, int32_t* n_inl_refined,
@@ -413,6 +419,14 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     if (p.bal && reinterpret_cast<uintptr_t>(pts) % 16 != 0) p.bal = 0;     // the balanced kernel stages with 16-byte async copies
     sa.cnt_all = p.bal ? (hyp_counts ? hyp_counts : reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_cnt)) : nullptr;
     sa.prefix = p.bal ? reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_prefix) : nullptr;
+    // K3 on the tensor cores (ransac_score_tc.cu): when asked for (pb_ransac_score_impl), and by default for batches
+    // large enough to give every multiprocessor several 128-point tiles
+    const int impl = pb_score_impl();
+    const bool use_tc = p.tc && p.bal && impl != 1 && (impl >= 2 || PB_SCORE_TC_DEFAULT);
+    sa.tprefix = use_tc ? reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_tprefix) : nullptr;
+    sa.tc_stats = use_tc ? reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_tcstats) : nullptr;
+    sa.tc_kappa = pb_score_tc_kappa();
+    if (use_tc) sa.prefix = nullptr;
     sa.cap = cap; sa.H = prm->n_hyp; sa.HS = p.HS; sa.Hs = p.Hs; sa.CH = p.CH; sa.PP = p.PP;
     sa.frame0 = frame0; sa.seed_lo = prm->seed_lo; sa.seed_hi = prm->seed_hi;
     sa.inv_thr = 1.0f / prm->thresh_px; sa.F = F;

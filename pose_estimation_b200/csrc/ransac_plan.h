@@ -13,6 +13,10 @@ struct ScoreArgs {
     int32_t* cnt_all;                // balanced mode: [F,H] inlier counts accumulated with atomics (-1 = no model)
     int32_t* prefix;                 // balanced mode: [F+1] exclusive prefix of the frames' point counts rounded up to 8
                                      // (written by block 0 of the hypothesis kernel, read by every scoring CTA)
+    int32_t* tprefix;                // tensor-core mode: [F+1] exclusive prefix of the frames' 128-point tile counts (same writer)
+    int32_t* tc_stats;               // tensor-core mode: [0] barrier timeout, [1] exact re-evaluations (groups of 4 tests x 32 lanes),
+                                     // [2] calibration: largest observed |s_tc - s_fp32| / band as float bits, [3] verdicts that differ outside the band
+    float tc_kappa;                  // tensor-core mode: multiplier of the re-evaluation band (1 = the derived bound)
     int cap, H, HS, Hs, CH, PP;      // Hs hypotheses per slice (power of two >= 32); PP point parts
     uint32_t frame0, seed_lo, seed_hi;
     float inv_thr;
@@ -24,11 +28,14 @@ struct Plan {
     size_t smem_score, smem_final, off_best, total;
     int bal, bal_grid, bal_nhl;      // balanced scoring (see ransac_score_bal_kernel): CTAs of equal point ranges
     size_t smem_bal, off_cnt, off_prefix;
+    int tc;                          // tensor-core scoring (ransac_score_tc.cu) is possible for this shape
+    size_t off_tprefix, off_tcstats;
 };
 
 // Hypotheses of a frame are cut into HS slices of Hs (power of two) so that few-frame launches
 // still fill 148 SMs; a slice narrower than the CTA splits the points PP ways instead.
 #define PB_SCORE_THREADS 128     /* CTA size of the scoring kernel (ST in ransac_score.cu) */
+#define PB_TC_STATS_BYTES 128     /* int32 stats[4] + twelve 64-bit clock sums of the profiling mode */
 #define PB_BAL_SUB 256           /* points per staging buffer of the balanced scoring kernel (two buffers) */
 
 static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm, int sms = 148) {
@@ -70,8 +77,25 @@ static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm, int sm
         p.off_prefix = (p.off_cnt + (size_t)F * H * sizeof(int32_t) + 255) / 256 * 256;
         p.total = p.off_prefix + (size_t)(F + 1) * sizeof(int32_t);
     }
+    // tensor-core scoring: same accumulation target (cnt_all) as the balanced kernel, H <= 256 hypotheses per frame
+    p.tc = (p.bal && H <= 256) ? 1 : 0;
+    p.off_tprefix = p.off_tcstats = p.total;
+    if (p.tc) {
+        p.off_tprefix = (p.total + 255) / 256 * 256;
+        p.off_tcstats = (p.off_tprefix + (size_t)(F + 1) * sizeof(int32_t) + 255) / 256 * 256;
+        p.total = p.off_tcstats + PB_TC_STATS_BYTES;
+    }
     return p;
 }
 
 // defined in ransac_score.cu
 int pb_launch_score(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st);
+// defined in ransac_score_tc.cu: K3 on the tensor cores (a.tprefix, a.tc_stats set; a.cnt_all initialised by the hypothesis kernel)
+int pb_launch_score_tc(const ScoreArgs& a, int mode /*0 product, 1 calibration, 2 clock breakdown*/, cudaStream_t st);
+// process-wide choice of the scoring kernel (abi: pb_ransac_score_impl): 0 = automatic, 1 = FP32 pipe only, 2 = tensor cores
+// whenever the shape allows, 3 = tensor cores with the calibration pass (slow; fills tc_stats[2..3]), 4 = tensor cores with the clock breakdown
+int pb_score_impl();
+float pb_score_tc_kappa();
+#ifndef PB_SCORE_TC_DEFAULT
+#define PB_SCORE_TC_DEFAULT 0    /* 1: the automatic choice (impl 0) takes the tensor-core kernel whenever the plan allows */
+#endif

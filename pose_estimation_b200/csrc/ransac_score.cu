@@ -26,16 +26,22 @@ namespace {
 
 constexpr int HT = 128;  // threads per CTA of the hypothesis kernel
 
-// exclusive prefix of the frames' point counts rounded up to 8 -> a.prefix[0..F] (one CTA; the balanced scoring kernel
-// cuts this padded index space into equal ranges, so every range and every frame segment starts at a multiple of 8)
-__device__ void frame_prefix_scan(const ScoreArgs& a) {
+// exclusive prefix over the frames of  v(P) = P rounded up to 8 (TILES = false: the balanced scoring kernel cuts this
+// padded index space into equal ranges, so every range and every frame segment starts at a multiple of 8) or of the
+// number of 128-point tiles (TILES = true: the tensor-core scoring kernel's work units) -> out[0..F]; one CTA
+template <bool TILES>
+__device__ void frame_prefix_scan(const ScoreArgs& a, int32_t* out) {
     __shared__ int wsum[HT / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int per = (a.F + HT - 1) / HT;
+    auto val = [&](int f) {
+        const int P = max(0, min(a.count[f], a.cap));
+        return TILES ? (P + 127) >> 7 : (P + 7) & ~7;
+    };
     int mine = 0;
     for (int k = 0; k < per; ++k) {
         const int f = tid * per + k;
-        if (f < a.F) mine += (max(0, min(a.count[f], a.cap)) + 7) & ~7;
+        if (f < a.F) mine += val(f);
     }
     int incl = mine;
 #pragma unroll
@@ -43,19 +49,21 @@ __device__ void frame_prefix_scan(const ScoreArgs& a) {
         const int v = __shfl_up_sync(0xffffffffu, incl, off);
         if (lane >= off) incl += v;
     }
+    __syncthreads();                                   // wsum may still be read by the previous scan
     if (lane == 31) wsum[warp] = incl;
     __syncthreads();
     int base = incl - mine;
     for (int w = 0; w < warp; ++w) base += wsum[w];
     for (int k = 0; k < per; ++k) {
         const int f = tid * per + k;
-        if (f < a.F) { a.prefix[f] = base; base += (max(0, min(a.count[f], a.cap)) + 7) & ~7; }
+        if (f < a.F) { out[f] = base; base += val(f); }
     }
-    if (tid == HT - 1) a.prefix[a.F] = base;
+    if (tid == HT - 1) out[a.F] = base;
 }
 
 __global__ void __launch_bounds__(HT) ransac_hypothesis_kernel(ScoreArgs a) {
-    if (blockIdx.x == 0 && a.prefix) frame_prefix_scan(a);        // uniform per CTA
+    if (blockIdx.x == 0 && a.prefix) frame_prefix_scan<false>(a, a.prefix);        // uniform per CTA
+    if (blockIdx.x == 0 && a.tprefix) frame_prefix_scan<true>(a, a.tprefix);
     const long long gid = (long long)blockIdx.x * HT + threadIdx.x;
     if (gid >= (long long)a.F * a.H) return;
     const int f = (int)(gid / a.H), h = (int)(gid - (long long)f * a.H);
@@ -489,6 +497,7 @@ int pb_launch_score(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
     ransac_hypothesis_kernel<<<(unsigned)((nh + HT - 1) / HT), HT, 0, st>>>(a);
     if (pb_check_launch("ransac_hypothesis_kernel")) return 1;
     pb_stage_mark(1, st);
+    if (a.tprefix && a.cnt_all) return pb_launch_score_tc(a, pb_score_impl() == 3 ? 1 : pb_score_impl() == 4 ? 2 : 0, st);
     if (p.bal && a.cnt_all) return p.bal_nhl == 2 ? launch_bal<2>(a, p, st) : launch_bal<1>(a, p, st);
     switch (p.NHL) {
         case 1: return launch<1>(a, p, F, st);

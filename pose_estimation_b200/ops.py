@@ -217,6 +217,28 @@ def pnp_ransac_pts(pts, count, K4, cfg: RansacConfig | None = None, frame0=0, sa
     return out
 
 
+_SCORE_IMPL = {"auto": 0, "fp32": 1, "tc": 2, "tc_calib": 3, "tc_prof": 4}
+
+
+def set_score_impl(impl="auto", band_scale=1.0):
+    """Which kernel scores the hypotheses (process-wide): 'auto', 'fp32' (FP32-pipe kernels), 'tc' (tensor cores whenever
+    the shape allows), 'tc_calib' (tensor cores + calibration statistics).  The integers they return are identical."""
+    call("pb_ransac_score_impl", _SCORE_IMPL[impl], float(band_scale))
+
+
+def ransac_tc_stats(ws, F, cap, cfg: RansacConfig | None = None):
+    """Statistics the tensor-core scoring kernel left in a pb_pnp_ransac_pts workspace (synchronises), or None."""
+    prm = (cfg or RansacConfig()).c_struct()
+    off = _lib.load().pb_ransac_tc_stats_offset(F, cap, C.byref(prm))
+    if off < 0:
+        return None
+    raw = ws.view(torch.uint8)[off:off + 128].cpu().numpy()
+    import numpy as np
+    i = raw.view(np.int32)
+    return dict(timeout=int(i[0]), reevaluated_groups=int(i[1]), calib_max_ratio=float(raw.view(np.float32)[2]),
+                calib_mismatch=int(i[3]), clocks=[int(x) for x in raw[16:112].view(np.uint64)])
+
+
 class MapCompactor:
     """Reusable K0 launcher: persistent pts [F,5,cap] / count [F] / workspace."""
 

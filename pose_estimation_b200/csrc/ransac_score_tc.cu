@@ -39,9 +39,10 @@
 namespace {
 
 constexpr int TP = 128;                       // points per tile = TMEM lanes
-constexpr int HG = 64;                        // hypotheses per MMA
+constexpr int HG = 32;                        // hypotheses per MMA
 constexpr int SETC = 3 * HG;                  // accumulator columns of one set: x | y | w
-constexpr int NG_MAX = 4;                     // H <= 256
+constexpr int NSET = 4;                       // accumulator sets in flight (384 of the 512 TMEM columns)
+constexpr int NG_MAX = 8;                     // H <= 256
 constexpr int NSTG = 4;                       // point-tile stages
 constexpr int EPI_WARPS = 16;
 constexpr int W_MMA = 16, W_PA = 17, W_PB = 18;
@@ -69,15 +70,18 @@ __device__ __forceinline__ float point_scale(float X, float Y, float Z, bool& bi
     return __int_as_float((253 - eb) << 23);       // 2^(126 - eb)
 }
 
-// bounded mbarrier wait that gives up quickly once any thread of the CTA has timed out
+// bounded mbarrier wait that gives up quickly once any thread of the CTA has timed out.  try_wait carries a suspend-time
+// hint: the thread sleeps in hardware until the phase completes (or the hint expires), so waiting warps do not spend
+// issue slots on polling -- a third of all executed instructions were polling loops without it.
 __device__ __forceinline__ bool wait_bar(uint64_t* bar, uint32_t parity, volatile int* bad) {
     const uint32_t a = tc::smem_u32(bar);
-    for (uint32_t spin = 0; spin < (1u << 23); ++spin) {
+#pragma unroll 1
+    for (uint32_t spin = 0; spin < (1u << 16); ++spin) {
         uint32_t ok;
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(a), "r"(parity), "r"(200000u) : "memory");
         if (ok) return true;
-        if ((spin & 1023u) == 1023u && *bad) return false;
+        if (*bad) return false;
     }
     *bad = 1;
     return false;
@@ -95,6 +99,25 @@ __device__ __forceinline__ void advance(const int* __restrict__ tp, int F, int t
     while (f + 1 < F && tp[f + 1] <= t) ++f;
 }
 
+typedef unsigned long long f32x2;   // two packed binary32 values
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+    return d;
+}
+__device__ __forceinline__ f32x2 pack2u(uint32_t lo, uint32_t hi) {      // adjacent registers of a tcgen05.ld: no instruction
+    return (f32x2)lo | ((f32x2)hi << 32);
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
 __device__ __forceinline__ float min3nan(float a, float b, float c) {   // NaN if any input is NaN
     float d;
     asm("min.NaN.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
@@ -168,7 +191,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
     unsigned char* sB = sA + NSTG * A_TILE_BYTES;                              // [2 frames][NG_MAX groups] hypothesis operands
     float* sProj = reinterpret_cast<float*>(sB + 2 * B_FRAME_BYTES);           // [2][HP][12] the contract's FP32 matrices
     float* sBand = sProj + 2 * HP * 12;                                        // [2][8]
-    __shared__ __align__(8) uint64_t a_full[NSTG], a_free[NSTG], b_full[2], b_free[2], acc_full[2], acc_free[2];
+    __shared__ __align__(8) uint64_t a_full[NSTG], a_free[NSTG], b_full[2], b_free[2], acc_full[NSET], acc_free[NSET];
     __shared__ uint32_t tmem_base;
     __shared__ int s_bad;
 
@@ -183,10 +206,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
 
     if (tid == 0) {
         for (int i = 0; i < NSTG; ++i) { tc::mbar_init(&a_full[i], 1); tc::mbar_init(&a_free[i], 1); }
-        for (int i = 0; i < 2; ++i) {
-            tc::mbar_init(&b_full[i], 1); tc::mbar_init(&b_free[i], EPI_WARPS);
-            tc::mbar_init(&acc_full[i], 1); tc::mbar_init(&acc_free[i], EPI_WARPS);
-        }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&b_full[i], 1); tc::mbar_init(&b_free[i], EPI_WARPS); }
+        for (int i = 0; i < NSET; ++i) { tc::mbar_init(&acc_full[i], 1); tc::mbar_init(&acc_free[i], EPI_WARPS); }
         s_bad = 0;
         tc::fence_mbar_init();
     }
@@ -201,11 +222,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
     if (warp == W_PA) {
         // ===== point tiles: FP32 (X, Y, Z) -> scaled FP16 pairs, rows (Xh,Xm,Xh,Xm, Yh,Ym,Yh,Ym | Zh,Zm,Zh,Zm, sc,sc,sc,0)
         int f = frame_of(tp, F, t0);
+        int tbeg = tp[f], tend = tp[f + 1], P = max(0, min(a.count[f], cap));
         for (int t = t0, tl = 0; t < t1 && ok; ++t, ++tl) {
-            advance(tp, F, t, f);
+            if (t >= tend) { advance(tp, F, t, f); tbeg = tp[f]; tend = tp[f + 1]; P = max(0, min(a.count[f], cap)); }
             const int s = tl % NSTG, use = tl / NSTG;
-            const int P = max(0, min(a.count[f], cap));
-            const int p0 = (t - tp[f]) * TP;
+            const int p0 = (t - tbeg) * TP;
             const float* X = a.pts + (size_t)f * 5 * cap;
             const float* Y = X + cap;
             const float* Z = Y + cap;
@@ -263,12 +284,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
             float A1 = 0.0f, A1c = 0.0f, A1w = 0.0f, Amax = 0.0f;
             unsigned char* sBf = sB + fb * B_FRAME_BYTES;
             float* sPf = sProj + fb * HP * 12;
+            const float qnan = __int_as_float(0x7fffffff);
+            float4 n0 = make_float4(0.0f, 0.0f, 0.0f, 0.0f), n1 = n0, n2 = make_float4(0.0f, 0.0f, 0.0f, qnan);
+            if (lane < H) {
+                const float4* o = reinterpret_cast<const float4*>(a.hypRt + ((size_t)f * H + lane) * 12);
+                n0 = o[0]; n1 = o[1]; n2 = o[2];
+            }
             for (int h = lane; h < NG * HG; h += 32) {
                 float mj[12];
                 bool valid = false;
+                const float4 r0 = n0, r1 = n1, r2 = n2;
+                n2.w = qnan;
+                if (h + 32 < H) {                                            // the next pose is in flight during this one's conversion
+                    const float4* o = reinterpret_cast<const float4*>(a.hypRt + ((size_t)f * H + h + 32) * 12);
+                    n0 = o[0]; n1 = o[1]; n2 = o[2];
+                }
                 if (h < H) {
-                    const float4* o = reinterpret_cast<const float4*>(a.hypRt + ((size_t)f * H + h) * 12);
-                    const float4 r0 = o[0], r1 = o[1], r2 = o[2];
                     valid = (r2.w == r2.w);
                     if (valid) {
                         const float R[9] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x};
@@ -337,11 +368,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
             t = min(t1, tp[f + 1]);                                            // first tile of the next frame
         }
     } else if (warp == W_MMA) {
-        // ===== MMA issuer: per tile NG MMAs (one per 64-hypothesis group) into the two accumulator sets in turn
+        // ===== MMA issuer: per tile NG MMAs (one per 32-hypothesis group) into the NSET accumulator sets in turn
         const uint32_t idesc = tc::idesc_f16_f32(TP, SETC);
         int f = frame_of(tp, F, t0), cur_f = -1, fl = -1, n = 0;
+        int tend = tp[f + 1];
         for (int t = t0, tl = 0; t < t1 && ok; ++t, ++tl) {
-            advance(tp, F, t, f);
+            if (t >= tend) { advance(tp, F, t, f); tend = tp[f + 1]; }
             K3CLK(c0);
             if (f != cur_f) {
                 cur_f = f; ++fl;
@@ -355,7 +387,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
             tc::fence_after_sync();
             const uint64_t ad = tc::smem_desc(tc::smem_u32(sA + s * A_TILE_BYTES), TP * 16, 128);
             for (int g = 0; g < NG && ok; ++g, ++n) {
-                const int set = n & 1, use = n >> 1;
+                const int set = n % NSET, use = n / NSET;
                 K3CLK(c3);
                 if (use > 0) ok = __all_sync(0xffffffffu, wait_bar(&acc_free[set], (uint32_t)(use - 1) & 1u, bad));
                 K3CLK(c4);
@@ -374,138 +406,186 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
         if (PROF && lane == 0)        // [4] waiting for hypothesis operands, [5] for point tiles, [6] for a free accumulator set
             for (int k = 0; k < 3; ++k) atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + 4 + k, (unsigned long long)prof[k]);
     } else {
-        // ===== epilogue: warp = (TMEM lane quadrant q, 16-hypothesis slice j of every group); thread = point
+        // ===== epilogue: warp = (TMEM lane quadrant q, 8-hypothesis slice j of every 32-hypothesis set); thread = point.
+        // Software pipeline over the CTA's accumulator sets: the loads of set n + 1 (x | y | w: three tcgen05.ld.x8)
+        // are in flight while set n is evaluated; a set is handed back to the MMA warp as soon as it is in registers.
         const int q = warp & 3, j = warp >> 2;
-        const uint32_t tlane = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(16 * j);
-        int f = frame_of(tp, F, t0), cur_f = -1, fl = -1, n = 0;
+        const uint32_t tlane = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(8 * j);
+        const int NS = (t1 - t0) * NG;                       // accumulator sets of this CTA
+        int f = frame_of(tp, F, t0), cur_f = -1, fl = -1;
+        int tbeg = tp[f], tend = tp[f + 1];                  // tiles of frame f (register copies: no load per tile)
         int cnt[2] = {0, 0};
         int nslow = 0, nmis = 0;
         float calmax = 0.0f;
         float u0 = 0.0f, v0 = 0.0f, A1 = 0.0f, A1c = 0.0f, A1w = 0.0f, Amax = 0.0f;
         int P = 0;
-        const float* Xp = a.pts;
         auto flush = [&](int ff) {
 #pragma unroll
             for (int wi = 0; wi < 2; ++wi) {
-                const int g = 2 * wi + (lane < 16 ? 1 : 0);
-                const int k = lane < 16 ? 15 - lane : 31 - lane;
-                const int h = g * HG + 16 * j + k;
+                const int k = (31 - lane) >> 3, c = (31 - lane) & 7;       // bit position L <- set 4 wi + k of the tile, test c
+                const int h = (4 * wi + k) * HG + 8 * j + c;
                 if (h < H && cnt[wi] > 0) atomicAdd(&a.cnt_all[(size_t)ff * H + h], cnt[wi]);
                 cnt[wi] = 0;
             }
         };
-        for (int t = t0; t < t1 && ok; ++t) {
-            K3CLK(e0);
-            advance(tp, F, t, f);
-            if (f != cur_f) {
-                if (cur_f >= 0) {
-                    flush(cur_f);
-                    __syncwarp();
-                    if (lane == 0) tc::mbar_arrive(&b_free[fl & 1]);
+        // this lane's point of the next tile: raw values fetched one tile ahead; rows beyond cap are not read
+        float nX = 0.0f, nY = 0.0f, nZ = 0.0f, nU = 0.0f, nV = 0.0f;
+        auto fetch_point = [&](int tile_in_frame, int ff) {
+            const int p = tile_in_frame * TP + 32 * q + lane;
+            const float* base = a.pts + (size_t)ff * 5 * cap;
+            if (p < cap) { nX = base[p]; nY = base[cap + p]; nZ = base[2 * (size_t)cap + p]; nU = base[3 * (size_t)cap + p]; nV = base[4 * (size_t)cap + p]; }
+        };
+        fetch_point(t0 - tbeg, f);
+        float X = 0.0f, Y = 0.0f, Z = 0.0f, us = 0.0f, vs = 0.0f, du = 0.0f, dv = 0.0f;
+        f32x2 ndu2 = 0ull, ndv2 = 0ull;
+        BandC bc = {0.0f, 0.0f, -1.0f};
+        bool valid = false;
+        const float* sPf = sProj;
+        uint32_t bits = 0u;
+        uint32_t ra[24], rb[24];
+        // evaluate the warp's 8 columns of a set held in r = x[8] | y[8] | w[8]; returns a 2-bit mask of the groups of
+        // 4 hypotheses that hold a value inside the band
+        auto eval8 = [&](const uint32_t (&r)[24]) -> uint32_t {
+            uint32_t fm = 0u;
+#pragma unroll
+            for (int gq = 0; gq < 2; ++gq) {
+                float smin = __int_as_float(0x7f800000), wmax = 0.0f;
+#pragma unroll
+                for (int pr = 0; pr < 2; ++pr) {
+                    const int c = 4 * gq + 2 * pr;
+                    const float w0 = __uint_as_float(r[16 + c]), w1 = __uint_as_float(r[16 + c + 1]);
+                    const f32x2 x2 = pack2u(r[c], r[c + 1]), y2 = pack2u(r[8 + c], r[8 + c + 1]), w2 = pack2u(r[16 + c], r[16 + c + 1]);
+                    const f32x2 dx2 = ffma2(ndu2, w2, x2), dy2 = ffma2(ndv2, w2, y2);
+                    const f32x2 nq2 = pack2(w0 * -fabsf(w0), w1 * -fabsf(w1));
+                    const f32x2 s2 = ffma2(dx2, dx2, ffma2(dy2, dy2, nq2));
+                    const uint32_t s0 = (uint32_t)s2, s1 = (uint32_t)(s2 >> 32);
+                    bits = __funnelshift_l(s0, bits, 1);
+                    bits = __funnelshift_l(s1, bits, 1);
+                    smin = min3nan(smin, fabsf(__uint_as_float(s0)), fabsf(__uint_as_float(s1)));
+                    wmax = fmax3(wmax, fabsf(w0), fabsf(w1));
                 }
-                cur_f = f; ++fl;
-                ok = __all_sync(0xffffffffu, wait_bar(&b_full[fl & 1], (uint32_t)(fl >> 1) & 1u, bad));
-                const float* bd = sBand + (fl & 1) * 8;
-                u0 = bd[0]; v0 = bd[1]; A1 = bd[2]; A1c = bd[3]; A1w = bd[4]; Amax = bd[5];
-                P = max(0, min(a.count[f], cap));
-                Xp = a.pts + (size_t)f * 5 * cap;
+                // band at the group's largest |w| against the group's smallest |s|: covers every one of its tests
+                const float band = fmaf(fmaf(bc.c2, wmax, bc.c1), wmax, bc.c0);
+                fm |= (!(smin > band)) ? (1u << gq) : 0u;
             }
-            const int p = (t - tp[f]) * TP + 32 * q + lane;
-            const bool valid = p < P;
-            float X = 0.0f, Y = 0.0f, Z = 0.0f, us = 0.0f, vs = 0.0f;
-            if (valid) {
-                X = Xp[p]; Y = Xp[cap + p]; Z = Xp[2 * (size_t)cap + p];
-                us = Xp[3 * (size_t)cap + p] * a.inv_thr; vs = Xp[4 * (size_t)cap + p] * a.inv_thr;
+            return fm;
+        };
+        // the rest of a set's work once its 8 columns are evaluated: exact re-evaluation inside the band, word completion
+        auto finish_set = [&](uint32_t fm, int g, const uint32_t (&r)[24]) {
+            if (CALIB) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int h = g * HG + 8 * j + c;
+                    const float4* mp = reinterpret_cast<const float4*>(sPf + h * 12);
+                    const float4 m0 = mp[0], m1 = mp[1], m2 = mp[2];
+                    const float M[12] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
+                    bool big2;
+                    const float sc = point_scale(X, Y, Z, big2);
+                    const float se = inlier_s(M, X, Y, Z, us, vs) * (sc * sc);
+                    const float xw = __uint_as_float(r[c]), yw = __uint_as_float(r[8 + c]), ww = __uint_as_float(r[16 + c]);
+                    const float dx = fmaf(-du, ww, xw), dy = fmaf(-dv, ww, yw);
+                    const float nq = ww * -fabsf(ww);
+                    const float sv = fmaf(dx, dx, fmaf(dy, dy, nq));
+                    const float band = fmaf(fmaf(bc.c2, fabsf(ww), bc.c1), fabsf(ww), bc.c0);
+                    const float ratio = fabsf(sv - se) / band;
+                    if (valid && ratio == ratio && band < 1e30f && fabsf(se) <= 0.25f * ww * ww) calmax = fmaxf(calmax, ratio);
+                    const bool inband = !(fabsf(sv) > band);
+                    if (valid && !inband && ((__float_as_uint(sv) ^ __float_as_uint(se)) >> 31)) ++nmis;
+                }
             }
-            bool big;
-            const float sc = point_scale(X, Y, Z, big);
-            const float du = us - u0, dv = vs - v0;
-            BandC bc = band_consts(us, vs, du, dv, sc, A1, A1c, A1w, Amax, big, a.tc_kappa);
-            if (!valid) { bc.c2 = 0.0f; bc.c1 = 0.0f; bc.c0 = -1.0f; }     // padding lanes (all-zero rows) never ask for a re-evaluation
-            const float* sPf = sProj + (fl & 1) * HP * 12;
-            uint32_t bits = 0u;
-            K3CLK(e1);
-            K3ACC(0, e0, e1);
+            if (__any_sync(0xffffffffu, fm != 0u)) {
 #pragma unroll
-            for (int g = 0; g < NG_MAX; ++g) {
-                if (g < NG && ok) {
-                    const int set = n & 1;
-                    K3CLK(e2);
-                    ok = __all_sync(0xffffffffu, wait_bar(&acc_full[set], (uint32_t)(n >> 1) & 1u, bad));
-                    K3CLK(e3);
-                    ++n;
-                    tc::fence_after_sync();
-                    uint32_t xr[16], yr[16], wr[16];
-                    const uint32_t tb = tlane + (uint32_t)(set * SETC);
-                    tc::tmem_ld16(tb, xr);
-                    tc::tmem_ld16(tb + HG, yr);
-                    tc::tmem_ld16(tb + 2 * HG, wr);
-                    tc::tmem_ld_wait();
-                    tc::fence_before_sync();
-                    __syncwarp();
-                    if (lane == 0) tc::mbar_arrive(&acc_free[set]);        // the values are in registers: the set can be overwritten
-                    K3CLK(e4);
-                    K3ACC(1, e2, e3); K3ACC(2, e3, e4);
-                    float tmin[4];
-#pragma unroll
-                    for (int qd = 0; qd < 4; ++qd) {
-                        float fv[4];
+                for (int qd = 0; qd < 2; ++qd) {
+                    if (__any_sync(0xffffffffu, (fm >> qd) & 1u)) {
+                        ++nslow;
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {
-                            const int c = 4 * qd + k;
-                            const float xw = __uint_as_float(xr[c]), yw = __uint_as_float(yr[c]), ww = __uint_as_float(wr[c]);
-                            const float dx = fmaf(-du, ww, xw), dy = fmaf(-dv, ww, yw);
-                            const float nq = ww * -fabsf(ww);
-                            const float s = fmaf(dx, dx, fmaf(dy, dy, nq));
-                            bits = __funnelshift_l(__float_as_uint(s), bits, 1);
-                            fv[k] = fmaf(-bc.c1, fabsf(ww), fmaf(bc.c2, nq, fabsf(s)));   // |s| - c2 w|w| - c1 |w|
-                        }
-                        tmin[qd] = min3nan(min3nan(fv[0], fv[1], fv[2]), fv[3], fv[3]);
-                    }
-                    if (CALIB) {
-#pragma unroll
-                        for (int c = 0; c < 16; ++c) {
-                            const int h = g * HG + 16 * j + c;
+                            const int c = 4 * qd + k, h = g * HG + 8 * j + c;
                             const float4* mp = reinterpret_cast<const float4*>(sPf + h * 12);
                             const float4 m0 = mp[0], m1 = mp[1], m2 = mp[2];
                             const float M[12] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
-                            const float se = inlier_s(M, X, Y, Z, us, vs) * (sc * sc);
-                            const float xw = __uint_as_float(xr[c]), yw = __uint_as_float(yr[c]), ww = __uint_as_float(wr[c]);
-                            const float dx = fmaf(-du, ww, xw), dy = fmaf(-dv, ww, yw);
-                            const float nq = ww * -fabsf(ww);
-                            const float s = fmaf(dx, dx, fmaf(dy, dy, nq));
-                            const float band = fmaf(bc.c2, ww * ww, fmaf(bc.c1, fabsf(ww), bc.c0));
-                            const float ratio = fabsf(s - se) / band;
-                            if (valid && ratio == ratio && band < 1e30f && fabsf(se) <= 0.25f * ww * ww) calmax = fmaxf(calmax, ratio);
-                            const bool inband = !(fmaf(-bc.c1, fabsf(ww), fmaf(bc.c2, nq, fabsf(s))) > bc.c0);
-                            if (valid && !inband && ((__float_as_uint(s) ^ __float_as_uint(se)) >> 31)) ++nmis;
+                            const uint32_t bit = __float_as_uint(inlier_s(M, X, Y, Z, us, vs)) >> 31;
+                            bits = (bits & ~(1u << (7 - c))) | (bit << (7 - c));
                         }
                     }
-                    // ---- groups of 4 hypotheses with a value inside the band: the contract's own arithmetic decides
-#pragma unroll
-                    for (int qd = 0; qd < 4; ++qd) {
-                        if (__any_sync(0xffffffffu, !(tmin[qd] > bc.c0))) {
-                            ++nslow;
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                const int c = 4 * qd + k, h = g * HG + 16 * j + c;
-                                const float4* mp = reinterpret_cast<const float4*>(sPf + h * 12);
-                                const float4 m0 = mp[0], m1 = mp[1], m2 = mp[2];
-                                const float M[12] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
-                                const uint32_t bit = __float_as_uint(inlier_s(M, X, Y, Z, us, vs)) >> 31;
-                                bits = (bits & ~(1u << (15 - c))) | (bit << (15 - c));
-                            }
-                        }
-                    }
-                    if ((g & 1) || g == NG - 1) {                          // a verdict word is complete
-                        if (!(g & 1)) bits <<= 16;
-                        cnt[g >> 1] += bit_column_counts(valid ? bits : 0u, lane);
-                        bits = 0u;
-                    }
-                    K3CLK(e5);
-                    K3ACC(3, e4, e5);
                 }
             }
+            if ((g & 3) == 3 || g == NG - 1) {                             // a verdict word is complete
+                bits <<= 8 * (3 - (g & 3));
+                const int c = bit_column_counts(valid ? bits : 0u, lane);
+                if (g >> 2) cnt[1] += c; else cnt[0] += c;
+                bits = 0u;
+            }
+        };
+        if (NS > 0) {
+            ok = __all_sync(0xffffffffu, wait_bar(&acc_full[0], 0u, bad));
+            tc::fence_after_sync();
+            tc::tmem_ld8(tlane, ra); tc::tmem_ld8(tlane + HG, ra + 8); tc::tmem_ld8(tlane + 2 * HG, ra + 16);
+        }
+        int g = 0, t = t0;
+        for (int n = 0; n < NS && ok; ++n) {
+            if (g == 0) {
+                // ---- a new tile: frame constants, this lane's point, its band
+                K3CLK(e0);
+                if (t >= tend) {                                           // (uniform) the next frame that has tiles
+                    advance(tp, F, t, f);
+                    tbeg = tp[f]; tend = tp[f + 1];
+                }
+                if (f != cur_f) {
+                    if (cur_f >= 0) {
+                        flush(cur_f);
+                        __syncwarp();
+                        if (lane == 0) tc::mbar_arrive(&b_free[fl & 1]);
+                    }
+                    cur_f = f; ++fl;
+                    ok = __all_sync(0xffffffffu, wait_bar(&b_full[fl & 1], (uint32_t)(fl >> 1) & 1u, bad));
+                    const float* bd = sBand + (fl & 1) * 8;
+                    u0 = bd[0]; v0 = bd[1]; A1 = bd[2]; A1c = bd[3]; A1w = bd[4]; Amax = bd[5];
+                    P = max(0, min(a.count[f], cap));
+                    sPf = sProj + (fl & 1) * HP * 12;
+                }
+                valid = (t - tbeg) * TP + 32 * q + lane < P;
+                X = valid ? nX : 0.0f; Y = valid ? nY : 0.0f; Z = valid ? nZ : 0.0f;
+                us = valid ? nU * a.inv_thr : 0.0f; vs = valid ? nV * a.inv_thr : 0.0f;
+                if (t + 1 < t1) {
+                    if (t + 1 < tend) fetch_point(t + 1 - tbeg, f);
+                    else { int f2 = f; advance(tp, F, t + 1, f2); fetch_point(t + 1 - tp[f2], f2); }
+                }
+                bool big;
+                const float sc = point_scale(X, Y, Z, big);
+                du = us - u0; dv = vs - v0;
+                ndu2 = pack2(-du, -du); ndv2 = pack2(-dv, -dv);
+                bc = band_consts(us, vs, du, dv, sc, A1, A1c, A1w, Amax, big, a.tc_kappa);
+                if (!valid) { bc.c2 = 0.0f; bc.c1 = 0.0f; bc.c0 = -1.0f; }     // padding lanes (all-zero rows) never ask for a re-evaluation
+                K3CLK(e1);
+                K3ACC(0, e0, e1);
+            }
+            K3CLK(e2);
+            tc::tmem_ld_wait();                                            // this set is in registers
+            tc::fence_before_sync();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&acc_free[n % NSET]);
+            K3CLK(e3);
+            const bool more = n + 1 < NS;
+            if (more) {
+                const int sn = (n + 1) % NSET;
+                ok = __all_sync(0xffffffffu, wait_bar(&acc_full[sn], (uint32_t)((n + 1) / NSET) & 1u, bad));
+                tc::fence_after_sync();
+            }
+            K3CLK(e4);
+            const uint32_t tn = tlane + (uint32_t)(((n + 1) % NSET) * SETC);
+            if (n & 1) {
+                if (more) { tc::tmem_ld8(tn, ra); tc::tmem_ld8(tn + HG, ra + 8); tc::tmem_ld8(tn + 2 * HG, ra + 16); }
+                const uint32_t fm = eval8(rb);
+                finish_set(fm, g, rb);
+            } else {
+                if (more) { tc::tmem_ld8(tn, rb); tc::tmem_ld8(tn + HG, rb + 8); tc::tmem_ld8(tn + 2 * HG, rb + 16); }
+                const uint32_t fm = eval8(ra);
+                finish_set(fm, g, ra);
+            }
+            K3CLK(e5);
+            K3ACC(2, e2, e3); K3ACC(1, e3, e4); K3ACC(3, e4, e5);
+            if (++g == NG) { g = 0; ++t; }
         }
         if (cur_f >= 0) flush(cur_f);
         if (PROF && warp == 0 && lane == 0)   // epilogue warp 0: [0] per-tile prologue, [1] waiting for the MMA, [2] TMEM loads, [3] arithmetic

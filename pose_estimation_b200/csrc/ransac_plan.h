@@ -13,7 +13,7 @@ struct ScoreArgs {
     int32_t* cnt_all;                // balanced mode: [F,H] inlier counts accumulated with atomics (-1 = no model)
     int32_t* prefix;                 // balanced mode: [F+1] exclusive prefix of the frames' point counts rounded up to 8
                                      // (written by block 0 of the hypothesis kernel, read by every scoring CTA)
-    int32_t* tprefix;                // tensor-core mode: [F+1] exclusive prefix of the frames' 128-point tile counts (same writer)
+    int32_t* tprefix;                // tensor-core mode: [F+1] exclusive prefix of the frames' PB_TC_TILE-point tile counts (same writer)
     int32_t* tc_stats;               // tensor-core mode: [0] barrier timeout, [1] exact re-evaluations (groups of 4 tests x 32 lanes),
                                      // [2] calibration: largest observed |s_tc - s_fp32| / band as float bits, [3] verdicts that differ outside the band
     float tc_kappa;                  // tensor-core mode: multiplier of the re-evaluation band (1 = the derived bound)
@@ -35,6 +35,7 @@ struct Plan {
 // Hypotheses of a frame are cut into HS slices of Hs (power of two) so that few-frame launches
 // still fill 148 SMs; a slice narrower than the CTA splits the points PP ways instead.
 #define PB_SCORE_THREADS 128     /* CTA size of the scoring kernel (ST in ransac_score.cu) */
+#define PB_TC_TILE 64            /* points per work unit of the tensor-core scoring kernel */
 #define PB_TC_STATS_BYTES 128     /* int32 stats[4] + twelve 64-bit clock sums of the profiling mode */
 #define PB_BAL_SUB 256           /* points per staging buffer of the balanced scoring kernel (two buffers) */
 

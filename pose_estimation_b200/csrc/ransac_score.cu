@@ -28,7 +28,7 @@ constexpr int HT = 128;  // threads per CTA of the hypothesis kernel
 
 // exclusive prefix over the frames of  v(P) = P rounded up to 8 (TILES = false: the balanced scoring kernel cuts this
 // padded index space into equal ranges, so every range and every frame segment starts at a multiple of 8) or of the
-// number of 128-point tiles (TILES = true: the tensor-core scoring kernel's work units) -> out[0..F]; one CTA
+// number of PB_TC_TILE-point tiles (TILES = true: the tensor-core scoring kernel's work units) -> out[0..F]; one CTA
 template <bool TILES>
 __device__ void frame_prefix_scan(const ScoreArgs& a, int32_t* out) {
     __shared__ int wsum[HT / 32];
@@ -36,7 +36,7 @@ __device__ void frame_prefix_scan(const ScoreArgs& a, int32_t* out) {
     const int per = (a.F + HT - 1) / HT;
     auto val = [&](int f) {
         const int P = max(0, min(a.count[f], a.cap));
-        return TILES ? (P + 127) >> 7 : (P + 7) & ~7;
+        return TILES ? (P + PB_TC_TILE - 1) / PB_TC_TILE : (P + 7) & ~7;
     };
     int mine = 0;
     for (int k = 0; k < per; ++k) {

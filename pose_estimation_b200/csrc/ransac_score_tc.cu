@@ -5,54 +5,77 @@
 //
 //   projection   x, y, w of a point under a hypothesis are three dot products of (X, Y, Z, 1) with rows of K[R|t]:
 //                a GEMM with K = 4.  Every FP32 operand is split into two FP16 (v ~ h + m, 22 bits; the constant
-//                column into three), the four cross products of every coordinate are laid out along K = 16, so ONE
-//                tcgen05.mma (kind::f16, M = 128 points, N = 192 = 64 hypotheses x {x, y, w}, FP32 accumulate in
-//                TMEM) gives 8192 projections.  Point rows are scaled by a power of two (largest coordinate in
-//                [0.5, 1)), hypothesis rows are centred on one of the frame's pixels (x - u0 w, y - v0 w) so that
-//                the accumulators hold small numbers; both leave the sign of  s = dx^2 + dy^2 - w|w|  unchanged.
-//   epilogue     thread = point (TMEM lane), columns = hypotheses: dx = x' - (u - u0) w, dy likewise, s as in the
-//                contract (5 FMA-pipe instructions instead of 14), verdict = sign bit pushed into a 32-bit word by a
-//                funnel shift.  Two more FMAs give  |s| - (c2 w^2 + c1 |w|): the band inside which the tensor-core
-//                value and the contract's FP32 chain may disagree (bound derived below, per point).  A group of
-//                4 hypotheses x 32 points with any value inside the band is re-evaluated with inlier_s itself from
-//                the FP32 matrices kept in shared memory -- so the counts equal the contract's, not approximately.
-//   counts       32 verdict words of a warp (32 points x 32 hypotheses) are reduced by a 5-step butterfly that
-//                doubles the field width at every step: lane L ends with the count of bit L.
-//   pipeline     one persistent CTA per SM (all 512 TMEM columns: two accumulator sets of 192), 19 warps:
-//                16 epilogue warps (TMEM lane quadrant x 16-hypothesis slice), the MMA issuer, a producer of point
-//                tiles and a producer of hypothesis operands (one frame ahead); hand-offs are mbarriers only.
-//                CTAs take equal ranges of the batch's 128-point tiles (prefix by the hypothesis kernel).
+//                column into three), the four cross products of every coordinate lie along K = 16, so ONE
+//                tcgen05.mma (kind::f16, M = 128 hypotheses, N = 64 points, FP32 accumulate in TMEM) gives 8192
+//                values of one component; three of them (x | y | w) fill an accumulator set of 192 columns.
+//                Points are scaled by a power of two per frame (largest coordinate in [0.5, 1)), the x / y rows are
+//                centred on one of the frame's pixels (x - u0 w, y - v0 w) so that the accumulators hold small
+//                numbers; both leave the sign of  s = dx^2 + dy^2 - w|w|  unchanged.
+//   epilogue     thread = hypothesis (TMEM lane), columns = points: dx = x' - (u - u0) w, dy likewise, s as in the
+//                contract, two points per packed FP32x2 instruction (5 instructions per hypothesis*point instead of
+//                14); verdict = sign bit pushed into a 32-bit word by a funnel shift, one popcount per 32 points.
+//                The pixel coordinates of the tile's points come from shared memory (one broadcast LDS.128 per
+//                two points).  A group of 8 points x 32 hypotheses whose smallest |s| is inside the band in which
+//                the tensor-core value and the contract's FP32 chain may disagree (per-hypothesis bound below) is
+//                re-evaluated with inlier_s itself -- so the counts equal the contract's, not approximately.
+//   pipeline     one persistent CTA per SM (two accumulator sets of 192 TMEM columns), 11 warps: 8 epilogue warps
+//                (TMEM lane quadrant x 32-column half; 32 tests per thread and hand-off, loads of the next 8 columns
+//                in flight under the evaluation of the current 8), the MMA issuer, a producer of point tiles and
+//                a producer of hypothesis operands (one frame ahead); hand-offs are mbarriers only.  CTAs take
+//                equal ranges of the batch's 64-point tiles (prefix by the hypothesis kernel).
 //
-// Error bound (u = 2^-24; S = sum of the absolute values of the terms of a dot product, in the point's scaled units):
+// Error bound (u = 2^-24; S = sum of the absolute values of the terms of a dot product, in the frame's scaled units):
 //   contract     |x_c - x| <= 3.1 u S_x  (three roundings of the FMA chain), likewise y, w;
 //   tensor core  |x_tc - x| <= 25 u S_x' : 8 u for the split residuals (2^-22 per operand), 1 u for the centring FMA,
 //                16 u allowed for the accumulation of the 16 exact products (the hardware's internal alignment is
-//                not documented; measured on C2 with the calibration pass, see profiles/r02_k3_tc.md);
+//                not documented; measured with the calibration pass, see profiles/r02_k3_tc.md);
 //   FP16 subnormal parts add at most 2^-25 per product (absolute).
-// With S_x <= (|us| + 1)|w| + 2 A1 near the threshold (A1 = largest absolute row sum of the rotation part over the
-// frame's hypotheses, |P'| <= 1), the difference of the two s values is at most  c2 w^2 + c1 |w| + c0  with the
-// per-point constants computed in band_consts() below.
+// With S_x <= (|us| + 1)|w| + 2 A1 near the threshold (A1 = absolute row sum of the hypothesis' rotation part,
+// |P'| <= 1), the two s values differ by at most  c2 w^2 + c1 |w| + c0 ; |w| <= Wb = A1w + |t_z| sc for every point of
+// the frame, so one number per hypothesis -- hyp_band() -- bounds it.
 #include <cuda_fp16.h>
 #include "ransac_plan.h"
 #include "tc.cuh"
 
 namespace {
 
-constexpr int TP = 128;                       // points per tile = TMEM lanes
-constexpr int HG = 32;                        // hypotheses per MMA
-constexpr int SETC = 3 * HG;                  // accumulator columns of one set: x | y | w
-constexpr int NSET = 4;                       // accumulator sets in flight (384 of the 512 TMEM columns)
-constexpr int NG_MAX = 8;                     // H <= 256
-constexpr int NSTG = 4;                       // point-tile stages
-constexpr int EPI_WARPS = 16;
-constexpr int W_MMA = 16, W_PA = 17, W_PB = 18;
-constexpr int TC_THREADS = 19 * 32;
-constexpr int A_TILE_BYTES = TP * 32;         // [kc 0..1][row][8 halves]
-constexpr int B_GROUP_BYTES = SETC * 32;
-constexpr int B_FRAME_BYTES = NG_MAX * B_GROUP_BYTES;
-constexpr int HP = NG_MAX * HG;               // hypothesis slots per frame buffer
-constexpr size_t TC_SMEM = (size_t)NSTG * A_TILE_BYTES + 2 * B_FRAME_BYTES + 2 * HP * 12 * sizeof(float) + 2 * 8 * sizeof(float);
+constexpr int TH = 128;                       // hypotheses per M tile = TMEM lanes
+constexpr int TPN = PB_TC_TILE;               // points per tile = columns per component
+constexpr int SETC = 3 * TPN;                 // accumulator columns of one set: x | y | w
+constexpr int NSET = 2;
+constexpr int MT_MAX = 2;                     // H <= 256
+constexpr int NSTG = 6;                       // point-tile stages
+constexpr int EPI_WARPS = 8;
+constexpr int W_MMA = 8, W_PP = 9, W_PH = 10;
+constexpr int TC_THREADS = 11 * 32;
+constexpr int A_COMP_BYTES = TH * 32;         // [kc 0..1][row][8 halves] of one (M tile, component)
+constexpr int A_FRAME_BYTES = MT_MAX * 3 * A_COMP_BYTES;
+constexpr int B_TILE_BYTES = TPN * 32;
+constexpr int PINFO_BYTES = (TPN / 2) * 16;   // (-du0, -du1, -dv0, -dv1) per pair of points
+constexpr int PEXACT_BYTES = 5 * TPN * 4;     // X | Y | Z | us | vs as the contract reads them
+constexpr int STAGE_BYTES = B_TILE_BYTES + PINFO_BYTES + PEXACT_BYTES;
+constexpr int FR_FLOATS = 16;                 // frame constants: see the hypothesis-operand producer
+constexpr size_t TC_SMEM = (size_t)2 * A_FRAME_BYTES + (size_t)NSTG * STAGE_BYTES + 2 * FR_FLOATS * sizeof(float);
 
+typedef unsigned long long f32x2;   // two packed binary32 values
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+    return d;
+}
+__device__ __forceinline__ f32x2 pack2u(uint32_t lo, uint32_t hi) {      // adjacent registers of a tcgen05.ld: no instruction
+    return (f32x2)lo | ((f32x2)hi << 32);
+}
+__device__ __forceinline__ float min3nan(float a, float b, float c) {   // NaN if any input is NaN
+    float d;
+    asm("min.NaN.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
 __device__ __forceinline__ uint32_t pkh(__half a, __half b) {
     return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
 }
@@ -60,19 +83,9 @@ __device__ __forceinline__ void split2h(float v, __half& h, __half& m) {
     h = __float2half_rn(v);
     m = __float2half_rn(v - __half2float(h));      // the difference is exact
 }
-// power-of-two scale of a point: largest |coordinate| * sc in [0.5, 1); clamped to what FP16 holds.
-// big = coordinates beyond 2^14 (or not finite): the point is always evaluated exactly.
-__device__ __forceinline__ float point_scale(float X, float Y, float Z, bool& big) {
-    const float m = fmaxf(fabsf(X), fmaxf(fabsf(Y), fabsf(Z)));
-    int eb = (__float_as_int(m) >> 23) & 0xff;
-    big = eb > 140 || !(X == X) || !(Y == Y) || !(Z == Z);
-    eb = min(max(eb, 113), 140);
-    return __int_as_float((253 - eb) << 23);       // 2^(126 - eb)
-}
 
 // bounded mbarrier wait that gives up quickly once any thread of the CTA has timed out.  try_wait carries a suspend-time
-// hint: the thread sleeps in hardware until the phase completes (or the hint expires), so waiting warps do not spend
-// issue slots on polling -- a third of all executed instructions were polling loops without it.
+// hint: the thread sleeps in hardware until the phase completes (or the hint expires).
 __device__ __forceinline__ bool wait_bar(uint64_t* bar, uint32_t parity, volatile int* bad) {
     const uint32_t a = tc::smem_u32(bar);
 #pragma unroll 1
@@ -99,83 +112,62 @@ __device__ __forceinline__ void advance(const int* __restrict__ tp, int F, int t
     while (f + 1 < F && tp[f + 1] <= t) ++f;
 }
 
-typedef unsigned long long f32x2;   // two packed binary32 values
-__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
-    f32x2 d;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-    return d;
-}
-__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
-    f32x2 d;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
-    return d;
-}
-__device__ __forceinline__ f32x2 pack2u(uint32_t lo, uint32_t hi) {      // adjacent registers of a tcgen05.ld: no instruction
-    return (f32x2)lo | ((f32x2)hi << 32);
-}
-__device__ __forceinline__ float fmax3(float a, float b, float c) {
-    float d;
-    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
-    return d;
-}
-__device__ __forceinline__ float min3nan(float a, float b, float c) {   // NaN if any input is NaN
-    float d;
-    asm("min.NaN.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
-    return d;
+// The contract's matrix of a hypothesis (or the never-inlier matrix when it has no model) and its centred rows.
+struct HypM { float m[12]; float c[8]; bool valid; };
+__device__ __forceinline__ HypM hyp_matrix(const ScoreArgs& a, int f, int h, float u0, float v0) {
+    HypM o;
+    o.valid = false;
+    if (h < a.H) {
+        const float4* p = reinterpret_cast<const float4*>(a.hypRt + ((size_t)f * a.H + h) * 12);
+        const float4 r0 = p[0], r1 = p[1], r2 = p[2];
+        o.valid = (r2.w == r2.w);
+        if (o.valid) {
+            const float R[9] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x};
+            const float tt[3] = {r2.y, r2.z, r2.w};
+            make_proj_s(a.K4[4 * f], a.K4[4 * f + 1], a.K4[4 * f + 2], a.K4[4 * f + 3], R, tt, a.inv_thr, o.m);
+        }
+    }
+    if (!o.valid) {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) o.m[k] = 0.0f;
+        o.m[11] = -1.0f;                                            // w < 0 for every point: never an inlier
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        o.c[k] = fmaf(-u0, o.m[8 + k], o.m[k]);
+        o.c[4 + k] = fmaf(-v0, o.m[8 + k], o.m[4 + k]);
+    }
+    return o;
 }
 
-// counts of the 32 bit positions over the warp's 32 words: lane L returns the number of lanes whose bit L is set
-__device__ __forceinline__ int bit_column_counts(uint32_t v, int lane) {
-    {
-        const uint32_t lo = v & 0x55555555u, hi = (v >> 1) & 0x55555555u;
-        const bool up = lane & 1;
-        v = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, 1);
-    }
-    {
-        const uint32_t lo = v & 0x33333333u, hi = (v >> 2) & 0x33333333u;
-        const bool up = lane & 2;
-        v = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, 2);
-    }
-    {
-        const uint32_t lo = v & 0x0F0F0F0Fu, hi = (v >> 4) & 0x0F0F0F0Fu;
-        const bool up = lane & 4;
-        v = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, 4);
-    }
-    {
-        const uint32_t lo = v & 0x00FF00FFu, hi = (v >> 8) & 0x00FF00FFu;
-        const bool up = lane & 8;
-        v = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, 8);
-    }
-    {
-        const uint32_t lo = v & 0x0000FFFFu, hi = v >> 16;
-        const bool up = lane & 16;
-        v = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, 16);
-    }
-    return (int)v;
-}
+// frame constants (sFr[buf][..], written by the hypothesis-operand producer)
+enum { FR_U0 = 0, FR_V0, FR_SC, FR_MAXUS, FR_MAXVS, FR_MAXDU, FR_MAXDV, FR_BIG };
 
-// frame constants written by the hypothesis-operand producer: sBand[buf][0..7]
-//   0 u0, 1 v0 (centre pixel in threshold units), 2 A1 of the x / y rows as the contract uses them, 3 A1 of the
-//   centred rows, 4 A1 of the w row, 5 largest absolute matrix entry (FP16 range guard)
-struct BandC { float c2, c1, c0; };
-__device__ __forceinline__ BandC band_consts(float us, float vs, float du, float dv, float sc, float A1, float A1c,
-                                             float A1w, float Amax, bool big, float kappa) {
-    const float u = 5.9604645e-8f;                  // 2^-24
-    const float aus = fabsf(us), avs = fabsf(vs), adu = fabsf(du), adv = fabsf(dv);
-    const float ax = u * (6.2f * aus + 51.0f * adu + 30.1f);
-    const float ay = u * (6.2f * avs + 51.0f * adv + 30.1f);
-    const float sub = 2.9802322e-8f;                // 2^-25: FP16 subnormal quantum / 2
-    const float bx = u * (6.2f * A1 + 50.0f * A1c + (6.2f * aus + 50.0f * adu) * A1w) + sub * ((A1c + 3.0f + sc) + adu * (A1w + 3.0f + sc));
-    const float by = u * (6.2f * A1 + 50.0f * A1c + (6.2f * avs + 50.0f * adv) * A1w) + sub * ((A1c + 3.0f + sc) + adv * (A1w + 3.0f + sc));
-    const float ew = 28.1f * u;                     // w: |w_c - w| + |w_tc - w| <= ew (|w| + 2 A1w) + sub (A1w + 3 + sc)
-    BandC b;
-    b.c2 = kappa * 1.02f * (2.0f * (ax + ay) + 2.0f * ew + 12.0f * u);
-    b.c1 = kappa * 1.02f * (2.0f * (bx + by) + 4.0f * ew * A1w + 2.0f * sub * (A1w + 3.0f + sc));
+// Largest difference between the tensor-core s and the contract's s over every point of the frame, for one hypothesis:
+// c2 Wb^2 + c1 Wb + c0 (see the header).  +inf: always re-evaluate.
+__device__ __forceinline__ float hyp_band(const HypM& hm, const float* fr, float kappa) {
+    const float u = 5.9604645e-8f, sub = 2.9802322e-8f;             // 2^-24, 2^-25
+    const float sc = fr[FR_SC], mus = fr[FR_MAXUS], mvs = fr[FR_MAXVS], mdu = fr[FR_MAXDU], mdv = fr[FR_MAXDV];
+    const float A1x = fabsf(hm.m[0]) + fabsf(hm.m[1]) + fabsf(hm.m[2]), A1y = fabsf(hm.m[4]) + fabsf(hm.m[5]) + fabsf(hm.m[6]);
+    const float A1w = fabsf(hm.m[8]) + fabsf(hm.m[9]) + fabsf(hm.m[10]);
+    const float A1xc = fabsf(hm.c[0]) + fabsf(hm.c[1]) + fabsf(hm.c[2]), A1yc = fabsf(hm.c[4]) + fabsf(hm.c[5]) + fabsf(hm.c[6]);
+    float amax = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) amax = fmaxf(amax, fabsf(hm.c[k]));
+#pragma unroll
+    for (int k = 8; k < 12; ++k) amax = fmaxf(amax, fabsf(hm.m[k]));
+    const float ax = u * (6.2f * mus + 51.0f * mdu + 30.1f), ay = u * (6.2f * mvs + 51.0f * mdv + 30.1f);
+    const float bx = u * (6.2f * A1x + 50.0f * A1xc + (6.2f * mus + 50.0f * mdu) * A1w) + sub * ((A1xc + 3.0f + sc) + mdu * (A1w + 3.0f + sc));
+    const float by = u * (6.2f * A1y + 50.0f * A1yc + (6.2f * mvs + 50.0f * mdv) * A1w) + sub * ((A1yc + 3.0f + sc) + mdv * (A1w + 3.0f + sc));
+    const float ew = 28.1f * u;
+    const float c2 = 1.02f * (2.0f * (ax + ay) + 2.0f * ew + 12.0f * u);
+    const float c1 = 1.02f * (2.0f * (bx + by) + 4.0f * ew * A1w + 2.0f * sub * (A1w + 3.0f + sc));
     const float e0 = 2.0f * ew * A1w + sub * (A1w + 3.0f + sc);
-    b.c0 = kappa * kappa * 4.0f * (bx * bx + by * by + e0 * e0);
-    // outside what the FP16 operands can hold, or a bound that is not a number: everything is re-evaluated
-    if (big || !(Amax < 32768.0f) || !(b.c1 == b.c1) || !(b.c2 == b.c2) || !(b.c0 == b.c0)) b.c0 = __int_as_float(0x7f800000);
-    return b;
+    const float c0 = 4.0f * (bx * bx + by * by + e0 * e0);
+    const float Wb = 1.001f * (A1w + fabsf(hm.m[11]) * sc);         // |w'| of every point of the frame (|P'| <= 1)
+    float band = kappa * fmaf(fmaf(c2, Wb, c1), Wb, 0.0f) + kappa * kappa * c0;
+    if (!(amax < 32768.0f) || fr[FR_BIG] != 0.0f || !(band == band)) band = __int_as_float(0x7f800000);
+    return band;
 }
 
 // MODE 0: product; 1: calibration (every test also evaluated exactly; fills tc_stats[2..3]); 2: clock64 breakdown of
@@ -187,11 +179,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
     constexpr bool CALIB = MODE == 1, PROF = MODE == 2;
     long long prof[4] = {0, 0, 0, 0};
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    unsigned char* sA = smem_raw;                                              // [NSTG] point tiles
-    unsigned char* sB = sA + NSTG * A_TILE_BYTES;                              // [2 frames][NG_MAX groups] hypothesis operands
-    float* sProj = reinterpret_cast<float*>(sB + 2 * B_FRAME_BYTES);           // [2][HP][12] the contract's FP32 matrices
-    float* sBand = sProj + 2 * HP * 12;                                        // [2][8]
-    __shared__ __align__(8) uint64_t a_full[NSTG], a_free[NSTG], b_full[2], b_free[2], acc_full[NSET], acc_free[NSET];
+    unsigned char* sA = smem_raw;                                              // [2 frames][MT][3 comps] hypothesis operands
+    unsigned char* sP = sA + 2 * A_FRAME_BYTES;                                // [NSTG] point tile | pixel pairs | exact values
+    float* sFr = reinterpret_cast<float*>(sP + NSTG * STAGE_BYTES);            // [2][FR_FLOATS]
+    __shared__ __align__(8) uint64_t p_full[NSTG], p_free[NSTG], h_full[2], h_free[2], acc_full[NSET], acc_free[NSET];
     __shared__ uint32_t tmem_base;
     __shared__ int s_bad;
 
@@ -202,11 +193,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
     const int U = (T + (int)gridDim.x - 1) / (int)gridDim.x;
     const int t0 = (int)blockIdx.x * U, t1 = min(T, t0 + U);
     if (t0 >= t1) return;                                                      // uniform per CTA
-    const int NG = (H + HG - 1) / HG;
+    const int MT = (H + TH - 1) / TH;
 
     if (tid == 0) {
-        for (int i = 0; i < NSTG; ++i) { tc::mbar_init(&a_full[i], 1); tc::mbar_init(&a_free[i], 1); }
-        for (int i = 0; i < 2; ++i) { tc::mbar_init(&b_full[i], 1); tc::mbar_init(&b_free[i], EPI_WARPS); }
+        for (int i = 0; i < NSTG; ++i) { tc::mbar_init(&p_full[i], 1); tc::mbar_init(&p_free[i], 1 + EPI_WARPS); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&h_full[i], 1); tc::mbar_init(&h_free[i], EPI_WARPS + 1); }
         for (int i = 0; i < NSET; ++i) { tc::mbar_init(&acc_full[i], 1); tc::mbar_init(&acc_free[i], EPI_WARPS); }
         s_bad = 0;
         tc::fence_mbar_init();
@@ -219,157 +210,143 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
     volatile int* bad = &s_bad;
     bool ok = true;
 
-    if (warp == W_PA) {
-        // ===== point tiles: FP32 (X, Y, Z) -> scaled FP16 pairs, rows (Xh,Xm,Xh,Xm, Yh,Ym,Yh,Ym | Zh,Zm,Zh,Zm, sc,sc,sc,0)
-        int f = frame_of(tp, F, t0);
-        int tbeg = tp[f], tend = tp[f + 1], P = max(0, min(a.count[f], cap));
-        for (int t = t0, tl = 0; t < t1 && ok; ++t, ++tl) {
-            if (t >= tend) { advance(tp, F, t, f); tbeg = tp[f]; tend = tp[f + 1]; P = max(0, min(a.count[f], cap)); }
-            const int s = tl % NSTG, use = tl / NSTG;
-            const int p0 = (t - tbeg) * TP;
-            const float* X = a.pts + (size_t)f * 5 * cap;
-            const float* Y = X + cap;
-            const float* Z = Y + cap;
-            float px[4], py[4], pz[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int p = p0 + 32 * i + lane;
-                const bool v = p < P;
-                px[i] = v ? X[p] : 0.0f; py[i] = v ? Y[p] : 0.0f; pz[i] = v ? Z[p] : 0.0f;
-            }
-            K3CLK(c0);
-            if (use > 0) ok = __all_sync(0xffffffffu, wait_bar(&a_free[s], (uint32_t)(use - 1) & 1u, bad));
-            K3CLK(c1);
-            K3ACC(0, c0, c1);
-            uint4* dst = reinterpret_cast<uint4*>(sA + s * A_TILE_BYTES);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int r = 32 * i + lane;
-                uint4 k0 = make_uint4(0u, 0u, 0u, 0u), k1 = k0;
-                if (p0 + r < P) {
-                    bool big;
-                    const float sc = point_scale(px[i], py[i], pz[i], big);
-                    __half xh, xm, yh, ym, zh, zm;
-                    split2h(px[i] * sc, xh, xm); split2h(py[i] * sc, yh, ym); split2h(pz[i] * sc, zh, zm);
-                    const __half sh = __float2half_rn(sc), z0 = __float2half_rn(0.0f);
-                    k0 = make_uint4(pkh(xh, xm), pkh(xh, xm), pkh(yh, ym), pkh(yh, ym));
-                    k1 = make_uint4(pkh(zh, zm), pkh(zh, zm), pkh(sh, sh), pkh(sh, z0));
-                }
-                dst[r] = k0; dst[TP + r] = k1;
-            }
-            tc::fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&a_full[s]);
-            K3CLK(c2);
-            K3ACC(1, c1, c2);
-        }
-        if (PROF && lane == 0) {      // [8] waiting for a free stage, [9] building tiles
-            atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + 8, (unsigned long long)prof[0]);
-            atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + 9, (unsigned long long)prof[1]);
-        }
-    } else if (warp == W_PB) {
-        // ===== hypothesis operands of a frame: rows (m0h,m0h,m0m,m0m, m1h,m1h,m1m,m1m | m2h,m2h,m2m,m2m, m3h,m3m,m3l,0),
-        // x and y rows centred on the pixel (u0, v0); the contract's FP32 matrices beside them
+    if (warp == W_PH) {
+        // ===== hypothesis operands of a frame: rows (m0h,m0h,m0m,m0m, m1h,m1h,m1m,m1m | m2h,m2h,m2m,m2m, m3h,m3m,m3l,0) of the
+        // centred x / y rows and the w row; before that the frame's constants (scale, centre pixel, coordinate maxima)
         int f = frame_of(tp, F, t0);
         int fl = 0;
         for (int t = t0; t < t1 && ok; ++fl) {
             advance(tp, F, t, f);
             const int fb = fl & 1, use = fl >> 1;
-            if (use > 0) ok = __all_sync(0xffffffffu, wait_bar(&b_free[fb], (uint32_t)(use - 1) & 1u, bad));
+            if (use > 0) ok = __all_sync(0xffffffffu, wait_bar(&h_free[fb], (uint32_t)(use - 1) & 1u, bad));
             const int P = max(0, min(a.count[f], cap));
-            const float* Up = a.pts + (size_t)f * 5 * cap + 3 * (size_t)cap;
-            const float u0 = P > 0 ? Up[P >> 1] * a.inv_thr : 0.0f;
-            const float v0 = P > 0 ? Up[cap + (P >> 1)] * a.inv_thr : 0.0f;
-            const float fx = a.K4[4 * f], fy = a.K4[4 * f + 1], cx = a.K4[4 * f + 2], cy = a.K4[4 * f + 3];
-            float A1 = 0.0f, A1c = 0.0f, A1w = 0.0f, Amax = 0.0f;
-            unsigned char* sBf = sB + fb * B_FRAME_BYTES;
-            float* sPf = sProj + fb * HP * 12;
-            const float qnan = __int_as_float(0x7fffffff);
-            float4 n0 = make_float4(0.0f, 0.0f, 0.0f, 0.0f), n1 = n0, n2 = make_float4(0.0f, 0.0f, 0.0f, qnan);
-            if (lane < H) {
-                const float4* o = reinterpret_cast<const float4*>(a.hypRt + ((size_t)f * H + lane) * 12);
-                n0 = o[0]; n1 = o[1]; n2 = o[2];
+            const float* Xp = a.pts + (size_t)f * 5 * cap;
+            const float u0 = P > 0 ? Xp[3 * (size_t)cap + (P >> 1)] * a.inv_thr : 0.0f;
+            const float v0 = P > 0 ? Xp[4 * (size_t)cap + (P >> 1)] * a.inv_thr : 0.0f;
+            float cmax = 0.0f, mus = 0.0f, mvs = 0.0f, mdu = 0.0f, mdv = 0.0f;
+            bool nan = false;
+            for (int p = lane; p < P; p += 32) {
+                const float X = Xp[p], Y = Xp[cap + p], Z = Xp[2 * (size_t)cap + p];
+                const float us = Xp[3 * (size_t)cap + p] * a.inv_thr, vs = Xp[4 * (size_t)cap + p] * a.inv_thr;
+                nan = nan || !(X == X) || !(Y == Y) || !(Z == Z) || !(us == us) || !(vs == vs);
+                cmax = fmaxf(cmax, fmaxf(fabsf(X), fmaxf(fabsf(Y), fabsf(Z))));
+                mus = fmaxf(mus, fabsf(us)); mvs = fmaxf(mvs, fabsf(vs));
+                mdu = fmaxf(mdu, fabsf(us - u0)); mdv = fmaxf(mdv, fabsf(vs - v0));
             }
-            for (int h = lane; h < NG * HG; h += 32) {
-                float mj[12];
-                bool valid = false;
-                const float4 r0 = n0, r1 = n1, r2 = n2;
-                n2.w = qnan;
-                if (h + 32 < H) {                                            // the next pose is in flight during this one's conversion
-                    const float4* o = reinterpret_cast<const float4*>(a.hypRt + ((size_t)f * H + h + 32) * 12);
-                    n0 = o[0]; n1 = o[1]; n2 = o[2];
-                }
-                if (h < H) {
-                    valid = (r2.w == r2.w);
-                    if (valid) {
-                        const float R[9] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x};
-                        const float tt[3] = {r2.y, r2.z, r2.w};
-                        make_proj_s(fx, fy, cx, cy, R, tt, a.inv_thr, mj);
-                    }
-                }
-                if (!valid) {
 #pragma unroll
-                    for (int k = 0; k < 12; ++k) mj[k] = 0.0f;
-                    mj[11] = -1.0f;                                            // w < 0 for every point: never an inlier
-                }
-                float4* pd = reinterpret_cast<float4*>(sPf + h * 12);
-                pd[0] = make_float4(mj[0], mj[1], mj[2], mj[3]);
-                pd[1] = make_float4(mj[4], mj[5], mj[6], mj[7]);
-                pd[2] = make_float4(mj[8], mj[9], mj[10], mj[11]);
-                float row[3][4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    row[0][k] = fmaf(-u0, mj[8 + k], mj[k]);
-                    row[1][k] = fmaf(-v0, mj[8 + k], mj[4 + k]);
-                    row[2][k] = mj[8 + k];
-                }
-                A1 = fmaxf(A1, fmaxf(fabsf(mj[0]) + fabsf(mj[1]) + fabsf(mj[2]), fabsf(mj[4]) + fabsf(mj[5]) + fabsf(mj[6])));
-                A1c = fmaxf(A1c, fmaxf(fabsf(row[0][0]) + fabsf(row[0][1]) + fabsf(row[0][2]),
-                                       fabsf(row[1][0]) + fabsf(row[1][1]) + fabsf(row[1][2])));
-                A1w = fmaxf(A1w, fabsf(mj[8]) + fabsf(mj[9]) + fabsf(mj[10]));
-                const int g = h / HG, hl = h % HG;
-                uint4* grp = reinterpret_cast<uint4*>(sBf + g * B_GROUP_BYTES);
+            for (int off = 16; off >= 1; off >>= 1) {
+                cmax = fmaxf(cmax, __shfl_xor_sync(0xffffffffu, cmax, off));
+                mus = fmaxf(mus, __shfl_xor_sync(0xffffffffu, mus, off));
+                mvs = fmaxf(mvs, __shfl_xor_sync(0xffffffffu, mvs, off));
+                mdu = fmaxf(mdu, __shfl_xor_sync(0xffffffffu, mdu, off));
+                mdv = fmaxf(mdv, __shfl_xor_sync(0xffffffffu, mdv, off));
+            }
+            nan = __any_sync(0xffffffffu, nan);
+            // power-of-two scale: largest |coordinate| * sc in [0.5, 1), clamped to what FP16 holds
+            int eb = (__float_as_int(cmax) >> 23) & 0xff;
+            const bool big = nan || eb > 140 || !(mus < 3.0e37f) || !(mvs < 3.0e37f);
+            eb = min(max(eb, 113), 140);
+            const float sc = __int_as_float((253 - eb) << 23);       // 2^(126 - eb)
+            if (lane == 0) {
+                float* fr = sFr + fb * FR_FLOATS;
+                fr[FR_U0] = u0; fr[FR_V0] = v0; fr[FR_SC] = sc; fr[FR_MAXUS] = mus; fr[FR_MAXVS] = mvs;
+                fr[FR_MAXDU] = mdu; fr[FR_MAXDV] = mdv; fr[FR_BIG] = big ? 1.0f : 0.0f;
+            }
+            unsigned char* sAf = sA + fb * A_FRAME_BYTES;
+            for (int h = lane; h < MT * TH; h += 32) {
+                const HypM hm = hyp_matrix(a, f, h, u0, v0);
+                const int mt = h / TH, row = h % TH;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
+                    const float* rw = c == 0 ? hm.c : c == 1 ? hm.c + 4 : hm.m + 8;
                     __half eh[3], em[3], h3, m3, l3;
 #pragma unroll
-                    for (int k = 0; k < 3; ++k) split2h(row[c][k], eh[k], em[k]);
+                    for (int k = 0; k < 3; ++k) split2h(rw[k], eh[k], em[k]);
                     {
-                        const float v = row[c][3];
+                        const float v = rw[3];
                         h3 = __float2half_rn(v);
                         const float r1 = v - __half2float(h3);
                         m3 = __float2half_rn(r1);
                         l3 = __float2half_rn(r1 - __half2float(m3));
                     }
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const float av = fabsf(row[c][k]);
-                        Amax = (av > Amax || !(av == av)) ? (av == av ? av : __int_as_float(0x7f800000)) : Amax;
-                    }
-                    const int rr = c * HG + hl;
-                    grp[rr] = make_uint4(pkh(eh[0], eh[0]), pkh(em[0], em[0]), pkh(eh[1], eh[1]), pkh(em[1], em[1]));
-                    grp[SETC + rr] = make_uint4(pkh(eh[2], eh[2]), pkh(em[2], em[2]), pkh(h3, m3), pkh(l3, __float2half_rn(0.0f)));
+                    uint4* dst = reinterpret_cast<uint4*>(sAf + (mt * 3 + c) * A_COMP_BYTES);
+                    dst[row] = make_uint4(pkh(eh[0], eh[0]), pkh(em[0], em[0]), pkh(eh[1], eh[1]), pkh(em[1], em[1]));
+                    dst[TH + row] = make_uint4(pkh(eh[2], eh[2]), pkh(em[2], em[2]), pkh(h3, m3), pkh(l3, __float2half_rn(0.0f)));
                 }
-            }
-#pragma unroll
-            for (int off = 16; off >= 1; off >>= 1) {
-                A1 = fmaxf(A1, __shfl_xor_sync(0xffffffffu, A1, off));
-                A1c = fmaxf(A1c, __shfl_xor_sync(0xffffffffu, A1c, off));
-                A1w = fmaxf(A1w, __shfl_xor_sync(0xffffffffu, A1w, off));
-                Amax = fmaxf(Amax, __shfl_xor_sync(0xffffffffu, Amax, off));
-            }
-            if (lane == 0) {
-                float* bd = sBand + fb * 8;
-                bd[0] = u0; bd[1] = v0; bd[2] = A1; bd[3] = A1c; bd[4] = A1w; bd[5] = Amax;
             }
             tc::fence_proxy_async();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&b_full[fb]);
+            if (lane == 0) tc::mbar_arrive(&h_full[fb]);
             t = min(t1, tp[f + 1]);                                            // first tile of the next frame
         }
+    } else if (warp == W_PP) {
+        // ===== point tiles: FP32 (X, Y, Z) -> scaled FP16 pairs, rows (Xh,Xm,Xh,Xm, Yh,Ym,Yh,Ym | Zh,Zm,Zh,Zm, sc,sc,sc,0);
+        // beside them the negated centred pixel coordinates (pairs of points) and the values the contract reads
+        int f = frame_of(tp, F, t0), cur_f = -1, fl = -1;
+        int tbeg = tp[f], tend = tp[f + 1], P = max(0, min(a.count[f], cap));
+        float u0 = 0.0f, v0 = 0.0f, sc = 1.0f;
+        for (int t = t0, tl = 0; t < t1 && ok; ++t, ++tl) {
+            if (t >= tend) { advance(tp, F, t, f); tbeg = tp[f]; tend = tp[f + 1]; P = max(0, min(a.count[f], cap)); }
+            const int s = tl % NSTG, use = tl / NSTG;
+            const int p0 = (t - tbeg) * TPN;
+            const float* Xp = a.pts + (size_t)f * 5 * cap;
+            float v[TPN / 32][5];
+#pragma unroll
+            for (int i = 0; i < TPN / 32; ++i) {
+                const int p = p0 + 32 * i + lane;
+                const bool in = p < P;
+#pragma unroll
+                for (int k = 0; k < 5; ++k) v[i][k] = in ? Xp[(size_t)k * cap + p] : 0.0f;
+            }
+            if (f != cur_f) {                                                  // the frame's constants (same order as the other roles)
+                __syncwarp();
+                if (lane == 0 && fl >= 0) tc::mbar_arrive(&h_free[fl & 1]);    // done with the previous frame's constants
+                cur_f = f; ++fl;
+                ok = __all_sync(0xffffffffu, wait_bar(&h_full[fl & 1], (uint32_t)(fl >> 1) & 1u, bad));
+                const float* fr = sFr + (fl & 1) * FR_FLOATS;
+                u0 = fr[FR_U0]; v0 = fr[FR_V0]; sc = fr[FR_SC];
+            }
+            K3CLK(c0);
+            if (use > 0) ok = __all_sync(0xffffffffu, wait_bar(&p_free[s], (uint32_t)(use - 1) & 1u, bad) && ok);
+            K3CLK(c1);
+            K3ACC(0, c0, c1);
+            unsigned char* st = sP + s * STAGE_BYTES;
+            uint4* dst = reinterpret_cast<uint4*>(st);
+            float* pinfo = reinterpret_cast<float*>(st + B_TILE_BYTES);
+            float* pex = reinterpret_cast<float*>(st + B_TILE_BYTES + PINFO_BYTES);
+            const __half sh = __float2half_rn(sc), z0 = __float2half_rn(0.0f);
+#pragma unroll
+            for (int i = 0; i < TPN / 32; ++i) {
+                const int r = 32 * i + lane;
+                const bool in = p0 + r < P;
+                const float X = v[i][0], Y = v[i][1], Z = v[i][2];
+                const float us = v[i][3] * a.inv_thr, vs = v[i][4] * a.inv_thr;
+                __half xh, xm, yh, ym, zh, zm;
+                split2h(X * sc, xh, xm); split2h(Y * sc, yh, ym); split2h(Z * sc, zh, zm);
+                dst[r] = make_uint4(pkh(xh, xm), pkh(xh, xm), pkh(yh, ym), pkh(yh, ym));
+                dst[TPN + r] = make_uint4(pkh(zh, zm), pkh(zh, zm), pkh(sh, sh), pkh(sh, z0));
+                // padding columns: the origin with a pixel far away -> s overflows to +inf, never an inlier, never in the band
+                pinfo[(r >> 1) * 4 + (r & 1)] = in ? -(us - u0) : 1.0e18f;
+                pinfo[(r >> 1) * 4 + 2 + (r & 1)] = in ? -(vs - v0) : 1.0e18f;
+                // (the contract's formula gives +inf or NaN for a pixel at infinity: a padding column is never counted)
+                const float pinf = __int_as_float(0x7f800000);
+                pex[r] = X; pex[TPN + r] = Y; pex[2 * TPN + r] = Z; pex[3 * TPN + r] = in ? us : pinf; pex[4 * TPN + r] = in ? vs : pinf;
+            }
+            tc::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&p_full[s]);
+            K3CLK(c2);
+            K3ACC(1, c1, c2);
+        }
+        __syncwarp();
+        if (lane == 0 && fl >= 0) tc::mbar_arrive(&h_free[fl & 1]);
+        if (PROF && lane == 0) {      // [8] waiting for a free stage, [9] building tiles
+            atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + 8, (unsigned long long)prof[0]);
+            atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + 9, (unsigned long long)prof[1]);
+        }
     } else if (warp == W_MMA) {
-        // ===== MMA issuer: per tile NG MMAs (one per 32-hypothesis group) into the NSET accumulator sets in turn
-        const uint32_t idesc = tc::idesc_f16_f32(TP, SETC);
+        // ===== MMA issuer: per point tile and M tile three MMAs (x | y | w) into the accumulator sets in turn
+        const uint32_t idesc = tc::idesc_f16_f32(TH, TPN);
         int f = frame_of(tp, F, t0), cur_f = -1, fl = -1, n = 0;
         int tend = tp[f + 1];
         for (int t = t0, tl = 0; t < t1 && ok; ++t, ++tl) {
@@ -377,218 +354,207 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
             K3CLK(c0);
             if (f != cur_f) {
                 cur_f = f; ++fl;
-                ok = wait_bar(&b_full[fl & 1], (uint32_t)(fl >> 1) & 1u, bad);
+                ok = wait_bar(&h_full[fl & 1], (uint32_t)(fl >> 1) & 1u, bad);
             }
             K3CLK(c1);
             const int s = tl % NSTG;
-            ok = __all_sync(0xffffffffu, wait_bar(&a_full[s], (uint32_t)(tl / NSTG) & 1u, bad) && ok);
+            ok = __all_sync(0xffffffffu, wait_bar(&p_full[s], (uint32_t)(tl / NSTG) & 1u, bad) && ok);
             K3CLK(c2);
             K3ACC(0, c0, c1); K3ACC(1, c1, c2);
             tc::fence_after_sync();
-            const uint64_t ad = tc::smem_desc(tc::smem_u32(sA + s * A_TILE_BYTES), TP * 16, 128);
-            for (int g = 0; g < NG && ok; ++g, ++n) {
+            const uint64_t bd = tc::smem_desc(tc::smem_u32(sP + s * STAGE_BYTES), TPN * 16, 128);
+            for (int mt = 0; mt < MT && ok; ++mt, ++n) {
                 const int set = n % NSET, use = n / NSET;
                 K3CLK(c3);
                 if (use > 0) ok = __all_sync(0xffffffffu, wait_bar(&acc_free[set], (uint32_t)(use - 1) & 1u, bad));
                 K3CLK(c4);
                 K3ACC(2, c3, c4);
                 tc::fence_after_sync();
-                const uint64_t bd = tc::smem_desc(tc::smem_u32(sB + (fl & 1) * B_FRAME_BYTES + g * B_GROUP_BYTES), SETC * 16, 128);
                 if (lane == 0 && ok) {
-                    tc::mma_bf16(tmem + (uint32_t)(set * SETC), ad, bd, idesc, 0);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const uint64_t ad = tc::smem_desc(tc::smem_u32(sA + (fl & 1) * A_FRAME_BYTES + (mt * 3 + c) * A_COMP_BYTES), TH * 16, 128);
+                        tc::mma_bf16(tmem + (uint32_t)(set * SETC + c * TPN), ad, bd, idesc, 0);
+                    }
                     tc::mma_commit(&acc_full[set]);
                 }
                 __syncwarp();
             }
-            if (lane == 0) tc::mma_commit(&a_free[s]);
+            if (lane == 0) tc::mma_commit(&p_free[s]);
             __syncwarp();
         }
         if (PROF && lane == 0)        // [4] waiting for hypothesis operands, [5] for point tiles, [6] for a free accumulator set
             for (int k = 0; k < 3; ++k) atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + 4 + k, (unsigned long long)prof[k]);
     } else {
-        // ===== epilogue: warp = (TMEM lane quadrant q, 8-hypothesis slice j of every 32-hypothesis set); thread = point.
-        // Software pipeline over the CTA's accumulator sets: the loads of set n + 1 (x | y | w: three tcgen05.ld.x8)
-        // are in flight while set n is evaluated; a set is handed back to the MMA warp as soon as it is in registers.
+        // ===== epilogue: warp = (TMEM lane quadrant q, column half j); thread = hypothesis 128 mt + 32 q + lane.
+        // Software pipeline over the warp's 32 columns of a set: two chunks of 16 (x | y | w: three tcgen05.ld.x16), the next
+        // chunk's loads in flight under the evaluation of the current one.
+        constexpr int CPW = TPN / 2;                         // columns per warp and component
+        constexpr int NCH = CPW / 16;                        // chunks of 16 columns per set
         const int q = warp & 3, j = warp >> 2;
-        const uint32_t tlane = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(8 * j);
-        const int NS = (t1 - t0) * NG;                       // accumulator sets of this CTA
+        const uint32_t tlane = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(CPW * j);
         int f = frame_of(tp, F, t0), cur_f = -1, fl = -1;
-        int tbeg = tp[f], tend = tp[f + 1];                  // tiles of frame f (register copies: no load per tile)
-        int cnt[2] = {0, 0};
+        int tend = tp[f + 1];
+        int cnt[MT_MAX] = {0, 0};
         int nslow = 0, nmis = 0;
         float calmax = 0.0f;
-        float u0 = 0.0f, v0 = 0.0f, A1 = 0.0f, A1c = 0.0f, A1w = 0.0f, Amax = 0.0f;
-        int P = 0;
+        HypM hm[MT_MAX];
+        float band[MT_MAX] = {0.0f, 0.0f};
+        float scf = 1.0f;
+        uint32_t ra[48], rb[48];
+        int n = 0;
         auto flush = [&](int ff) {
 #pragma unroll
-            for (int wi = 0; wi < 2; ++wi) {
-                const int k = (31 - lane) >> 3, c = (31 - lane) & 7;       // bit position L <- set 4 wi + k of the tile, test c
-                const int h = (4 * wi + k) * HG + 8 * j + c;
-                if (h < H && cnt[wi] > 0) atomicAdd(&a.cnt_all[(size_t)ff * H + h], cnt[wi]);
-                cnt[wi] = 0;
+            for (int mt = 0; mt < MT_MAX; ++mt) {
+                const int h = mt * TH + 32 * q + lane;
+                if (h < H && cnt[mt] > 0) atomicAdd(&a.cnt_all[(size_t)ff * H + h], cnt[mt]);
+                cnt[mt] = 0;
             }
         };
-        // this lane's point of the next tile: raw values fetched one tile ahead; rows beyond cap are not read
-        float nX = 0.0f, nY = 0.0f, nZ = 0.0f, nU = 0.0f, nV = 0.0f;
-        auto fetch_point = [&](int tile_in_frame, int ff) {
-            const int p = tile_in_frame * TP + 32 * q + lane;
-            const float* base = a.pts + (size_t)ff * 5 * cap;
-            if (p < cap) { nX = base[p]; nY = base[cap + p]; nZ = base[2 * (size_t)cap + p]; nU = base[3 * (size_t)cap + p]; nV = base[4 * (size_t)cap + p]; }
+        auto ld16 = [&](uint32_t taddr, uint32_t (&r)[48]) {
+            tc::tmem_ld16p(taddr, r); tc::tmem_ld16p(taddr + TPN, r + 16); tc::tmem_ld16p(taddr + 2 * TPN, r + 32);
         };
-        fetch_point(t0 - tbeg, f);
-        float X = 0.0f, Y = 0.0f, Z = 0.0f, us = 0.0f, vs = 0.0f, du = 0.0f, dv = 0.0f;
-        f32x2 ndu2 = 0ull, ndv2 = 0ull;
-        BandC bc = {0.0f, 0.0f, -1.0f};
-        bool valid = false;
-        const float* sPf = sProj;
-        uint32_t bits = 0u;
-        uint32_t ra[24], rb[24];
-        // evaluate the warp's 8 columns of a set held in r = x[8] | y[8] | w[8]; returns a 2-bit mask of the groups of
-        // 4 hypotheses that hold a value inside the band
-        auto eval8 = [&](const uint32_t (&r)[24]) -> uint32_t {
-            uint32_t fm = 0u;
-#pragma unroll
-            for (int gq = 0; gq < 2; ++gq) {
-                float smin = __int_as_float(0x7f800000), wmax = 0.0f;
-#pragma unroll
-                for (int pr = 0; pr < 2; ++pr) {
-                    const int c = 4 * gq + 2 * pr;
-                    const float w0 = __uint_as_float(r[16 + c]), w1 = __uint_as_float(r[16 + c + 1]);
-                    const f32x2 x2 = pack2u(r[c], r[c + 1]), y2 = pack2u(r[8 + c], r[8 + c + 1]), w2 = pack2u(r[16 + c], r[16 + c + 1]);
-                    const f32x2 dx2 = ffma2(ndu2, w2, x2), dy2 = ffma2(ndv2, w2, y2);
-                    const f32x2 nq2 = pack2(w0 * -fabsf(w0), w1 * -fabsf(w1));
-                    const f32x2 s2 = ffma2(dx2, dx2, ffma2(dy2, dy2, nq2));
-                    const uint32_t s0 = (uint32_t)s2, s1 = (uint32_t)(s2 >> 32);
-                    bits = __funnelshift_l(s0, bits, 1);
-                    bits = __funnelshift_l(s1, bits, 1);
-                    smin = min3nan(smin, fabsf(__uint_as_float(s0)), fabsf(__uint_as_float(s1)));
-                    wmax = fmax3(wmax, fabsf(w0), fabsf(w1));
+        for (int t = t0, tl = 0; t < t1 && ok; ++t, ++tl) {
+            K3CLK(e0);
+            if (t >= tend) { advance(tp, F, t, f); tend = tp[f + 1]; }
+            if (f != cur_f) {
+                if (cur_f >= 0) {
+                    flush(cur_f);
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive(&h_free[fl & 1]);
                 }
-                // band at the group's largest |w| against the group's smallest |s|: covers every one of its tests
-                const float band = fmaf(fmaf(bc.c2, wmax, bc.c1), wmax, bc.c0);
-                fm |= (!(smin > band)) ? (1u << gq) : 0u;
-            }
-            return fm;
-        };
-        // the rest of a set's work once its 8 columns are evaluated: exact re-evaluation inside the band, word completion
-        auto finish_set = [&](uint32_t fm, int g, const uint32_t (&r)[24]) {
-            if (CALIB) {
+                cur_f = f; ++fl;
+                ok = __all_sync(0xffffffffu, wait_bar(&h_full[fl & 1], (uint32_t)(fl >> 1) & 1u, bad));
+                const float* fr = sFr + (fl & 1) * FR_FLOATS;
+                scf = fr[FR_SC];
 #pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    const int h = g * HG + 8 * j + c;
-                    const float4* mp = reinterpret_cast<const float4*>(sPf + h * 12);
-                    const float4 m0 = mp[0], m1 = mp[1], m2 = mp[2];
-                    const float M[12] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
-                    bool big2;
-                    const float sc = point_scale(X, Y, Z, big2);
-                    const float se = inlier_s(M, X, Y, Z, us, vs) * (sc * sc);
-                    const float xw = __uint_as_float(r[c]), yw = __uint_as_float(r[8 + c]), ww = __uint_as_float(r[16 + c]);
-                    const float dx = fmaf(-du, ww, xw), dy = fmaf(-dv, ww, yw);
-                    const float nq = ww * -fabsf(ww);
-                    const float sv = fmaf(dx, dx, fmaf(dy, dy, nq));
-                    const float band = fmaf(fmaf(bc.c2, fabsf(ww), bc.c1), fabsf(ww), bc.c0);
-                    const float ratio = fabsf(sv - se) / band;
-                    if (valid && ratio == ratio && band < 1e30f && fabsf(se) <= 0.25f * ww * ww) calmax = fmaxf(calmax, ratio);
-                    const bool inband = !(fabsf(sv) > band);
-                    if (valid && !inband && ((__float_as_uint(sv) ^ __float_as_uint(se)) >> 31)) ++nmis;
+                for (int mt = 0; mt < MT_MAX; ++mt) {
+                    hm[mt] = hyp_matrix(a, f, mt * TH + 32 * q + lane, fr[FR_U0], fr[FR_V0]);
+                    band[mt] = hyp_band(hm[mt], fr, a.tc_kappa);
                 }
             }
-            if (__any_sync(0xffffffffu, fm != 0u)) {
+            const int s = tl % NSTG;
+            const unsigned char* st = sP + s * STAGE_BYTES;
+            const ulonglong2* pinfo = reinterpret_cast<const ulonglong2*>(st + B_TILE_BYTES) + (CPW / 2) * j;
+            const float* pex = reinterpret_cast<const float*>(st + B_TILE_BYTES + PINFO_BYTES) + CPW * j;
+            K3CLK(e1);
+            K3ACC(0, e0, e1);
 #pragma unroll
-                for (int qd = 0; qd < 2; ++qd) {
-                    if (__any_sync(0xffffffffu, (fm >> qd) & 1u)) {
+            for (int mt = 0; mt < MT_MAX; ++mt) {
+                if (mt < MT && ok) {
+                    const int set = n % NSET;
+                    K3CLK(e2);
+                    ok = __all_sync(0xffffffffu, wait_bar(&acc_full[set], (uint32_t)(n / NSET) & 1u, bad));
+                    ++n;
+                    K3CLK(e3);
+                    K3ACC(1, e2, e3);
+                    tc::fence_after_sync();
+                    const uint32_t tb = tlane + (uint32_t)(set * SETC);
+                    const float bnd = band[mt];
+                    uint32_t bits = 0u;
+                    // evaluate 16 columns held in r = x[16] | y[16] | w[16] as two independent halves of 8 (verdict words,
+                    // minima); returns a 2-bit mask of the halves that hold a value inside the band
+                    auto eval16 = [&](const uint32_t (&r)[48], int ch) -> uint32_t {
+                        uint32_t b[2] = {0u, 0u};
+                        float smin[2] = {__int_as_float(0x7f800000), __int_as_float(0x7f800000)};
+#pragma unroll
+                        for (int pr = 0; pr < 4; ++pr) {
+#pragma unroll
+                            for (int hf = 0; hf < 2; ++hf) {
+                                const int c = 8 * hf + 2 * pr;
+                                const ulonglong2 pi = pinfo[8 * ch + 4 * hf + pr];      // (-du0, -du1), (-dv0, -dv1)
+                                const float w0 = __uint_as_float(r[32 + c]), w1 = __uint_as_float(r[32 + c + 1]);
+                                const f32x2 x2 = pack2u(r[c], r[c + 1]), y2 = pack2u(r[16 + c], r[16 + c + 1]), w2 = pack2u(r[32 + c], r[32 + c + 1]);
+                                const f32x2 dx2 = ffma2(pi.x, w2, x2), dy2 = ffma2(pi.y, w2, y2);
+                                const f32x2 nq2 = pack2(w0 * -fabsf(w0), w1 * -fabsf(w1));
+                                const f32x2 s2 = ffma2(dx2, dx2, ffma2(dy2, dy2, nq2));
+                                const uint32_t s0 = (uint32_t)s2, s1 = (uint32_t)(s2 >> 32);
+                                b[hf] = __funnelshift_l(s0, b[hf], 1);
+                                b[hf] = __funnelshift_l(s1, b[hf], 1);
+                                smin[hf] = min3nan(smin[hf], fabsf(__uint_as_float(s0)), fabsf(__uint_as_float(s1)));
+                            }
+                        }
+                        bits = (bits << 16) | (b[0] << 8) | b[1];
+                        return ((!(smin[0] > bnd)) ? 1u : 0u) | ((!(smin[1] > bnd)) ? 2u : 0u);
+                    };
+                    // half hf of chunk ch (8 columns; their verdicts are bits 15 - 8 hf .. 8 - 8 hf of `bits`) holds a value inside the
+                    // band for some hypothesis of the warp: find the columns, let the contract's own arithmetic decide them
+                    auto exact8 = [&](const uint32_t (&r)[48], int ch, int hf) {
                         ++nslow;
+                        uint32_t inb = 0u;
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const int c = 4 * qd + k, h = g * HG + 8 * j + c;
-                            const float4* mp = reinterpret_cast<const float4*>(sPf + h * 12);
-                            const float4 m0 = mp[0], m1 = mp[1], m2 = mp[2];
-                            const float M[12] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
-                            const uint32_t bit = __float_as_uint(inlier_s(M, X, Y, Z, us, vs)) >> 31;
-                            bits = (bits & ~(1u << (7 - c))) | (bit << (7 - c));
+                        for (int c8 = 0; c8 < 8; ++c8) {
+                            const int c = 8 * hf + c8;
+                            const float* pf = reinterpret_cast<const float*>(pinfo + 8 * ch + (c >> 1));
+                            const float ww = __uint_as_float(r[32 + c]);
+                            const float dx = fmaf(pf[c & 1], ww, __uint_as_float(r[c])), dy = fmaf(pf[2 + (c & 1)], ww, __uint_as_float(r[16 + c]));
+                            const float sv = fmaf(dx, dx, fmaf(dy, dy, ww * -fabsf(ww)));
+                            inb |= (!(fabsf(sv) > bnd)) ? (1u << c8) : 0u;
+                        }
+                        inb = __reduce_or_sync(0xffffffffu, inb);
+#pragma unroll 1
+                        while (inb) {
+                            const int c8 = __ffs(inb) - 1;
+                            inb &= inb - 1;
+                            const int col = 16 * ch + 8 * hf + c8;
+                            const uint32_t bit = __float_as_uint(inlier_s(hm[mt].m, pex[col], pex[TPN + col], pex[2 * TPN + col],
+                                                                          pex[3 * TPN + col], pex[4 * TPN + col])) >> 31;
+                            const int pos = 15 - 8 * hf - c8;
+                            bits = (bits & ~(1u << pos)) | (bit << pos);
+                        }
+                    };
+                    auto calib16 = [&](const uint32_t (&r)[48], int ch) {
+#pragma unroll 1
+                        for (int c = 0; c < 16; ++c) {
+                            const int col = 16 * ch + c;
+                            const float se = inlier_s(hm[mt].m, pex[col], pex[TPN + col], pex[2 * TPN + col], pex[3 * TPN + col], pex[4 * TPN + col]) * (scf * scf);
+                            const float* pf = reinterpret_cast<const float*>(pinfo + 8 * ch + (c >> 1));
+                            const float ndu = pf[c & 1], ndv = pf[2 + (c & 1)];
+                            float xw = 0.0f, yw = 0.0f, ww = 0.0f;
+#pragma unroll
+                            for (int k = 0; k < 16; ++k) if (k == c) { xw = __uint_as_float(r[k]); yw = __uint_as_float(r[16 + k]); ww = __uint_as_float(r[32 + k]); }
+                            const float dx = fmaf(ndu, ww, xw), dy = fmaf(ndv, ww, yw);
+                            const float sv = fmaf(dx, dx, fmaf(dy, dy, ww * -fabsf(ww)));
+                            const float ratio = fabsf(sv - se) / bnd;
+                            const bool real = ndu < 1.0e17f;
+                            if (real && ratio == ratio && bnd < 1e30f && fabsf(se) <= 0.25f * ww * ww) calmax = fmaxf(calmax, ratio);
+                            if (real && fabsf(sv) > bnd && ((__float_as_uint(sv) ^ __float_as_uint(se)) >> 31)) ++nmis;
+                        }
+                    };
+                    K3CLK(e4);
+                    ld16(tb, ra);
+#pragma unroll
+                    for (int ch = 0; ch < NCH; ++ch) {
+                        tc::tmem_ld_wait();
+                        if (ch + 1 < NCH) {
+                            if (ch & 1) ld16(tb + 16u * (ch + 1), ra); else ld16(tb + 16u * (ch + 1), rb);
+                        } else {
+                            tc::fence_before_sync();                               // the whole set is in registers
+                            __syncwarp();
+                            if (lane == 0) tc::mbar_arrive(&acc_free[set]);
+                        }
+                        const uint32_t fm = (ch & 1) ? eval16(rb, ch) : eval16(ra, ch);
+                        if (CALIB) { if (ch & 1) calib16(rb, ch); else calib16(ra, ch); }
+                        if (__any_sync(0xffffffffu, fm != 0u)) {
+#pragma unroll
+                            for (int hf = 0; hf < 2; ++hf)
+                                if (__any_sync(0xffffffffu, (fm >> hf) & 1u)) { if (ch & 1) exact8(rb, ch, hf); else exact8(ra, ch, hf); }
                         }
                     }
+                    cnt[mt] += __popc(bits);
+                    K3CLK(e5);
+                    K3ACC(3, e4, e5);
                 }
             }
-            if ((g & 3) == 3 || g == NG - 1) {                             // a verdict word is complete
-                bits <<= 8 * (3 - (g & 3));
-                const int c = bit_column_counts(valid ? bits : 0u, lane);
-                if (g >> 2) cnt[1] += c; else cnt[0] += c;
-                bits = 0u;
-            }
-        };
-        if (NS > 0) {
-            ok = __all_sync(0xffffffffu, wait_bar(&acc_full[0], 0u, bad));
-            tc::fence_after_sync();
-            tc::tmem_ld8(tlane, ra); tc::tmem_ld8(tlane + HG, ra + 8); tc::tmem_ld8(tlane + 2 * HG, ra + 16);
-        }
-        int g = 0, t = t0;
-        for (int n = 0; n < NS && ok; ++n) {
-            if (g == 0) {
-                // ---- a new tile: frame constants, this lane's point, its band
-                K3CLK(e0);
-                if (t >= tend) {                                           // (uniform) the next frame that has tiles
-                    advance(tp, F, t, f);
-                    tbeg = tp[f]; tend = tp[f + 1];
-                }
-                if (f != cur_f) {
-                    if (cur_f >= 0) {
-                        flush(cur_f);
-                        __syncwarp();
-                        if (lane == 0) tc::mbar_arrive(&b_free[fl & 1]);
-                    }
-                    cur_f = f; ++fl;
-                    ok = __all_sync(0xffffffffu, wait_bar(&b_full[fl & 1], (uint32_t)(fl >> 1) & 1u, bad));
-                    const float* bd = sBand + (fl & 1) * 8;
-                    u0 = bd[0]; v0 = bd[1]; A1 = bd[2]; A1c = bd[3]; A1w = bd[4]; Amax = bd[5];
-                    P = max(0, min(a.count[f], cap));
-                    sPf = sProj + (fl & 1) * HP * 12;
-                }
-                valid = (t - tbeg) * TP + 32 * q + lane < P;
-                X = valid ? nX : 0.0f; Y = valid ? nY : 0.0f; Z = valid ? nZ : 0.0f;
-                us = valid ? nU * a.inv_thr : 0.0f; vs = valid ? nV * a.inv_thr : 0.0f;
-                if (t + 1 < t1) {
-                    if (t + 1 < tend) fetch_point(t + 1 - tbeg, f);
-                    else { int f2 = f; advance(tp, F, t + 1, f2); fetch_point(t + 1 - tp[f2], f2); }
-                }
-                bool big;
-                const float sc = point_scale(X, Y, Z, big);
-                du = us - u0; dv = vs - v0;
-                ndu2 = pack2(-du, -du); ndv2 = pack2(-dv, -dv);
-                bc = band_consts(us, vs, du, dv, sc, A1, A1c, A1w, Amax, big, a.tc_kappa);
-                if (!valid) { bc.c2 = 0.0f; bc.c1 = 0.0f; bc.c0 = -1.0f; }     // padding lanes (all-zero rows) never ask for a re-evaluation
-                K3CLK(e1);
-                K3ACC(0, e0, e1);
-            }
-            K3CLK(e2);
-            tc::tmem_ld_wait();                                            // this set is in registers
-            tc::fence_before_sync();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&acc_free[n % NSET]);
-            K3CLK(e3);
-            const bool more = n + 1 < NS;
-            if (more) {
-                const int sn = (n + 1) % NSET;
-                ok = __all_sync(0xffffffffu, wait_bar(&acc_full[sn], (uint32_t)((n + 1) / NSET) & 1u, bad));
-                tc::fence_after_sync();
-            }
-            K3CLK(e4);
-            const uint32_t tn = tlane + (uint32_t)(((n + 1) % NSET) * SETC);
-            if (n & 1) {
-                if (more) { tc::tmem_ld8(tn, ra); tc::tmem_ld8(tn + HG, ra + 8); tc::tmem_ld8(tn + 2 * HG, ra + 16); }
-                const uint32_t fm = eval8(rb);
-                finish_set(fm, g, rb);
-            } else {
-                if (more) { tc::tmem_ld8(tn, rb); tc::tmem_ld8(tn + HG, rb + 8); tc::tmem_ld8(tn + 2 * HG, rb + 16); }
-                const uint32_t fm = eval8(ra);
-                finish_set(fm, g, ra);
-            }
-            K3CLK(e5);
-            K3ACC(2, e2, e3); K3ACC(1, e3, e4); K3ACC(3, e4, e5);
-            if (++g == NG) { g = 0; ++t; }
+            if (lane == 0) tc::mbar_arrive(&p_free[s]);                            // this warp is done with the stage's pixel / exact arrays
         }
-        if (cur_f >= 0) flush(cur_f);
-        if (PROF && warp == 0 && lane == 0)   // epilogue warp 0: [0] per-tile prologue, [1] waiting for the MMA, [2] TMEM loads, [3] arithmetic
+        if (cur_f >= 0) {
+            flush(cur_f);
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&h_free[fl & 1]);
+        }
+        if (PROF && warp == 0 && lane == 0)   // epilogue warp 0: [0] per-tile prologue, [1] waiting for the MMA, [3] loads + arithmetic
             for (int k = 0; k < 4; ++k) atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + k, (unsigned long long)prof[k]);
         nslow = __shfl_sync(0xffffffffu, nslow, 0);
         if (lane == 0 && nslow) atomicAdd(&a.tc_stats[1], nslow);
@@ -615,6 +581,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
 
 int pb_launch_score_tc(const ScoreArgs& a, int mode, cudaStream_t st) {
     static_assert(TC_SMEM <= 200 * 1024, "shared-memory plan");
+    static_assert(TPN == 64, "the epilogue's column split assumes 64-point tiles");
     cudaMemsetAsync(a.tc_stats, 0, PB_TC_STATS_BYTES, st);
     const int grid = pb_sm_count();
     if (mode == 1) {

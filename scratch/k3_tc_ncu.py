@@ -9,7 +9,7 @@ dev = torch.device("cuda", 0)
 inp = bench.build_inputs(torch, dev, 0, F)
 pts, count = ops.compact_map(inp["xyz"], inp["mask"], inp["extent"], inp["lfborder"], 1280)
 pr = ops.PtsRansac(F, 1280, ops.RansacConfig(), device=dev)
-ops.set_score_impl(sys.argv[2] if len(sys.argv) > 2 else "tc")
+ops.set_score_impl(sys.argv[2] if len(sys.argv) > 2 else "tc", float(sys.argv[3]) if len(sys.argv) > 3 else 1.0)
 for _ in range(3):
     pr(pts, count, inp["K4"])
 torch.cuda.synchronize()

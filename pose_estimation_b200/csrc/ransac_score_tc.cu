@@ -18,10 +18,11 @@
 //                two points).  A group of 8 points x 32 hypotheses whose smallest |s| is inside the band in which
 //                the tensor-core value and the contract's FP32 chain may disagree (per-hypothesis bound below) is
 //                re-evaluated with inlier_s itself -- so the counts equal the contract's, not approximately.
-//   pipeline     one persistent CTA per SM (two accumulator sets of 192 TMEM columns), 11 warps: 8 epilogue warps
-//                (TMEM lane quadrant x 32-column half; 32 tests per thread and hand-off, loads of the next 8 columns
-//                in flight under the evaluation of the current 8), the MMA issuer, a producer of point tiles and
-//                a producer of hypothesis operands (one frame ahead); hand-offs are mbarriers only.  CTAs take
+//   pipeline     one persistent CTA per SM (two accumulator sets of 192 TMEM columns), 19 warps: two groups of 8 epilogue
+//                warps (TMEM lane quadrant x 32-column half; 32 tests per thread and hand-off, loads of the next 8
+//                columns in flight under the evaluation of the current 8), each group bound to one accumulator set so
+//                that one group evaluates while the other's MMA is in flight; the MMA issuer, a producer of point tiles
+//                and a producer of hypothesis operands (one frame ahead); hand-offs are mbarriers only.  CTAs take
 //                equal ranges of the batch's 64-point tiles (prefix by the hypothesis kernel).
 //
 // Error bound (u = 2^-24; S = sum of the absolute values of the terms of a dot product, in the frame's scaled units):
@@ -45,9 +46,10 @@ constexpr int SETC = 3 * TPN;                 // accumulator columns of one set:
 constexpr int NSET = 2;
 constexpr int MT_MAX = 2;                     // H <= 256
 constexpr int NSTG = 6;                       // point-tile stages
-constexpr int EPI_WARPS = 8;
-constexpr int W_MMA = 8, W_PP = 9, W_PH = 10;
-constexpr int TC_THREADS = 11 * 32;
+constexpr int EPI_WARPS = 16;                 // two groups of 8: group g reads accumulator set g (M tile g when H > 128)
+constexpr int GRP_WARPS = 8;
+constexpr int W_MMA = 16, W_PP = 18, W_PH = 19;   // warps 16 and 17 issue the MMAs of accumulator set 0 and 1
+constexpr int TC_THREADS = 20 * 32;
 constexpr int A_COMP_BYTES = TH * 32;         // [kc 0..1][row][8 halves] of one (M tile, component)
 constexpr int A_FRAME_BYTES = MT_MAX * 3 * A_COMP_BYTES;
 constexpr int B_TILE_BYTES = TPN * 32;
@@ -55,7 +57,8 @@ constexpr int PINFO_BYTES = (TPN / 2) * 16;   // (-du0, -du1, -dv0, -dv1) per pa
 constexpr int PEXACT_BYTES = 5 * TPN * 4;     // X | Y | Z | us | vs as the contract reads them
 constexpr int STAGE_BYTES = B_TILE_BYTES + PINFO_BYTES + PEXACT_BYTES;
 constexpr int FR_FLOATS = 16;                 // frame constants: see the hypothesis-operand producer
-constexpr size_t TC_SMEM = (size_t)2 * A_FRAME_BYTES + (size_t)NSTG * STAGE_BYTES + 2 * FR_FLOATS * sizeof(float);
+constexpr int HP = MT_MAX * TH;               // hypothesis slots per frame buffer
+constexpr size_t TC_SMEM = (size_t)2 * A_FRAME_BYTES + (size_t)NSTG * STAGE_BYTES + 2 * FR_FLOATS * sizeof(float) + 2 * HP * 12 * sizeof(float);
 
 typedef unsigned long long f32x2;   // two packed binary32 values
 __device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
@@ -182,6 +185,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
     unsigned char* sA = smem_raw;                                              // [2 frames][MT][3 comps] hypothesis operands
     unsigned char* sP = sA + 2 * A_FRAME_BYTES;                                // [NSTG] point tile | pixel pairs | exact values
     float* sFr = reinterpret_cast<float*>(sP + NSTG * STAGE_BYTES);            // [2][FR_FLOATS]
+    float* sProj = sFr + 2 * FR_FLOATS;                                        // [2][HP][12] the contract's FP32 matrices
     __shared__ __align__(8) uint64_t p_full[NSTG], p_free[NSTG], h_full[2], h_free[2], acc_full[NSET], acc_free[NSET];
     __shared__ uint32_t tmem_base;
     __shared__ int s_bad;
@@ -196,9 +200,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
     const int MT = (H + TH - 1) / TH;
 
     if (tid == 0) {
-        for (int i = 0; i < NSTG; ++i) { tc::mbar_init(&p_full[i], 1); tc::mbar_init(&p_free[i], 1 + EPI_WARPS); }
+        for (int i = 0; i < NSTG; ++i) { tc::mbar_init(&p_full[i], 1); tc::mbar_init(&p_free[i], 2 + EPI_WARPS); }
         for (int i = 0; i < 2; ++i) { tc::mbar_init(&h_full[i], 1); tc::mbar_init(&h_free[i], EPI_WARPS + 1); }
-        for (int i = 0; i < NSET; ++i) { tc::mbar_init(&acc_full[i], 1); tc::mbar_init(&acc_free[i], EPI_WARPS); }
+        for (int i = 0; i < NSET; ++i) { tc::mbar_init(&acc_full[i], 1); tc::mbar_init(&acc_free[i], GRP_WARPS); }
         s_bad = 0;
         tc::fence_mbar_init();
     }
@@ -256,6 +260,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
             for (int h = lane; h < MT * TH; h += 32) {
                 const HypM hm = hyp_matrix(a, f, h, u0, v0);
                 const int mt = h / TH, row = h % TH;
+                float4* pd = reinterpret_cast<float4*>(sProj + ((size_t)fb * HP + h) * 12);
+                pd[0] = make_float4(hm.m[0], hm.m[1], hm.m[2], hm.m[3]);
+                pd[1] = make_float4(hm.m[4], hm.m[5], hm.m[6], hm.m[7]);
+                pd[2] = make_float4(hm.m[8], hm.m[9], hm.m[10], hm.m[11]);
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     const float* rw = c == 0 ? hm.c : c == 1 ? hm.c + 4 : hm.m + 8;
@@ -344,75 +352,72 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
             atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + 8, (unsigned long long)prof[0]);
             atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + 9, (unsigned long long)prof[1]);
         }
-    } else if (warp == W_MMA) {
-        // ===== MMA issuer: per point tile and M tile three MMAs (x | y | w) into the accumulator sets in turn
+    } else if (warp == W_MMA || warp == W_MMA + 1) {
+        // ===== MMA issuers: warp W_MMA + g issues the three MMAs (x | y | w) of accumulator set g -- M tile g of every point
+        // tile when H > 128, every second point tile otherwise.  Two issuers because a tcgen05.mma occupies its issuing
+        // thread for ~100 cycles whatever its size.
+        const int g = warp - W_MMA;
+        const int mt = MT == 2 ? g : 0;
         const uint32_t idesc = tc::idesc_f16_f32(TH, TPN);
-        int f = frame_of(tp, F, t0), cur_f = -1, fl = -1, n = 0;
+        int f = frame_of(tp, F, t0), cur_f = -1, fl = -1, k = 0;
         int tend = tp[f + 1];
         for (int t = t0, tl = 0; t < t1 && ok; ++t, ++tl) {
             if (t >= tend) { advance(tp, F, t, f); tend = tp[f + 1]; }
             K3CLK(c0);
             if (f != cur_f) {
                 cur_f = f; ++fl;
-                ok = wait_bar(&h_full[fl & 1], (uint32_t)(fl >> 1) & 1u, bad);
+                ok = __all_sync(0xffffffffu, wait_bar(&h_full[fl & 1], (uint32_t)(fl >> 1) & 1u, bad));
             }
             K3CLK(c1);
             const int s = tl % NSTG;
-            ok = __all_sync(0xffffffffu, wait_bar(&p_full[s], (uint32_t)(tl / NSTG) & 1u, bad) && ok);
-            K3CLK(c2);
-            K3ACC(0, c0, c1); K3ACC(1, c1, c2);
-            tc::fence_after_sync();
-            const uint64_t bd = tc::smem_desc(tc::smem_u32(sP + s * STAGE_BYTES), TPN * 16, 128);
-            for (int mt = 0; mt < MT && ok; ++mt, ++n) {
-                const int set = n % NSET, use = n / NSET;
-                K3CLK(c3);
-                if (use > 0) ok = __all_sync(0xffffffffu, wait_bar(&acc_free[set], (uint32_t)(use - 1) & 1u, bad));
+            const bool mine = MT == 2 || (tl & 1) == g;
+            if (mine) {
+                ok = __all_sync(0xffffffffu, wait_bar(&p_full[s], (uint32_t)(tl / NSTG) & 1u, bad) && ok);
+                K3CLK(c2);
+                K3ACC(0, c0, c1); K3ACC(1, c1, c2);
+                if (k > 0) ok = __all_sync(0xffffffffu, wait_bar(&acc_free[g], (uint32_t)(k - 1) & 1u, bad) && ok);
+                ++k;
                 K3CLK(c4);
-                K3ACC(2, c3, c4);
+                K3ACC(2, c2, c4);
                 tc::fence_after_sync();
                 if (lane == 0 && ok) {
+                    const uint64_t bd = tc::smem_desc(tc::smem_u32(sP + s * STAGE_BYTES), TPN * 16, 128);
 #pragma unroll
                     for (int c = 0; c < 3; ++c) {
                         const uint64_t ad = tc::smem_desc(tc::smem_u32(sA + (fl & 1) * A_FRAME_BYTES + (mt * 3 + c) * A_COMP_BYTES), TH * 16, 128);
-                        tc::mma_bf16(tmem + (uint32_t)(set * SETC + c * TPN), ad, bd, idesc, 0);
+                        tc::mma_bf16(tmem + (uint32_t)(g * SETC + c * TPN), ad, bd, idesc, 0);
                     }
-                    tc::mma_commit(&acc_full[set]);
+                    tc::mma_commit(&acc_full[g]);
+                    tc::mma_commit(&p_free[s]);
                 }
-                __syncwarp();
+            } else if (lane == 0) {
+                tc::mbar_arrive(&p_free[s]);
             }
-            if (lane == 0) tc::mma_commit(&p_free[s]);
             __syncwarp();
         }
-        if (PROF && lane == 0)        // [4] waiting for hypothesis operands, [5] for point tiles, [6] for a free accumulator set
-            for (int k = 0; k < 3; ++k) atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + 4 + k, (unsigned long long)prof[k]);
+        if (PROF && lane == 0 && g == 0)  // [4] waiting for hypothesis operands, [5] for point tiles, [6] for a free accumulator set
+            for (int i = 0; i < 3; ++i) atomicAdd(reinterpret_cast<unsigned long long*>(a.tc_stats + 4) + 4 + i, (unsigned long long)prof[i]);
     } else {
-        // ===== epilogue: warp = (TMEM lane quadrant q, column half j); thread = hypothesis 128 mt + 32 q + lane.
-        // Software pipeline over the warp's 32 columns of a set: two chunks of 16 (x | y | w: three tcgen05.ld.x16), the next
+        // ===== epilogue: warp = (group g, TMEM lane quadrant q, column half j); thread = hypothesis 128 mt + 32 q + lane.
+        // Group g owns accumulator set g: with two M tiles (H > 128) it is M tile g of every point tile, with one it is every
+        // second point tile -- so while a group waits for its next MMA the other one keeps the multiprocessor busy.
+        // Software pipeline over the warp's 32 columns of a set: four chunks of 8 (x | y | w: three tcgen05.ld.x8), the next
         // chunk's loads in flight under the evaluation of the current one.
         constexpr int CPW = TPN / 2;                         // columns per warp and component
-        constexpr int NCH = CPW / 16;                        // chunks of 16 columns per set
-        const int q = warp & 3, j = warp >> 2;
-        const uint32_t tlane = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(CPW * j);
+        constexpr int NCH = CPW / 8;                         // chunks per set
+        const int g = warp >> 3, q = warp & 3, j = (warp >> 2) & 1;
+        const int mt = MT == 2 ? g : 0;
+        const int hyp = mt * TH + 32 * q + lane;
+        const uint32_t tb = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * SETC + CPW * j);
         int f = frame_of(tp, F, t0), cur_f = -1, fl = -1;
         int tend = tp[f + 1];
-        int cnt[MT_MAX] = {0, 0};
-        int nslow = 0, nmis = 0;
-        float calmax = 0.0f;
-        HypM hm[MT_MAX];
-        float band[MT_MAX] = {0.0f, 0.0f};
-        float scf = 1.0f;
-        uint32_t ra[48], rb[48];
-        int n = 0;
+        int cnt = 0, nslow = 0, nmis = 0, k = 0;             // k: uses of this group's accumulator set so far
+        float calmax = 0.0f, bnd = 0.0f, scf = 1.0f;
+        const float* sPf = sProj;
+        uint32_t ra[24], rb[24];
         auto flush = [&](int ff) {
-#pragma unroll
-            for (int mt = 0; mt < MT_MAX; ++mt) {
-                const int h = mt * TH + 32 * q + lane;
-                if (h < H && cnt[mt] > 0) atomicAdd(&a.cnt_all[(size_t)ff * H + h], cnt[mt]);
-                cnt[mt] = 0;
-            }
-        };
-        auto ld16 = [&](uint32_t taddr, uint32_t (&r)[48]) {
-            tc::tmem_ld16p(taddr, r); tc::tmem_ld16p(taddr + TPN, r + 16); tc::tmem_ld16p(taddr + 2 * TPN, r + 32);
+            if (hyp < H && cnt > 0) atomicAdd(&a.cnt_all[(size_t)ff * H + hyp], cnt);
+            cnt = 0;
         };
         for (int t = t0, tl = 0; t < t1 && ok; ++t, ++tl) {
             K3CLK(e0);
@@ -427,11 +432,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
                 ok = __all_sync(0xffffffffu, wait_bar(&h_full[fl & 1], (uint32_t)(fl >> 1) & 1u, bad));
                 const float* fr = sFr + (fl & 1) * FR_FLOATS;
                 scf = fr[FR_SC];
-#pragma unroll
-                for (int mt = 0; mt < MT_MAX; ++mt) {
-                    hm[mt] = hyp_matrix(a, f, mt * TH + 32 * q + lane, fr[FR_U0], fr[FR_V0]);
-                    band[mt] = hyp_band(hm[mt], fr, a.tc_kappa);
-                }
+                sPf = sProj + ((size_t)(fl & 1) * HP + hyp) * 12;
+                const HypM hm = hyp_matrix(a, f, hyp, fr[FR_U0], fr[FR_V0]);
+                bnd = hyp_band(hm, fr, a.tc_kappa);
             }
             const int s = tl % NSTG;
             const unsigned char* st = sP + s * STAGE_BYTES;
@@ -439,112 +442,100 @@ __global__ void __launch_bounds__(TC_THREADS, 1) ransac_score_tc_kernel(ScoreArg
             const float* pex = reinterpret_cast<const float*>(st + B_TILE_BYTES + PINFO_BYTES) + CPW * j;
             K3CLK(e1);
             K3ACC(0, e0, e1);
+            if ((MT == 2 || (tl & 1) == g) && ok) {
+                K3CLK(e2);
+                ok = __all_sync(0xffffffffu, wait_bar(&acc_full[g], (uint32_t)k & 1u, bad));
+                ++k;
+                K3CLK(e3);
+                K3ACC(1, e2, e3);
+                tc::fence_after_sync();
+                uint32_t bits = 0u;
+                // evaluate 8 columns held in r = x[8] | y[8] | w[8]; returns true when a value is inside the band
+                auto eval8 = [&](const uint32_t (&r)[24], int ch) -> bool {
+                    float smin = __int_as_float(0x7f800000);
 #pragma unroll
-            for (int mt = 0; mt < MT_MAX; ++mt) {
-                if (mt < MT && ok) {
-                    const int set = n % NSET;
-                    K3CLK(e2);
-                    ok = __all_sync(0xffffffffu, wait_bar(&acc_full[set], (uint32_t)(n / NSET) & 1u, bad));
-                    ++n;
-                    K3CLK(e3);
-                    K3ACC(1, e2, e3);
-                    tc::fence_after_sync();
-                    const uint32_t tb = tlane + (uint32_t)(set * SETC);
-                    const float bnd = band[mt];
-                    uint32_t bits = 0u;
-                    // evaluate 16 columns held in r = x[16] | y[16] | w[16] as two independent halves of 8 (verdict words,
-                    // minima); returns a 2-bit mask of the halves that hold a value inside the band
-                    auto eval16 = [&](const uint32_t (&r)[48], int ch) -> uint32_t {
-                        uint32_t b[2] = {0u, 0u};
-                        float smin[2] = {__int_as_float(0x7f800000), __int_as_float(0x7f800000)};
-#pragma unroll
-                        for (int pr = 0; pr < 4; ++pr) {
-#pragma unroll
-                            for (int hf = 0; hf < 2; ++hf) {
-                                const int c = 8 * hf + 2 * pr;
-                                const ulonglong2 pi = pinfo[8 * ch + 4 * hf + pr];      // (-du0, -du1), (-dv0, -dv1)
-                                const float w0 = __uint_as_float(r[32 + c]), w1 = __uint_as_float(r[32 + c + 1]);
-                                const f32x2 x2 = pack2u(r[c], r[c + 1]), y2 = pack2u(r[16 + c], r[16 + c + 1]), w2 = pack2u(r[32 + c], r[32 + c + 1]);
-                                const f32x2 dx2 = ffma2(pi.x, w2, x2), dy2 = ffma2(pi.y, w2, y2);
-                                const f32x2 nq2 = pack2(w0 * -fabsf(w0), w1 * -fabsf(w1));
-                                const f32x2 s2 = ffma2(dx2, dx2, ffma2(dy2, dy2, nq2));
-                                const uint32_t s0 = (uint32_t)s2, s1 = (uint32_t)(s2 >> 32);
-                                b[hf] = __funnelshift_l(s0, b[hf], 1);
-                                b[hf] = __funnelshift_l(s1, b[hf], 1);
-                                smin[hf] = min3nan(smin[hf], fabsf(__uint_as_float(s0)), fabsf(__uint_as_float(s1)));
-                            }
-                        }
-                        bits = (bits << 16) | (b[0] << 8) | b[1];
-                        return ((!(smin[0] > bnd)) ? 1u : 0u) | ((!(smin[1] > bnd)) ? 2u : 0u);
-                    };
-                    // half hf of chunk ch (8 columns; their verdicts are bits 15 - 8 hf .. 8 - 8 hf of `bits`) holds a value inside the
-                    // band for some hypothesis of the warp: find the columns, let the contract's own arithmetic decide them
-                    auto exact8 = [&](const uint32_t (&r)[48], int ch, int hf) {
-                        ++nslow;
-                        uint32_t inb = 0u;
-#pragma unroll
-                        for (int c8 = 0; c8 < 8; ++c8) {
-                            const int c = 8 * hf + c8;
-                            const float* pf = reinterpret_cast<const float*>(pinfo + 8 * ch + (c >> 1));
-                            const float ww = __uint_as_float(r[32 + c]);
-                            const float dx = fmaf(pf[c & 1], ww, __uint_as_float(r[c])), dy = fmaf(pf[2 + (c & 1)], ww, __uint_as_float(r[16 + c]));
-                            const float sv = fmaf(dx, dx, fmaf(dy, dy, ww * -fabsf(ww)));
-                            inb |= (!(fabsf(sv) > bnd)) ? (1u << c8) : 0u;
-                        }
-                        inb = __reduce_or_sync(0xffffffffu, inb);
-#pragma unroll 1
-                        while (inb) {
-                            const int c8 = __ffs(inb) - 1;
-                            inb &= inb - 1;
-                            const int col = 16 * ch + 8 * hf + c8;
-                            const uint32_t bit = __float_as_uint(inlier_s(hm[mt].m, pex[col], pex[TPN + col], pex[2 * TPN + col],
-                                                                          pex[3 * TPN + col], pex[4 * TPN + col])) >> 31;
-                            const int pos = 15 - 8 * hf - c8;
-                            bits = (bits & ~(1u << pos)) | (bit << pos);
-                        }
-                    };
-                    auto calib16 = [&](const uint32_t (&r)[48], int ch) {
-#pragma unroll 1
-                        for (int c = 0; c < 16; ++c) {
-                            const int col = 16 * ch + c;
-                            const float se = inlier_s(hm[mt].m, pex[col], pex[TPN + col], pex[2 * TPN + col], pex[3 * TPN + col], pex[4 * TPN + col]) * (scf * scf);
-                            const float* pf = reinterpret_cast<const float*>(pinfo + 8 * ch + (c >> 1));
-                            const float ndu = pf[c & 1], ndv = pf[2 + (c & 1)];
-                            float xw = 0.0f, yw = 0.0f, ww = 0.0f;
-#pragma unroll
-                            for (int k = 0; k < 16; ++k) if (k == c) { xw = __uint_as_float(r[k]); yw = __uint_as_float(r[16 + k]); ww = __uint_as_float(r[32 + k]); }
-                            const float dx = fmaf(ndu, ww, xw), dy = fmaf(ndv, ww, yw);
-                            const float sv = fmaf(dx, dx, fmaf(dy, dy, ww * -fabsf(ww)));
-                            const float ratio = fabsf(sv - se) / bnd;
-                            const bool real = ndu < 1.0e17f;
-                            if (real && ratio == ratio && bnd < 1e30f && fabsf(se) <= 0.25f * ww * ww) calmax = fmaxf(calmax, ratio);
-                            if (real && fabsf(sv) > bnd && ((__float_as_uint(sv) ^ __float_as_uint(se)) >> 31)) ++nmis;
-                        }
-                    };
-                    K3CLK(e4);
-                    ld16(tb, ra);
-#pragma unroll
-                    for (int ch = 0; ch < NCH; ++ch) {
-                        tc::tmem_ld_wait();
-                        if (ch + 1 < NCH) {
-                            if (ch & 1) ld16(tb + 16u * (ch + 1), ra); else ld16(tb + 16u * (ch + 1), rb);
-                        } else {
-                            tc::fence_before_sync();                               // the whole set is in registers
-                            __syncwarp();
-                            if (lane == 0) tc::mbar_arrive(&acc_free[set]);
-                        }
-                        const uint32_t fm = (ch & 1) ? eval16(rb, ch) : eval16(ra, ch);
-                        if (CALIB) { if (ch & 1) calib16(rb, ch); else calib16(ra, ch); }
-                        if (__any_sync(0xffffffffu, fm != 0u)) {
-#pragma unroll
-                            for (int hf = 0; hf < 2; ++hf)
-                                if (__any_sync(0xffffffffu, (fm >> hf) & 1u)) { if (ch & 1) exact8(rb, ch, hf); else exact8(ra, ch, hf); }
-                        }
+                    for (int pr = 0; pr < 4; ++pr) {
+                        const int c = 2 * pr;
+                        const ulonglong2 pi = pinfo[4 * ch + pr];               // (-du0, -du1), (-dv0, -dv1)
+                        const float w0 = __uint_as_float(r[16 + c]), w1 = __uint_as_float(r[16 + c + 1]);
+                        const f32x2 x2 = pack2u(r[c], r[c + 1]), y2 = pack2u(r[8 + c], r[8 + c + 1]), w2 = pack2u(r[16 + c], r[16 + c + 1]);
+                        const f32x2 dx2 = ffma2(pi.x, w2, x2), dy2 = ffma2(pi.y, w2, y2);
+                        const f32x2 nq2 = pack2(w0 * -fabsf(w0), w1 * -fabsf(w1));
+                        const f32x2 s2 = ffma2(dx2, dx2, ffma2(dy2, dy2, nq2));
+                        const uint32_t s0 = (uint32_t)s2, s1 = (uint32_t)(s2 >> 32);
+                        bits = __funnelshift_l(s0, bits, 1);
+                        bits = __funnelshift_l(s1, bits, 1);
+                        smin = min3nan(smin, fabsf(__uint_as_float(s0)), fabsf(__uint_as_float(s1)));
                     }
-                    cnt[mt] += __popc(bits);
-                    K3CLK(e5);
-                    K3ACC(3, e4, e5);
+                    return !(smin > bnd);
+                };
+                // chunk ch (its verdicts are the low 8 bits of `bits`) holds a value inside the band for some hypothesis of the
+                // warp: find the columns, let the contract's own arithmetic decide them
+                auto exact8 = [&](const uint32_t (&r)[24], int ch) {
+                    ++nslow;
+                    uint32_t inb = 0u;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        const float* pf = reinterpret_cast<const float*>(pinfo + 4 * ch + (c >> 1));
+                        const float ww = __uint_as_float(r[16 + c]);
+                        const float dx = fmaf(pf[c & 1], ww, __uint_as_float(r[c])), dy = fmaf(pf[2 + (c & 1)], ww, __uint_as_float(r[8 + c]));
+                        const float sv = fmaf(dx, dx, fmaf(dy, dy, ww * -fabsf(ww)));
+                        inb |= (!(fabsf(sv) > bnd)) ? (1u << c) : 0u;
+                    }
+                    inb = __reduce_or_sync(0xffffffffu, inb);
+                    const float4 m0 = reinterpret_cast<const float4*>(sPf)[0], m1 = reinterpret_cast<const float4*>(sPf)[1],
+                                 m2 = reinterpret_cast<const float4*>(sPf)[2];
+                    const float M[12] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
+#pragma unroll 1
+                    while (inb) {
+                        const int c = __ffs(inb) - 1;
+                        inb &= inb - 1;
+                        const int col = 8 * ch + c;
+                        const uint32_t bit = __float_as_uint(inlier_s(M, pex[col], pex[TPN + col], pex[2 * TPN + col],
+                                                                      pex[3 * TPN + col], pex[4 * TPN + col])) >> 31;
+                        bits = (bits & ~(1u << (7 - c))) | (bit << (7 - c));
+                    }
+                };
+                auto calib8 = [&](const uint32_t (&r)[24], int ch) {
+                    const float4 m0 = reinterpret_cast<const float4*>(sPf)[0], m1 = reinterpret_cast<const float4*>(sPf)[1],
+                                 m2 = reinterpret_cast<const float4*>(sPf)[2];
+                    const float M[12] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        const int col = 8 * ch + c;
+                        const float se = inlier_s(M, pex[col], pex[TPN + col], pex[2 * TPN + col], pex[3 * TPN + col], pex[4 * TPN + col]) * (scf * scf);
+                        const float* pf = reinterpret_cast<const float*>(pinfo + 4 * ch + (c >> 1));
+                        const float ndu = pf[c & 1], ndv = pf[2 + (c & 1)];
+                        const float xw = __uint_as_float(r[c]), yw = __uint_as_float(r[8 + c]), ww = __uint_as_float(r[16 + c]);
+                        const float dx = fmaf(ndu, ww, xw), dy = fmaf(ndv, ww, yw);
+                        const float sv = fmaf(dx, dx, fmaf(dy, dy, ww * -fabsf(ww)));
+                        const float ratio = fabsf(sv - se) / bnd;
+                        const bool real = ndu < 1.0e17f;
+                        if (real && ratio == ratio && bnd < 1e30f && fabsf(se) <= 0.25f * ww * ww) calmax = fmaxf(calmax, ratio);
+                        if (real && fabsf(sv) > bnd && ((__float_as_uint(sv) ^ __float_as_uint(se)) >> 31)) ++nmis;
+                    }
+                };
+                K3CLK(e4);
+                tc::tmem_ld8(tb, ra); tc::tmem_ld8(tb + TPN, ra + 8); tc::tmem_ld8(tb + 2 * TPN, ra + 16);
+#pragma unroll
+                for (int ch = 0; ch < NCH; ++ch) {
+                    tc::tmem_ld_wait();
+                    if (ch + 1 < NCH) {
+                        const uint32_t tn = tb + 8u * (ch + 1);
+                        if (ch & 1) { tc::tmem_ld8(tn, ra); tc::tmem_ld8(tn + TPN, ra + 8); tc::tmem_ld8(tn + 2 * TPN, ra + 16); }
+                        else { tc::tmem_ld8(tn, rb); tc::tmem_ld8(tn + TPN, rb + 8); tc::tmem_ld8(tn + 2 * TPN, rb + 16); }
+                    } else {
+                        tc::fence_before_sync();                               // the whole set is in registers
+                        __syncwarp();
+                        if (lane == 0) tc::mbar_arrive(&acc_free[g]);
+                    }
+                    const bool flag = (ch & 1) ? eval8(rb, ch) : eval8(ra, ch);
+                    if (CALIB) { if (ch & 1) calib8(rb, ch); else calib8(ra, ch); }
+                    if (__any_sync(0xffffffffu, flag)) { if (ch & 1) exact8(rb, ch); else exact8(ra, ch); }
                 }
+                cnt += __popc(bits);
+                K3CLK(e5);
+                K3ACC(3, e4, e5);
             }
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&p_free[s]);                            // this warp is done with the stage's pixel / exact arrays

@@ -12,8 +12,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libposeb200.so")
-SOURCES = ["abi.cu", "cloud.cu", "compact.cu", "ransac.cu", "ransac_score.cu", "ransac_score_tc.cu", "knn.cu", "knn_tc.cu", "metrics.cu", "sim3.cu", "fps.cu", "bpnp.cu", "possloss.cu", "region.cu", "synthgen.cu", "probe.cu"]
-HEADERS = ["common.cuh", "p3p.cuh", "nn.cuh", "ransac_plan.h", "tc.cuh", os.path.join("..", "..", "include", "poseb200.h")]
+SOURCES = ["abi.cu", "cloud.cu", "compact.cu", "ransac.cu", "ransac_score.cu", "ransac_score_tc.cu", "ransac_score_mma.cu", "knn.cu", "knn_tc.cu", "metrics.cu", "sim3.cu", "fps.cu", "bpnp.cu", "possloss.cu", "region.cu", "synthgen.cu", "probe.cu"]
+HEADERS = ["common.cuh", "p3p.cuh", "nn.cuh", "ransac_plan.h", "tc.cuh", "score_tc_common.cuh", os.path.join("..", "..", "include", "poseb200.h")]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",

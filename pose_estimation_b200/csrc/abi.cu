@@ -43,7 +43,7 @@ float g_score_kappa = 1.0f;
 int pb_score_impl() { return g_score_impl; }
 float pb_score_tc_kappa() { return g_score_kappa; }
 extern "C" int pb_ransac_score_impl(int impl, float band_scale) {
-    PB_REQUIRE(impl >= 0 && impl <= 4, "pb_ransac_score_impl: impl=%d (0 automatic, 1 FP32 pipe, 2 tensor cores, 3 tensor cores + calibration)", impl);
+    PB_REQUIRE(impl >= 0 && impl <= 6, "pb_ransac_score_impl: impl=%d (0 automatic, 1 FP32 pipe, 2 tensor cores, 3 tensor cores + calibration)", impl);
     PB_REQUIRE(band_scale > 0.0f && band_scale <= 1024.0f, "pb_ransac_score_impl: band_scale out of range");
     g_score_impl = impl;
     g_score_kappa = band_scale;

@@ -419,12 +419,15 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     if (p.bal && reinterpret_cast<uintptr_t>(pts) % 16 != 0) p.bal = 0;     // the balanced kernel stages with 16-byte async copies
     sa.cnt_all = p.bal ? (hyp_counts ? hyp_counts : reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_cnt)) : nullptr;
     sa.prefix = p.bal ? reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_prefix) : nullptr;
-    // K3 on the tensor cores (ransac_score_tc.cu): when asked for (pb_ransac_score_impl), and by default for batches
-    // large enough to give every multiprocessor several 128-point tiles
+    // K3 with the projection on the tensor cores: the warp-level path (ransac_score_mma.cu: impl 5 / 6, and the automatic
+    // choice when PB_SCORE_MMA_DEFAULT) or tcgen05 + TMEM (ransac_score_tc.cu: impl 2 / 3 / 4)
     const int impl = pb_score_impl();
-    const bool use_tc = p.tc && p.bal && impl != 1 && (impl >= 2 || PB_SCORE_TC_DEFAULT);
+    const bool can_tc = p.tc && p.bal;
+    const bool use_tc = can_tc && impl >= 2 && impl <= 4;
+    const bool use_mma = can_tc && (impl == 5 || impl == 6 || (impl == 0 && PB_SCORE_MMA_DEFAULT));
     sa.tprefix = use_tc ? reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_tprefix) : nullptr;
-    sa.tc_stats = use_tc ? reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_tcstats) : nullptr;
+    sa.tc_stats = (use_tc || use_mma) ? reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_tcstats) : nullptr;
+    sa.fstats = use_mma ? reinterpret_cast<float*>(static_cast<char*>(ws) + p.off_fstats) : nullptr;
     sa.tc_kappa = pb_score_tc_kappa();
     if (use_tc) sa.prefix = nullptr;
     sa.cap = cap; sa.H = prm->n_hyp; sa.HS = p.HS; sa.Hs = p.Hs; sa.CH = p.CH; sa.PP = p.PP;

@@ -17,6 +17,7 @@ struct ScoreArgs {
     int32_t* tc_stats;               // tensor-core mode: [0] barrier timeout, [1] exact re-evaluations (groups of 4 tests x 32 lanes),
                                      // [2] calibration: largest observed |s_tc - s_fp32| / band as float bits, [3] verdicts that differ outside the band
     float tc_kappa;                  // tensor-core mode: multiplier of the re-evaluation band (1 = the derived bound)
+    float* fstats;                   // mma.sync mode: [F][8] frame constants (written by frame_stats_kernel before the scoring kernel)
     int cap, H, HS, Hs, CH, PP;      // Hs hypotheses per slice (power of two >= 32); PP point parts
     uint32_t frame0, seed_lo, seed_hi;
     float inv_thr;
@@ -29,7 +30,7 @@ struct Plan {
     int bal, bal_grid, bal_nhl;      // balanced scoring (see ransac_score_bal_kernel): CTAs of equal point ranges
     size_t smem_bal, off_cnt, off_prefix;
     int tc;                          // tensor-core scoring (ransac_score_tc.cu) is possible for this shape
-    size_t off_tprefix, off_tcstats;
+    size_t off_tprefix, off_tcstats, off_fstats;
 };
 
 // Hypotheses of a frame are cut into HS slices of Hs (power of two) so that few-frame launches
@@ -80,11 +81,12 @@ static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm, int sm
     }
     // tensor-core scoring: same accumulation target (cnt_all) as the balanced kernel, H <= 256 hypotheses per frame
     p.tc = (p.bal && H <= 256) ? 1 : 0;
-    p.off_tprefix = p.off_tcstats = p.total;
+    p.off_tprefix = p.off_tcstats = p.off_fstats = p.total;
     if (p.tc) {
         p.off_tprefix = (p.total + 255) / 256 * 256;
         p.off_tcstats = (p.off_tprefix + (size_t)(F + 1) * sizeof(int32_t) + 255) / 256 * 256;
-        p.total = p.off_tcstats + PB_TC_STATS_BYTES;
+        p.off_fstats = (p.off_tcstats + PB_TC_STATS_BYTES + 255) / 256 * 256;
+        p.total = p.off_fstats + (size_t)F * 8 * sizeof(float);
     }
     return p;
 }
@@ -94,9 +96,12 @@ int pb_launch_score(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st);
 // defined in ransac_score_tc.cu: K3 on the tensor cores (a.tprefix, a.tc_stats set; a.cnt_all initialised by the hypothesis kernel)
 int pb_launch_score_tc(const ScoreArgs& a, int mode /*0 product, 1 calibration, 2 clock breakdown*/, cudaStream_t st);
 // process-wide choice of the scoring kernel (abi: pb_ransac_score_impl): 0 = automatic, 1 = FP32 pipe only, 2 = tensor cores
-// whenever the shape allows, 3 = tensor cores with the calibration pass (slow; fills tc_stats[2..3]), 4 = tensor cores with the clock breakdown
+// whenever the shape allows, 3 = tensor cores with the calibration pass (slow; fills tc_stats[2..3]), 4 = tensor cores with the clock breakdown,
+// 5 = the warp-level tensor path (mma.sync) whenever the shape allows, 6 = the same with the calibration pass
+// defined in ransac_score_mma.cu: K3 with the projection on the warp-level tensor path (a.prefix, a.fstats, a.tc_stats set)
+int pb_launch_score_mma(const ScoreArgs& a, int calib, cudaStream_t st);
 int pb_score_impl();
 float pb_score_tc_kappa();
-#ifndef PB_SCORE_TC_DEFAULT
-#define PB_SCORE_TC_DEFAULT 0    /* 1: the automatic choice (impl 0) takes the tensor-core kernel whenever the plan allows */
+#ifndef PB_SCORE_MMA_DEFAULT
+#define PB_SCORE_MMA_DEFAULT 0   /* 1: the automatic choice (impl 0) takes the mma.sync kernel whenever the plan allows */
 #endif

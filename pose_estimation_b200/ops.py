@@ -217,7 +217,7 @@ def pnp_ransac_pts(pts, count, K4, cfg: RansacConfig | None = None, frame0=0, sa
     return out
 
 
-_SCORE_IMPL = {"auto": 0, "fp32": 1, "tc": 2, "tc_calib": 3, "tc_prof": 4}
+_SCORE_IMPL = {"auto": 0, "fp32": 1, "tc": 2, "tc_calib": 3, "tc_prof": 4, "mma": 5, "mma_calib": 6}
 
 
 def set_score_impl(impl="auto", band_scale=1.0):

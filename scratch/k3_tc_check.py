@@ -38,12 +38,14 @@ def main():
     cfg = ops.RansacConfig()
     res = {"F": F, "cap": cap, "n_hyp": cfg.n_hyp, "thresh_px": cfg.thresh_px, "points": int(count.sum())}
     outs = {}
-    for impl in ("fp32", "tc"):
+    TC = os.environ.get("K3_IMPL", "tc")                      # "tc" (tcgen05) or "mma" (mma.sync)
+    for impl in ("fp32", TC):
         ops.set_score_impl(impl)
         o = ops.pnp_ransac_pts(pts, count, inp["K4"], cfg, want_counts=True)
         torch.cuda.synchronize()
         outs[impl] = {k: v.clone() for k, v in o.items()}
-    a, b = outs["fp32"], outs["tc"]
+    a, b = outs["fp32"], outs[TC]
+    res["impl"] = TC
     res["counts_equal"] = bool(torch.equal(a["hyp_counts"], b["hyp_counts"]))
     res["counts_diff"] = int((a["hyp_counts"] != b["hyp_counts"]).sum())
     if res["counts_diff"]:
@@ -53,24 +55,25 @@ def main():
     res["pose_equal"] = bool(torch.equal(a["R"], b["R"]) and torch.equal(a["t"], b["t"]))
     # persistent launcher: stats and timing
     pr = ops.PtsRansac(F, cap, cfg, device=dev)
-    for impl in ("fp32", "tc"):
+    for impl in ("fp32", TC):
         ops.set_score_impl(impl)
         res[f"stage_ms_{impl}"] = stage_ms(lambda: pr(pts, count, inp["K4"]))
-        if impl == "tc":
+        if impl == TC:
             res["tc_stats"] = ops.ransac_tc_stats(pr.ws, F, cap, cfg)
-    for kappa in (0.25, 0.0625):
-        ops.set_score_impl("tc", kappa)
+    for kappa in (0.5, 0.25, 0.0625):
+        ops.set_score_impl(TC, kappa)
         o = ops.pnp_ransac_pts(pts, count, inp["K4"], cfg, want_counts=True)
         torch.cuda.synchronize()
         res[f"kappa_{kappa}"] = dict(counts_diff=int((a["hyp_counts"] != o["hyp_counts"]).sum()),
                                      stage_ms=stage_ms(lambda: pr(pts, count, inp["K4"])),
                                      stats=ops.ransac_tc_stats(pr.ws, F, cap, cfg))
-    ops.set_score_impl("tc_calib", 1.0)
+    ops.set_score_impl(TC + "_calib", 1.0)
     pr(pts, count, inp["K4"])
     res["calib"] = ops.ransac_tc_stats(pr.ws, F, cap, cfg)
-    ops.set_score_impl("tc_prof", 1.0)
-    pr(pts, count, inp["K4"])
-    res["prof"] = ops.ransac_tc_stats(pr.ws, F, cap, cfg)["clocks"]
+    if TC == "tc":
+        ops.set_score_impl("tc_prof", 1.0)
+        pr(pts, count, inp["K4"])
+        res["prof"] = ops.ransac_tc_stats(pr.ws, F, cap, cfg)["clocks"]
     ops.set_score_impl("auto", 1.0)
     print(json.dumps(res))
     if out_path:

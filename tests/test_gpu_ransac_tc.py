@@ -1,5 +1,6 @@
-"""K3 on the tensor cores (csrc/ransac_score_tc.cu, opt-in through pb_ransac_score_impl) against the FP32-pipe
-kernels and the C oracle: every integer (inlier counts of every hypothesis, chosen hypothesis, bitmap, status) and the
+"""K3 with the projection on the tensor cores -- csrc/ransac_score_tc.cu (tcgen05 + TMEM, impl "tc") and
+csrc/ransac_score_mma.cu (warp-level mma.sync, impl "mma"), both opt-in through pb_ransac_score_impl -- against the
+FP32-pipe kernels and the C oracle: every integer (inlier counts of every hypothesis, chosen hypothesis, bitmap, status) and the
 pose must be IDENTICAL -- the tensor-core values only pre-sort the tests, the contract's arithmetic decides inside the
 band.  Shapes: two M tiles (256 hypotheses), one (96), a partial second one (200); ragged / empty / too-small /
 non-finite frames; another threshold; a narrower band must still be exact on these data, and the kernel must report
@@ -32,16 +33,16 @@ def _t(a, dev):
     return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
 
 
-def _both(pts, cnt, K4, cfg, dev, frame0=0, band_scale=1.0):
+def _both(pts, cnt, K4, cfg, dev, frame0=0, band_scale=1.0, tc="tc"):
     F, _, cap = pts.shape
     outs = {}
     try:
-        for impl in ("fp32", "tc"):
+        for impl in ("fp32", tc):
             ops.set_score_impl(impl, band_scale)
             pr = ops.PtsRansac(F, cap, cfg, device=dev)            # its workspace holds the kernel's statistics
             o = ops.pnp_ransac_pts(_t(pts, dev), _t(cnt, dev), _t(K4, dev), cfg, frame0=frame0, want_counts=True, want_bitmap=True)
             outs[impl] = {k: v.cpu().numpy() for k, v in o.items()}
-            if impl == "tc":
+            if impl == tc:
                 pr(_t(pts, dev), _t(cnt, dev), _t(K4, dev), frame0=frame0)
                 st = ops.ransac_tc_stats(pr.ws, F, cap, cfg)
                 assert st is not None, "the shape did not take the tensor-core kernel"
@@ -49,8 +50,9 @@ def _both(pts, cnt, K4, cfg, dev, frame0=0, band_scale=1.0):
                 outs["stats"] = st
     finally:
         ops.set_score_impl("auto", 1.0)
+    outs["tc"] = outs[tc]
     for k in KEYS:
-        assert np.array_equal(outs["fp32"][k], outs["tc"][k], equal_nan=True), k
+        assert np.array_equal(outs["fp32"][k], outs["tc"][k], equal_nan=True), (tc, k)
     return outs
 
 
@@ -60,13 +62,14 @@ def _frames(F):
     return (base * ((F + 15) // 16))[:F]
 
 
-@pytest.mark.parametrize("n_hyp,F,thr", [(256, 320, 1.0), (96, 300, 1.0), (200, 304, 3.0)])
-def test_tc_scoring_equals_fp32_and_oracle(cref, dev, n_hyp, F, thr):
+@pytest.mark.parametrize("tc", ["tc", "mma"])
+@pytest.mark.parametrize("n_hyp,F,thr", [(256, 320, 1.0), (96, 300, 1.0), (200, 304, 3.0), (40, 300, 1.0)])
+def test_tc_scoring_equals_fp32_and_oracle(cref, dev, n_hyp, F, thr, tc):
     cap = 1280
     pts, cnt = pack_pts(_frames(F), cap)
     K4 = np.tile(synth.LINEMOD_K4, (F, 1))
     cfg = ops.RansacConfig(n_hyp=n_hyp, thresh_px=thr, lo_rounds=1)
-    outs = _both(pts, cnt, K4, cfg, dev, frame0=5)
+    outs = _both(pts, cnt, K4, cfg, dev, frame0=5, tc=tc)
     assert outs["stats"]["reevaluated_groups"] > 0                 # the band is exercised
     for f in (0, 3, 5, 6, 9, 12, 17, F - 1):
         if cnt[f] < 4:
@@ -77,7 +80,8 @@ def test_tc_scoring_equals_fp32_and_oracle(cref, dev, n_hyp, F, thr):
         assert outs["tc"]["best_hyp"][f] == o["best_hyp"] and outs["tc"]["n_inl"][f] == o["n_inl"], f
 
 
-def test_tc_scoring_ragged_and_degenerate_frames(dev):
+@pytest.mark.parametrize("tc", ["tc", "mma"])
+def test_tc_scoring_ragged_and_degenerate_frames(dev, tc):
     cap = 1280
     base = [synth.compact_points(s) for s in synth.make_batch_sparse(0x5EED, 2, 6)]
     frames = [base[0][:, :n].copy() for n in (0, 1, 3, 4, 5, 31, 32, 33, 63, 64, 65, 127, 128, 129)]
@@ -98,10 +102,11 @@ def test_tc_scoring_ragged_and_degenerate_frames(dev):
     pts, cnt = pack_pts(frames, cap)
     K4 = np.tile(synth.LINEMOD_K4, (len(frames), 1))
     for n_hyp in (256, 64):
-        _both(pts, cnt, K4, ops.RansacConfig(n_hyp=n_hyp), dev, frame0=100)
+        _both(pts, cnt, K4, ops.RansacConfig(n_hyp=n_hyp), dev, frame0=100, tc=tc)
 
 
-def test_tc_scoring_narrower_band_still_exact_and_cheaper(dev):
+@pytest.mark.parametrize("tc", ["tc", "mma"])
+def test_tc_scoring_narrower_band_still_exact_and_cheaper(dev, tc):
     """Half the derived band is still exact on these data (the calibration pass measures the largest deviation at about
     an eighth of the bound) and re-evaluates fewer groups."""
     cap = 1280
@@ -109,11 +114,11 @@ def test_tc_scoring_narrower_band_still_exact_and_cheaper(dev):
     pts, cnt = pack_pts(_frames(F), cap)
     K4 = np.tile(synth.LINEMOD_K4, (F, 1))
     cfg = ops.RansacConfig()
-    full = _both(pts, cnt, K4, cfg, dev)["stats"]["reevaluated_groups"]
-    half = _both(pts, cnt, K4, cfg, dev, band_scale=0.5)["stats"]["reevaluated_groups"]
+    full = _both(pts, cnt, K4, cfg, dev, tc=tc)["stats"]["reevaluated_groups"]
+    half = _both(pts, cnt, K4, cfg, dev, band_scale=0.5, tc=tc)["stats"]["reevaluated_groups"]
     assert half < full
     try:
-        ops.set_score_impl("tc_calib", 1.0)
+        ops.set_score_impl(tc + "_calib", 1.0)
         pr = ops.PtsRansac(F, cap, cfg, device=dev)
         pr(_t(pts, dev), _t(cnt, dev), _t(K4, dev))
         st = ops.ransac_tc_stats(pr.ws, F, cap, cfg)

@@ -252,6 +252,44 @@ def build_inputs(torch, dev, first_frame, n_frames):
     return out
 
 
+def k3_alternatives(torch, dev, inp, cfg, cap, steps):
+    """The scoring stage (K3) of the same batch through the two tensor-core formulations kept in the library beside the
+    FP32-pipe kernel the step uses (profiles/r02_k3_tc.md): stage time from the library's own CUDA events, and whether
+    every integer and the pose equal the FP32-pipe kernel's."""
+    import ctypes as C
+    from pose_estimation_b200 import _lib, ops
+    lib = _lib.load()
+    pts, count = ops.compact_map(inp["xyz"], inp["mask"], inp["extent"], inp["lfborder"], cap)
+    F = pts.shape[0]
+    out, ref = {}, None
+    try:
+        for impl in ("fp32", "tc", "mma"):
+            ops.set_score_impl(impl)
+            o = ops.pnp_ransac_pts(pts, count, inp["K4"], cfg, want_counts=True)
+            pr = ops.PtsRansac(F, cap, cfg, device=dev)
+            for _ in range(3):
+                pr(pts, count, inp["K4"])
+            torch.cuda.synchronize()
+            lib.pb_stage_timing(1)
+            for _ in range(steps):
+                pr(pts, count, inp["K4"])
+            ms3, ncalls = (C.c_float * 3)(), C.c_int(0)
+            lib.pb_stage_timing_read(ms3, C.byref(ncalls))
+            lib.pb_stage_timing(0)
+            if ref is None:
+                ref = o
+            same = all(bool(torch.equal(o[k], ref[k])) for k in ("hyp_counts", "best_hyp", "n_inl", "status", "R", "t"))
+            out[impl] = {"score_stage_ms": round(float(ms3[1]), 5), "identical_to_fp32": same}
+            if impl != "fp32":
+                st = ops.ransac_tc_stats(pr.ws, F, cap, cfg)
+                out[impl].update(barrier_timeouts=st["timeout"], reevaluated_blocks=st["reevaluated_groups"])
+    finally:
+        ops.set_score_impl("auto")
+    out["note"] = ("fp32 = ransac_score_bal_kernel (what the step runs); tc = tcgen05 + TMEM (csrc/ransac_score_tc.cu); "
+                   "mma = warp-level mma.sync (csrc/ransac_score_mma.cu, its frame-constants kernel included); band x1")
+    return out
+
+
 def ours_arm(args):
     import torch
     import torch.distributed as dist
@@ -534,6 +572,7 @@ def ours_arm(args):
             cargs = types.SimpleNamespace(iters=5, c3_batch=4096, c4_frames=256, cpu=not args.no_cpu_baseline)
             with contextlib.redirect_stdout(io.StringIO()):
                 other = {"C1": bench_configs.c1(cargs, dev), "C3": bench_configs.c3(cargs, dev), "C4": bench_configs.c4(cargs, dev)}
+            other["K3_tensor_core_alternatives"] = k3_alternatives(torch, dev, inp, cfg, CAP, args.steps)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_clean / args.steps, "higher_is_better": True,

@@ -15,12 +15,14 @@
 //   operands    as in ransac_score_tc.cu: every FP32 value split into two FP16 (the constant column into three), the
 //               four cross products of a coordinate along K = 16; points scaled by a power of two per frame, x / y rows
 //               centred on one of the frame's pixels.  A = 16 hypotheses x K (fragments in registers for the whole
-//               frame segment: 4 row blocks x {x, y, w} per warp = 64 hypotheses), B = K x 8 points (two 32-bit
-//               shared-memory loads per thread and group of 8 points).
+//               frame segment: 2 row blocks x {x, y, w} per warp = 32 hypotheses, 8 warps = the frame's 256), B = K x 8
+//               points (two 32-bit shared-memory loads per thread and group of 8 points).
 //   epilogue    a thread holds rows g, g + 8 and columns 2t, 2t + 1 of every 16 x 8 tile: per row the two points go
 //               through packed FP32x2 FMAs (dx, dy, s as in the contract), the sign bits are pushed into the row's
-//               verdict word, min |s| is kept per row.  After 4 groups (8 tests per row) a row whose min |s| is inside
-//               the hypothesis' band (score_tc_common.cuh::hyp_band) is re-evaluated with inlier_s itself.
+//               verdict word; a (row, group) whose smaller |s| is inside the hypothesis' band
+//               (score_tc_common.cuh::hyp_band) is re-evaluated with inlier_s itself after the block of 4 groups.
+//   measured    0.162 ms with the derived band, 0.148 ms with 1/16 of it, against 0.150 ms for the FP32-pipe kernel
+//               (profiles/r02_k3_tc.md): level, not ahead, so it is opt-in.
 //   work        CTAs take equal ranges of the batch's concatenated point list exactly as the balanced FP32 kernel does
 //               (same prefix, same asynchronous staging of <= 256 points of one frame into two buffers); a conversion
 //               pass per sub-chunk writes the FP16 rows and the negated centred pixel coordinates.
@@ -29,7 +31,6 @@
 namespace {
 using namespace k3tc;
 
-constexpr int MT_ = 128;             // threads per CTA: 4 warps
 constexpr int SUBM = PB_BAL_SUB;     // points per staging buffer
 
 __device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
@@ -43,10 +44,12 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // D = A (16 x 16, row) * B (16 x 8, col), FP16 in, FP32 out, C = 0
-__device__ __forceinline__ void hmma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
-                 : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
-                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "f"(0.0f));
+__device__ __forceinline__ void hmma16816(uint32_t (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    float d0, d1, d2, d3;
+    asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+        : "=f"(d0), "=f"(d1), "=f"(d2), "=f"(d3)
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "f"(0.0f));
+    d[0] = __float_as_uint(d0); d[1] = __float_as_uint(d1); d[2] = __float_as_uint(d2); d[3] = __float_as_uint(d3);
 }
 
 // One warp per frame: the constants the scoring kernel needs of a frame -> fstats[f][0..7] (FR_* of score_tc_common.cuh):
@@ -87,13 +90,21 @@ __global__ void __launch_bounds__(128) frame_stats_kernel(ScoreArgs a) {
     }
 }
 
-// NRB row blocks of 16 hypotheses per warp: H <= 64 * NRB.  CALIB: every test also evaluated exactly (tc_stats[2..3]).
-template <int NRB, bool CALIB>
-__global__ void __launch_bounds__(MT_, 4) ransac_score_mma_kernel(ScoreArgs a) {
-    __shared__ __align__(16) float sbuf[2][5][SUBM];             // X | Y | Z | U | V as they lie in the correspondence list
-    __shared__ __align__(16) uint32_t srow[2][SUBM][8];          // FP16 operand row of a point: 16 halves
-    __shared__ __align__(16) float snd[2][2][SUBM];              // -(us - u0) | -(vs - v0)
-    __shared__ __align__(16) float sproj[64 * NRB * 4 / 4][12];  // the contract's matrices of the CTA's hypotheses (one frame)
+// One warp = 32 hypotheses (two row blocks of 16), one CTA = every hypothesis of the frame: 32 * NW threads, NW = ceil(H / 32)
+// <= 8.  CALIB: every test also evaluated exactly (tc_stats[2..3]).
+constexpr int NRB = 2;
+constexpr int MMA_OFF_ROW = 2 * 5 * SUBM * 4, MMA_OFF_ND = MMA_OFF_ROW + 2 * SUBM * 32, MMA_OFF_PROJ = MMA_OFF_ND + 2 * 2 * SUBM * 4;
+constexpr int mma_smem_bytes(int nw) { return MMA_OFF_PROJ + 32 * nw * (48 + 96 + 4); }
+template <int NW, bool CALIB>
+__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 3 : NW >= 4 ? 6 : 12)) ransac_score_mma_kernel(ScoreArgs a) {
+    constexpr int NT = 32 * NW;
+    extern __shared__ __align__(16) unsigned char mma_smem[];
+    float (*sbuf)[5][SUBM] = reinterpret_cast<float (*)[5][SUBM]>(mma_smem);                       // [2] X | Y | Z | U | V as in the list
+    uint32_t (*srow)[SUBM][8] = reinterpret_cast<uint32_t (*)[SUBM][8]>(mma_smem + MMA_OFF_ROW);   // [2] FP16 operand row of a point
+    float (*snd)[2][SUBM] = reinterpret_cast<float (*)[2][SUBM]>(mma_smem + MMA_OFF_ND);           // [2] -(us - u0) | -(vs - v0)
+    float (*sproj)[12] = reinterpret_cast<float (*)[12]>(mma_smem + MMA_OFF_PROJ);                 // [NT] the contract's matrices
+    uint32_t (*sfrag)[3][8] = reinterpret_cast<uint32_t (*)[3][8]>(mma_smem + MMA_OFF_PROJ + NT * 48);   // [NT] FP16 rows x' | y' | w
+    float* sband = reinterpret_cast<float*>(mma_smem + MMA_OFF_PROJ + NT * (48 + 96));             // [NT]
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const int F = a.F, H = a.H;
     const int* __restrict__ prefix = a.prefix;
@@ -124,7 +135,7 @@ __global__ void __launch_bounds__(MT_, 4) ransac_score_mma_kernel(ScoreArgs a) {
     auto stage = [&](int b, int sf, int sp0, int sn) {
         const int P = max(0, min(a.count[sf], a.cap));
         const float* base = a.pts + (size_t)sf * 5 * a.cap + sp0;
-        for (int e = tid; e < (sn >> 2) * 5; e += MT_) {
+        for (int e = tid; e < (sn >> 2) * 5; e += NT) {
             const int arr = e / (sn >> 2), i = (e - arr * (sn >> 2)) << 2;
             float* dst = &sbuf[b][arr][i];
             const float* src = base + (size_t)arr * a.cap + i;
@@ -140,8 +151,8 @@ __global__ void __launch_bounds__(MT_, 4) ransac_score_mma_kernel(ScoreArgs a) {
         cp_async_commit();
     };
 
-    // per-thread state of the current frame: this thread's rows are hypotheses hbase + 16 rb + g (+ 8)
-    const int hbase = warp * 16 * NRB;
+    // per-thread state of the current frame: this thread's four rows are hypotheses hbase + 16 rb + 8 hr + g
+    const int hbase = warp * 32;
     uint32_t A[NRB][3][4];
     float bandv[NRB][2];
     int cnt[NRB][2];
@@ -165,45 +176,50 @@ __global__ void __launch_bounds__(MT_, 4) ransac_score_mma_kernel(ScoreArgs a) {
                 cnt[rb][hr] = 0;
             }
     };
+    // thread tid converts hypothesis tid of the frame (matrix, band, FP16 rows) into shared memory; then every thread
+    // picks the fragment words of its four rows: K columns (2t, 2t+1) and (2t+8, 2t+9) of
+    // (m0h,m0h,m0m,m0m, m1h,m1h,m1m,m1m | m2h,m2h,m2m,m2m, m3h,m3m,m3l,0)
     auto load_frame = [&](int ff) {
         const float* fr = a.fstats + (size_t)ff * 8;
         u0 = fr[FR_U0]; v0 = fr[FR_V0]; sc = fr[FR_SC];
-        __syncthreads();                                           // nobody is still reading the previous frame's matrices
+        __syncthreads();                                           // nobody is still reading the previous frame's rows
+        {
+            const HypM hm = hyp_matrix(a, ff, tid, u0, v0);
+            sband[tid] = hyp_band(hm, fr, a.tc_kappa);
+            float4* pd = reinterpret_cast<float4*>(sproj[tid]);
+            pd[0] = make_float4(hm.m[0], hm.m[1], hm.m[2], hm.m[3]);
+            pd[1] = make_float4(hm.m[4], hm.m[5], hm.m[6], hm.m[7]);
+            pd[2] = make_float4(hm.m[8], hm.m[9], hm.m[10], hm.m[11]);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const float* rw = c == 0 ? hm.c : c == 1 ? hm.c + 4 : hm.m + 8;
+                __half h0, m0, h1, m1, h2, m2, h3, m3, l3;
+                split2h(rw[0], h0, m0); split2h(rw[1], h1, m1); split2h(rw[2], h2, m2);
+                {
+                    const float v = rw[3];
+                    h3 = __float2half_rn(v);
+                    const float r1 = v - __half2float(h3);
+                    m3 = __float2half_rn(r1);
+                    l3 = __float2half_rn(r1 - __half2float(m3));
+                }
+                uint4* d = reinterpret_cast<uint4*>(sfrag[tid][c]);
+                d[0] = make_uint4(pkh(h0, h0), pkh(m0, m0), pkh(h1, h1), pkh(m1, m1));
+                d[1] = make_uint4(pkh(h2, h2), pkh(m2, m2), pkh(h3, m3), pkh(l3, __float2half_rn(0.0f)));
+            }
+        }
+        __syncthreads();
 #pragma unroll
         for (int rb = 0; rb < NRB; ++rb)
 #pragma unroll
             for (int hr = 0; hr < 2; ++hr) {
-                const int hl = 16 * rb + 8 * hr + g;
-                const HypM hm = hyp_matrix(a, ff, hbase + hl, u0, v0);
-                bandv[rb][hr] = hyp_band(hm, fr, a.tc_kappa);
-                if (t == 0) {
-                    float4* pd = reinterpret_cast<float4*>(sproj[hbase + hl]);
-                    pd[0] = make_float4(hm.m[0], hm.m[1], hm.m[2], hm.m[3]);
-                    pd[1] = make_float4(hm.m[4], hm.m[5], hm.m[6], hm.m[7]);
-                    pd[2] = make_float4(hm.m[8], hm.m[9], hm.m[10], hm.m[11]);
-                }
-                // fragment registers of this row: K columns (2t, 2t+1) and (2t+8, 2t+9) of
-                // (m0h,m0h,m0m,m0m, m1h,m1h,m1m,m1m | m2h,m2h,m2m,m2m, m3h,m3m,m3l,0)
+                const int hl = hbase + 16 * rb + 8 * hr + g;
+                bandv[rb][hr] = sband[hl];
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
-                    const float* rw = c == 0 ? hm.c : c == 1 ? hm.c + 4 : hm.m + 8;
-                    __half h0, m0, h1, m1, h2, m2, h3, m3, l3;
-                    split2h(rw[0], h0, m0); split2h(rw[1], h1, m1); split2h(rw[2], h2, m2);
-                    {
-                        const float v = rw[3];
-                        h3 = __float2half_rn(v);
-                        const float r1 = v - __half2float(h3);
-                        m3 = __float2half_rn(r1);
-                        l3 = __float2half_rn(r1 - __half2float(m3));
-                    }
-                    const __half z = __float2half_rn(0.0f);
-                    const uint32_t lo = t == 0 ? pkh(h0, h0) : t == 1 ? pkh(m0, m0) : t == 2 ? pkh(h1, h1) : pkh(m1, m1);
-                    const uint32_t hi = t == 0 ? pkh(h2, h2) : t == 1 ? pkh(m2, m2) : t == 2 ? pkh(h3, m3) : pkh(l3, z);
-                    A[rb][c][hr] = lo;                             // a0,a1 (row g) / a2,a3 (row g + 8): K 2t, 2t+1
-                    A[rb][c][2 + hr] = hi;                         // a4,a5 / a6,a7: K 2t+8, 2t+9
+                    A[rb][c][hr] = sfrag[hl][c][t];                // a0,a1 (row g) / a2,a3 (row g + 8): K 2t, 2t+1
+                    A[rb][c][2 + hr] = sfrag[hl][c][4 + t];        // a4,a5 / a6,a7: K 2t+8, 2t+9
                 }
             }
-        __syncthreads();
     };
 
     int sf, sp0, sn, nf = 0, np0 = 0, nn = 0;
@@ -226,7 +242,7 @@ __global__ void __launch_bounds__(MT_, 4) ransac_score_mma_kernel(ScoreArgs a) {
         {
             const int P = max(0, min(a.count[sf], a.cap));
             const __half sh = __float2half_rn(sc), z = __float2half_rn(0.0f);
-            for (int i = tid; i < sn; i += MT_) {
+            for (int i = tid; i < sn; i += NT) {
                 const bool in = sp0 + i < P;
                 __half xh, xm, yh, ym, zh, zm;
                 split2h(sbuf[b][0][i] * sc, xh, xm); split2h(sbuf[b][1][i] * sc, yh, ym); split2h(sbuf[b][2][i] * sc, zh, zm);
@@ -240,41 +256,44 @@ __global__ void __launch_bounds__(MT_, 4) ransac_score_mma_kernel(ScoreArgs a) {
         }
         __syncthreads();
         // ---- blocks of 4 groups of 8 points: 8 tests per hypothesis row and thread
+        const uint32_t* rowp = &srow[b][g][t];                     // + 64 words per group
+        const float* ndup = &snd[b][0][2 * t];                     // + 8 floats per group
+        const float* ndvp = &snd[b][1][2 * t];
 #pragma unroll 1
-        for (int i0 = 0; i0 < sn; i0 += 32) {
+        for (int i0 = 0; i0 < sn; i0 += 32, rowp += 256, ndup += 32, ndvp += 32) {
             const int ngrp = min(4, (sn - i0) >> 3);
             uint32_t bits[NRB][2];
-            float smin[NRB][2];
 #pragma unroll
-            for (int rb = 0; rb < NRB; ++rb) { bits[rb][0] = bits[rb][1] = 0u; smin[rb][0] = smin[rb][1] = pinf; }
+            for (int rb = 0; rb < NRB; ++rb) bits[rb][0] = bits[rb][1] = 0u;
+            uint32_t fm = 0u;                                      // bit 4 * (2 rb + hr) + grp: that row's two tests of the group
 #pragma unroll
             for (int grp = 0; grp < 4; ++grp) {
                 if (grp < ngrp) {
-                    const int ib = i0 + 8 * grp;
-                    const uint32_t b0 = srow[b][ib + g][t], b1 = srow[b][ib + g][4 + t];
-                    const f32x2 ndu2 = *reinterpret_cast<const f32x2*>(&snd[b][0][ib + 2 * t]);
-                    const f32x2 ndv2 = *reinterpret_cast<const f32x2*>(&snd[b][1][ib + 2 * t]);
+                    const uint32_t b0 = rowp[64 * grp], b1 = rowp[64 * grp + 4];
+                    const f32x2 ndu2 = *reinterpret_cast<const f32x2*>(ndup + 8 * grp);
+                    const f32x2 ndv2 = *reinterpret_cast<const f32x2*>(ndvp + 8 * grp);
 #pragma unroll
                     for (int rb = 0; rb < NRB; ++rb) {
-                        float cx[4], cy[4], cw[4];
+                        uint32_t cx[4], cy[4], cw[4];
                         hmma16816(cx, A[rb][0], b0, b1);
                         hmma16816(cy, A[rb][1], b0, b1);
                         hmma16816(cw, A[rb][2], b0, b1);
 #pragma unroll
                         for (int hr = 0; hr < 2; ++hr) {
-                            const float w0 = cw[2 * hr], w1 = cw[2 * hr + 1];
-                            const f32x2 x2 = pack2(cx[2 * hr], cx[2 * hr + 1]), y2 = pack2(cy[2 * hr], cy[2 * hr + 1]), w2 = pack2(w0, w1);
+                            const float w0 = __uint_as_float(cw[2 * hr]), w1 = __uint_as_float(cw[2 * hr + 1]);
+                            const f32x2 x2 = pack2u(cx[2 * hr], cx[2 * hr + 1]), y2 = pack2u(cy[2 * hr], cy[2 * hr + 1]), w2 = pack2u(cw[2 * hr], cw[2 * hr + 1]);
                             const f32x2 dx2 = ffma2(ndu2, w2, x2), dy2 = ffma2(ndv2, w2, y2);
                             const f32x2 nq2 = pack2(w0 * -fabsf(w0), w1 * -fabsf(w1));
                             const f32x2 s2 = ffma2(dx2, dx2, ffma2(dy2, dy2, nq2));
                             const uint32_t s0 = (uint32_t)s2, s1 = (uint32_t)(s2 >> 32);
                             bits[rb][hr] = __funnelshift_l(s0, bits[rb][hr], 1);
                             bits[rb][hr] = __funnelshift_l(s1, bits[rb][hr], 1);
-                            smin[rb][hr] = min3nan(smin[rb][hr], fabsf(__uint_as_float(s0)), fabsf(__uint_as_float(s1)));
+                            const float sm = min3nan(fabsf(__uint_as_float(s0)), fabsf(__uint_as_float(s1)), pinf);
+                            if (!(sm > bandv[rb][hr])) fm |= 1u << (4 * (2 * rb + hr) + grp);
                             if (CALIB) {
 #pragma unroll
                                 for (int cc = 0; cc < 2; ++cc) {
-                                    const int p = ib + 2 * t + cc;
+                                    const int p = i0 + 8 * grp + 2 * t + cc;
                                     const float* M = sproj[hbase + 16 * rb + 8 * hr + g];
                                     const float se = inlier_s(M, sbuf[b][0][p], sbuf[b][1][p], sbuf[b][2][p], sbuf[b][3][p] * a.inv_thr,
                                                               sbuf[b][4][p] * a.inv_thr) * (sc * sc);
@@ -289,36 +308,31 @@ __global__ void __launch_bounds__(MT_, 4) ransac_score_mma_kernel(ScoreArgs a) {
                     }
                 }
             }
-            // ---- rows with a value inside their band: the contract's own arithmetic decides their 2 * ngrp tests
-            uint32_t fm = 0u;
-#pragma unroll
-            for (int rb = 0; rb < NRB; ++rb)
-#pragma unroll
-                for (int hr = 0; hr < 2; ++hr) fm |= (!(smin[rb][hr] > bandv[rb][hr])) ? (1u << (2 * rb + hr)) : 0u;
-            if (__any_sync(0xffffffffu, fm != 0u)) {
+            // ---- (row, group) pairs with a value inside the row's band: the contract's own arithmetic decides their two tests
+            uint32_t any = __reduce_or_sync(0xffffffffu, fm);
+#pragma unroll 1
+            while (any) {
+                const int bit = __ffs(any) - 1;
+                any &= any - 1;
+                const int r = bit >> 2, grp = bit & 3;             // r = 2 rb + hr
+                ++nslow;
+                const float* Mp = sproj[hbase + 16 * (r >> 1) + 8 * (r & 1) + g];
+                const float4 m0 = reinterpret_cast<const float4*>(Mp)[0], m1 = reinterpret_cast<const float4*>(Mp)[1],
+                             m2 = reinterpret_cast<const float4*>(Mp)[2];
+                const float M[12] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
+                const int p = i0 + 8 * grp + 2 * t;
+                const uint32_t e0 = __float_as_uint(inlier_s(M, sbuf[b][0][p], sbuf[b][1][p], sbuf[b][2][p], sbuf[b][3][p] * a.inv_thr,
+                                                             sbuf[b][4][p] * a.inv_thr)) >> 31;
+                const uint32_t e1 = __float_as_uint(inlier_s(M, sbuf[b][0][p + 1], sbuf[b][1][p + 1], sbuf[b][2][p + 1],
+                                                             sbuf[b][3][p + 1] * a.inv_thr, sbuf[b][4][p + 1] * a.inv_thr)) >> 31;
+                // the group's two verdicts sit at bits 2 (ngrp - 1 - grp) + 1 and + 0 of the row's word
+                const int sh = 2 * (ngrp - 1 - grp);
+                const uint32_t patch = ((e0 << 1) | e1) << sh, keep = ~(3u << sh);
 #pragma unroll
                 for (int rb = 0; rb < NRB; ++rb)
 #pragma unroll
-                    for (int hr = 0; hr < 2; ++hr) {
-                        if (__any_sync(0xffffffffu, (fm >> (2 * rb + hr)) & 1u)) {
-                            ++nslow;
-                            const float* Mp = sproj[hbase + 16 * rb + 8 * hr + g];
-                            const float4 m0 = reinterpret_cast<const float4*>(Mp)[0], m1 = reinterpret_cast<const float4*>(Mp)[1],
-                                         m2 = reinterpret_cast<const float4*>(Mp)[2];
-                            const float M[12] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x, m2.y, m2.z, m2.w};
-                            uint32_t w = 0u;
-#pragma unroll 1
-                            for (int grp = 0; grp < ngrp; ++grp)
-#pragma unroll
-                                for (int cc = 0; cc < 2; ++cc) {
-                                    const int p = i0 + 8 * grp + 2 * t + cc;
-                                    const float s = inlier_s(M, sbuf[b][0][p], sbuf[b][1][p], sbuf[b][2][p], sbuf[b][3][p] * a.inv_thr,
-                                                             sbuf[b][4][p] * a.inv_thr);
-                                    w = (w << 1) | (__float_as_uint(s) >> 31);
-                                }
-                            bits[rb][hr] = w;
-                        }
-                    }
+                    for (int hr = 0; hr < 2; ++hr)
+                        if (r == 2 * rb + hr) bits[rb][hr] = (bits[rb][hr] & keep) | patch;
             }
 #pragma unroll
             for (int rb = 0; rb < NRB; ++rb) { cnt[rb][0] += __popc(bits[rb][0]); cnt[rb][1] += __popc(bits[rb][1]); }
@@ -342,10 +356,17 @@ __global__ void __launch_bounds__(MT_, 4) ransac_score_mma_kernel(ScoreArgs a) {
     }
 }
 
-template <int NRB>
-int launch_mma(const ScoreArgs& a, int calib, int grid, cudaStream_t st) {
-    if (calib) ransac_score_mma_kernel<NRB, true><<<grid, MT_, 0, st>>>(a);
-    else ransac_score_mma_kernel<NRB, false><<<grid, MT_, 0, st>>>(a);
+template <int NW>
+int launch_mma(const ScoreArgs& a, int calib, cudaStream_t st) {
+    const int grid = pb_sm_count() * (NW >= 8 ? 3 : NW >= 4 ? 6 : 12);
+    constexpr int smem = mma_smem_bytes(NW);
+    if (calib) {
+        cudaFuncSetAttribute(ransac_score_mma_kernel<NW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        ransac_score_mma_kernel<NW, true><<<grid, 32 * NW, smem, st>>>(a);
+    } else {
+        cudaFuncSetAttribute(ransac_score_mma_kernel<NW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        ransac_score_mma_kernel<NW, false><<<grid, 32 * NW, smem, st>>>(a);
+    }
     return pb_check_launch("ransac_score_mma_kernel");
 }
 
@@ -355,8 +376,7 @@ int pb_launch_score_mma(const ScoreArgs& a, int calib, cudaStream_t st) {
     cudaMemsetAsync(a.tc_stats, 0, PB_TC_STATS_BYTES, st);
     frame_stats_kernel<<<(a.F + 3) / 4, 128, 0, st>>>(a);
     if (pb_check_launch("frame_stats_kernel")) return 1;
-    const int grid = pb_sm_count() * 4;
-    if (a.H <= 64) return launch_mma<1>(a, calib, grid, st);
-    if (a.H <= 128) return launch_mma<2>(a, calib, grid, st);
-    return launch_mma<4>(a, calib, grid, st);
+    if (a.H <= 64) return launch_mma<2>(a, calib, st);
+    if (a.H <= 128) return launch_mma<4>(a, calib, st);
+    return launch_mma<8>(a, calib, st);
 }

@@ -19,13 +19,17 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-// bounded spin: returns false if the phase never completed (caller traps instead of hanging the GPU)
+// bounded wait: returns false if the phase never completed (caller flags an error instead of hanging the GPU).  try_wait
+// carries a suspend-time hint, so a waiting thread sleeps in hardware (NANOSLEEP.SYNCS) until the phase completes instead of
+// spending issue slots on polling -- a third of the executed instructions of a warp-specialised kernel were polling loops
+// without it (profiles/r02_k3_tc.md).
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t a = smem_u32(bar);
-    for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+#pragma unroll 1
+    for (uint32_t spin = 0; spin < (1u << 14); ++spin) {
         uint32_t ok;
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(a), "r"(parity), "r"(200000u) : "memory");
         if (ok) return true;
     }
     return false;

@@ -149,13 +149,19 @@ int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const float* K4, i
                       void* ws, size_t ws_bytes, void* stream);
 
 /* Which kernel scores the hypotheses (K3; the iteration loop of cv2.solvePnPRansac, tools/trainer.py:423-427).
- * Process-wide setting read at every pb_pnp_ransac_* call: 0 = automatic, 1 = FP32-pipe kernels only, 2 = the
- * tensor-core kernel (csrc/ransac_score_tc.cu) whenever the shape allows (n_hyp <= 256 and a batch large enough for
- * the balanced plan), 3 = the same with a calibration pass (slow).  All of them return identical integers.
- * band_scale multiplies the band inside which the tensor-core kernel re-evaluates a test with the FP32 contract
+ * Process-wide setting (not thread-safe; set it before launching work) read at every pb_pnp_ransac_* call:
+ *   0 = automatic (the FP32-pipe kernels), 1 = FP32-pipe kernels only,
+ *   2 = projection by tcgen05 + TMEM (csrc/ransac_score_tc.cu), 3 = the same with a calibration pass, 4 = with a clock
+ *       breakdown of its warps' waits,
+ *   5 = projection by warp-level mma.sync (csrc/ransac_score_mma.cu), 6 = the same with a calibration pass.
+ * 2 - 6 apply whenever the shape allows (n_hyp <= 256 and a batch large enough for the balanced plan), otherwise the
+ * FP32-pipe kernels run.  All of them return identical integers and poses; 2 and 5 are measured alternatives that are
+ * not faster on B200 (profiles/r02_k3_tc.md), which is why 0 does not choose them.
+ * band_scale multiplies the band inside which the tensor-core kernels re-evaluate a test with the FP32 contract
  * (1 = the derived bound).  pb_ransac_tc_stats_offset: byte offset inside the pb_pnp_ransac_pts workspace of
- * int32 stats[4] = {barrier timeout, re-evaluated groups, calibration: largest |s_tc - s_fp32| / band as float
- * bits, calibration: verdicts that differ outside the band}, or -1 when the shape never takes that kernel.     */
+ * int32 stats[4] = {barrier timeout, re-evaluated blocks, calibration: largest |s_tc - s_fp32| / band as float
+ * bits, calibration: verdicts that differ outside the band} followed by twelve 64-bit clock sums (mode 4), or -1 when
+ * the shape never takes those kernels.                                                                             */
 int pb_ransac_score_impl(int impl, float band_scale);
 long long pb_ransac_tc_stats_offset(int F, int cap, const pb_ransac_params* prm);
 

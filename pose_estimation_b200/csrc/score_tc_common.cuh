@@ -1,6 +1,9 @@
 // score_tc_common.cuh -- pieces shared by the two tensor-core formulations of K3 (ransac_score_tc.cu: tcgen05 + TMEM;
 // ransac_score_mma.cu: warp-level mma.sync): FP16 operand splitting, packed FP32x2 arithmetic, the contract's matrix of a
 // hypothesis with its centred rows, and the per-hypothesis band inside which the contract's own arithmetic decides.
+// The band allows 16 u (u = 2^-24 of the sum of the absolute terms) for the tensor core's internal accumulation; measured
+// on B200: <= 5.6 u for exponent spreads up to 2^12 per operand and a dominant term (scratch/hmma_acc_lab.cu,
+// profiles/r02_hmma_acc_lab.txt).
 #pragma once
 #include <cuda_fp16.h>
 #include "ransac_plan.h"

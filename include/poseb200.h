@@ -288,6 +288,10 @@ int pb_knn1(const float* x, const float* y, int B, int N, int M, int y_shared, i
 size_t pb_knn1_tc_workspace_bytes(int B, int N, int M);
 int pb_knn1_tc(const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx, float* d2,
                void* ws, size_t ws_bytes, void* stream);
+/* Which sweep pb_knn1_tc / pb_add_adds_tc / pb_pose_loss_fwd_tc use (process-wide): 0 = automatic (tcgen05 + TMEM),
+ * 1 = tcgen05 + TMEM, 2 = warp-level mma.sync (a measured alternative, slower on B200).  Identical indices and
+ * distances; no counterpart in the reference (one KeOps handle).                                                  */
+int pb_knn_tc_impl(int impl);
 
 /* replaces Metric.cal_adds_cuda (lib/utils/metric.py:17-36): add[b] = mean_i |pred_i - tgt_i|;
  * adds[b] = mean_i min_j |pred_j - tgt_i| computed where want_adds[b] != 0 (NULL -> all),

@@ -47,6 +47,7 @@ SIGNATURES = {
     "pb_resample_inliers": (I, [P, P, I, I, I, U32, U32, U32, P, P]),
     "pb_knn1": (I, [P, P, I, I, I, I, P, P, P]),
     "pb_knn1_tc_workspace_bytes": (SZ, [I, I, I]),
+    "pb_knn_tc_impl": (I, [I]),
     "pb_knn1_tc": (I, [P, P, I, I, I, I, P, P, P, SZ, P]),
     "pb_add_adds": (I, [P, P, I, I, P, P, P, P]),
     "pb_add_adds_tc_workspace_bytes": (SZ, [I, I]),

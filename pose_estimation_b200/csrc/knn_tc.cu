@@ -56,13 +56,14 @@ struct PrepArgs {
     uint4* Aop; uint4* Bop; float* tol; float* centre;   // per chunk-local batch element
     int b0;
     const int* blist;                                     // optional: batch element of list position b0 + bl
+    int frag_layout;                                      // database tiles in the mma.sync sweep's fragment order (see knn_mma_kernel)
 };
 
 // K = 16 operand row of one point.  Query rows (IS_A): per coordinate (h, h, m, m) of -2p, then 1, 1, 1, 0.
 // Database rows: per coordinate (h, m, h, m) of q, then |q|^2 as three bf16, 0.  h + m carries 16 mantissa bits
 // of a coordinate, so the twelve cross products give -2 p.q to 2^-16 R^2.
 template <bool IS_A>
-__device__ __forceinline__ void write_row(uint4* tile_base, int r, float px, float py, float pz, bool pad) {
+__device__ __forceinline__ void write_row(uint4* tile_base, int r, float px, float py, float pz, bool pad, bool frag_layout = false) {
     __nv_bfloat16 e[16];
     const __nv_bfloat16 zero = __float2bfloat16_rn(0.0f), one = __float2bfloat16_rn(1.0f);
 #pragma unroll
@@ -83,6 +84,14 @@ __device__ __forceinline__ void write_row(uint4* tile_base, int r, float px, flo
         }
     } else if (!IS_A) {
         e[12] = __float2bfloat16_rn(1.0e30f);          // padded database row: never a candidate
+    }
+    if (frag_layout) {
+        // word (kc, row = 32 chunk + 8 nt + g, t) -> uint32 index 256 chunk + 8 (4 g + t) + 2 nt + kc: thread (g, t) of the mma.sync
+        // sweep finds its eight fragment words of a 32-row chunk in 32 consecutive bytes
+        uint2* w = reinterpret_cast<uint2*>(tile_base) + ((r >> 5) * 128 + (r & 7) * 16 + ((r >> 3) & 3));
+#pragma unroll
+        for (int t = 0; t < 4; ++t) w[4 * t] = make_uint2(pk(e[2 * t], e[2 * t + 1]), pk(e[8 + 2 * t], e[8 + 2 * t + 1]));
+        return;
     }
 #pragma unroll
     for (int kc = 0; kc < 2; ++kc)
@@ -140,7 +149,7 @@ __global__ void __launch_bounds__(256) knn_tc_prepare_kernel(PrepArgs a) {
         float px = 0.0f, py = 0.0f, pz = 0.0f;
         if (!pad) { px = yb[3 * (size_t)j] - c0; py = yb[3 * (size_t)j + 1] - c1; pz = yb[3 * (size_t)j + 2] - c2; }
         r2 = fmaxf(r2, fmaf(pz, pz, fmaf(py, py, px * px)));
-        write_row<false>(Bt + (size_t)(j / TM) * TILE_U4, j % TM, px, py, pz, pad);
+        write_row<false>(Bt + (size_t)(j / TM) * TILE_U4, j % TM, px, py, pz, pad, a.frag_layout != 0);
     }
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) r2 = fmaxf(r2, __shfl_xor_sync(0xffffffffu, r2, off));
@@ -689,6 +698,207 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
     }
 }
 
+// ---- the same contraction through the warp-level tensor path (mma.sync.m16n8k16, BF16 in, FP32 accumulators in the
+// registers of the warp that takes the minima): a measured alternative, opt-in (pb_knn_tc_impl(2)) ---------------------
+// With mma.sync the accumulators arrive in the evaluating thread's registers: no TMEM, no hand-off between an issuing
+// warp and epilogue warps.  One m16n8k16 costs 8.0 cycles per scheduler (scratch/hmma_lab.cu), 64 scores per clock per
+// SM -- a floor of 1.6 ms for C3.  Measured: 6.7 ms against 3.9 ms for the tcgen05 sweep above (profiles/r02_knn_mma.md):
+// a thread owns 2 columns of every 8-column tile and 4 rows, so the candidate bookkeeping is per (thread, row) with only
+// 8 scores per 32-column chunk behind it (4x the tcgen05 kernel's per-score cost) -- done per 128-column tile instead, the
+// exact re-rank has 4x the columns to look at and diverges.  Identical indices and distances (tests/test_gpu_knn_tc.py).
+//   grid (row tiles, batch elements), 4 consumer warps + 1 producer warp (1-D TMA bulk copies of the database tiles, which
+//   the prepare kernel wrote in fragment order, through 4 shared-memory stages): warp w owns query rows 32 w .. 32 w + 31
+//   (two row blocks of 16); a thread holds rows g, g + 8, g + 16, g + 24 (g = lane / 4) and, of every 8-column tile,
+//   columns 2t, 2t + 1.  Per 128-column tile and row: minimum of the thread's 32 scores; a tile below  running minimum + T
+//   keeps a slot of the row's ring (the thread's own running minimum is >= the row's, so every column within T of the row
+//   minimum is kept).  After the sweep the row minimum is the minimum over the quad; every remembered tile within T of it
+//   is re-evaluated with the exact FP32 formula on the thread's 32 columns; quad-reduce with the lowest index on ties.
+constexpr int KM_T = 128;          // consumer threads (4 warps); a fifth warp streams the database tiles
+constexpr int KM_THREADS = KM_T + 32;
+constexpr int KM_CAND = 8;
+constexpr int KM_STG = 4;          // shared-memory stages of database tiles (16 KB in flight per CTA)
+
+__device__ __forceinline__ void hmma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+        : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "f"(0.0f));
+}
+
+__global__ void __launch_bounds__(KM_THREADS, 4) knn_mma_kernel(MainArgs a) {
+    __shared__ __align__(128) uint4 sB[KM_STG][TILE_U4];   // database tiles in fragment order
+    __shared__ float s_min[KM_CAND][4][KM_T];              // ring: tile minimum ...
+    __shared__ uint16_t s_id[KM_CAND][4][KM_T];            // ... and tile index, per (slot, row of the thread, thread)
+    __shared__ __align__(8) uint64_t bar_full[KM_STG], bar_empty[KM_STG];
+    __shared__ int s_bad;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const int rt = blockIdx.x, bl = blockIdx.y, b = a.blist ? a.blist[a.b0 + bl] : a.b0 + bl;
+    const int ntM = a.ntM;
+    if (tid == 0) {
+        for (int i = 0; i < KM_STG; ++i) { tc::mbar_init(&bar_full[i], 1); tc::mbar_init(&bar_empty[i], 4); }
+        s_bad = 0;
+        tc::fence_mbar_init();
+    }
+    __syncthreads();
+    if (warp == 4) {
+        // ===== producer: one bulk copy (1-D TMA) per database tile through KM_STG stages
+        if (lane == 0) {
+            const uint4* Bg = a.Bop + (size_t)bl * ntM * TILE_U4;
+            bool ok = true;
+            for (int v = 0; v < ntM && ok; ++v) {
+                const int st = v % KM_STG;
+                if (v >= KM_STG) ok = tc::mbar_wait(&bar_empty[st], (uint32_t)(v / KM_STG - 1) & 1u);
+                tc::mbar_expect_tx(&bar_full[st], TILE_BYTES);
+                tc::bulk_g2s(sB[st], Bg + (size_t)v * TILE_U4, TILE_BYTES, &bar_full[st]);
+            }
+            if (!ok) s_bad = 1;
+        }
+        return;
+    }
+    const uint32_t* __restrict__ Aw = reinterpret_cast<const uint32_t*>(a.Aop + ((size_t)bl * a.ntN + rt) * TILE_U4);
+    const float T = a.tol[bl] * TC_TOL_REL;
+    // ---- A fragments: word (kc, row, t) of the (canonical) tile = uint32 index ((kc * 128 + row) * 4 + t)
+    uint32_t A[2][4];
+#pragma unroll
+    for (int rb = 0; rb < 2; ++rb) {
+        const int r = 32 * warp + 16 * rb + g;
+        A[rb][0] = Aw[(r) * 4 + t];
+        A[rb][1] = Aw[(r + 8) * 4 + t];
+        A[rb][2] = Aw[(TM + r) * 4 + t];
+        A[rb][3] = Aw[(TM + r + 8) * 4 + t];
+    }
+    float run[4], lost[4];
+    int cnt[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { run[k] = INFINITY; lost[k] = INFINITY; cnt[k] = 0; }
+    // ---- sweep: per database tile four chunks of 32 columns (thread (g, t)'s eight fragment words of chunk c are the 32 bytes
+    // at uint4 index 64 c + 2 (4 g + t) of the stage); one ring step per tile and row
+    bool ok = true;
+#pragma unroll 1
+    for (int v = 0; v < ntM; ++v) {
+        const int st = v % KM_STG;
+        ok = tc::mbar_wait(&bar_full[st], (uint32_t)(v / KM_STG) & 1u) && ok;
+        const uint4* sq = sB[st] + 2 * (4 * g + t);
+        float cm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const uint4 c0 = sq[64 * c], c1 = sq[64 * c + 1];
+            const uint32_t bw[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt) {
+#pragma unroll
+                for (int rb = 0; rb < 2; ++rb) {
+                    float d[4];
+                    hmma_bf16(d, A[rb], bw[2 * nt], bw[2 * nt + 1]);
+                    cm[2 * rb] = fmin3(cm[2 * rb], d[0], d[1]);
+                    cm[2 * rb + 1] = fmin3(cm[2 * rb + 1], d[2], d[3]);
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&bar_empty[st]);            // this warp has read the stage
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int slot = cnt[k] & (KM_CAND - 1);
+            s_min[slot][k][tid] = cm[k];
+            s_id[slot][k][tid] = (uint16_t)v;
+            if (cm[k] < run[k] + T) {
+                ++cnt[k];                                          // keep it; the next slot becomes scratch
+                if (cnt[k] >= KM_CAND) lost[k] = fminf(lost[k], s_min[cnt[k] & (KM_CAND - 1)][k][tid]);   // ... and what it held is dropped
+            }
+            run[k] = fminf(run[k], cm[k]);
+        }
+    }
+    if (!ok) s_bad = 1;
+    asm volatile("bar.sync 1, %0;" ::"n"(KM_T) : "memory");
+    const bool sweep_ok = s_bad == 0;
+    // ---- exact FP32 re-rank of the remembered tiles within T of the row minimum (lowest index on ties).  A thread first
+    // collects its (row, slot) pairs that qualify in a bit mask and then walks them, so the warp's trip count is the largest
+    // number of qualifying tiles of any lane (2 - 4), not rows x ring slots
+    const float* xb = a.x + (size_t)b * a.N * 3;
+    const float* yb = a.y + (a.y_shared ? 0 : (size_t)b * a.M * 3);
+    int nexact = 0;
+    float best[4];
+    int bidx[4];
+    bool bad[4];
+    uint32_t todo = 0u;                                            // bit 8 k + slot
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        float m = run[k];
+        m = fminf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+        m = fminf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+        const float lim = m + T;
+        const int row = rt * TM + 32 * warp + 16 * (k >> 1) + 8 * (k & 1) + g;
+        bad[k] = lost[k] < lim || !(m == m) || !sweep_ok;
+        best[k] = INFINITY; bidx[k] = 0x7fffffff;
+        if (row < a.N)
+            for (int i = cnt[k] > KM_CAND - 1 ? cnt[k] - (KM_CAND - 1) : 0; i < cnt[k]; ++i) {
+                const int slot = i & (KM_CAND - 1);
+                if (s_min[slot][k][tid] < lim) todo |= 1u << (8 * k + slot);
+            }
+    }
+    while (todo) {
+        const int bit = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int k = bit >> 3, slot = bit & 7;
+        const int row = rt * TM + 32 * warp + 16 * (k >> 1) + 8 * (k & 1) + g;
+        const float qx = xb[3 * (size_t)row], qy = xb[3 * (size_t)row + 1], qz = xb[3 * (size_t)row + 2];
+        const int c0 = (int)s_id[slot][k][tid] * TM + 2 * t;        // this thread's columns of the tile: 8 nt + 2 t + {0, 1}
+        float bb = INFINITY;
+        int bi = 0x7fffffff;
+#pragma unroll 4
+        for (int nt = 0; nt < 16; ++nt) {
+            const int j = c0 + 8 * nt;
+            if (j + 1 < a.M) {
+                const float* yp = yb + 3 * (size_t)j;
+                const float d0 = sqdist3(qx, qy, qz, yp[0], yp[1], yp[2]), d1 = sqdist3(qx, qy, qz, yp[3], yp[4], yp[5]);
+                nexact += 2;
+                if (d0 < bb) { bb = d0; bi = j; }                   // columns ascend: a strict test keeps the lowest index
+                if (d1 < bb) { bb = d1; bi = j + 1; }
+            } else if (j < a.M) {
+                const float d0 = sqdist3(qx, qy, qz, yb[3 * (size_t)j], yb[3 * (size_t)j + 1], yb[3 * (size_t)j + 2]);
+                ++nexact;
+                if (d0 < bb) { bb = d0; bi = j; }
+            }
+        }
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+            if (kk == k && (bb < best[kk] || (bb == best[kk] && bi < bidx[kk]))) { best[kk] = bb; bidx[kk] = bi; }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int row = rt * TM + 32 * warp + 16 * (k >> 1) + 8 * (k & 1) + g;
+        const bool valid = row < a.N;
+        float bs = best[k];
+        int bx = bidx[k];
+        bool bd = bad[k];
+#pragma unroll
+        for (int off = 1; off <= 2; off <<= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, bs, off);
+            const int oi = __shfl_xor_sync(0xffffffffu, bx, off);
+            const int obad = __shfl_xor_sync(0xffffffffu, (int)bd, off);   // (unconditionally: every lane takes part)
+            if (ob < bs || (ob == bs && oi < bx)) { bs = ob; bx = oi; }
+            bd = bd || obad != 0;
+        }
+        if (valid && t == 0) {
+            if (bd || bs == INFINITY) {                              // ring overflow / NaN input: exact scan
+                const float qx = xb[3 * (size_t)row], qy = xb[3 * (size_t)row + 1], qz = xb[3 * (size_t)row + 2];
+                bs = INFINITY; bx = 0;
+                atomicAdd(a.err + 1, 1);
+                for (int j = 0; j < a.M; ++j) {
+                    const float d = sqdist3(qx, qy, qz, yb[3 * (size_t)j], yb[3 * (size_t)j + 1], yb[3 * (size_t)j + 2]);
+                    if (d < bs) { bs = d; bx = j; }
+                }
+            }
+            if (a.idx) a.idx[(size_t)b * a.N + row] = bx;
+            if (a.d2) a.d2[(size_t)b * a.N + row] = bs;
+        }
+    }
+    nexact = __reduce_add_sync(0xffffffffu, nexact);
+    if (lane == 0 && nexact) atomicAdd(a.err + 2, nexact);
+    if (tid == 0 && !sweep_ok) *a.err = 1;
+}
+
+int g_knn_impl = 0;                // pb_knn_tc_impl
 constexpr int TC_CHUNK = 256;      // batch elements per prepare/main pair: operands (~90 MB for C3) stay in L2
 constexpr size_t MAIN_SMEM = (size_t)(1 + NSTG) * TILE_BYTES + (size_t)CAND * EPI_T * 20;
 
@@ -753,6 +963,13 @@ extern "C" int pb_tc_selftest(const void* A, const void* B, float* D, int* err, 
     return pb_check_launch("tc_selftest_kernel") ? -2 : 0;
 }
 
+// 0 = automatic (the tcgen05 + TMEM sweep: 3.9 ms on C3), 1 = tcgen05, 2 = the warp-level mma.sync sweep (6.7 ms); identical results
+extern "C" int pb_knn_tc_impl(int impl) {
+    PB_REQUIRE(impl >= 0 && impl <= 2, "pb_knn_tc_impl: impl=%d (0 automatic, 1 tcgen05, 2 mma.sync)", impl);
+    g_knn_impl = impl;
+    return 0;
+}
+
 extern "C" size_t pb_knn1_tc_workspace_bytes(int B, int N, int M) {
     if (B <= 0 || N <= 0 || M <= 0) return 0;
     return tc_ws_bytes(B, N, M);
@@ -763,7 +980,7 @@ extern "C" size_t pb_knn1_tc_workspace_bytes(int B, int N, int M) {
 int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, int N, int M, int y_shared, int64_t* idx,
                         float* d2, void* ws, size_t ws_bytes, const int* blist, int nlist, cudaStream_t st) {
     const int nl = blist ? nlist : B;
-    PB_REQUIRE(M <= (1 << 24), "%s: M too large", who);
+    PB_REQUIRE(M <= (1 << 23), "%s: M too large", who);         // tile indices are kept in 16 bits by the mma.sync sweep
     const size_t need = tc_ws_bytes(B, N, M);
     PB_REQUIRE(ws && ws_bytes >= need, "%s: workspace too small (%zu < %zu)", who, ws_bytes, need);
     PB_REQUIRE(reinterpret_cast<uintptr_t>(ws) % 128 == 0, "%s: workspace must be 128-byte aligned", who);
@@ -800,7 +1017,7 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
             knn_tc_prepare_sorted_kernel<<<dim3(nb, 2), 256, 0, st>>>(sa);
             if (pb_check_launch("knn_tc_prepare_sorted_kernel")) return -2;
         } else {
-            PrepArgs pa{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, centre, b0, blist};
+            PrepArgs pa{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, centre, b0, blist, g_knn_impl == 2 ? 1 : 0};
             int split = (4 * pb_sm_count() + nb - 1) / nb;         // about four CTAs per SM in total
             const int max_split = (max(ntN, ntM) * TM + 255) / 256;
             split = split < PREP_SPLIT ? PREP_SPLIT : (split > 64 ? 64 : split);
@@ -809,6 +1026,11 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
             if (pb_check_launch("knn_tc_prepare_kernel")) return -2;
         }
         MainArgs ma{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, idx, d2, b0, err, blist, permX, permY, xs, ys, xbox, ybox, centre};
+        if (!sorted && g_knn_impl == 2) {
+            knn_mma_kernel<<<dim3(ntN, nb), KM_THREADS, 0, st>>>(ma);
+            if (pb_check_launch("knn_mma_kernel")) return -2;
+            continue;
+        }
         if (sorted) knn_tc_kernel<true><<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);
         else knn_tc_kernel<false><<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);
         if (pb_check_launch("knn_tc_kernel")) return -2;

@@ -21,6 +21,12 @@ TC_MIN_DB = 768            # ... and below this many database points (a CTA swee
 LAST_TC_STATS = None       # device int32 [4] of the last tensor-core call: timeout flag, fallback rows, exact evaluations
 
 
+def set_knn_tc_impl(sweep="auto"):
+    """Which sweep the tensor-core nearest-neighbour entry points use (process-wide): 'auto' (= 'tcgen05'), 'tcgen05',
+    'mma' (warp-level mma.sync: a measured alternative, slower on B200).  Identical results."""
+    call("pb_knn_tc_impl", {"auto": 0, "tcgen05": 1, "mma": 2}[sweep])
+
+
 def knn1(x, y, want_d2=False, impl="auto"):
     """x [B,N,3] or [N,3]; y [B,M,3], [M,3] (shared) -> idx int64 [B,N] (and d2 f32).
     impl: "tc" = tcgen05 contraction + exact FP32 re-rank, "simt" = exact FP32 scan, "auto" picks by

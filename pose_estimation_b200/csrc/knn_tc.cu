@@ -341,6 +341,13 @@ constexpr int NB = PB_TC_NB;       // accumulators per warpgroup holding WHOLE t
                                    // next tile is already in the other -- the hand-off chain (issue -> complete -> commit ->
                                    // wake -> read -> arrive -> wake) was the sweep's period with one (1200 cycles per tile)
 static_assert(NH == 1 || NB == 1, "half-tile accumulators and several whole-tile accumulators are not combined");
+#ifndef PB_TC_TILE_RING
+#define PB_TC_TILE_RING 0          // measured on C3 (round 2): 6.1 ms against 3.85 ms -> off
+#endif
+// ring step per 128-column tile instead of per 32-column chunk (unsorted sweep): a slot holds the tile's four chunk minima;
+// the exact re-rank then looks at 32-column chunks instead of 8-column groups.  A quarter of the sweep's bookkeeping, but 4x
+// the exact evaluations in the latency-bound tail that every CTA runs while it still holds its TMEM columns: slower.
+constexpr bool TILE_RING = PB_TC_TILE_RING && NH == 1;
 constexpr int NACC = NH * NWG * NB;
 constexpr int TH = TM / NH;        // columns per accumulator
 constexpr int NSTG = 6;            // shared-memory stages of database tiles (24 KB in flight per CTA)
@@ -355,6 +362,17 @@ __device__ __forceinline__ float fmin3(float a, float b, float c) {
 __device__ __forceinline__ float group_min(const uint32_t* r) {
     const float* v = reinterpret_cast<const float*>(r);
     return fmin3(fmin3(v[0], v[1], v[2]), fmin3(v[3], v[4], v[5]), fminf(v[6], v[7]));
+}
+
+// minimum of 32 consecutive scores: sixteen 3-input minima
+__device__ __forceinline__ float chunk_min(const uint32_t* r) {
+    const float* v = reinterpret_cast<const float*>(r);
+    float m[11];
+#pragma unroll
+    for (int i = 0; i < 10; ++i) m[i] = fmin3(v[3 * i], v[3 * i + 1], v[3 * i + 2]);
+    m[10] = fminf(v[30], v[31]);
+    const float a0 = fmin3(m[0], m[1], m[2]), a1 = fmin3(m[3], m[4], m[5]), a2 = fmin3(m[6], m[7], m[8]), a3 = fminf(m[9], m[10]);
+    return fmin3(fmin3(a0, a1, a2), a3, a3);
 }
 
 #ifdef PB_TC_DEBUG
@@ -588,6 +606,34 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
                 cur = w + T;                               // NaN scores: comparisons below are false, nothing is skipped
                 lb4 = *reinterpret_cast<const float4*>(&s_lb[wq][vt * 4]);
             }
+            if (!SORTED && TILE_RING) {
+                ok = tc::mbar_wait(&bar_mma[abase], ph) && ok;
+                tc::fence_after_sync();
+                float cmv[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t r[32];
+                    tc::tmem_ld32(taddr + c * 32, r);
+                    tc::tmem_ld_wait();
+                    cmv[c] = chunk_min(r);
+                }
+                tc::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(&bar_free[abase]);              // this warp is done with the accumulator
+                const float tm = fminf(fminf(cmv[0], cmv[1]), fminf(cmv[2], cmv[3]));
+                const int slot = cnt & (CAND - 1);
+                lgrp[slot * EPI_T] = make_float4(cmv[0], cmv[1], cmv[2], cmv[3]);
+                lid[slot * EPI_T] = vt;
+                if (tm < m_run + T) {
+                    ++cnt;                                      // keep it; the next slot becomes scratch
+                    if (cnt >= CAND) {                          // ... and the flagged tile it still holds is dropped
+                        const float4 o = lgrp[(cnt & (CAND - 1)) * EPI_T];
+                        lost = fminf(lost, fminf(fminf(o.x, o.y), fminf(o.z, o.w)));
+                    }
+                }
+                m_run = fminf(m_run, tm);
+                continue;
+            }
 #pragma unroll
             for (int half = 0; half < NH; ++half) {
                 TCCLK(t0);
@@ -658,11 +704,18 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
                 const uint32_t mask = (g.x < lim ? 1u : 0u) | (g.y < lim ? 2u : 0u) | (g.z < lim ? 4u : 0u) | (g.w < lim ? 8u : 0u);
                 flag |= mask << (4 * slot);
             }
-            while (flag) {                      // lanes walk their own flagged groups together
+            while (flag) {                      // lanes walk their own flagged groups (tile ring: chunks) together
                 const int pos = __ffs(flag) - 1;
                 flag &= flag - 1;
-                const int chunk = lid[(pos >> 2) * EPI_T];
-                exact_group(ydb, permY, a.M, chunk * 32 + (pos & 3) * 8, qx, qy, qz, best, bidx, nexact);
+                if (!SORTED && TILE_RING) {
+                    const int j0 = lid[(pos >> 2) * EPI_T] * TM + (pos & 3) * 32;
+#pragma unroll 1
+                    for (int q = 0; q < 4; ++q)
+                        if (j0 + 8 * q < a.M) exact_group(ydb, permY, a.M, j0 + 8 * q, qx, qy, qz, best, bidx, nexact);
+                } else {
+                    const int chunk = lid[(pos >> 2) * EPI_T];
+                    exact_group(ydb, permY, a.M, chunk * 32 + (pos & 3) * 8, qx, qy, qz, best, bidx, nexact);
+                }
             }
         }
         s_best[tid] = best; s_bidx[tid] = bidx; s_rowbad[tid] = rowbad ? 1 : 0;

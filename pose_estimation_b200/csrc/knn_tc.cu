@@ -323,6 +323,7 @@ struct MainArgs {
     // spatially sorted mode (N, M <= SORT_MAX): NULL otherwise
     const int* permX; const int* permY; const float* xs; const float* ys; const float* xbox; const float* ybox;
     const float* centre;
+    uint32_t* cand;            // split re-rank: [rows][NWG][8] = count (or ~0: exact scan) + up to 7 entries (first column | groups << 28)
 };
 
 constexpr int CAND = 8;            // ring slots per epilogue thread: the CAND - 1 latest flagged chunks + one scratch slot
@@ -341,6 +342,11 @@ constexpr int NB = PB_TC_NB;       // accumulators per warpgroup holding WHOLE t
                                    // next tile is already in the other -- the hand-off chain (issue -> complete -> commit ->
                                    // wake -> read -> arrive -> wake) was the sweep's period with one (1200 cycles per tile)
 static_assert(NH == 1 || NB == 1, "half-tile accumulators and several whole-tile accumulators are not combined");
+#ifndef PB_TC_SPLIT
+#define PB_TC_SPLIT 0              // 1: the exact re-rank runs as its own thread-per-row kernel (knn_rerank_kernel) instead of as the
+#endif                             // tail of every sweep CTA (unsorted sweep only).  Measured on C3 (round 2): 4.24 ms against 3.85 ms
+                                   // with the chunk ring, 6.67 ms with the tile ring (sweep 179 us + re-rank 234 us per 256-element
+                                   // pass: a thread per row is unbalanced on surface clouds with many near ties) -> off
 #ifndef PB_TC_TILE_RING
 #define PB_TC_TILE_RING 0          // measured on C3 (round 2): 6.1 ms against 3.85 ms -> off
 #endif
@@ -696,6 +702,28 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
         float best = INFINITY;
         int bidx = 0, nexact = 0;
         const bool rowbad = !sweep_ok || lost < lim;
+        if (!SORTED && PB_TC_SPLIT) {
+            // ---- split re-rank: this thread's qualifying groups (tile ring: chunks) go to the candidate list of its row
+            uint32_t* cd = a.cand + (((size_t)bl * a.ntN + rt) * TM + rloc) * (NWG * 8) + wg * 8;
+            uint32_t n = 0;
+            bool over = rowbad;
+            if (rvalid && !rowbad) {
+                for (int i = cnt > CAND - 1 ? cnt - (CAND - 1) : 0; i < cnt; ++i) {
+                    const int slot = i & (CAND - 1);
+                    const float4 g = lgrp[slot * EPI_T];
+                    const int id = lid[slot * EPI_T];
+                    const float gv[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if (gv[q] < lim) {
+                            if (n < 7) cd[1 + n] = TILE_RING ? ((uint32_t)(id * TM + q * 32) | (4u << 28)) : ((uint32_t)(id * 32 + q * 8) | (1u << 28));
+                            else over = true;
+                            ++n;
+                        }
+                }
+            }
+            if (rvalid) cd[0] = over ? 0xFFFFFFFFu : n;
+        } else {
         if (rvalid && !rowbad) {
             uint32_t flag = 0;                  // bit 4*slot+q: group q of that ring slot is within T of the row minimum
             for (int i = cnt > CAND - 1 ? cnt - (CAND - 1) : 0; i < cnt; ++i) {
@@ -743,6 +771,7 @@ __global__ void __launch_bounds__(KT2, 3) knn_tc_kernel(MainArgs a) {
         nexact = __reduce_add_sync(0xffffffffu, nexact);
         if (lane == 0 && nexact) atomicAdd(a.err + 2, nexact);      // statistics: exact evaluations
         if (lane == 0 && sorted) atomicAdd(a.err + 3, nchunks);     // statistics: (warp, chunk) pairs not skipped
+        }
     }
     __syncthreads();
     if (tid == 0) {
@@ -952,6 +981,50 @@ __global__ void __launch_bounds__(KM_THREADS, 4) knn_mma_kernel(MainArgs a) {
 }
 
 int g_knn_impl = 0;                // pb_knn_tc_impl
+// Split re-rank: one THREAD per query row walks the candidate lists its two epilogue threads left (a handful of 8-column groups or
+// 32-column chunks), exact FP32 distances, lowest index on ties; a row whose list overflowed (or whose sweep failed) is scanned.
+// Run as its own kernel the dependent, scattered loads overlap across 10^5 rows instead of stretching every sweep CTA's life.
+__global__ void __launch_bounds__(256) knn_rerank_kernel(MainArgs a, int nb) {
+    const size_t gid = (size_t)blockIdx.x * 256 + threadIdx.x;
+    const int rows = a.ntN * TM;
+    if (gid >= (size_t)nb * rows) return;
+    const int bl = (int)(gid / rows), row = (int)(gid - (size_t)bl * rows);
+    if (row >= a.N) return;
+    const int b = a.blist ? a.blist[a.b0 + bl] : a.b0 + bl;
+    const float* xb = a.x + (size_t)b * a.N * 3;
+    const float* yb = a.y + (a.y_shared ? 0 : (size_t)b * a.M * 3);
+    const float qx = xb[3 * (size_t)row], qy = xb[3 * (size_t)row + 1], qz = xb[3 * (size_t)row + 2];
+    const uint32_t* cd = a.cand + gid * (NWG * 8);
+    float best = INFINITY;
+    int bidx = 0, nexact = 0;
+    bool bad = false;
+#pragma unroll
+    for (int wg = 0; wg < NWG; ++wg) {
+        const uint4 c0 = reinterpret_cast<const uint4*>(cd + wg * 8)[0], c1 = reinterpret_cast<const uint4*>(cd + wg * 8)[1];
+        const uint32_t e[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+        if (e[0] == 0xFFFFFFFFu) { bad = true; continue; }
+#pragma unroll
+        for (int i = 0; i < 7; ++i)
+            if ((uint32_t)i < e[0]) {
+                const int j0 = (int)(e[1 + i] & 0x0FFFFFFFu), ng = (int)(e[1 + i] >> 28);
+                for (int q = 0; q < ng; ++q)
+                    if (j0 + 8 * q < a.M) exact_group(yb, nullptr, a.M, j0 + 8 * q, qx, qy, qz, best, bidx, nexact);
+            }
+    }
+    if (bad || best == INFINITY) {                                  // ring overflow / timeout / NaN input: exact scan
+        best = INFINITY; bidx = 0;
+        atomicAdd(a.err + 1, 1);
+        for (int j = 0; j < a.M; ++j) {
+            const float d = sqdist3(qx, qy, qz, yb[3 * (size_t)j], yb[3 * (size_t)j + 1], yb[3 * (size_t)j + 2]);
+            if (d < best) { best = d; bidx = j; }
+        }
+    }
+    if (a.idx) a.idx[(size_t)b * a.N + row] = bidx;
+    if (a.d2) a.d2[(size_t)b * a.N + row] = best;
+    nexact = __reduce_add_sync(__activemask(), nexact);
+    if ((threadIdx.x & 31) == (__ffs(__activemask()) - 1) && nexact) atomicAdd(a.err + 2, nexact);
+}
+
 constexpr int TC_CHUNK = 256;      // batch elements per prepare/main pair: operands (~90 MB for C3) stay in L2
 constexpr size_t MAIN_SMEM = (size_t)(1 + NSTG) * TILE_BYTES + (size_t)CAND * EPI_T * 20;
 
@@ -962,6 +1035,7 @@ size_t tc_ws_bytes(int B, int N, int M) {
     size_t n = 128 + (size_t)nb * (ntN + ntM) * TILE_BYTES + al128((size_t)nb * 4 * sizeof(float)) + 128;   // head: int stats[4]
     if (PB_TC_SORTED && N <= SORT_MAX && M <= SORT_MAX)      // sorted mode: perm (4 B) + sorted coordinates (12 B) per point, a box per 32
         n += al128((size_t)nb * (ntN + ntM) * TM * 16) + al128((size_t)nb * (ntN + ntM) * 4 * 6 * sizeof(float)) + 256;
+    n += 128 + (size_t)nb * ntN * TM * NWG * 8 * sizeof(uint32_t);   // split re-rank: candidate lists
     return n;
 }
 
@@ -1059,6 +1133,7 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
         xbox = reinterpret_cast<float*>(q); q += (size_t)nb_max * ntN * 4 * 6 * sizeof(float);
         ybox = reinterpret_cast<float*>(q);
     }
+    uint32_t* cand = reinterpret_cast<uint32_t*>(al128(reinterpret_cast<uintptr_t>(base) + need - 128 - (size_t)nb_max * ntN * TM * NWG * 8 * sizeof(uint32_t)) );
     cudaFuncSetAttribute(knn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAIN_SMEM);
     cudaFuncSetAttribute(knn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAIN_SMEM);
     cudaMemsetAsync(err, 0, 4 * sizeof(int), st);   // [0] barrier timeout, [1] fallback rows, [2] exact evaluations
@@ -1078,7 +1153,7 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
             knn_tc_prepare_kernel<<<dim3(nb, split), 256, 0, st>>>(pa);
             if (pb_check_launch("knn_tc_prepare_kernel")) return -2;
         }
-        MainArgs ma{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, idx, d2, b0, err, blist, permX, permY, xs, ys, xbox, ybox, centre};
+        MainArgs ma{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, idx, d2, b0, err, blist, permX, permY, xs, ys, xbox, ybox, centre, cand};
         if (!sorted && g_knn_impl == 2) {
             knn_mma_kernel<<<dim3(ntN, nb), KM_THREADS, 0, st>>>(ma);
             if (pb_check_launch("knn_mma_kernel")) return -2;
@@ -1087,6 +1162,11 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
         if (sorted) knn_tc_kernel<true><<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);
         else knn_tc_kernel<false><<<dim3(ntN, nb), KT2, MAIN_SMEM, st>>>(ma);
         if (pb_check_launch("knn_tc_kernel")) return -2;
+        if (!sorted && PB_TC_SPLIT) {
+            const size_t nrows = (size_t)nb * ntN * TM;
+            knn_rerank_kernel<<<(unsigned)((nrows + 255) / 256), 256, 0, st>>>(ma, nb);
+            if (pb_check_launch("knn_rerank_kernel")) return -2;
+        }
     }
     return 0;
 }

@@ -67,7 +67,9 @@ static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm, int sm
     // numbers of points and the launch lasts as long as the SM with the largest sum.  Then CTAs take equal
     // ranges of the concatenated point list instead (H <= 256 hypotheses held by one CTA).
     p.smem_bal = 0;                                    // the balanced kernel's two 256-point buffers are static (10 KB)
-    const int per_sm = 6;                              // <= 85 registers x 128 threads: six CTAs per SM, one wave
+    const int per_sm = 6;                              // <= 85 registers x 128 threads: six CTAs per SM, one wave (measured with
+                                                       // 5 / 4 / 3: 0.1526 / 0.1542 / 0.1581 ms against 0.1518, and the three-stream
+                                                       // sweep gains nothing from the freed registers: 0.302 / 0.304 / 0.314 ms per step)
     // also for fewer frames when they can hold many points (dense masks: 2 k .. 50 k pixels per frame, very uneven)
     const bool many = F >= two_waves || (long long)F * cap >= 4ll * sms * per_sm * PB_BAL_SUB;
     p.bal = (H <= 2 * PB_SCORE_THREADS && many && cap % 4 == 0) ? 1 : 0;

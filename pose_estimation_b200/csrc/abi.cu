@@ -1,4 +1,5 @@
 // abi.cu -- error reporting and the composed map -> pose entry point of libposeb200.so.
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include "common.cuh"
@@ -37,16 +38,16 @@ int pb_sm_count() {
 
 // ---- choice of the scoring kernel (process-wide, read at every pb_pnp_ransac_* call) ----
 namespace {
-int g_score_impl = 0;
-float g_score_kappa = 1.0f;
+std::atomic<int> g_score_impl{0};
+std::atomic<float> g_score_kappa{1.0f};
 }
-int pb_score_impl() { return g_score_impl; }
-float pb_score_tc_kappa() { return g_score_kappa; }
+int pb_score_impl() { return g_score_impl.load(std::memory_order_relaxed); }
+float pb_score_tc_kappa() { return g_score_kappa.load(std::memory_order_relaxed); }
 extern "C" int pb_ransac_score_impl(int impl, float band_scale) {
     PB_REQUIRE(impl >= 0 && impl <= 6, "pb_ransac_score_impl: impl=%d (0 automatic, 1 FP32 pipe, 2 tensor cores, 3 tensor cores + calibration)", impl);
     PB_REQUIRE(band_scale > 0.0f && band_scale <= 1024.0f, "pb_ransac_score_impl: band_scale out of range");
-    g_score_impl = impl;
-    g_score_kappa = band_scale;
+    g_score_impl.store(impl, std::memory_order_relaxed);
+    g_score_kappa.store(band_scale, std::memory_order_relaxed);
     return 0;
 }
 

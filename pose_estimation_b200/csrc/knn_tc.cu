@@ -25,6 +25,7 @@
 //            the SIMT kernel's exact FP32 formula (lowest index on ties); a row whose ring dropped a chunk
 //            that could matter, a barrier timeout or non-finite input falls back to an exact scan.
 // The MMA of tile n+1 and the bulk copy (1-D TMA) of tile n+2 overlap the epilogue of tile n.
+#include <atomic>
 #include <cuda_bf16.h>
 #include "common.cuh"
 #include "tc.cuh"
@@ -980,7 +981,7 @@ __global__ void __launch_bounds__(KM_THREADS, 4) knn_mma_kernel(MainArgs a) {
     if (tid == 0 && !sweep_ok) *a.err = 1;
 }
 
-int g_knn_impl = 0;                // pb_knn_tc_impl
+std::atomic<int> g_knn_impl{0};     // pb_knn_tc_impl
 // Split re-rank: one THREAD per query row walks the candidate lists its two epilogue threads left (a handful of 8-column groups or
 // 32-column chunks), exact FP32 distances, lowest index on ties; a row whose list overflowed (or whose sweep failed) is scanned.
 // Run as its own kernel the dependent, scattered loads overlap across 10^5 rows instead of stretching every sweep CTA's life.
@@ -1093,7 +1094,7 @@ extern "C" int pb_tc_selftest(const void* A, const void* B, float* D, int* err, 
 // 0 = automatic (the tcgen05 + TMEM sweep: 3.9 ms on C3), 1 = tcgen05, 2 = the warp-level mma.sync sweep (6.7 ms); identical results
 extern "C" int pb_knn_tc_impl(int impl) {
     PB_REQUIRE(impl >= 0 && impl <= 2, "pb_knn_tc_impl: impl=%d (0 automatic, 1 tcgen05, 2 mma.sync)", impl);
-    g_knn_impl = impl;
+    g_knn_impl.store(impl, std::memory_order_relaxed);
     return 0;
 }
 
@@ -1134,6 +1135,7 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
         ybox = reinterpret_cast<float*>(q);
     }
     uint32_t* cand = reinterpret_cast<uint32_t*>(al128(reinterpret_cast<uintptr_t>(base) + need - 128 - (size_t)nb_max * ntN * TM * NWG * 8 * sizeof(uint32_t)) );
+    const int knn_impl = g_knn_impl.load(std::memory_order_relaxed);     // one reading per call: prepare and sweep must agree
     cudaFuncSetAttribute(knn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAIN_SMEM);
     cudaFuncSetAttribute(knn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAIN_SMEM);
     cudaMemsetAsync(err, 0, 4 * sizeof(int), st);   // [0] barrier timeout, [1] fallback rows, [2] exact evaluations
@@ -1145,7 +1147,7 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
             knn_tc_prepare_sorted_kernel<<<dim3(nb, 2), 256, 0, st>>>(sa);
             if (pb_check_launch("knn_tc_prepare_sorted_kernel")) return -2;
         } else {
-            PrepArgs pa{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, centre, b0, blist, g_knn_impl == 2 ? 1 : 0};
+            PrepArgs pa{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, centre, b0, blist, knn_impl == 2 ? 1 : 0};
             int split = (4 * pb_sm_count() + nb - 1) / nb;         // about four CTAs per SM in total
             const int max_split = (max(ntN, ntM) * TM + 255) / 256;
             split = split < PREP_SPLIT ? PREP_SPLIT : (split > 64 ? 64 : split);
@@ -1154,7 +1156,7 @@ int pb_internal_knn1_tc(const char* who, const float* x, const float* y, int B, 
             if (pb_check_launch("knn_tc_prepare_kernel")) return -2;
         }
         MainArgs ma{x, y, N, M, y_shared, ntN, ntM, Aop, Bop, tol, idx, d2, b0, err, blist, permX, permY, xs, ys, xbox, ybox, centre, cand};
-        if (!sorted && g_knn_impl == 2) {
+        if (!sorted && knn_impl == 2) {
             knn_mma_kernel<<<dim3(ntN, nb), KM_THREADS, 0, st>>>(ma);
             if (pb_check_launch("knn_mma_kernel")) return -2;
             continue;

@@ -429,6 +429,7 @@ extern "C" int pb_pnp_ransac_pts(const float* pts, const int32_t* count, const f
     sa.tc_stats = (use_tc || use_mma) ? reinterpret_cast<int32_t*>(static_cast<char*>(ws) + p.off_tcstats) : nullptr;
     sa.fstats = use_mma ? reinterpret_cast<float*>(static_cast<char*>(ws) + p.off_fstats) : nullptr;
     sa.tc_kappa = pb_score_tc_kappa();
+    sa.tc_mode = (impl == 3 || impl == 6) ? 1 : impl == 4 ? 2 : 0;
     if (use_tc) sa.prefix = nullptr;
     sa.cap = cap; sa.H = prm->n_hyp; sa.HS = p.HS; sa.Hs = p.Hs; sa.CH = p.CH; sa.PP = p.PP;
     sa.frame0 = frame0; sa.seed_lo = prm->seed_lo; sa.seed_hi = prm->seed_hi;

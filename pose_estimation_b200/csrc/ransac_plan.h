@@ -17,6 +17,7 @@ struct ScoreArgs {
     int32_t* tc_stats;               // tensor-core mode: [0] barrier timeout, [1] exact re-evaluations (groups of 4 tests x 32 lanes),
                                      // [2] calibration: largest observed |s_tc - s_fp32| / band as float bits, [3] verdicts that differ outside the band
     float tc_kappa;                  // tensor-core mode: multiplier of the re-evaluation band (1 = the derived bound)
+    int tc_mode;                     // tensor-core modes: 0 product, 1 calibration pass, 2 clock breakdown (tcgen05 only)
     float* fstats;                   // mma.sync mode: [F][8] frame constants (written by frame_stats_kernel before the scoring kernel)
     int cap, H, HS, Hs, CH, PP;      // Hs hypotheses per slice (power of two >= 32); PP point parts
     uint32_t frame0, seed_lo, seed_hi;

@@ -497,8 +497,8 @@ int pb_launch_score(const ScoreArgs& a, const Plan& p, int F, cudaStream_t st) {
     ransac_hypothesis_kernel<<<(unsigned)((nh + HT - 1) / HT), HT, 0, st>>>(a);
     if (pb_check_launch("ransac_hypothesis_kernel")) return 1;
     pb_stage_mark(1, st);
-    if (a.fstats && a.cnt_all) return pb_launch_score_mma(a, pb_score_impl() == 6, st);
-    if (a.tprefix && a.cnt_all) return pb_launch_score_tc(a, pb_score_impl() == 3 ? 1 : pb_score_impl() == 4 ? 2 : 0, st);
+    if (a.fstats && a.cnt_all) return pb_launch_score_mma(a, a.tc_mode == 1, st);
+    if (a.tprefix && a.cnt_all) return pb_launch_score_tc(a, a.tc_mode, st);
     if (p.bal && a.cnt_all) return p.bal_nhl == 2 ? launch_bal<2>(a, p, st) : launch_bal<1>(a, p, st);
     switch (p.NHL) {
         case 1: return launch<1>(a, p, F, st);

@@ -489,6 +489,10 @@ def ours_arm(args):
         replay = None
         if kind == "choose_graph":     # the same pass as "choose", captured once and replayed as a CUDA graph
             replay = hs.capture_choose(xyz_h, choose_h, small_h, cls_h, xmap_h=xm_h, ymap_h=ym_h, n_valid_h=nv_h, frame0=rank * F)
+        elif kind == "choose_dev_graph":
+            replay = hs.capture_choose(inp["xyz"], choose_h, small_h, cls_h, xmap_h=xm_h, ymap_h=ym_h, n_valid_h=nv_h, frame0=rank * F)
+        elif kind == "choose_dev32_graph":
+            replay = hs.capture_choose(inp["xyz"], choose32_h, small_h, cls_h, n_valid_h=nv_h, frame0=rank * F)
 
         def once():
             if replay is not None:
@@ -520,13 +524,16 @@ def ours_arm(args):
     eager_value, list_bytes, tb_eager = run_e2e("choose", F // nchunk, args.steps)
     e2e_value, _, tb_host = run_e2e("choose_graph", F // nchunk, args.steps)
     e2e_bytes = list_bytes + sectors * 3 * 32
-    dev_value, dev_bytes, tb_dev = run_e2e("choose_dev", F // nchunk, args.steps)
-    dev32_value, dev32_bytes, tb_dev32 = run_e2e("choose_dev32", F // nchunk, args.steps)
+    ndev = int(os.environ.get("PB_DEV_SPLIT", "2"))      # maps on the device: two chunks (one per lane) measure best
+    dev_eager, dev_bytes, tb_dev = run_e2e("choose_dev", F // ndev, args.steps)
+    dev32_eager, dev32_bytes, tb_dev32 = run_e2e("choose_dev32", F // ndev, args.steps)
+    dev_value, _, tb_devg = run_e2e("choose_dev_graph", F // ndev, args.steps)
+    dev32_value, _, tb_dev32g = run_e2e("choose_dev32_graph", F // ndev, args.steps)
     zc_value, zc_bytes, tb_zc = run_e2e("mask", F // nchunk, min(args.steps, 10))
     zc_bytes += sectors * 3 * 32
     staged_value, staged_bytes, tb_staged = run_e2e("staged", 128, min(args.steps, 5))
     tcpu = table.cpu()
-    same = all(bool(torch.equal(t_, tcpu)) for t_ in (tb_host, tb_eager, tb_dev, tb_dev32, tb_zc, tb_staged))
+    same = all(bool(torch.equal(t_, tcpu)) for t_ in (tb_host, tb_eager, tb_dev, tb_dev32, tb_devg, tb_dev32g, tb_zc, tb_staged))
 
     clocks = sampler.stop() if sampler else None
     if rank == 0:
@@ -598,10 +605,12 @@ def ours_arm(args):
                     "table_equals_device_path": same,
                     "eager_variant": {"value": eager_value, "unit": UNIT, "h2d_bytes_per_step": e2e_bytes,
                                       "api": "HostEvalSweep.run_choose called every step (no graph): ~100 launches / copies from Python"},
-                    "device_map_variant": {"value": dev_value, "unit": UNIT, "h2d_bytes_per_step": dev_bytes,
-                                           "api": "run_choose with pred['xyz'] still on the device (it is the network's "
-                                                  "output); the int64 / f32 lists and per-frame data from the host"},
-                    "device_map_int32_variant": {"value": dev32_value, "unit": UNIT, "h2d_bytes_per_step": dev32_bytes,
+                    "device_map_variant": {"value": dev_value, "eager_value": dev_eager, "unit": UNIT, "h2d_bytes_per_step": dev_bytes,
+                                           "api": "capture_choose / replay with pred['xyz'] still on the device (it is the "
+                                                  "network's output); the int64 / f32 lists and per-frame data from the host; "
+                                                  "two chunks; eager_value = run_choose called every step"},
+                    "device_map_int32_variant": {"value": dev32_value, "eager_value": dev32_eager, "unit": UNIT,
+                                                 "h2d_bytes_per_step": dev32_bytes,
                                                  "api": "the same with int32 choose and the pixel coordinates taken from "
                                                         "the index (no x / y lists)"},
                     "mask_zero_copy_variant": {"value": zc_value, "unit": UNIT, "h2d_bytes_per_step": zc_bytes,

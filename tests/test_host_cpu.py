@@ -37,6 +37,24 @@ def test_library_exports_every_declared_symbol():
     assert b"pb_knn1" in lib.pb_last_error()
 
 
+def test_kernel_switches_validate_their_arguments():
+    """The opt-in kernel switches (pb_ransac_score_impl, pb_knn_tc_impl) touch no device: out-of-range selectors are
+    refused with a message, valid ones are accepted and the default is restored."""
+    from pose_estimation_b200 import ops
+    lib = _lib.load()
+    assert lib.pb_ransac_score_impl(7, 1.0) == -1 and b"pb_ransac_score_impl" in lib.pb_last_error()
+    assert lib.pb_ransac_score_impl(-1, 1.0) == -1
+    assert lib.pb_ransac_score_impl(2, 0.0) == -1 and b"band_scale" in lib.pb_last_error()
+    assert lib.pb_knn_tc_impl(3) == -1 and b"pb_knn_tc_impl" in lib.pb_last_error()
+    with pytest.raises(KeyError):
+        ops.set_score_impl("no-such-kernel")
+    for name in ("fp32", "tc", "tc_calib", "mma", "mma_calib", "auto"):
+        ops.set_score_impl(name, 0.5)
+    ops.set_score_impl("auto", 1.0)
+    for name in ("mma", "tcgen05", "auto"):
+        ops_metric.set_knn_tc_impl(name)
+
+
 def test_missing_library_fails_loudly(monkeypatch):
     monkeypatch.setattr(_lib, "_lib", None)
     monkeypatch.setattr(_lib, "SO_PATH", "/nonexistent/libposeb200.so")

@@ -40,6 +40,12 @@ struct Plan {
 #define PB_TC_TILE 64            /* points per work unit of the tensor-core scoring kernel */
 #define PB_TC_STATS_BYTES 128     /* int32 stats[4] + twelve 64-bit clock sums of the profiling mode */
 #define PB_BAL_SUB 256           /* points per staging buffer of the balanced scoring kernel (two buffers) */
+#ifndef PB_BAL_DYN_PCT
+#define PB_BAL_DYN_PCT 0         /* per cent of the points the balanced scoring kernel deals out through a counter */
+#endif
+#ifndef PB_BAL_WAVES
+#define PB_BAL_WAVES 1           /* CTAs of the balanced scoring kernel = SMs x resident CTAs x this */
+#endif
 
 static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm, int sms = 148) {
     if (sms <= 0) sms = 148;
@@ -75,12 +81,12 @@ static inline Plan make_plan(int F, int cap, const pb_ransac_params* prm, int sm
     const bool many = F >= two_waves || (long long)F * cap >= 4ll * sms * per_sm * PB_BAL_SUB;
     p.bal = (H <= 2 * PB_SCORE_THREADS && many && cap % 4 == 0) ? 1 : 0;
     p.bal_nhl = H > PB_SCORE_THREADS ? 2 : 1;          // hypotheses per thread of the balanced kernel (the slice plan above is its fallback's)
-    p.bal_grid = sms * per_sm;
+    p.bal_grid = sms * per_sm * PB_BAL_WAVES;
     p.off_cnt = (p.total + 255) / 256 * 256;
     p.off_prefix = p.off_cnt;
     if (p.bal) {
         p.off_prefix = (p.off_cnt + (size_t)F * H * sizeof(int32_t) + 255) / 256 * 256;
-        p.total = p.off_prefix + (size_t)(F + 1) * sizeof(int32_t);
+        p.total = p.off_prefix + (size_t)(F + 2) * sizeof(int32_t);    // prefix[0..F] + the unit counter
     }
     // tensor-core scoring: same accumulation target (cnt_all) as the balanced kernel, H <= 256 hypotheses per frame
     p.tc = (p.bal && H <= 256) ? 1 : 0;

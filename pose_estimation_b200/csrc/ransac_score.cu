@@ -62,7 +62,10 @@ __device__ void frame_prefix_scan(const ScoreArgs& a, int32_t* out) {
 }
 
 __global__ void __launch_bounds__(HT) ransac_hypothesis_kernel(ScoreArgs a) {
-    if (blockIdx.x == 0 && a.prefix) frame_prefix_scan<false>(a, a.prefix);        // uniform per CTA
+    if (blockIdx.x == 0 && a.prefix) {                                             // uniform per CTA
+        frame_prefix_scan<false>(a, a.prefix);
+        if (threadIdx.x == 0) a.prefix[a.F + 1] = 0;                               // the balanced scorer's unit counter
+    }
     if (blockIdx.x == 0 && a.tprefix) frame_prefix_scan<true>(a, a.tprefix);
     const long long gid = (long long)blockIdx.x * HT + threadIdx.x;
     if (gid >= (long long)a.F * a.H) return;
@@ -322,27 +325,60 @@ constexpr int SUB = PB_BAL_SUB;      // points per staging buffer
 // prefix comes from the hypothesis kernel (one scan per launch, not one per CTA).  For every frame segment the CTA
 // holds that frame's hypotheses (two per thread) and adds its counts to cnt_all[f][h]; inlier counts are integer sums,
 // so the result does not depend on the cut.  The arg-max is taken by the finalize kernel.
+#ifndef PB_K3_TIMELINE
+#define PB_K3_TIMELINE 0     // 1 (measurement builds only, scratch/k3_timeline.py): per-CTA start / end times and SM ids
+#endif
+#if PB_K3_TIMELINE
+__device__ unsigned long long g_k3_timeline[4096][4];
+__device__ __forceinline__ unsigned long long k3_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#endif
+
 template <int NHL>
 __global__ void __launch_bounds__(ST, 6) ransac_score_bal_kernel(ScoreArgs a) {
     __shared__ __align__(16) float sbuf[2][5][SUB];
     const int tid = threadIdx.x;
+#if PB_K3_TIMELINE
+    if (tid == 0 && blockIdx.x < 4096) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        g_k3_timeline[blockIdx.x][0] = k3_now();
+        g_k3_timeline[blockIdx.x][1] = 0;
+        g_k3_timeline[blockIdx.x][2] = smid;
+        g_k3_timeline[blockIdx.x][3] = clock64();
+    }
+#endif
     const int F = a.F;
     const int* __restrict__ prefix = a.prefix;
     const int T = prefix[F];
+#if PB_BAL_DYN_PCT > 0
+    // every CTA takes a fixed range of (100 - PB_BAL_DYN_PCT) % of an equal share, then units of SUB points from the rest
+    // through a counter (zeroed by the hypothesis kernel): the warp schedulers favour the oldest CTA of an SM, so CTAs of
+    // equal ranges end one after the other and the SM runs its last ranges with few warps
+    __shared__ int s_unit;
+    int U = (int)((long long)T * (100 - PB_BAL_DYN_PCT) / 100 / (int)gridDim.x) & ~7;
+    const int pool0 = U * (int)gridDim.x;
+    int g0 = blockIdx.x * U, g1 = g0 + U;
+#else
     int U = (T + (int)gridDim.x - 1) / (int)gridDim.x;
     U = (U + 7) & ~7;
     const long long g0l = (long long)blockIdx.x * U;
     if (g0l >= T) return;
     const int g0 = (int)g0l, g1 = min(T, g0 + U);
+#endif
     int f = 0;
-    {   // last frame with prefix[f] <= g0 (frames without points share a prefix value: take the last of them)
+    // last frame with prefix[f] <= g (frames without points share a prefix value: take the last of them)
+    auto find_frame = [&](int g) {
         int lo = 0, hi = F;
         while (hi - lo > 1) {
             const int mid = (lo + hi) >> 1;
-            if (prefix[mid] <= g0) lo = mid; else hi = mid;
+            if (prefix[mid] <= g) lo = mid; else hi = mid;
         }
-        f = lo;
-    }
+        return lo;
+    };
     const bool scale = a.inv_thr != 1.0f;
     const float ninf = __int_as_float(0x7f800000);
 
@@ -391,6 +427,19 @@ __global__ void __launch_bounds__(ST, 6) ransac_score_bal_kernel(ScoreArgs a) {
     for (int j = 0; j < NHL; ++j) c[j] = 0;
     int cur_f = -1;
     int sf, sp0, sn, nf = 0, np0 = 0, nn = 0;
+#if PB_BAL_DYN_PCT > 0
+    for (bool first = true;; first = false) {
+    if (!first) {
+        if (tid == 0) s_unit = atomicAdd(a.prefix + F + 1, 1);
+        __syncthreads();
+        const long long gl = (long long)pool0 + (long long)s_unit * SUB;
+        __syncthreads();                                           // s_unit is read before the next fetch overwrites it
+        if (gl >= T) break;
+        g0 = (int)gl; g1 = min(T, g0 + SUB);
+    }
+    if (g1 <= g0) continue;
+#endif
+    f = find_frame(g0);
     int g = g0;
     bool have = describe(g, f, sf, sp0, sn);
     if (have) stage(0, sf, sp0, sn);
@@ -467,6 +516,9 @@ __global__ void __launch_bounds__(ST, 6) ransac_score_bal_kernel(ScoreArgs a) {
         __syncthreads();                                           // buffer b is free for the sub-chunk after next
         have = more; sf = nf; sp0 = np0; sn = nn;
     }
+#if PB_BAL_DYN_PCT > 0
+    }
+#endif
     if (cur_f >= 0) {
 #pragma unroll
         for (int j = 0; j < NHL; ++j) {
@@ -474,7 +526,22 @@ __global__ void __launch_bounds__(ST, 6) ransac_score_bal_kernel(ScoreArgs a) {
             if (h < a.H && c[j] > 0) atomicAdd(&a.cnt_all[(size_t)cur_f * a.H + h], c[j]);   // c > 0 only for valid hypotheses
         }
     }
+#if PB_K3_TIMELINE
+    __syncthreads();
+    if (tid == 0 && blockIdx.x < 4096) {
+        g_k3_timeline[blockIdx.x][1] = k3_now();
+        g_k3_timeline[blockIdx.x][3] = clock64() - g_k3_timeline[blockIdx.x][3];
+    }
+#endif
 }
+
+#if PB_K3_TIMELINE
+}  // namespace
+extern "C" int pb_debug_k3_timeline(unsigned long long* out, int n) {
+    return cudaMemcpyFromSymbol(out, g_k3_timeline, (size_t)n * 4 * sizeof(unsigned long long)) == cudaSuccess ? 0 : -1;
+}
+namespace {
+#endif
 
 template <int NHL>
 int launch_bal(const ScoreArgs& a, const Plan& p, cudaStream_t st) {

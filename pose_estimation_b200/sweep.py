@@ -517,10 +517,58 @@ class HostEvalSweep:
             tab_out.copy_(self._tables.sum(dim=0))
         self._graph_keep = (graph, tab_out, args)          # the graph reads these tensors: keep them alive
 
-        def replay(group=None):
-            graph.replay()
-            reduce_table(tab_out, group)
-            self.table_host.copy_(tab_out, non_blocking=True)
-            torch.cuda.current_stream(self.dev).synchronize()
+        done = torch.cuda.Event()
+
+        def submit(group=None, stream=None):
+            """Enqueue the pass (graph, table all-reduce, result copy) on ``stream`` (default: the current one); no sync."""
+            s_ = stream if stream is not None else torch.cuda.current_stream(self.dev)
+            with torch.cuda.stream(s_):
+                graph.replay()
+                reduce_table(tab_out, group)
+                self.table_host.copy_(tab_out, non_blocking=True)
+                done.record(s_)
+
+        def wait():
+            done.synchronize()
             return self.table_host
+
+        def replay(group=None):
+            submit(group)
+            return wait()
+        replay.submit, replay.wait = submit, wait
         return replay
+
+
+class PipelinedPasses:
+    """Captured passes in flight together -- the serving loop's double buffering.  ``replays`` are the callables
+    HostEvalSweep.capture_choose returned, EACH FROM ITS OWN HostEvalSweep (own staging buffers, lanes and tables; the
+    caller refills that instance's pinned host buffers before submitting it again).  They are replayed in turn on their own
+    streams, so the list copies and the zero-copy gather of pass k+1 cross PCIe under the scoring tail, table reduction and
+    result copy of pass k.  ``submit()`` enqueues the next pass and returns the table (a host copy) of the oldest pass
+    still in flight once ``len(replays)`` are, else None; ``drain()`` returns the tables still outstanding, oldest first."""
+
+    def __init__(self, replays, device="cuda"):
+        if len(replays) < 2:
+            raise ValueError("PipelinedPasses needs at least two captured passes")
+        self.replays = list(replays)
+        self.streams = [torch.cuda.Stream(device=torch.device(device)) for _ in self.replays]
+        self.next = 0
+        self.pending = []                       # indices of the passes in flight, oldest first
+
+    def submit(self, group=None):
+        k = self.next
+        self.next = (k + 1) % len(self.replays)
+        out = None
+        if k in self.pending:                   # (only when the caller skipped the returned tables: depth exceeded)
+            raise RuntimeError("pass still in flight")
+        self.replays[k].submit(group, self.streams[k])
+        self.pending.append(k)
+        if len(self.pending) == len(self.replays):
+            out = self.replays[self.pending.pop(0)].wait().clone()
+        return out
+
+    def drain(self):
+        outs = [self.replays[k].wait().clone() for k in self.pending]
+        self.pending = []
+        return outs
+

@@ -428,3 +428,34 @@ def test_host_eval_sweep_choose_graph_replay_equals_eager(dev):
         want = hs.run_choose(bufs[0], bufs[1], bufs[2], bufs[3], xmap_h=bufs[4], ymap_h=bufs[5], n_valid_h=bufs[6]).clone()
         assert torch.equal(got, want) and got[0].sum() == F, first
         assert torch.equal(replay(), want)                                   # replays do not accumulate
+
+
+def test_pipelined_passes_return_each_pass_table_in_order(dev):
+    """sweep.PipelinedPasses: two captured passes (own sweep objects, own pinned buffers holding DIFFERENT batches) kept in
+    flight together return, in submission order, exactly the tables the synchronous replays give."""
+    from pose_estimation_b200 import sweep
+    F, chunk = 32, 8
+    models = torch.from_numpy(synth.class_models(500))
+    diam, sym = torch.from_numpy(synth.DIAMETER), torch.from_numpy(synth.IS_SYM)
+    replays, want = [], []
+    for first in (0, 100):
+        sps = synth.make_batch_sparse(0x5EED, 2, F, first_frame=first)
+        b = batch_arrays(sps)
+        choose, xm, ym, nv = _choose_lists(sps, 1216)
+        small = sweep.pack_small(b["extent"], b["lfborder"], b["K4"], b["R_gt"], b["t_gt"], chunk)
+        bufs = [t.pin_memory() for t in (torch.from_numpy(b["xyz"]), torch.from_numpy(choose), small, torch.from_numpy(b["cls"]),
+                                         torch.from_numpy(xm), torch.from_numpy(ym), torch.from_numpy(nv))]
+        hs = sweep.HostEvalSweep(models, diam, sym, synth.IMG_H, synth.IMG_W, 1280, chunk=chunk, device=dev, zero_copy=True)
+        r = hs.capture_choose(bufs[0], bufs[1], bufs[2], bufs[3], xmap_h=bufs[4], ymap_h=bufs[5], n_valid_h=bufs[6])
+        replays.append(r)
+        want.append(r().clone())
+    assert not torch.equal(want[0], want[1])
+    pipe = sweep.PipelinedPasses(replays, device=dev)
+    got = [pipe.submit() for _ in range(5)]                    # passes 0 1 0 1 0: None, then tables of passes 0 1 0 1
+    assert got[0] is None
+    for k, tb in enumerate(got[1:]):
+        assert torch.equal(tb, want[k & 1]), k
+    rest = pipe.drain()
+    assert len(rest) == 1 and torch.equal(rest[0], want[0]) and pipe.drain() == []
+    with pytest.raises(ValueError):
+        sweep.PipelinedPasses(replays[:1], device=dev)
